@@ -1,0 +1,210 @@
+/*
+ * pcp.h — C-ABI of the B200-native neighbourhood-PCA hot path (libpcp.so).
+ *
+ * This is the drop-in boundary for the reference's `pcaAnalysist` stage and for
+ * `RingProjector::projectPointCloud`.  Plain C: pointers and sizes only, no C++ types,
+ * no torch types, no exceptions across the boundary.  Every entry point returns a
+ * `pcp_status` (0 = OK, negative = error); `pcp_last_error(ctx)` gives the message.
+ *
+ * There is NO CPU fallback behind this ABI: every compute call runs CUDA kernels compiled
+ * for sm_100a and fails with PCP_ERR_CUDA / PCP_ERR_NO_DEVICE when no such GPU is present.
+ *
+ * One `pcp_ctx` per host thread per GPU.  A ctx owns one CUDA stream and all device
+ * memory it allocates; the caller owns every pointer it passes in.  Calls taking host
+ * pointers synchronise the ctx stream before returning; calls taking device pointers
+ * (`*_device`, or `out_is_device != 0`) only enqueue work on the ctx stream.
+ *
+ * Each function cites the reference interface it replaces (paths relative to the
+ * reference tree YangSiri/pointCloudProcessing).
+ */
+#ifndef PCP_H_
+#define PCP_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define PCP_API __attribute__((visibility("default")))
+#else
+#define PCP_API
+#endif
+
+typedef struct pcp_ctx pcp_ctx;
+
+typedef enum pcp_status {
+  PCP_OK = 0,
+  PCP_ERR_INVALID_ARG = -1,
+  PCP_ERR_NO_DEVICE = -2,      /* no CUDA device / not sm_100 */
+  PCP_ERR_CUDA = -3,           /* a CUDA runtime call or kernel failed */
+  PCP_ERR_NO_CLOUD = -4,       /* compute call before pcp_set_cloud_* */
+  PCP_ERR_NO_GRID = -5,        /* compute call before pcp_build_grid */
+  PCP_ERR_GRID_TOO_LARGE = -6, /* dense cell table would exceed the configured budget */
+  PCP_ERR_K_UNSUPPORTED = -7,  /* k outside [1, PCP_MAX_K] */
+  PCP_ERR_OOM = -8,
+  PCP_ERR_IO = -9,             /* calibration file could not be read / parsed */
+  PCP_ERR_NEIGHBOR_OVERFLOW = -10 /* a radius neighbourhood exceeded the per-query on-chip buffer */
+} pcp_status;
+
+#define PCP_MAX_K 32
+
+/* Record layout-identical to `pcaAnalysist::pcaFeature` (include/pcaAnalysis.h:34-45):
+ * lamda{la1,la2,la3} ascending; vec{v1,v2,v3} as three packed 3-float columns;
+ * ptID; ptNum; lineStruc; planeStruc; scatterStruc.  68 bytes, align 4. */
+typedef struct pcp_feature68 {
+  float la1, la2, la3;
+  float v1[3], v2[3], v3[3];
+  int32_t ptID;
+  int32_t ptNum;
+  float lineStruc, planeStruc, scatterStruc;
+} pcp_feature68;
+
+/* (nx,ny,nz,curvature): layout of pcl::Normal's first four floats, the output of
+ * `preprocess::normalestimate` (src/smoothing.cpp:236-248). */
+typedef struct pcp_normal16 {
+  float nx, ny, nz, curvature;
+} pcp_normal16;
+
+/* Centre of the second moment. */
+enum {
+  PCP_CENTER_QUERY = 0, /* about the query point itself — src/pcaAnalysis.cpp:53-55 */
+  PCP_CENTER_MEAN = 1   /* about the neighbourhood mean — pcl::NormalEstimation twin */
+};
+
+/* Stage indices for pcp_last_timings (milliseconds, CUDA events on the ctx stream). */
+enum {
+  PCP_T_BBOX = 0,
+  PCP_T_KEYS = 1,
+  PCP_T_SORT = 2,
+  PCP_T_TABLE = 3,
+  PCP_T_SEARCH_PCA = 4, /* the fused search + moment + eigen kernel */
+  PCP_T_CARRY = 5,
+  PCP_T_H2D = 6,
+  PCP_T_D2H = 7,
+  PCP_T_COUNT = 8
+};
+
+/* ---- lifetime ------------------------------------------------------------------- */
+
+/* Creates a context on CUDA device `device`.  Fails with PCP_ERR_NO_DEVICE when the
+ * device is missing or is not compute capability 10.x. */
+PCP_API int pcp_create(pcp_ctx** out, int device);
+PCP_API int pcp_destroy(pcp_ctx* ctx);
+PCP_API const char* pcp_last_error(const pcp_ctx* ctx);
+PCP_API const char* pcp_version(void);
+/* cudaStream_t of the context, as an opaque pointer (for event timing by the caller). */
+PCP_API void* pcp_stream(pcp_ctx* ctx);
+PCP_API int pcp_synchronize(pcp_ctx* ctx);
+/* Copies the PCP_T_COUNT stage times of the last build/compute calls into ms[0..n). */
+PCP_API int pcp_last_timings(pcp_ctx* ctx, float* ms, int n);
+/* Number of kernel launches issued by this ctx since creation. */
+PCP_API int64_t pcp_launch_count(const pcp_ctx* ctx);
+
+/* ---- cloud input ------------------------------------------------------------------
+ * Replaces `pcl::KdTreeFLANN<pcl::PointXYZI>::setInputCloud` at src/pcaAnalysis.cpp:14-15
+ * (the cloud hand-over half of it; the index build is pcp_build_grid). */
+
+/* Host AoS cloud: `stride_bytes` between points, x,y,z as three leading floats
+ * (32 for pcl::PointXYZI, 16 for a packed float4).  Copies to the device. */
+PCP_API int pcp_set_cloud_host(pcp_ctx* ctx, const void* pts, int64_t n, int stride_bytes);
+/* Device-resident packed float4 cloud (x,y,z,intensity); not copied, must stay alive
+ * until the next pcp_set_cloud_* or pcp_destroy. */
+PCP_API int pcp_set_cloud_device(pcp_ctx* ctx, const void* d_xyzi, int64_t n);
+/* Sharded form (multi-GPU tiles, frame batches): the first `n_query` points are this
+ * shard's own points (they get outputs); points [n_query, n) are halo points that only
+ * serve as neighbours.  `d_global_id` (device, n × int32, may be NULL = identity) is the
+ * index used for tie-breaking and written to ptID, so results are identical to the
+ * unsharded run. */
+PCP_API int pcp_set_cloud_device_sharded(pcp_ctx* ctx, const void* d_xyzi, const int32_t* d_global_id,
+                                         int64_t n, int64_t n_query);
+
+/* ---- index build ------------------------------------------------------------------
+ * Replaces the FLANN KDTreeSingleIndex build inside setInputCloud (src/pcaAnalysis.cpp:15):
+ * bbox reduce → cell keys → radix sort → cell table (prefix scan).  `cell` > 0 is the
+ * cell edge in metres; for radius search it must be >= the radius (the 27-cell stencil
+ * is then exact).  `cell` <= 0 picks one from the point density for a k-NN of `k_hint`. */
+PCP_API int pcp_build_grid(pcp_ctx* ctx, float cell, int k_hint);
+/* Grid facts for diagnostics: dims[3], cell edge, number of cells. */
+PCP_API int pcp_grid_info(pcp_ctx* ctx, int32_t dims[3], float* cell, int64_t* n_cells);
+
+/* ---- fused search + PCA -----------------------------------------------------------
+ * Replaces the hot loop of `pcaAnalysist::calculatePCAofPointCloud`
+ * (src/pcaAnalysis.cpp:18-40): radiusSearch (:25) + calculatePCAofPoint(int) (:44-87) +
+ * the three structure features (:29-31), one 68-byte record per point, out[i].ptID == i.
+ *   radius        : as the reference's float argument; r2 = (float)((double)r*(double)r),
+ *                   membership is strict d2 < r2, the query is its own neighbour.
+ *   min_pts       : 13 in the reference (:50); records with ptNum < min_pts keep only
+ *                   ptID/ptNum valid unless carry_forward is set.
+ *   carry_forward : reproduce the stale-`tempFea` behaviour (:16,:26,:39): an invalid
+ *                   record repeats λ/vectors/features of the last valid lower-index
+ *                   record (zeros before the first valid one).
+ *   out           : n_query records, host (out_is_device = 0) or device memory. */
+PCP_API int pcp_radius_pca(pcp_ctx* ctx, float radius, int min_pts, int center_mode,
+                           int carry_forward, pcp_feature68* out, int out_is_device);
+
+/* k-nearest variant (the search primitive behind `pcl::NormalEstimation::setKSearch`,
+ * src/smoothing.cpp:239-246): the k nearest including the query itself, ordered by
+ * (d2, index).  Writes the pcaFeature record and, when `normals` is non-NULL, the
+ * (normal, curvature) of the PCL twin: moment about the mean, curvature =
+ * |λmin / trace|, normal flipped toward the viewpoint (0,0,0). */
+PCP_API int pcp_knn_pca(pcp_ctx* ctx, int k, int center_mode, pcp_feature68* out,
+                        pcp_normal16* normals, int out_is_device);
+
+/* ---- neighbour lists (verification and the consumers: mean-shift, DBSCAN) ----------
+ * Replace `kdtree.nearestKSearch` / `kdtree.radiusSearch` call sites
+ * (src/pcaAnalysis.cpp:25, src/buildingFacadeExtraction.cpp:83, src/lidarOdometry.cpp:76,
+ * include/dbscanCLuster.h:156,282,292). */
+
+/* idx/d2: n_query × k, row i = neighbours of point i in (d2, index) order. */
+PCP_API int pcp_knn_neighbors(pcp_ctx* ctx, int k, int32_t* idx, float* d2, int out_is_device);
+/* Two-call protocol: first call with idx == NULL fills counts[n_query]; the caller builds
+ * offsets (exclusive prefix sum, n_query+1 entries) and calls again with idx/d2 sized
+ * offsets[n_query].  Rows are in (d2, index) order. */
+PCP_API int pcp_radius_neighbors(pcp_ctx* ctx, float radius, int32_t* counts, const int64_t* offsets,
+                                 int32_t* idx, float* d2, int out_is_device);
+
+/* ---- segment PCA ------------------------------------------------------------------
+ * Replaces `pcaAnalysist::calculatePCAofPoint(cloud, centro, idx, fea)`
+ * (src/pcaAnalysis.cpp:89-121; caller src/buildingFacadeExtraction.cpp:212-219):
+ * CSR segments of point indices into the current cloud, one centre per segment, no
+ * minimum-count gate, ptID left 0.  Host pointers. */
+PCP_API int pcp_segment_pca(pcp_ctx* ctx, const float* centres_xyz, const int64_t* seg_offsets,
+                            const int32_t* seg_idx, int64_t n_seg, pcp_feature68* out);
+
+/* ---- ring projection ----------------------------------------------------------------
+ * Replaces `RingProjector::projectPointCloud` (src/ringProjection.cpp:24-81). */
+typedef struct pcp_ring_calib {
+  int32_t n_scan;       /* 16   (include/ringProjection.h:16) */
+  int32_t horizon_scan; /* 1800 (include/ringProjection.h:17) */
+  float ang_res_x;      /* 0.2  */
+  float ang_res_y;      /* 2.0  */
+  float ang_bottom;     /* 15.0 + 0.1 */
+  float vert_deg[64];   /* per-laser vertical correction from 16db.xml (for frame synthesis) */
+  float dist_lsb_cm;    /* 16db.xml:5 */
+  int32_t n_enabled;
+} pcp_ring_calib;
+
+/* Reference constants (include/ringProjection.h:16-20) + the VLP-16 beam table. */
+PCP_API int pcp_ring_calib_default(pcp_ring_calib* calib);
+/* Parses the Boost-serialization XML calibration (16db.xml) on the host and derives
+ * n_scan / ang_res_y / ang_bottom from the enabled lasers' vertical corrections. */
+PCP_API int pcp_ring_calib_from_xml(const char* path, pcp_ring_calib* calib);
+
+/* Projects `n_frames` frames stored back to back in the current cloud
+ * (frame f = points [frame_offsets[f], frame_offsets[f+1]); frame_offsets is always a HOST
+ * array of n_frames+1 entries; NULL means a single frame covering the whole cloud).  Per frame, host or device outputs:
+ *   range_img  : n_scan × horizon_scan floats, FLT_MAX where empty   (rangeMat)
+ *   pt_index   : n_scan × horizon_scan int32, −1 where empty, else the frame-local index
+ *                of the LAST point in input order that fell in the cell (fullInfoCloud.x)
+ *   long_range : per frame, count of in-image points with range > 60 (may be NULL). */
+PCP_API int pcp_ring_project(pcp_ctx* ctx, const pcp_ring_calib* calib, const int64_t* frame_offsets,
+                             int64_t n_frames, float* range_img, int32_t* pt_index,
+                             int32_t* long_range, int out_is_device);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PCP_H_ */

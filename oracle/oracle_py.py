@@ -1,0 +1,198 @@
+"""ctypes wrapper of oracle/liboracle.so — TEST INFRASTRUCTURE ONLY (see pcp_oracle.h).
+
+Imported by tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference
+legs, never by the product package.  PARITY UNPINNED (no reference fixtures exist).
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "liboracle.so")
+
+FEATURE_DTYPE = np.dtype(
+    [("la", np.float32, (3,)), ("v1", np.float32, (3,)), ("v2", np.float32, (3,)), ("v3", np.float32, (3,)),
+     ("ptID", np.int32), ("ptNum", np.int32), ("lineStruc", np.float32), ("planeStruc", np.float32),
+     ("scatterStruc", np.float32)]
+)
+assert FEATURE_DTYPE.itemsize == 68
+
+_lib = None
+
+
+def build():
+    subprocess.check_call(["make", "-s", "-C", _HERE, "liboracle.so"])
+
+
+def load() -> C.CDLL:
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        build()
+    lib = C.CDLL(LIB_PATH)
+    vp, i32, i64, f32 = C.c_void_p, C.c_int, C.c_int64, C.c_float
+    sig = {
+        "orc_radius2": (f32, [f32]),
+        "orc_radius_brute": (i64, [vp, i64, i64, f32, vp, vp, i64]),
+        "orc_knn_brute": (i64, [vp, i64, i64, i32, vp, vp]),
+        "orc_kdtree_build": (vp, [vp, i64, i32]),
+        "orc_kdtree_free": (None, [vp]),
+        "orc_kdtree_radius": (i64, [vp, i64, f32, vp, vp, i64]),
+        "orc_kdtree_knn": (i64, [vp, i64, i32, vp, vp]),
+        "orc_kdtree_knn_all": (None, [vp, i32, vp, vp, i32]),
+        "orc_kdtree_radius_counts": (None, [vp, f32, vp, i32]),
+        "orc_kdtree_radius_all": (None, [vp, f32, vp, vp, vp, i32]),
+        "orc_covariance_about": (None, [vp, vp, i64, vp, vp]),
+        "orc_eigen_sym3_qr": (i32, [vp, vp, vp]),
+        "orc_pcl_eigen33": (None, [vp, vp, vp]),
+        "orc_structure_features": (None, [f32, f32, f32, vp]),
+        "orc_radius_pca_cloud": (None, [vp, i64, f32, i32, i32, vp, vp, i32]),
+        "orc_knn_pca_cloud": (None, [vp, i64, i32, i32, vp, vp, i32]),
+        "orc_segment_pca": (None, [vp, vp, vp, vp, i64, vp]),
+        "orc_ring_project": (i32, [vp, i64, i32, i32, f32, f32, f32, vp, vp, vp]),
+        "orc_num_threads": (i32, []),
+    }
+    for name, (res, args) in sig.items():
+        fn = getattr(lib, name)
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib
+
+
+def _f4(pts):
+    pts = np.ascontiguousarray(pts, np.float32)
+    assert pts.ndim == 2 and pts.shape[1] == 4
+    return pts
+
+
+def num_threads() -> int:
+    return int(load().orc_num_threads())
+
+
+def radius2(r: float) -> float:
+    return float(load().orc_radius2(r))
+
+
+def knn_brute(pts, q: int, k: int):
+    pts = _f4(pts)
+    idx = np.zeros(k, np.int32)
+    d2 = np.zeros(k, np.float32)
+    m = load().orc_knn_brute(pts.ctypes.data, pts.shape[0], q, k, idx.ctypes.data, d2.ctypes.data)
+    return idx[:m], d2[:m]
+
+
+def radius_brute(pts, q: int, radius: float):
+    pts = _f4(pts)
+    r2 = radius2(radius)
+    m = load().orc_radius_brute(pts.ctypes.data, pts.shape[0], q, r2, None, None, 0)
+    idx = np.zeros(max(m, 1), np.int32)
+    d2 = np.zeros(max(m, 1), np.float32)
+    load().orc_radius_brute(pts.ctypes.data, pts.shape[0], q, r2, idx.ctypes.data, d2.ctypes.data, m)
+    return idx[:m], d2[:m]
+
+
+class KdTree:
+    def __init__(self, pts, leaf_max: int = 15):
+        self.pts = _f4(pts)
+        self.n = self.pts.shape[0]
+        self.h = load().orc_kdtree_build(self.pts.ctypes.data, self.n, leaf_max)
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            load().orc_kdtree_free(self.h)
+            self.h = None
+
+    def knn_all(self, k: int, nthreads: int = 0):
+        idx = np.zeros((self.n, k), np.int32)
+        d2 = np.zeros((self.n, k), np.float32)
+        load().orc_kdtree_knn_all(self.h, k, idx.ctypes.data, d2.ctypes.data, nthreads or num_threads())
+        return idx, d2
+
+    def radius_all(self, radius: float, nthreads: int = 0):
+        r2 = radius2(radius)
+        nt = nthreads or num_threads()
+        counts = np.zeros(self.n, np.int32)
+        load().orc_kdtree_radius_counts(self.h, r2, counts.ctypes.data, nt)
+        offsets = np.zeros(self.n + 1, np.int64)
+        np.cumsum(counts, out=offsets[1:])
+        total = int(offsets[-1])
+        idx = np.zeros(max(total, 1), np.int32)
+        d2 = np.zeros(max(total, 1), np.float32)
+        load().orc_kdtree_radius_all(self.h, r2, offsets.ctypes.data, idx.ctypes.data, d2.ctypes.data, nt)
+        return offsets, idx[:total], d2[:total]
+
+
+def covariance_about(pts, idx, centre):
+    pts = _f4(pts)
+    idx = np.ascontiguousarray(idx, np.int32)
+    centre = np.ascontiguousarray(centre, np.float32)
+    Cm = np.zeros(9, np.float32)
+    load().orc_covariance_about(pts.ctypes.data, idx.ctypes.data, idx.shape[0], centre.ctypes.data, Cm.ctypes.data)
+    return Cm.reshape(3, 3)
+
+
+def eigen_sym3_qr(Cm):
+    Cm = np.ascontiguousarray(Cm, np.float32).reshape(9)
+    ev = np.zeros(3, np.float32)
+    Q = np.zeros(9, np.float32)
+    it = load().orc_eigen_sym3_qr(Cm.ctypes.data, ev.ctypes.data, Q.ctypes.data)
+    return ev, Q.reshape(3, 3), it
+
+
+def pcl_eigen33(Cm):
+    Cm = np.ascontiguousarray(Cm, np.float32).reshape(9)
+    ev = np.zeros(1, np.float32)
+    v = np.zeros(3, np.float32)
+    load().orc_pcl_eigen33(Cm.ctypes.data, ev.ctypes.data, v.ctypes.data)
+    return float(ev[0]), v
+
+
+def structure_features(la1, la2, la3):
+    o = np.zeros(3, np.float32)
+    load().orc_structure_features(la1, la2, la3, o.ctypes.data)
+    return o
+
+
+def radius_pca_cloud(pts, radius: float, min_pts: int = 13, carry_forward: bool = True, nthreads: int = 1):
+    pts = _f4(pts)
+    out = np.zeros(pts.shape[0], FEATURE_DTYPE)
+    valid = np.zeros(pts.shape[0], np.uint8)
+    load().orc_radius_pca_cloud(pts.ctypes.data, pts.shape[0], radius, min_pts, int(carry_forward), out.ctypes.data,
+                                valid.ctypes.data, nthreads)
+    return out, valid
+
+
+def knn_pca_cloud(pts, k: int, center_mode: int = 0, want_normals: bool = False, nthreads: int = 0, want_features: bool = True):
+    pts = _f4(pts)
+    out = np.zeros(pts.shape[0], FEATURE_DTYPE) if want_features else None
+    nrm = np.zeros((pts.shape[0], 4), np.float32) if want_normals else None
+    load().orc_knn_pca_cloud(pts.ctypes.data, pts.shape[0], k, center_mode, out.ctypes.data if want_features else None,
+                             nrm.ctypes.data if want_normals else None, nthreads or num_threads())
+    return (out, nrm) if want_normals else out
+
+
+def segment_pca(pts, centres, offsets, idx):
+    pts = _f4(pts)
+    centres = np.ascontiguousarray(centres, np.float32)
+    offsets = np.ascontiguousarray(offsets, np.int64)
+    idx = np.ascontiguousarray(idx, np.int32)
+    nseg = offsets.shape[0] - 1
+    out = np.zeros(nseg, FEATURE_DTYPE)
+    load().orc_segment_pca(pts.ctypes.data, centres.ctypes.data, offsets.ctypes.data, idx.ctypes.data, nseg, out.ctypes.data)
+    return out
+
+
+def ring_project(pts, n_scan=16, horizon=1800, ang_res_x=0.2, ang_res_y=2.0, ang_bottom=15.0 + 0.1):
+    pts = _f4(pts)
+    rng = np.zeros((n_scan, horizon), np.float32)
+    pti = np.zeros((n_scan, horizon), np.int32)
+    tag = np.zeros((n_scan, horizon), np.float32)
+    lr = load().orc_ring_project(pts.ctypes.data, pts.shape[0], n_scan, horizon, np.float32(ang_res_x), np.float32(ang_res_y),
+                                 np.float32(ang_bottom), rng.ctypes.data, pti.ctypes.data, tag.ctypes.data)
+    return rng, pti, tag, int(lr)

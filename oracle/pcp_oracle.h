@@ -1,0 +1,94 @@
+/*
+ * pcp_oracle.h — CPU restatement of the reference's neighbourhood-PCA path.
+ *
+ * TEST INFRASTRUCTURE ONLY.  Nothing under oracle/ is part of the product: only tests/,
+ * __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may load it,
+ * and only as the checker or the timed CPU baseline.  libpcp.so never links or calls it.
+ *
+ * PARITY UNPINNED: the reference ships no tests, golden vectors or fixtures for this path
+ *  and PCL 1.8.1 / FLANN 1.8.x / Eigen 3.3 are not vendored in the
+ * reference tree nor installed in this image, so the upstream arithmetic is restated from
+ * the published algorithms and pinned by brute-force cross-checks and analytic known-answer
+ * cases (tests/test_oracle_*.py), not by outputs of the reference itself.
+ *
+ * Clouds are packed float4 (x,y,z,intensity), n×4 floats.
+ */
+#ifndef PCP_ORACLE_H_
+#define PCP_ORACLE_H_
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* same 68-byte layout as pcaAnalysist::pcaFeature (include/pcaAnalysis.h:34-45) */
+typedef struct orc_feature68 {
+  float la1, la2, la3;
+  float v1[3], v2[3], v3[3];
+  int32_t ptID, ptNum;
+  float lineStruc, planeStruc, scatterStruc;
+} orc_feature68;
+
+/* r2 exactly as PCL hands it to FLANN: (float)((double)r*(double)r)   */
+float orc_radius2(float radius);
+
+/* ---- search: brute force (defines membership/order) and a FLANN-like kd-tree ---- */
+/* neighbours of query q (an index into the cloud) with d2 < r2, sorted by (d2, idx).
+ * Returns the count; writes at most cap entries. */
+int64_t orc_radius_brute(const float* xyzi, int64_t n, int64_t q, float r2, int32_t* idx, float* d2, int64_t cap);
+/* first k of the (d2, idx) order; returns min(k, n) */
+int64_t orc_knn_brute(const float* xyzi, int64_t n, int64_t q, int k, int32_t* idx, float* d2);
+
+typedef struct orc_kdtree orc_kdtree;
+orc_kdtree* orc_kdtree_build(const float* xyzi, int64_t n, int leaf_max);
+void orc_kdtree_free(orc_kdtree* t);
+int64_t orc_kdtree_radius(const orc_kdtree* t, int64_t q, float r2, int32_t* idx, float* d2, int64_t cap);
+int64_t orc_kdtree_knn(const orc_kdtree* t, int64_t q, int k, int32_t* idx, float* d2);
+/* all queries, kNN lists (n×k), nthreads OpenMP threads */
+void orc_kdtree_knn_all(const orc_kdtree* t, int k, int32_t* idx, float* d2, int nthreads);
+/* per-query counts for a radius search (for CSR sizing) */
+void orc_kdtree_radius_counts(const orc_kdtree* t, float r2, int32_t* counts, int nthreads);
+/* CSR fill: offsets has n+1 entries */
+void orc_kdtree_radius_all(const orc_kdtree* t, float r2, const int64_t* offsets, int32_t* idx, float* d2, int nthreads);
+
+/* ---- numeric kernels ---- */
+/* pcl::computeCovarianceMatrixNormalized(cloud, indices, centroid, C) — SURVEY A.2.
+ * C is row-major 3×3. */
+void orc_covariance_about(const float* xyzi, const int32_t* idx, int64_t m, const float centre[3], float C[9]);
+/* Eigen::SelfAdjointEigenSolver<Matrix3f>::compute (tridiagonal QR) — SURVEY A.3.
+ * evals ascending; evecs row-major, column k = eigenvector k.  Returns iterations used. */
+int orc_eigen_sym3_qr(const float C[9], float evals[3], float evecs[9]);
+/* pcl::eigen33 smallest eigenpair — SURVEY A.4 */
+void orc_pcl_eigen33(const float C[9], float* eval, float evec[3]);
+/* features of src/pcaAnalysis.cpp:29-31 on ascending λ */
+void orc_structure_features(float la1, float la2, float la3, float out3[3]);
+
+/* ---- drivers: restated reference path ---- */
+/* pcaAnalysist::calculatePCAofPointCloud (src/pcaAnalysis.cpp:11-42): kd-tree build,
+ * per point radius search, PCA about the query, features, stale-tempFea carry (Q4, leading
+ * invalid entries zero-filled).  out has n records.  nthreads == 1 is the faithful
+ * single-thread run; > 1 parallelises the loop and applies the carry afterwards.
+ * valid[i] (optional) = 1 when ptNum >= min_pts. */
+void orc_radius_pca_cloud(const float* xyzi, int64_t n, float radius, int min_pts, int carry_forward,
+                          orc_feature68* out, uint8_t* valid, int nthreads);
+/* k-NN flavour: neighbours = first k of (d2, idx); PCA about the query (center_mode 0) or
+ * the mean (1); optional PCL-twin normals (nx,ny,nz,curvature) per point (n×4) */
+void orc_knn_pca_cloud(const float* xyzi, int64_t n, int k, int center_mode, orc_feature68* out,
+                       float* normals4, int nthreads);
+/* pcaAnalysist::calculatePCAofPoint(cloud, centro, idx, fea) (src/pcaAnalysis.cpp:89-121) */
+void orc_segment_pca(const float* xyzi, const float* centres_xyz, const int64_t* seg_offsets,
+                     const int32_t* seg_idx, int64_t n_seg, orc_feature68* out);
+
+/* RingProjector::projectPointCloud (src/ringProjection.cpp:24-81) for one frame.
+ * range_img: n_scan*horizon floats (FLT_MAX init); pt_index: int32 (−1 init), last writer
+ * wins; full_intensity (optional): the row + col/10000 tag per cell (NaN init... here −1).
+ * Returns the long-range (>60) count. */
+int32_t orc_ring_project(const float* xyzi, int64_t n, int n_scan, int horizon, float ang_res_x,
+                         float ang_res_y, float ang_bottom, float* range_img, int32_t* pt_index,
+                         float* full_intensity);
+
+int orc_num_threads(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

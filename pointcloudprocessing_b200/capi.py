@@ -1,0 +1,276 @@
+"""ctypes binding of libpcp.so — the C-ABI declared in include/pcp.h.
+
+This is the reference-side stub a Python caller would use; the C++ drop-in (`host/`) binds
+the same symbols.  There is no fallback: a missing library raises at import of `load()`,
+and every compute call raises `PcpError` when the CUDA path fails.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from typing import Optional
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libpcp.so")
+
+# numpy mirror of pcaAnalysist::pcaFeature (include/pcaAnalysis.h:34-45), 68 bytes
+FEATURE_DTYPE = np.dtype(
+    [
+        ("la", np.float32, (3,)),
+        ("v1", np.float32, (3,)),
+        ("v2", np.float32, (3,)),
+        ("v3", np.float32, (3,)),
+        ("ptID", np.int32),
+        ("ptNum", np.int32),
+        ("lineStruc", np.float32),
+        ("planeStruc", np.float32),
+        ("scatterStruc", np.float32),
+    ]
+)
+assert FEATURE_DTYPE.itemsize == 68
+
+CENTER_QUERY, CENTER_MEAN = 0, 1
+STAGES = ("bbox", "keys", "sort", "table", "search_pca", "carry", "h2d", "d2h")
+MAX_K = 32
+
+# every symbol include/pcp.h declares (checked by tests/test_abi.py)
+EXPORTS = (
+    "pcp_create", "pcp_destroy", "pcp_last_error", "pcp_version", "pcp_stream", "pcp_synchronize",
+    "pcp_last_timings", "pcp_launch_count", "pcp_set_cloud_host", "pcp_set_cloud_device",
+    "pcp_set_cloud_device_sharded", "pcp_build_grid", "pcp_grid_info", "pcp_radius_pca", "pcp_knn_pca",
+    "pcp_knn_neighbors", "pcp_radius_neighbors", "pcp_segment_pca", "pcp_ring_calib_default",
+    "pcp_ring_calib_from_xml", "pcp_ring_project",
+)
+
+
+class RingCalib(C.Structure):
+    _fields_ = [
+        ("n_scan", C.c_int32),
+        ("horizon_scan", C.c_int32),
+        ("ang_res_x", C.c_float),
+        ("ang_res_y", C.c_float),
+        ("ang_bottom", C.c_float),
+        ("vert_deg", C.c_float * 64),
+        ("dist_lsb_cm", C.c_float),
+        ("n_enabled", C.c_int32),
+    ]
+
+
+class PcpError(RuntimeError):
+    def __init__(self, status: int, msg: str):
+        super().__init__(f"pcp status {status}: {msg}")
+        self.status = status
+
+
+_lib = None
+
+
+def load() -> C.CDLL:
+    """Loads libpcp.so (built in-tree by __graft_entry__.build()).  No fallback."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(f"{LIB_PATH} is missing: run `python -c 'import __graft_entry__ as g; g.build()'`")
+    lib = C.CDLL(LIB_PATH)
+    vp, i32, i64, f32 = C.c_void_p, C.c_int, C.c_int64, C.c_float
+    sig = {
+        "pcp_create": (i32, [C.POINTER(vp), i32]),
+        "pcp_destroy": (i32, [vp]),
+        "pcp_last_error": (C.c_char_p, [vp]),
+        "pcp_version": (C.c_char_p, []),
+        "pcp_stream": (vp, [vp]),
+        "pcp_synchronize": (i32, [vp]),
+        "pcp_last_timings": (i32, [vp, vp, i32]),
+        "pcp_launch_count": (i64, [vp]),
+        "pcp_set_cloud_host": (i32, [vp, vp, i64, i32]),
+        "pcp_set_cloud_device": (i32, [vp, vp, i64]),
+        "pcp_set_cloud_device_sharded": (i32, [vp, vp, vp, i64, i64]),
+        "pcp_build_grid": (i32, [vp, f32, i32]),
+        "pcp_grid_info": (i32, [vp, vp, vp, vp]),
+        "pcp_radius_pca": (i32, [vp, f32, i32, i32, i32, vp, i32]),
+        "pcp_knn_pca": (i32, [vp, i32, i32, vp, vp, i32]),
+        "pcp_knn_neighbors": (i32, [vp, i32, vp, vp, i32]),
+        "pcp_radius_neighbors": (i32, [vp, f32, vp, vp, vp, vp, i32]),
+        "pcp_segment_pca": (i32, [vp, vp, vp, vp, i64, vp]),
+        "pcp_ring_calib_default": (i32, [C.POINTER(RingCalib)]),
+        "pcp_ring_calib_from_xml": (i32, [C.c_char_p, C.POINTER(RingCalib)]),
+        "pcp_ring_project": (i32, [vp, C.POINTER(RingCalib), vp, i64, vp, vp, vp, i32]),
+    }
+    for name, (res, args) in sig.items():
+        fn = getattr(lib, name)
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib
+
+
+def _ptr(a) -> Optional[int]:
+    """Address of a numpy array, a raw int device pointer, or None."""
+    if a is None:
+        return None
+    if isinstance(a, (int, np.integer)):
+        return int(a)
+    return a.ctypes.data
+
+
+def ring_calib_default() -> RingCalib:
+    c = RingCalib()
+    st = load().pcp_ring_calib_default(C.byref(c))
+    if st:
+        raise PcpError(st, "pcp_ring_calib_default")
+    return c
+
+
+def ring_calib_from_xml(path: str) -> RingCalib:
+    c = RingCalib()
+    st = load().pcp_ring_calib_from_xml(path.encode(), C.byref(c))
+    if st:
+        raise PcpError(st, f"pcp_ring_calib_from_xml({path})")
+    return c
+
+
+class Pcp:
+    """One pcp_ctx (one CUDA stream on one GPU)."""
+
+    def __init__(self, device: int = 0):
+        self.lib = load()
+        h = C.c_void_p()
+        st = self.lib.pcp_create(C.byref(h), device)
+        if st:
+            raise PcpError(st, "pcp_create failed (no sm_100 CUDA device?)")
+        self.h = h
+        self.n = 0
+        self.n_query = 0
+        self._keep = None
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.pcp_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    def _ck(self, st: int):
+        if st:
+            raise PcpError(st, self.lib.pcp_last_error(self.h).decode())
+
+    # ---- plumbing
+    @property
+    def stream(self) -> int:
+        return int(self.lib.pcp_stream(self.h) or 0)
+
+    def synchronize(self):
+        self._ck(self.lib.pcp_synchronize(self.h))
+
+    def timings(self) -> dict:
+        ms = np.zeros(len(STAGES), np.float32)
+        self._ck(self.lib.pcp_last_timings(self.h, ms.ctypes.data, len(STAGES)))
+        return dict(zip(STAGES, ms.tolist()))
+
+    def launch_count(self) -> int:
+        return int(self.lib.pcp_launch_count(self.h))
+
+    # ---- cloud + grid
+    def set_cloud(self, pts: np.ndarray):
+        """pts: (n, 4) float32 packed xyzi, or (n, 8) float32 = pcl::PointXYZI's 32-byte layout."""
+        pts = np.ascontiguousarray(pts, np.float32)
+        assert pts.ndim == 2 and pts.shape[1] in (3, 4, 8)
+        self._ck(self.lib.pcp_set_cloud_host(self.h, pts.ctypes.data, pts.shape[0], pts.shape[1] * 4))
+        self.n = self.n_query = pts.shape[0]
+
+    def set_cloud_host_ptr(self, ptr: int, n: int, stride: int):
+        self._ck(self.lib.pcp_set_cloud_host(self.h, ptr, n, stride))
+        self.n = self.n_query = n
+
+    def set_cloud_device(self, d_ptr: int, n: int, d_gid: Optional[int] = None, n_query: Optional[int] = None, keep=None):
+        nq = n if n_query is None else n_query
+        self._ck(self.lib.pcp_set_cloud_device_sharded(self.h, d_ptr, d_gid, n, nq))
+        self.n, self.n_query, self._keep = n, nq, keep
+
+    def build_grid(self, cell: float = 0.0, k_hint: int = 0):
+        self._ck(self.lib.pcp_build_grid(self.h, float(cell), int(k_hint)))
+
+    def grid_info(self):
+        dims = np.zeros(3, np.int32)
+        cell = C.c_float()
+        nc = C.c_int64()
+        self._ck(self.lib.pcp_grid_info(self.h, dims.ctypes.data, C.addressof(cell), C.addressof(nc)))
+        return dims.tolist(), cell.value, nc.value
+
+    # ---- compute (host outputs unless device pointers are given)
+    def radius_pca(self, radius: float, min_pts: int = 13, center_mode: int = CENTER_QUERY, carry_forward: bool = True,
+                   out_device: Optional[int] = None):
+        if out_device is not None:
+            self._ck(self.lib.pcp_radius_pca(self.h, radius, min_pts, center_mode, int(carry_forward), out_device, 1))
+            return None
+        out = np.zeros(self.n_query, FEATURE_DTYPE)
+        self._ck(self.lib.pcp_radius_pca(self.h, radius, min_pts, center_mode, int(carry_forward), out.ctypes.data, 0))
+        return out
+
+    def knn_pca(self, k: int, center_mode: int = CENTER_QUERY, want_normals: bool = False, out_device: Optional[int] = None,
+                normals_device: Optional[int] = None, out_host_ptr: Optional[int] = None):
+        if out_device is not None or normals_device is not None:
+            self._ck(self.lib.pcp_knn_pca(self.h, k, center_mode, out_device, normals_device, 1))
+            return None
+        if out_host_ptr is not None:
+            self._ck(self.lib.pcp_knn_pca(self.h, k, center_mode, out_host_ptr, None, 0))
+            return None
+        out = np.zeros(self.n_query, FEATURE_DTYPE)
+        nrm = np.zeros((self.n_query, 4), np.float32) if want_normals else None
+        self._ck(self.lib.pcp_knn_pca(self.h, k, center_mode, out.ctypes.data, _ptr(nrm), 0))
+        return (out, nrm) if want_normals else out
+
+    def knn_neighbors(self, k: int):
+        idx = np.zeros((self.n_query, k), np.int32)
+        d2 = np.zeros((self.n_query, k), np.float32)
+        self._ck(self.lib.pcp_knn_neighbors(self.h, k, idx.ctypes.data, d2.ctypes.data, 0))
+        return idx, d2
+
+    def radius_neighbors(self, radius: float):
+        counts = np.zeros(self.n_query, np.int32)
+        self._ck(self.lib.pcp_radius_neighbors(self.h, radius, counts.ctypes.data, None, None, None, 0))
+        offsets = np.zeros(self.n_query + 1, np.int64)
+        np.cumsum(counts, out=offsets[1:])
+        total = int(offsets[-1])
+        idx = np.zeros(max(total, 1), np.int32)
+        d2 = np.zeros(max(total, 1), np.float32)
+        self._ck(self.lib.pcp_radius_neighbors(self.h, radius, None, offsets.ctypes.data, idx.ctypes.data, d2.ctypes.data, 0))
+        return offsets, idx[:total], d2[:total]
+
+    def segment_pca(self, centres: np.ndarray, offsets: np.ndarray, idx: np.ndarray):
+        centres = np.ascontiguousarray(centres, np.float32)
+        offsets = np.ascontiguousarray(offsets, np.int64)
+        idx = np.ascontiguousarray(idx, np.int32)
+        nseg = offsets.shape[0] - 1
+        out = np.zeros(nseg, FEATURE_DTYPE)
+        self._ck(self.lib.pcp_segment_pca(self.h, centres.ctypes.data, offsets.ctypes.data, idx.ctypes.data, nseg, out.ctypes.data))
+        return out
+
+    def ring_project(self, calib: Optional[RingCalib] = None, frame_offsets: Optional[np.ndarray] = None,
+                     range_device: Optional[int] = None, index_device: Optional[int] = None, long_device: Optional[int] = None):
+        calib = calib or ring_calib_default()
+        nf = 1 if frame_offsets is None else frame_offsets.shape[0] - 1
+        fo = None if frame_offsets is None else np.ascontiguousarray(frame_offsets, np.int64)
+        cells = calib.n_scan * calib.horizon_scan
+        if range_device is not None:
+            self._ck(self.lib.pcp_ring_project(self.h, C.byref(calib), _ptr(fo), nf, range_device, index_device, long_device, 1))
+            return None
+        rng = np.zeros((nf, calib.n_scan, calib.horizon_scan), np.float32)
+        pti = np.zeros((nf, calib.n_scan, calib.horizon_scan), np.int32)
+        lr = np.zeros(nf, np.int32)
+        assert rng.size == cells * nf
+        self._ck(self.lib.pcp_ring_project(self.h, C.byref(calib), _ptr(fo), nf, rng.ctypes.data, pti.ctypes.data, lr.ctypes.data, 0))
+        return rng, pti, lr

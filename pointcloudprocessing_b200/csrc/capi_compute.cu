@@ -1,0 +1,317 @@
+// capi_compute.cu — compute entry points of the pcp_* C-ABI (include/pcp.h).
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "pcp_internal.cuh"
+
+int pcp_segment_pca_impl(pcp_ctx* ctx, const float* d_centres, const int64_t* d_offs, const int32_t* d_idx, int64_t n_seg,
+                         pcp_feature68* d_out);
+int pcp_ring_project_impl(pcp_ctx* ctx, const pcp_ring_calib* calib, const int64_t* h_offsets, int64_t n_frames, float* d_range,
+                          int32_t* d_index, int32_t* d_long);
+
+namespace {
+
+int require_grid(pcp_ctx* ctx, const char* who) {
+  if (!ctx) return PCP_ERR_INVALID_ARG;
+  if (!ctx->d_cloud || ctx->n <= 0) return pcp_fail(ctx, PCP_ERR_NO_CLOUD, who);
+  if (!ctx->grid_ok) return pcp_fail(ctx, PCP_ERR_NO_GRID, who);
+  cudaError_t e = cudaSetDevice(ctx->device);
+  if (e != cudaSuccess) return pcp_fail(ctx, PCP_ERR_CUDA, "cudaSetDevice", e);
+  return PCP_OK;
+}
+
+// device output: the caller's pointer when out_is_device, else a ctx-owned buffer
+template <typename T>
+int pick_out(pcp_ctx* ctx, DevBuf& own, T* user, int out_is_device, size_t count, T** dev) {
+  if (!user) {
+    *dev = nullptr;
+    return PCP_OK;
+  }
+  if (out_is_device) {
+    *dev = user;
+    return PCP_OK;
+  }
+  int rc = pcp_reserve(ctx, own, count * sizeof(T));
+  if (rc) return rc;
+  *dev = (T*)own.p;
+  return PCP_OK;
+}
+
+template <typename T>
+int copy_back(pcp_ctx* ctx, T* user, const T* dev, int out_is_device, size_t count) {
+  if (!user || out_is_device || count == 0) return PCP_OK;
+  PCP_CUDA(cudaMemcpyAsync(user, dev, count * sizeof(T), cudaMemcpyDeviceToHost, ctx->stream));
+  return PCP_OK;
+}
+
+// smallest stencil half-width whose guaranteed coverage (R − 1e-6)·cell holds the radius
+int stencil_for_radius(const GridDesc& g, float r2) {
+  double r = std::sqrt((double)r2) * (1.0 + 2e-6);
+  int R = (int)std::ceil(r * g.inv_cell + 2e-6);
+  return R < 1 ? 1 : R;
+}
+
+}  // namespace
+
+extern "C" {
+
+PCP_API int pcp_radius_pca(pcp_ctx* ctx, float radius, int min_pts, int center_mode, int carry_forward, pcp_feature68* out,
+                           int out_is_device) {
+  int rc = require_grid(ctx, "pcp_radius_pca");
+  if (rc) return rc;
+  if (!out || !(radius > 0.f) || (center_mode != PCP_CENTER_QUERY && center_mode != PCP_CENTER_MEAN))
+    return pcp_fail(ctx, PCP_ERR_INVALID_ARG, "pcp_radius_pca: bad argument");
+  const int64_t nq = ctx->n_query;
+  SearchParams sp;
+  memset(&sp, 0, sizeof(sp));
+  sp.mode = 1;
+  sp.r2 = (float)((double)radius * (double)radius);  // PCL: static_cast<float>(r*r) in double
+  sp.R0 = stencil_for_radius(ctx->grid, sp.r2);
+  sp.min_pts = min_pts;
+  sp.center_mode = center_mode;
+  if ((rc = pick_out(ctx, ctx->out_feat, out, out_is_device, (size_t)nq, &sp.out))) return rc;
+  if ((rc = pcp_reserve(ctx, ctx->valid, (size_t)nq))) return rc;
+  if ((rc = pcp_reserve(ctx, ctx->flags, sizeof(int)))) return rc;
+  sp.valid = (uint8_t*)ctx->valid.p;
+  sp.overflow_flag = (int*)ctx->flags.p;
+  PCP_CUDA(cudaMemsetAsync(ctx->flags.p, 0, sizeof(int), ctx->stream));
+  if ((rc = pcp_search_launch(ctx, sp))) return rc;
+  if (carry_forward && (rc = pcp_carry_forward_impl(ctx, sp.out, sp.valid, nq))) return rc;
+  int h_flag = 0;
+  pcp_tic(ctx, PCP_T_D2H);
+  if ((rc = copy_back(ctx, out, sp.out, out_is_device, (size_t)nq))) return rc;
+  pcp_toc(ctx, PCP_T_D2H);
+  PCP_CUDA(cudaMemcpyAsync(&h_flag, ctx->flags.p, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+  PCP_CUDA(cudaStreamSynchronize(ctx->stream));
+  if (h_flag) return pcp_fail(ctx, PCP_ERR_NEIGHBOR_OVERFLOW, "pcp_radius_pca: a neighbourhood exceeded the per-query buffer");
+  return PCP_OK;
+}
+
+PCP_API int pcp_knn_pca(pcp_ctx* ctx, int k, int center_mode, pcp_feature68* out, pcp_normal16* normals, int out_is_device) {
+  int rc = require_grid(ctx, "pcp_knn_pca");
+  if (rc) return rc;
+  if (k < 1 || k > PCP_MAX_K) return pcp_fail(ctx, PCP_ERR_K_UNSUPPORTED, "pcp_knn_pca: k outside [1, PCP_MAX_K]");
+  if ((!out && !normals) || (center_mode != PCP_CENTER_QUERY && center_mode != PCP_CENTER_MEAN))
+    return pcp_fail(ctx, PCP_ERR_INVALID_ARG, "pcp_knn_pca: bad argument");
+  const int64_t nq = ctx->n_query;
+  SearchParams sp;
+  memset(&sp, 0, sizeof(sp));
+  sp.mode = 0;
+  sp.k = k;
+  sp.R0 = 1;
+  sp.center_mode = center_mode;
+  if ((rc = pick_out(ctx, ctx->out_feat, out, out_is_device, (size_t)nq, &sp.out))) return rc;
+  if ((rc = pick_out(ctx, ctx->out_norm, normals, out_is_device, (size_t)nq, &sp.normals))) return rc;
+  if ((rc = pcp_search_launch(ctx, sp))) return rc;
+  pcp_tic(ctx, PCP_T_D2H);
+  if ((rc = copy_back(ctx, out, sp.out, out_is_device, (size_t)nq))) return rc;
+  if ((rc = copy_back(ctx, normals, sp.normals, out_is_device, (size_t)nq))) return rc;
+  pcp_toc(ctx, PCP_T_D2H);
+  if (!out_is_device) PCP_CUDA(cudaStreamSynchronize(ctx->stream));
+  return PCP_OK;
+}
+
+PCP_API int pcp_knn_neighbors(pcp_ctx* ctx, int k, int32_t* idx, float* d2, int out_is_device) {
+  int rc = require_grid(ctx, "pcp_knn_neighbors");
+  if (rc) return rc;
+  if (k < 1 || k > PCP_MAX_K) return pcp_fail(ctx, PCP_ERR_K_UNSUPPORTED, "pcp_knn_neighbors: k outside [1, PCP_MAX_K]");
+  if (!idx) return pcp_fail(ctx, PCP_ERR_INVALID_ARG, "pcp_knn_neighbors: idx is NULL");
+  const size_t cnt = (size_t)ctx->n_query * (size_t)k;
+  SearchParams sp;
+  memset(&sp, 0, sizeof(sp));
+  sp.mode = 0;
+  sp.k = k;
+  sp.R0 = 1;
+  if ((rc = pick_out(ctx, ctx->out_idx, idx, out_is_device, cnt, &sp.nn_idx))) return rc;
+  if ((rc = pick_out(ctx, ctx->out_d2, d2, out_is_device, cnt, &sp.nn_d2))) return rc;
+  if ((rc = pcp_search_launch(ctx, sp))) return rc;
+  if ((rc = copy_back(ctx, idx, sp.nn_idx, out_is_device, cnt))) return rc;
+  if ((rc = copy_back(ctx, d2, sp.nn_d2, out_is_device, cnt))) return rc;
+  if (!out_is_device) PCP_CUDA(cudaStreamSynchronize(ctx->stream));
+  return PCP_OK;
+}
+
+PCP_API int pcp_radius_neighbors(pcp_ctx* ctx, float radius, int32_t* counts, const int64_t* offsets, int32_t* idx, float* d2,
+                                 int out_is_device) {
+  int rc = require_grid(ctx, "pcp_radius_neighbors");
+  if (rc) return rc;
+  if (!(radius > 0.f) || (!counts && !idx) || (idx && !offsets))
+    return pcp_fail(ctx, PCP_ERR_INVALID_ARG, "pcp_radius_neighbors: bad argument");
+  const int64_t nq = ctx->n_query;
+  SearchParams sp;
+  memset(&sp, 0, sizeof(sp));
+  sp.mode = 1;
+  sp.r2 = (float)((double)radius * (double)radius);
+  sp.R0 = stencil_for_radius(ctx->grid, sp.r2);
+  sp.min_pts = 0x7FFFFFFF;  // no PCA
+  if ((rc = pcp_reserve(ctx, ctx->flags, sizeof(int)))) return rc;
+  sp.overflow_flag = (int*)ctx->flags.p;
+  PCP_CUDA(cudaMemsetAsync(ctx->flags.p, 0, sizeof(int), ctx->stream));
+  size_t total = 0;
+  const int64_t* d_offsets = offsets;
+  if (idx) {
+    if (out_is_device) {
+      int64_t last = 0;
+      PCP_CUDA(cudaMemcpyAsync(&last, offsets + nq, sizeof(int64_t), cudaMemcpyDeviceToHost, ctx->stream));
+      PCP_CUDA(cudaStreamSynchronize(ctx->stream));
+      total = (size_t)last;
+    } else {
+      total = (size_t)offsets[nq];
+      if ((rc = pcp_reserve(ctx, ctx->staging, (size_t)(nq + 1) * sizeof(int64_t)))) return rc;
+      PCP_CUDA(cudaMemcpyAsync(ctx->staging.p, offsets, (size_t)(nq + 1) * sizeof(int64_t), cudaMemcpyHostToDevice, ctx->stream));
+      d_offsets = (const int64_t*)ctx->staging.p;
+    }
+  }
+  sp.offsets = idx ? d_offsets : nullptr;
+  if ((rc = pick_out(ctx, ctx->out_counts, counts, out_is_device, (size_t)nq, &sp.counts))) return rc;
+  if ((rc = pick_out(ctx, ctx->out_idx, idx, out_is_device, total, &sp.nn_idx))) return rc;
+  if ((rc = pick_out(ctx, ctx->out_d2, d2, out_is_device, total, &sp.nn_d2))) return rc;
+  if ((rc = pcp_search_launch(ctx, sp))) return rc;
+  if ((rc = copy_back(ctx, counts, sp.counts, out_is_device, (size_t)nq))) return rc;
+  if ((rc = copy_back(ctx, idx, sp.nn_idx, out_is_device, total))) return rc;
+  if ((rc = copy_back(ctx, d2, sp.nn_d2, out_is_device, total))) return rc;
+  int h_flag = 0;
+  PCP_CUDA(cudaMemcpyAsync(&h_flag, ctx->flags.p, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+  PCP_CUDA(cudaStreamSynchronize(ctx->stream));
+  if (h_flag && idx) return pcp_fail(ctx, PCP_ERR_NEIGHBOR_OVERFLOW, "pcp_radius_neighbors: a neighbourhood exceeded the per-query buffer");
+  return PCP_OK;
+}
+
+PCP_API int pcp_segment_pca(pcp_ctx* ctx, const float* centres_xyz, const int64_t* seg_offsets, const int32_t* seg_idx, int64_t n_seg,
+                            pcp_feature68* out) {
+  if (!ctx) return PCP_ERR_INVALID_ARG;
+  if (!ctx->d_cloud || ctx->n <= 0) return pcp_fail(ctx, PCP_ERR_NO_CLOUD, "pcp_segment_pca: no cloud set");
+  if (n_seg < 0 || (n_seg > 0 && (!centres_xyz || !seg_offsets || !seg_idx || !out)))
+    return pcp_fail(ctx, PCP_ERR_INVALID_ARG, "pcp_segment_pca: bad argument");
+  if (n_seg == 0) return PCP_OK;
+  PCP_CUDA(cudaSetDevice(ctx->device));
+  const size_t n_idx = (size_t)seg_offsets[n_seg];
+  for (size_t i = 0; i < n_idx; ++i)
+    if (seg_idx[i] < 0 || seg_idx[i] >= ctx->n) return pcp_fail(ctx, PCP_ERR_INVALID_ARG, "pcp_segment_pca: index out of range");
+  const size_t b_cent = (size_t)n_seg * 3 * sizeof(float), b_off = (size_t)(n_seg + 1) * sizeof(int64_t), b_idx = n_idx * sizeof(int32_t);
+  const size_t o_off = (b_cent + 15) & ~(size_t)15, o_idx = (o_off + b_off + 15) & ~(size_t)15;
+  int rc = pcp_reserve(ctx, ctx->staging, o_idx + b_idx + 16);
+  if (rc) return rc;
+  if ((rc = pcp_reserve(ctx, ctx->out_feat, (size_t)n_seg * sizeof(pcp_feature68)))) return rc;
+  char* st = (char*)ctx->staging.p;
+  PCP_CUDA(cudaMemcpyAsync(st, centres_xyz, b_cent, cudaMemcpyHostToDevice, ctx->stream));
+  PCP_CUDA(cudaMemcpyAsync(st + o_off, seg_offsets, b_off, cudaMemcpyHostToDevice, ctx->stream));
+  if (b_idx) PCP_CUDA(cudaMemcpyAsync(st + o_idx, seg_idx, b_idx, cudaMemcpyHostToDevice, ctx->stream));
+  rc = pcp_segment_pca_impl(ctx, (const float*)st, (const int64_t*)(st + o_off), (const int32_t*)(st + o_idx), n_seg,
+                            (pcp_feature68*)ctx->out_feat.p);
+  if (rc) return rc;
+  PCP_CUDA(cudaMemcpyAsync(out, ctx->out_feat.p, (size_t)n_seg * sizeof(pcp_feature68), cudaMemcpyDeviceToHost, ctx->stream));
+  PCP_CUDA(cudaStreamSynchronize(ctx->stream));
+  return PCP_OK;
+}
+
+// ---- ring projection -------------------------------------------------------------------------
+
+PCP_API int pcp_ring_calib_default(pcp_ring_calib* c) {
+  if (!c) return PCP_ERR_INVALID_ARG;
+  memset(c, 0, sizeof(*c));
+  c->n_scan = 16;
+  c->horizon_scan = 1800;
+  c->ang_res_x = 0.2f;
+  c->ang_res_y = 2.0f;
+  c->ang_bottom = (float)(15.0 + 0.1);
+  c->dist_lsb_cm = 0.2f;
+  c->n_enabled = 16;
+  for (int i = 0; i < 64; ++i) c->vert_deg[i] = 0.f;
+  for (int i = 0; i < 32; ++i) {
+    int j = i % 16;
+    c->vert_deg[i] = (j % 2 == 0) ? (float)(-15 + j) : (float)(j);  // −15,1,−13,3,…,−1,15
+  }
+  return PCP_OK;
+}
+
+PCP_API int pcp_ring_calib_from_xml(const char* path, pcp_ring_calib* c) {
+  if (!path || !c) return PCP_ERR_INVALID_ARG;
+  FILE* f = fopen(path, "rb");
+  if (!f) return PCP_ERR_IO;
+  std::string s;
+  char chunk[65536];
+  size_t got;
+  while ((got = fread(chunk, 1, sizeof(chunk), f)) > 0) s.append(chunk, got);
+  fclose(f);
+  pcp_ring_calib_default(c);
+  auto tag_value = [&](const char* tag, size_t from, size_t* after) -> const char* {
+    std::string open = std::string("<") + tag + ">";
+    size_t p = s.find(open, from);
+    if (p == std::string::npos) return nullptr;
+    if (after) *after = p + open.size();
+    return s.c_str() + p + open.size();
+  };
+  size_t pos = 0;
+  const char* v = tag_value("distLSB_", 0, &pos);
+  if (!v) return PCP_ERR_IO;
+  c->dist_lsb_cm = (float)atof(v);
+  // enabled_ : <count>64</count> then 64 <item>
+  size_t en = s.find("<enabled_>");
+  size_t en_end = s.find("</enabled_>");
+  if (en == std::string::npos || en_end == std::string::npos) return PCP_ERR_IO;
+  int enabled[64] = {0};
+  int ne = 0;
+  for (size_t p = s.find("<item>", en); p != std::string::npos && p < en_end && ne < 64; p = s.find("<item>", p + 6))
+    enabled[ne++] = atoi(s.c_str() + p + 6);
+  // per-laser vertical corrections in file order, with their ids
+  int n_px = 0;
+  size_t p = 0;
+  for (;;) {
+    size_t idp;
+    const char* idv = tag_value("id_", p, &idp);
+    if (!idv) break;
+    size_t vp;
+    const char* vv = tag_value("vertCorrection_", idp, &vp);
+    if (!vv) break;
+    int id = atoi(idv);
+    if (id >= 0 && id < 64) c->vert_deg[id] = (float)atof(vv);
+    p = vp;
+    ++n_px;
+  }
+  if (n_px == 0) return PCP_ERR_IO;
+  float lo = 1e9f, hi = -1e9f;
+  int n_en = 0;
+  for (int i = 0; i < 64; ++i)
+    if (enabled[i]) {
+      ++n_en;
+      lo = fminf(lo, c->vert_deg[i]);
+      hi = fmaxf(hi, c->vert_deg[i]);
+    }
+  if (n_en < 2) return PCP_ERR_IO;
+  c->n_enabled = n_en;
+  c->n_scan = n_en;
+  c->ang_res_y = (hi - lo) / (float)(n_en - 1);
+  c->ang_bottom = -lo + 0.1f;  // the reference's literal 15.0+0.1 (include/ringProjection.h:20)
+  return PCP_OK;
+}
+
+PCP_API int pcp_ring_project(pcp_ctx* ctx, const pcp_ring_calib* calib, const int64_t* frame_offsets, int64_t n_frames,
+                             float* range_img, int32_t* pt_index, int32_t* long_range, int out_is_device) {
+  if (!ctx) return PCP_ERR_INVALID_ARG;
+  if (!ctx->d_cloud || ctx->n <= 0) return pcp_fail(ctx, PCP_ERR_NO_CLOUD, "pcp_ring_project: no cloud set");
+  if (!calib || !range_img || !pt_index || n_frames < 1 || n_frames > 65535 || calib->n_scan < 1 || calib->horizon_scan < 1)
+    return pcp_fail(ctx, PCP_ERR_INVALID_ARG, "pcp_ring_project: bad argument");
+  if (!frame_offsets && n_frames != 1) return pcp_fail(ctx, PCP_ERR_INVALID_ARG, "pcp_ring_project: frame_offsets required");
+  if (frame_offsets && (frame_offsets[0] < 0 || frame_offsets[n_frames] > ctx->n))
+    return pcp_fail(ctx, PCP_ERR_INVALID_ARG, "pcp_ring_project: frame_offsets outside the cloud");
+  PCP_CUDA(cudaSetDevice(ctx->device));
+  const size_t cells = (size_t)calib->n_scan * calib->horizon_scan * (size_t)n_frames;
+  float* d_range;
+  int32_t *d_index, *d_long;
+  int rc;
+  if ((rc = pick_out(ctx, ctx->ring_range, range_img, out_is_device, cells, &d_range))) return rc;
+  if ((rc = pick_out(ctx, ctx->ring_idx, pt_index, out_is_device, cells, &d_index))) return rc;
+  if ((rc = pick_out(ctx, ctx->ring_long, long_range, out_is_device, (size_t)n_frames, &d_long))) return rc;
+  if ((rc = pcp_ring_project_impl(ctx, calib, frame_offsets, n_frames, d_range, d_index, d_long))) return rc;
+  if ((rc = copy_back(ctx, range_img, d_range, out_is_device, cells))) return rc;
+  if ((rc = copy_back(ctx, pt_index, d_index, out_is_device, cells))) return rc;
+  if ((rc = copy_back(ctx, long_range, d_long, out_is_device, (size_t)n_frames))) return rc;
+  if (!out_is_device) PCP_CUDA(cudaStreamSynchronize(ctx->stream));
+  return PCP_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,172 @@
+// capi_core.cu — lifetime, buffers, timing and cloud hand-over of the pcp_* C-ABI (include/pcp.h).
+#include <cstdio>
+#include <cstring>
+#include <new>
+
+#include "pcp_internal.cuh"
+
+int pcp_fail(pcp_ctx* ctx, int status, const char* what, cudaError_t ce) {
+  if (ctx) {
+    ctx->err = what ? what : "";
+    if (ce != cudaSuccess) {
+      ctx->err += ": ";
+      ctx->err += cudaGetErrorString(ce);
+    }
+  }
+  return status;
+}
+
+int pcp_reserve(pcp_ctx* ctx, DevBuf& b, size_t bytes) {
+  if (bytes <= b.cap && b.p) return PCP_OK;
+  if (b.p) {
+    cudaStreamSynchronize(ctx->stream);
+    cudaFree(b.p);
+    b.p = nullptr;
+    b.cap = 0;
+  }
+  size_t want = bytes < 256 ? 256 : bytes;
+  cudaError_t e = cudaMalloc(&b.p, want);
+  if (e != cudaSuccess) {
+    b.p = nullptr;
+    return pcp_fail(ctx, PCP_ERR_OOM, "cudaMalloc", e);
+  }
+  b.cap = want;
+  return PCP_OK;
+}
+
+void pcp_tic(pcp_ctx* ctx, int stage) { cudaEventRecord(ctx->ev[2 * stage], ctx->stream); }
+void pcp_toc(pcp_ctx* ctx, int stage) {
+  cudaEventRecord(ctx->ev[2 * stage + 1], ctx->stream);
+  ctx->ev_used[stage] = true;
+}
+void pcp_collect_timings(pcp_ctx* ctx) {
+  for (int s = 0; s < PCP_T_COUNT; ++s) {
+    if (!ctx->ev_used[s]) continue;
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, ctx->ev[2 * s], ctx->ev[2 * s + 1]) == cudaSuccess) ctx->t_ms[s] = ms;
+  }
+}
+
+static void free_buf(DevBuf& b) {
+  if (b.p) cudaFree(b.p);
+  b.p = nullptr;
+  b.cap = 0;
+}
+
+extern "C" {
+
+PCP_API const char* pcp_version(void) { return "pcp 0.1 (sm_100a)"; }
+
+PCP_API int pcp_create(pcp_ctx** out, int device) {
+  if (!out) return PCP_ERR_INVALID_ARG;
+  *out = nullptr;
+  int count = 0;
+  if (cudaGetDeviceCount(&count) != cudaSuccess || device < 0 || device >= count) return PCP_ERR_NO_DEVICE;
+  cudaDeviceProp prop;
+  if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) return PCP_ERR_NO_DEVICE;
+  if (prop.major != 10) return PCP_ERR_NO_DEVICE;  // kernels are built for sm_100a only
+  if (cudaSetDevice(device) != cudaSuccess) return PCP_ERR_CUDA;
+  pcp_ctx* ctx = new (std::nothrow) pcp_ctx();
+  if (!ctx) return PCP_ERR_OOM;
+  ctx->device = device;
+  if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) {
+    delete ctx;
+    return PCP_ERR_CUDA;
+  }
+  for (int i = 0; i < 2 * PCP_T_COUNT; ++i) cudaEventCreate(&ctx->ev[i]);
+  *out = ctx;
+  return PCP_OK;
+}
+
+PCP_API int pcp_destroy(pcp_ctx* ctx) {
+  if (!ctx) return PCP_OK;
+  cudaSetDevice(ctx->device);
+  cudaStreamSynchronize(ctx->stream);
+  DevBuf* bufs[] = {&ctx->own_cloud, &ctx->bbox, &ctx->keys_in, &ctx->keys_sorted, &ctx->vals_in, &ctx->vals_sorted,
+                    &ctx->sort_tmp, &ctx->sorted_pts, &ctx->sorted_slot, &ctx->cell_end, &ctx->scan_tmp, &ctx->out_feat,
+                    &ctx->out_norm, &ctx->out_idx, &ctx->out_d2, &ctx->out_counts, &ctx->flags, &ctx->valid,
+                    &ctx->last_valid, &ctx->staging, &ctx->ring_range, &ctx->ring_idx, &ctx->ring_long,
+                    &ctx->ring_offsets, &ctx->ring_key};
+  for (DevBuf* b : bufs) free_buf(*b);
+  for (int i = 0; i < 2 * PCP_T_COUNT; ++i)
+    if (ctx->ev[i]) cudaEventDestroy(ctx->ev[i]);
+  cudaStreamDestroy(ctx->stream);
+  delete ctx;
+  return PCP_OK;
+}
+
+PCP_API const char* pcp_last_error(const pcp_ctx* ctx) { return ctx ? ctx->err.c_str() : "null context"; }
+PCP_API void* pcp_stream(pcp_ctx* ctx) { return ctx ? (void*)ctx->stream : nullptr; }
+PCP_API int64_t pcp_launch_count(const pcp_ctx* ctx) { return ctx ? ctx->launches : 0; }
+
+PCP_API int pcp_synchronize(pcp_ctx* ctx) {
+  if (!ctx) return PCP_ERR_INVALID_ARG;
+  PCP_CUDA(cudaStreamSynchronize(ctx->stream));
+  return PCP_OK;
+}
+
+PCP_API int pcp_last_timings(pcp_ctx* ctx, float* ms, int n) {
+  if (!ctx || !ms) return PCP_ERR_INVALID_ARG;
+  PCP_CUDA(cudaStreamSynchronize(ctx->stream));
+  pcp_collect_timings(ctx);
+  for (int i = 0; i < n && i < PCP_T_COUNT; ++i) ms[i] = ctx->t_ms[i];
+  return PCP_OK;
+}
+
+// strided host AoS -> packed float4 on the device (one 2-D copy: 16 of every stride bytes)
+PCP_API int pcp_set_cloud_host(pcp_ctx* ctx, const void* pts, int64_t n, int stride_bytes) {
+  if (!ctx || (!pts && n > 0) || n < 0 || stride_bytes < 12) return pcp_fail(ctx, PCP_ERR_INVALID_ARG, "pcp_set_cloud_host");
+  PCP_CUDA(cudaSetDevice(ctx->device));
+  ctx->grid_ok = false;
+  ctx->n = ctx->n_query = n;
+  ctx->d_gid = nullptr;
+  int rc = pcp_reserve(ctx, ctx->own_cloud, (size_t)std::max<int64_t>(n, 1) * sizeof(float4));
+  if (rc) return rc;
+  ctx->d_cloud = (const float4*)ctx->own_cloud.p;
+  if (n == 0) return PCP_OK;
+  pcp_tic(ctx, PCP_T_H2D);
+  if (stride_bytes >= 16) {
+    PCP_CUDA(cudaMemcpy2DAsync(ctx->own_cloud.p, 16, pts, (size_t)stride_bytes, 16, (size_t)n, cudaMemcpyHostToDevice, ctx->stream));
+  } else {
+    // packed xyz (12 B): widen on the way
+    PCP_CUDA(cudaMemsetAsync(ctx->own_cloud.p, 0, (size_t)n * 16, ctx->stream));
+    PCP_CUDA(cudaMemcpy2DAsync(ctx->own_cloud.p, 16, pts, (size_t)stride_bytes, 12, (size_t)n, cudaMemcpyHostToDevice, ctx->stream));
+  }
+  pcp_toc(ctx, PCP_T_H2D);
+  PCP_CUDA(cudaStreamSynchronize(ctx->stream));
+  return PCP_OK;
+}
+
+PCP_API int pcp_set_cloud_device_sharded(pcp_ctx* ctx, const void* d_xyzi, const int32_t* d_global_id, int64_t n, int64_t n_query) {
+  if (!ctx || (!d_xyzi && n > 0) || n < 0 || n_query < 0 || n_query > n) return pcp_fail(ctx, PCP_ERR_INVALID_ARG, "pcp_set_cloud_device");
+  PCP_CUDA(cudaSetDevice(ctx->device));
+  ctx->grid_ok = false;
+  ctx->d_cloud = (const float4*)d_xyzi;
+  ctx->d_gid = d_global_id;
+  ctx->n = n;
+  ctx->n_query = n_query;
+  return PCP_OK;
+}
+
+PCP_API int pcp_set_cloud_device(pcp_ctx* ctx, const void* d_xyzi, int64_t n) {
+  return pcp_set_cloud_device_sharded(ctx, d_xyzi, nullptr, n, n);
+}
+
+PCP_API int pcp_build_grid(pcp_ctx* ctx, float cell, int k_hint) {
+  if (!ctx) return PCP_ERR_INVALID_ARG;
+  if (!ctx->d_cloud || ctx->n <= 0) return pcp_fail(ctx, PCP_ERR_NO_CLOUD, "pcp_build_grid: no cloud set");
+  PCP_CUDA(cudaSetDevice(ctx->device));
+  return pcp_grid_build_impl(ctx, cell, k_hint);
+}
+
+PCP_API int pcp_grid_info(pcp_ctx* ctx, int32_t dims[3], float* cell, int64_t* n_cells) {
+  if (!ctx) return PCP_ERR_INVALID_ARG;
+  if (!ctx->grid_ok) return pcp_fail(ctx, PCP_ERR_NO_GRID, "pcp_grid_info: no grid");
+  if (dims)
+    for (int a = 0; a < 3; ++a) dims[ctx->grid.ax[a]] = ctx->grid.dim[a];
+  if (cell) *cell = ctx->grid.cell;
+  if (n_cells) *n_cells = ctx->grid.n_cells;
+  return PCP_OK;
+}
+
+}  // extern "C"

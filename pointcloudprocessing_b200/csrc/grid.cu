@@ -1,0 +1,227 @@
+// grid.cu — device build of the cell-sorted uniform grid that replaces the FLANN
+// KDTreeSingleIndex build inside pcl::KdTreeFLANN::setInputCloud (reference call site
+// src/pcaAnalysis.cpp:14-15).  Stages: bbox reduce → cell keys → radix sort (key, local
+// index) → gather to cell order + cell-end marks → max-scan into the lower-bound table.
+#include <cub/device/device_radix_sort.cuh>
+#include <cub/device/device_scan.cuh>
+
+#include <cfloat>
+#include <cmath>
+#include <cstring>
+
+#include "pcp_internal.cuh"
+
+namespace {
+
+__device__ __forceinline__ uint32_t enc_ordered(float f) {
+  uint32_t b = __float_as_uint(f);
+  return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
+}
+inline float dec_ordered(uint32_t u) {
+  uint32_t b = (u & 0x80000000u) ? (u & 0x7FFFFFFFu) : ~u;
+  float f;
+  memcpy(&f, &b, 4);
+  return f;
+}
+
+__device__ __forceinline__ bool finite3(float4 p) { return isfinite(p.x) && isfinite(p.y) && isfinite(p.z); }
+
+// bbox[0..2] = min xyz, bbox[3..5] = max xyz (ordered-uint encoding); grid-stride, one
+// float4 per thread per step (coalesced 16-B loads), warp-shuffle then one atomic per warp.
+__global__ void __launch_bounds__(256) bbox_kernel(const float4* __restrict__ pts, int64_t n,
+                                                   uint32_t* __restrict__ bbox) {
+  float lo[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, hi[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    float4 p = __ldg(pts + i);
+    if (finite3(p)) {
+      lo[0] = fminf(lo[0], p.x); hi[0] = fmaxf(hi[0], p.x);
+      lo[1] = fminf(lo[1], p.y); hi[1] = fmaxf(hi[1], p.y);
+      lo[2] = fminf(lo[2], p.z); hi[2] = fmaxf(hi[2], p.z);
+    }
+  }
+#pragma unroll
+  for (int d = 0; d < 3; ++d) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      lo[d] = fminf(lo[d], __shfl_xor_sync(0xffffffffu, lo[d], o));
+      hi[d] = fmaxf(hi[d], __shfl_xor_sync(0xffffffffu, hi[d], o));
+    }
+  }
+  if ((threadIdx.x & 31) == 0) {
+#pragma unroll
+    for (int d = 0; d < 3; ++d) {
+      atomicMin(bbox + d, enc_ordered(lo[d]));
+      atomicMax(bbox + 3 + d, enc_ordered(hi[d]));
+    }
+  }
+}
+
+__global__ void bbox_init_kernel(uint32_t* bbox) {
+  if (threadIdx.x < 3) bbox[threadIdx.x] = 0xFFFFFFFFu;
+  else if (threadIdx.x < 6) bbox[threadIdx.x] = 0u;
+}
+
+// Cell coordinates in double: (p − origin) is exact for fp32 inputs, so a neighbour within
+// (R − 1e-6) cells of a query in true distance is never more than R cells away in index.
+__device__ __forceinline__ uint32_t cell_of(const GridDesc& g, float4 p) {
+  const float c[3] = {p.x, p.y, p.z};
+  uint32_t id = 0;
+#pragma unroll
+  for (int a = 2; a >= 0; --a) {
+    int axis = g.ax[a];
+    double t = ((double)c[axis] - g.origin[axis]) * g.inv_cell;
+    int ci = (int)floor(t);
+    ci = max(0, min(ci, g.dim[a] - 1));
+    id = id * (uint32_t)g.dim[a] + (uint32_t)ci;
+  }
+  return id;
+}
+
+__global__ void __launch_bounds__(256) keys_kernel(const float4* __restrict__ pts, int64_t n, GridDesc g,
+                                                   uint32_t* __restrict__ keys, int32_t* __restrict__ vals) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  float4 p = __ldg(pts + i);
+  keys[i] = finite3(p) ? cell_of(g, p) : g.n_cells;
+  vals[i] = (int32_t)i;
+}
+
+// Gather into cell order; mark E[key+1] = pos+1 at the last point of every cell.
+__global__ void __launch_bounds__(256)
+    gather_kernel(const float4* __restrict__ pts, const int32_t* __restrict__ gid, const uint32_t* __restrict__ keys_sorted,
+                  const int32_t* __restrict__ vals_sorted, int64_t n, int64_t n_query, float4* __restrict__ sorted,
+                  int32_t* __restrict__ slot, uint32_t* __restrict__ cell_end) {
+  int64_t pos = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (pos >= n) return;
+  int32_t li = vals_sorted[pos];
+  float4 p = __ldg(pts + li);
+  int32_t g = gid ? __ldg(gid + li) : li;
+  p.w = __int_as_float(g);
+  sorted[pos] = p;
+  slot[pos] = li < n_query ? li : -1;
+  uint32_t k = keys_sorted[pos];
+  if (pos == n - 1 || keys_sorted[pos + 1] != k) cell_end[k + 1] = (uint32_t)(pos + 1);
+}
+
+struct MaxOp {
+  __device__ __forceinline__ uint32_t operator()(uint32_t a, uint32_t b) const { return a > b ? a : b; }
+};
+
+int bits_for(uint32_t v) {
+  int b = 1;
+  while (b < 32 && (v >> b) != 0) ++b;
+  return b;
+}
+
+}  // namespace
+
+int pcp_grid_build_impl(pcp_ctx* ctx, float cell, int k_hint) {
+  const int64_t n = ctx->n;
+  ctx->grid_ok = false;
+  if (n <= 0) return pcp_fail(ctx, PCP_ERR_NO_CLOUD, "pcp_build_grid: empty cloud");
+  if (n >= (int64_t)0x7FFFFF00) return pcp_fail(ctx, PCP_ERR_INVALID_ARG, "pcp_build_grid: n exceeds int32 indexing");
+  cudaStream_t st = ctx->stream;
+  int rc;
+
+  // ---- bbox
+  if ((rc = pcp_reserve(ctx, ctx->bbox, 6 * sizeof(uint32_t)))) return rc;
+  pcp_tic(ctx, PCP_T_BBOX);
+  bbox_init_kernel<<<1, 32, 0, st>>>((uint32_t*)ctx->bbox.p);
+  PCP_LAUNCH_CHECK("bbox_init_kernel");
+  {
+    int blocks = (int)std::min<int64_t>((n + 255) / 256, 148 * 8);
+    bbox_kernel<<<blocks, 256, 0, st>>>(ctx->d_cloud, n, (uint32_t*)ctx->bbox.p);
+    PCP_LAUNCH_CHECK("bbox_kernel");
+  }
+  pcp_toc(ctx, PCP_T_BBOX);
+  uint32_t hb[6];
+  PCP_CUDA(cudaMemcpyAsync(hb, ctx->bbox.p, sizeof(hb), cudaMemcpyDeviceToHost, st));
+  PCP_CUDA(cudaStreamSynchronize(st));
+  double lo[3], hi[3], ext[3];
+  for (int d = 0; d < 3; ++d) {
+    lo[d] = dec_ordered(hb[d]);
+    hi[d] = dec_ordered(hb[3 + d]);
+    if (!(hi[d] >= lo[d])) { lo[d] = 0; hi[d] = 0; }  // no finite point at all
+    ext[d] = hi[d] - lo[d];
+  }
+
+  // ---- grid geometry
+  GridDesc g;
+  // axis order: ax[2] (slowest) = longest extent, ax[0] (fastest, the run axis) = next, ax[1] = shortest
+  int order[3] = {0, 1, 2};
+  for (int i = 0; i < 3; ++i)
+    for (int j = i + 1; j < 3; ++j)
+      if (ext[order[j]] > ext[order[i]]) std::swap(order[i], order[j]);
+  g.ax[2] = order[0];
+  g.ax[0] = order[1];
+  g.ax[1] = order[2];
+  bool auto_cell = !(cell > 0.f);
+  if (auto_cell) {
+    // surface-like density estimate: n points over the two largest extents; aim at about
+    // 0.5*k points in an average cell so that a 3×3×3 stencil usually covers the k-NN ball.
+    double area = std::max(ext[order[0]], 1e-3) * std::max(ext[order[1]], 1e-3);
+    int k = k_hint > 0 ? k_hint : 20;
+    cell = (float)std::sqrt(0.5 * k * area / (double)n);
+    if (!(cell > 0.f)) cell = 1.f;
+  }
+  const double max_cells = 1.0e9;
+  for (;;) {
+    double total = 1.0;
+    for (int a = 0; a < 3; ++a) {
+      double cnt = std::floor(ext[g.ax[a]] / (double)cell) + 1.0;
+      if (cnt > 2.0e9) cnt = 2.0e9;
+      g.dim[a] = (int)cnt;
+      total *= cnt;
+    }
+    if (total <= max_cells) { g.n_cells = (uint32_t)total; break; }
+    if (!auto_cell) return pcp_fail(ctx, PCP_ERR_GRID_TOO_LARGE, "pcp_build_grid: dense cell table above 1e9 cells; use a larger cell");
+    cell *= 1.26f;
+  }
+  g.cell = cell;
+  g.inv_cell = 1.0 / (double)cell;
+  for (int d = 0; d < 3; ++d) g.origin[d] = lo[d];
+  ctx->grid = g;
+
+  // ---- keys
+  if ((rc = pcp_reserve(ctx, ctx->keys_in, n * sizeof(uint32_t)))) return rc;
+  if ((rc = pcp_reserve(ctx, ctx->keys_sorted, (n + 1) * sizeof(uint32_t)))) return rc;
+  if ((rc = pcp_reserve(ctx, ctx->vals_in, n * sizeof(int32_t)))) return rc;
+  if ((rc = pcp_reserve(ctx, ctx->vals_sorted, n * sizeof(int32_t)))) return rc;
+  if ((rc = pcp_reserve(ctx, ctx->sorted_pts, n * sizeof(float4)))) return rc;
+  if ((rc = pcp_reserve(ctx, ctx->sorted_slot, n * sizeof(int32_t)))) return rc;
+  const size_t table_entries = (size_t)g.n_cells + 2;
+  if ((rc = pcp_reserve(ctx, ctx->cell_end, table_entries * sizeof(uint32_t)))) return rc;
+  const int nb = (int)((n + 255) / 256);
+  pcp_tic(ctx, PCP_T_KEYS);
+  keys_kernel<<<nb, 256, 0, st>>>(ctx->d_cloud, n, g, (uint32_t*)ctx->keys_in.p, (int32_t*)ctx->vals_in.p);
+  PCP_LAUNCH_CHECK("keys_kernel");
+  pcp_toc(ctx, PCP_T_KEYS);
+
+  // ---- radix sort of (cell id, local index); stable, so equal cells keep index order
+  const int end_bit = bits_for(g.n_cells);
+  size_t tmp_bytes = 0;
+  PCP_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, (const uint32_t*)ctx->keys_in.p, (uint32_t*)ctx->keys_sorted.p,
+                                           (const int32_t*)ctx->vals_in.p, (int32_t*)ctx->vals_sorted.p, (int)n, 0, end_bit, st));
+  if ((rc = pcp_reserve(ctx, ctx->sort_tmp, tmp_bytes))) return rc;
+  pcp_tic(ctx, PCP_T_SORT);
+  PCP_CUDA(cub::DeviceRadixSort::SortPairs(ctx->sort_tmp.p, tmp_bytes, (const uint32_t*)ctx->keys_in.p, (uint32_t*)ctx->keys_sorted.p,
+                                           (const int32_t*)ctx->vals_in.p, (int32_t*)ctx->vals_sorted.p, (int)n, 0, end_bit, st));
+  ctx->launches += 4;  // onesweep: histogram + a few digit passes (CUB-internal kernels)
+  pcp_toc(ctx, PCP_T_SORT);
+
+  // ---- gather + cell table
+  pcp_tic(ctx, PCP_T_TABLE);
+  PCP_CUDA(cudaMemsetAsync(ctx->cell_end.p, 0, table_entries * sizeof(uint32_t), st));
+  gather_kernel<<<nb, 256, 0, st>>>(ctx->d_cloud, ctx->d_gid, (const uint32_t*)ctx->keys_sorted.p, (const int32_t*)ctx->vals_sorted.p, n,
+                                    ctx->n_query, (float4*)ctx->sorted_pts.p, (int32_t*)ctx->sorted_slot.p, (uint32_t*)ctx->cell_end.p);
+  PCP_LAUNCH_CHECK("gather_kernel");
+  size_t scan_bytes = 0;
+  uint32_t* E = (uint32_t*)ctx->cell_end.p;
+  PCP_CUDA(cub::DeviceScan::InclusiveScan(nullptr, scan_bytes, E, E, MaxOp(), (int)table_entries, st));
+  if ((rc = pcp_reserve(ctx, ctx->scan_tmp, scan_bytes))) return rc;
+  PCP_CUDA(cub::DeviceScan::InclusiveScan(ctx->scan_tmp.p, scan_bytes, E, E, MaxOp(), (int)table_entries, st));
+  ctx->launches += 2;
+  pcp_toc(ctx, PCP_T_TABLE);
+  ctx->grid_ok = true;
+  return PCP_OK;
+}

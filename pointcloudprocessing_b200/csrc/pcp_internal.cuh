@@ -1,0 +1,99 @@
+// pcp_internal.cuh — context object and shared helpers of libpcp.so (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <string>
+
+#include "pcp.h"
+
+#define PCP_WARP 32
+
+// Uniform grid over the cloud's bounding box.  Cell (c0,c1,c2) are coordinates along the
+// permuted axes ax[0] (fastest in the linear cell index, so the 2R+1 cells of a stencil
+// row are one contiguous run of the sorted point array), ax[1], ax[2] (slowest = the
+// longest box axis, so three consecutive slabs stay L2-resident while queries sweep).
+struct GridDesc {
+  double origin[3];   // box minimum along x,y,z
+  double inv_cell;    // 1 / cell edge
+  float cell;         // cell edge
+  int ax[3];          // permuted axis -> x/y/z
+  int dim[3];         // cells along permuted axes
+  uint32_t n_cells;   // dim0*dim1*dim2; cell id n_cells is the trash cell (non-finite points)
+};
+
+struct DevBuf {
+  void* p = nullptr;
+  size_t cap = 0;
+};
+
+struct pcp_ctx {
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  std::string err;
+  int64_t launches = 0;
+  float t_ms[PCP_T_COUNT] = {0};
+  cudaEvent_t ev[2 * PCP_T_COUNT] = {nullptr};
+  bool ev_used[PCP_T_COUNT] = {false};
+
+  // cloud (packed float4 x,y,z,intensity on the device)
+  const float4* d_cloud = nullptr;
+  const int32_t* d_gid = nullptr;  // optional global ids (sharded)
+  int64_t n = 0, n_query = 0;
+  DevBuf own_cloud;  // when the cloud came from the host
+
+  // grid
+  bool grid_ok = false;
+  GridDesc grid;
+  DevBuf bbox;        // 6 ordered-uint encodings
+  DevBuf keys_in, keys_sorted, vals_in, vals_sorted, sort_tmp;
+  DevBuf sorted_pts;  // float4 {x,y,z, gid bits} in cell order
+  DevBuf sorted_slot; // int32 output slot (−1 for halo points) per sorted position
+  DevBuf cell_end;    // uint32 E[c] = #points with cell id < c, n_cells + 2 entries
+  DevBuf scan_tmp;
+
+  // outputs / scratch
+  DevBuf out_feat, out_norm, out_idx, out_d2, out_counts, flags, valid, last_valid, staging;
+  DevBuf ring_range, ring_idx, ring_long, ring_offsets, ring_key;
+};
+
+int pcp_fail(pcp_ctx* ctx, int status, const char* what, cudaError_t ce = cudaSuccess);
+int pcp_reserve(pcp_ctx* ctx, DevBuf& b, size_t bytes);
+void pcp_tic(pcp_ctx* ctx, int stage);
+void pcp_toc(pcp_ctx* ctx, int stage);
+void pcp_collect_timings(pcp_ctx* ctx);
+
+#define PCP_CUDA(call)                                               \
+  do {                                                               \
+    cudaError_t e__ = (call);                                        \
+    if (e__ != cudaSuccess) return pcp_fail(ctx, PCP_ERR_CUDA, #call, e__); \
+  } while (0)
+
+#define PCP_LAUNCH_CHECK(name)                                       \
+  do {                                                               \
+    ctx->launches++;                                                 \
+    cudaError_t e__ = cudaGetLastError();                            \
+    if (e__ != cudaSuccess) return pcp_fail(ctx, PCP_ERR_CUDA, name, e__); \
+  } while (0)
+
+// implemented in grid.cu / search_pca.cu / ring.cu
+int pcp_grid_build_impl(pcp_ctx* ctx, float cell, int k_hint);
+
+struct SearchParams {
+  int mode;           // 0 = k-NN, 1 = radius
+  int k;              // k-NN
+  float r2;           // radius: (float)((double)r*(double)r)
+  int R0;             // initial stencil half-width in cells
+  int min_pts;        // radius: gate (13 in the reference)
+  int center_mode;    // PCP_CENTER_*
+  pcp_feature68* out; // device, n_query records (may be null)
+  pcp_normal16* normals; // device (may be null)
+  int32_t* nn_idx;    // device neighbour lists (may be null)
+  float* nn_d2;
+  int32_t* counts;    // radius: per-query neighbour count (may be null)
+  const int64_t* offsets; // radius CSR offsets for nn_idx / nn_d2
+  uint8_t* valid;     // per output slot: 1 when the record was computed (may be null)
+  int* overflow_flag; // device int: set when a radius neighbourhood exceeded the warp buffer
+};
+int pcp_search_launch(pcp_ctx* ctx, const SearchParams& sp);
+int pcp_carry_forward_impl(pcp_ctx* ctx, pcp_feature68* d_out, const uint8_t* d_valid, int64_t n);

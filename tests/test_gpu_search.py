@@ -1,0 +1,70 @@
+"""GPU parity: neighbour index sets (bit-exact, ties by index) — through the C-ABI."""
+import numpy as np
+import pytest
+
+from pointcloudprocessing_b200 import synth
+
+pytestmark = pytest.mark.gpu
+
+
+def _cloud(kind, n, seed):
+    if kind == "urban":
+        return synth.urban(seed, n, extent=40.0)
+    if kind == "frame":
+        return synth.vlp16_frame(seed)[:n]
+    if kind == "lattice":  # exact distance ties everywhere
+        g = np.arange(int(round(n ** (1 / 3))) + 1, dtype=np.float32)
+        x, y, z = np.meshgrid(g, g, g, indexing="ij")
+        p = np.stack([x.ravel(), y.ravel(), z.ravel(), np.zeros(x.size, np.float32)], 1)[:n]
+        return np.ascontiguousarray(p[np.random.default_rng(seed).permutation(p.shape[0])])
+    raise ValueError(kind)
+
+
+@pytest.mark.parametrize("kind,n,k", [("urban", 20000, 20), ("urban", 30000, 30), ("frame", 25000, 10), ("lattice", 4000, 20),
+                                      ("urban", 50, 20), ("urban", 7, 10), ("urban", 20000, 1), ("urban", 20000, 32)])
+def test_knn_indices_bit_exact(pcp, oracle, kind, n, k):
+    pts = _cloud(kind, n, 11)
+    pcp.set_cloud(pts)
+    pcp.build_grid(0.0, k)
+    idx, d2 = pcp.knn_neighbors(k)
+    ridx, rd2 = oracle.KdTree(pts).knn_all(k)
+    np.testing.assert_array_equal(idx, ridx)
+    np.testing.assert_array_equal(d2.view(np.uint32), rd2.view(np.uint32))
+
+
+@pytest.mark.parametrize("cell_scale", [0.25, 1.0, 4.0])
+def test_knn_any_cell_size(pcp, oracle, cell_scale):
+    """The answer must not depend on the grid resolution (ring expansion / coverage logic)."""
+    pts = _cloud("urban", 15000, 5)
+    pcp.set_cloud(pts)
+    pcp.build_grid(0.8 * cell_scale, 20)
+    idx, _ = pcp.knn_neighbors(20)
+    ridx, _ = oracle.KdTree(pts).knn_all(20)
+    np.testing.assert_array_equal(idx, ridx)
+
+
+@pytest.mark.parametrize("kind,n,r,cell", [("urban", 20000, 0.5, 0.0), ("urban", 20000, 0.5, 0.2), ("frame", 25000, 0.3, 0.0),
+                                           ("lattice", 4000, 1.0, 0.0), ("lattice", 4000, 1.5, 0.0), ("urban", 5, 0.5, 0.0)])
+def test_radius_indices_bit_exact(pcp, oracle, kind, n, r, cell):
+    pts = _cloud(kind, n, 12)
+    pcp.set_cloud(pts)
+    pcp.build_grid(cell if cell > 0 else r * 1.0001, 0)
+    off, idx, d2 = pcp.radius_neighbors(r)
+    roff, ridx, rd2 = oracle.KdTree(pts).radius_all(r)
+    np.testing.assert_array_equal(off, roff)
+    np.testing.assert_array_equal(idx, ridx)
+    np.testing.assert_array_equal(d2.view(np.uint32), rd2.view(np.uint32))
+
+
+def test_radius_strict_boundary(pcp, oracle):
+    """Points exactly at distance r are excluded (strict d2 < r2), r2 = (float)(r*r in double)."""
+    pts = np.zeros((40, 4), np.float32)
+    pts[1:, 0] = np.linspace(0.05, 1.0, 39, dtype=np.float32)
+    pts[20, 0] = 0.5
+    pcp.set_cloud(pts)
+    pcp.build_grid(0.6, 0)
+    off, idx, _ = pcp.radius_neighbors(0.5)
+    roff, ridx, _ = oracle.KdTree(pts).radius_all(0.5)
+    np.testing.assert_array_equal(off, roff)
+    np.testing.assert_array_equal(idx, ridx)
+    assert 20 not in idx[off[0]:off[1]]
