@@ -87,20 +87,32 @@ __global__ void __launch_bounds__(256) keys_kernel(const float4* __restrict__ pt
 }
 
 // Gather into cell order; mark E[key+1] = pos+1 at the last point of every cell.
+// .w of the sorted point carries `ord`, the point's rank in index order (SURVEY Q7 tie rule):
+// the local index for a plain cloud, the rank of its global id for a shard.
 __global__ void __launch_bounds__(256)
-    gather_kernel(const float4* __restrict__ pts, const int32_t* __restrict__ gid, const uint32_t* __restrict__ keys_sorted,
+    gather_kernel(const float4* __restrict__ pts, const int32_t* __restrict__ ord_of_li, const uint32_t* __restrict__ keys_sorted,
                   const int32_t* __restrict__ vals_sorted, int64_t n, int64_t n_query, float4* __restrict__ sorted,
-                  int32_t* __restrict__ slot, uint32_t* __restrict__ cell_end) {
+                  int32_t* __restrict__ slot, uint32_t* __restrict__ inv, uint32_t* __restrict__ cell_end) {
   int64_t pos = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (pos >= n) return;
   int32_t li = vals_sorted[pos];
   float4 p = __ldg(pts + li);
-  int32_t g = gid ? __ldg(gid + li) : li;
-  p.w = __int_as_float(g);
+  int32_t ord = ord_of_li ? __ldg(ord_of_li + li) : li;
+  p.w = __int_as_float(ord);
   sorted[pos] = p;
+  inv[ord] = (uint32_t)pos;
   slot[pos] = li < n_query ? li : -1;
   uint32_t k = keys_sorted[pos];
   if (pos == n - 1 || keys_sorted[pos + 1] != k) cell_end[k + 1] = (uint32_t)(pos + 1);
+}
+
+__global__ void __launch_bounds__(256) iota_kernel(int32_t* __restrict__ v, int64_t n) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i < n) v[i] = (int32_t)i;
+}
+__global__ void __launch_bounds__(256) invert_kernel(const int32_t* __restrict__ li_of_ord, int32_t* __restrict__ ord_of_li, int64_t n) {
+  int64_t o = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (o < n) ord_of_li[li_of_ord[o]] = (int32_t)o;
 }
 
 struct MaxOp {
@@ -182,6 +194,26 @@ int pcp_grid_build_impl(pcp_ctx* ctx, float cell, int k_hint) {
   for (int d = 0; d < 3; ++d) g.origin[d] = lo[d];
   ctx->grid = g;
 
+  // ---- sharded clouds: ord = rank of the global id (ties are broken by global index)
+  if (ctx->d_gid) {
+    if ((rc = pcp_reserve(ctx, ctx->gid_sorted, n * sizeof(int32_t)))) return rc;
+    if ((rc = pcp_reserve(ctx, ctx->gid_tmp, n * sizeof(int32_t)))) return rc;
+    if ((rc = pcp_reserve(ctx, ctx->ord_of_li, n * sizeof(int32_t)))) return rc;
+    if ((rc = pcp_reserve(ctx, ctx->li_of_ord, n * sizeof(int32_t)))) return rc;
+    const int nbi = (int)((n + 255) / 256);
+    iota_kernel<<<nbi, 256, 0, st>>>((int32_t*)ctx->gid_tmp.p, n);
+    PCP_LAUNCH_CHECK("iota_kernel");
+    size_t tb = 0;
+    PCP_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tb, (const uint32_t*)ctx->d_gid, (uint32_t*)ctx->gid_sorted.p,
+                                             (const int32_t*)ctx->gid_tmp.p, (int32_t*)ctx->li_of_ord.p, (int)n, 0, 32, st));
+    if ((rc = pcp_reserve(ctx, ctx->sort_tmp, tb))) return rc;
+    PCP_CUDA(cub::DeviceRadixSort::SortPairs(ctx->sort_tmp.p, tb, (const uint32_t*)ctx->d_gid, (uint32_t*)ctx->gid_sorted.p,
+                                             (const int32_t*)ctx->gid_tmp.p, (int32_t*)ctx->li_of_ord.p, (int)n, 0, 32, st));
+    ctx->launches += 5;
+    invert_kernel<<<nbi, 256, 0, st>>>((const int32_t*)ctx->li_of_ord.p, (int32_t*)ctx->ord_of_li.p, n);
+    PCP_LAUNCH_CHECK("invert_kernel");
+  }
+
   // ---- keys
   if ((rc = pcp_reserve(ctx, ctx->keys_in, n * sizeof(uint32_t)))) return rc;
   if ((rc = pcp_reserve(ctx, ctx->keys_sorted, (n + 1) * sizeof(uint32_t)))) return rc;
@@ -189,6 +221,7 @@ int pcp_grid_build_impl(pcp_ctx* ctx, float cell, int k_hint) {
   if ((rc = pcp_reserve(ctx, ctx->vals_sorted, n * sizeof(int32_t)))) return rc;
   if ((rc = pcp_reserve(ctx, ctx->sorted_pts, n * sizeof(float4)))) return rc;
   if ((rc = pcp_reserve(ctx, ctx->sorted_slot, n * sizeof(int32_t)))) return rc;
+  if ((rc = pcp_reserve(ctx, ctx->inv_pos, n * sizeof(uint32_t)))) return rc;
   const size_t table_entries = (size_t)g.n_cells + 2;
   if ((rc = pcp_reserve(ctx, ctx->cell_end, table_entries * sizeof(uint32_t)))) return rc;
   const int nb = (int)((n + 255) / 256);
@@ -212,8 +245,10 @@ int pcp_grid_build_impl(pcp_ctx* ctx, float cell, int k_hint) {
   // ---- gather + cell table
   pcp_tic(ctx, PCP_T_TABLE);
   PCP_CUDA(cudaMemsetAsync(ctx->cell_end.p, 0, table_entries * sizeof(uint32_t), st));
-  gather_kernel<<<nb, 256, 0, st>>>(ctx->d_cloud, ctx->d_gid, (const uint32_t*)ctx->keys_sorted.p, (const int32_t*)ctx->vals_sorted.p, n,
-                                    ctx->n_query, (float4*)ctx->sorted_pts.p, (int32_t*)ctx->sorted_slot.p, (uint32_t*)ctx->cell_end.p);
+  gather_kernel<<<nb, 256, 0, st>>>(ctx->d_cloud, ctx->d_gid ? (const int32_t*)ctx->ord_of_li.p : nullptr,
+                                    (const uint32_t*)ctx->keys_sorted.p, (const int32_t*)ctx->vals_sorted.p, n, ctx->n_query,
+                                    (float4*)ctx->sorted_pts.p, (int32_t*)ctx->sorted_slot.p, (uint32_t*)ctx->inv_pos.p,
+                                    (uint32_t*)ctx->cell_end.p);
   PCP_LAUNCH_CHECK("gather_kernel");
   size_t scan_bytes = 0;
   uint32_t* E = (uint32_t*)ctx->cell_end.p;

@@ -47,7 +47,9 @@ struct pcp_ctx {
   GridDesc grid;
   DevBuf bbox;        // 6 ordered-uint encodings
   DevBuf keys_in, keys_sorted, vals_in, vals_sorted, sort_tmp;
-  DevBuf sorted_pts;  // float4 {x,y,z, gid bits} in cell order
+  DevBuf sorted_pts;  // float4 {x,y,z, ord bits} in cell order (ord = rank in index order)
+  DevBuf inv_pos;     // uint32 ord -> sorted position
+  DevBuf gid_sorted, gid_tmp, ord_of_li, li_of_ord;  // sharded clouds: ord <-> local index <-> global id
   DevBuf sorted_slot; // int32 output slot (−1 for halo points) per sorted position
   DevBuf cell_end;    // uint32 E[c] = #points with cell id < c, n_cells + 2 entries
   DevBuf scan_tmp;

@@ -2,12 +2,11 @@
 //
 // Candidate ordering everywhere is the reference's (d2, index) order (FLANN
 // DistanceIndex::operator<).  A candidate is carried as one 64-bit key
-//     key = (bits(d2) << 32) | sorted_position
-// d2 >= 0, so its IEEE bit pattern orders like the value.  Ordering two keys with different
-// d2 is a plain 64-bit compare; only when the d2 bits are EQUAL (exact fp32 ties) the index
-// stored in .w of the sorted point decides, which costs two L1-resident loads on a rare path.
-// Carrying the sorted position (not the index) lets the moment stage re-read neighbour
-// coordinates from the cell-ordered array, i.e. from lines the scan just touched.
+//     key = (bits(d2) << 32) | ord
+// where d2 >= 0 (its IEEE bit pattern orders like the value) and `ord` is the point's rank in
+// index order (the local index itself for an unsharded cloud, the rank of its global id for a
+// shard), so the reference order is a plain unsigned 64-bit compare: no tie path, no loads.
+// `inv[ord]` gives the cell-sorted position, from which the moment stage re-reads coordinates.
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -15,17 +14,6 @@
 typedef unsigned long long u64;
 #define PCP_KEY_INF 0xFFFFFFFFFFFFFFFFull
 #define PCP_FULL 0xffffffffu
-
-__device__ __forceinline__ bool key_less(u64 a, u64 b, const float4* __restrict__ sorted) {
-  uint32_t ha = (uint32_t)(a >> 32), hb = (uint32_t)(b >> 32);
-  if (ha != hb) return ha < hb;
-  uint32_t pa = (uint32_t)a, pb = (uint32_t)b;
-  if (pa == pb) return false;
-  if (ha == 0xFFFFFFFFu) return pa < pb;  // padding entries
-  int ga = __float_as_int(__ldg(&sorted[pa].w));
-  int gb = __float_as_int(__ldg(&sorted[pb].w));
-  return ga != gb ? ga < gb : pa < pb;
-}
 
 // FLANN L2_Simple<float>: ((dx*dx) + dy*dy) + dz*dz with separate multiplies and adds.
 __device__ __forceinline__ float dist2_nofma(float qx, float qy, float qz, float4 p) {
@@ -36,56 +24,66 @@ __device__ __forceinline__ float dist2_nofma(float qx, float qy, float qz, float
   return r;
 }
 
-__device__ __forceinline__ u64 shfl_u64(u64 v, int src) {
-  return __shfl_sync(PCP_FULL, v, src);
-}
-__device__ __forceinline__ u64 shfl_xor_u64(u64 v, int m) {
-  return __shfl_xor_sync(PCP_FULL, v, m);
-}
+__device__ __forceinline__ u64 shfl_u64(u64 v, int src) { return __shfl_sync(PCP_FULL, v, src); }
+__device__ __forceinline__ u64 shfl_xor_u64(u64 v, int m) { return __shfl_xor_sync(PCP_FULL, v, m); }
 
-// ascending bitonic sort of one key per lane
-__device__ __forceinline__ u64 warp_sort32(u64 v, int lane, const float4* __restrict__ sorted) {
+// Direction bits of the 32-lane bitonic network, one bit per compare-exchange step in issue
+// order (15 sort steps, then the 5 steps of the final merge network are the last 5 of those):
+// bit s set = this lane keeps the SMALLER key in step s.
+__device__ __forceinline__ uint32_t bitonic_dirs(int lane) {
+  uint32_t d = 0;
+  int s = 0;
 #pragma unroll
   for (int k = 2; k <= 32; k <<= 1) {
 #pragma unroll
-    for (int j = k >> 1; j > 0; j >>= 1) {
-      u64 o = shfl_xor_u64(v, j);
+    for (int j = k >> 1; j > 0; j >>= 1, ++s) {
       bool lower = (lane & j) == 0;
       bool asc = (k == 32) ? true : ((lane & k) == 0);
-      bool take_min = (lower == asc);
-      bool o_less = key_less(o, v, sorted);
-      v = (take_min == o_less) ? o : v;
+      if (lower == asc) d |= 1u << s;
+    }
+  }
+  return d;
+}
+
+// ascending bitonic sort of one key per lane
+__device__ __forceinline__ u64 warp_sort32(u64 v, uint32_t dirs) {
+  int s = 0;
+#pragma unroll
+  for (int k = 2; k <= 32; k <<= 1) {
+#pragma unroll
+    for (int j = k >> 1; j > 0; j >>= 1, ++s) {
+      u64 o = shfl_xor_u64(v, j);
+      bool take_min = (dirs >> s) & 1u;
+      v = ((o < v) == take_min) ? o : v;
     }
   }
   return v;
 }
 
 // best (ascending, one per lane) <- the 32 smallest of best ∪ v, v ascending
-__device__ __forceinline__ u64 warp_merge32(u64 best, u64 v, int lane, const float4* __restrict__ sorted) {
+__device__ __forceinline__ u64 warp_merge32(u64 best, u64 v, int lane, uint32_t dirs) {
   u64 vr = shfl_u64(v, 31 - lane);
-  u64 w = key_less(vr, best, sorted) ? vr : best;  // bitonic sequence of the 32 smallest
+  u64 w = vr < best ? vr : best;  // bitonic sequence holding the 32 smallest
+  int s = 10;                     // the k = 32 stage of the network: steps 10..14
 #pragma unroll
-  for (int j = 16; j > 0; j >>= 1) {
+  for (int j = 16; j > 0; j >>= 1, ++s) {
     u64 o = shfl_xor_u64(w, j);
-    bool lower = (lane & j) == 0;
-    bool o_less = key_less(o, w, sorted);
-    w = (lower == o_less) ? o : w;
+    bool take_min = (dirs >> s) & 1u;
+    w = ((o < w) == take_min) ? o : w;
   }
   return w;
 }
 
 // in-place ascending bitonic sort of m (power of two, >= 64) keys in warp-private shared memory
-__device__ __forceinline__ void smem_sort_pow2(u64* buf, int m, int lane, const float4* __restrict__ sorted) {
+__device__ __forceinline__ void smem_sort_pow2(u64* buf, int m, int lane) {
   for (int k = 2; k <= m; k <<= 1) {
     for (int j = k >> 1; j > 0; j >>= 1) {
       for (int t = lane; t < (m >> 1); t += 32) {
-        // t-th pair of this stage: insert a zero bit at position log2(j)
-        int i = ((t & ~(j - 1)) << 1) | (t & (j - 1));
+        int i = ((t & ~(j - 1)) << 1) | (t & (j - 1));  // t-th pair: insert a zero bit at log2(j)
         int p = i | j;
         bool asc = (i & k) == 0;
         u64 a = buf[i], b = buf[p];
-        bool b_less = key_less(b, a, sorted);
-        if (b_less == asc) {
+        if ((b < a) == asc) {
           buf[i] = b;
           buf[p] = a;
         }

@@ -31,23 +31,29 @@ constexpr int RADIUS_CAP = 512;     // radius mode: neighbours kept per query in
 constexpr int REC_WORDS = 17;       // 68-byte record
 
 struct KArgs {
-  const float4* sorted;
-  const uint32_t* keys;
-  const int32_t* slot;
-  const uint32_t* E;
+  const float4* sorted;       // cell-ordered points, .w = ord bits
+  const uint32_t* keys;       // cell id per sorted position
+  const int32_t* slot;        // output slot per sorted position (−1 = halo)
+  const uint32_t* E;          // E[c] = #points with cell id < c
+  const uint32_t* inv;        // ord -> sorted position
+  const int32_t* gid_of_ord;  // ord -> global id (null = identity)
   GridDesc g;
   int64_t n;
   SearchParams sp;
 };
 
-// shared memory of one warp
+// shared memory of one warp; the record staging area reuses the search buffers (disjoint phases)
 template <int MODE>
 struct WarpSmem {
-  u64 buf[MODE == 0 ? 64 : RADIUS_CAP];
-  float prod[6][32];
+  union U {
+    struct S {
+      u64 buf[MODE == 0 ? 64 : RADIUS_CAP];
+      float prod[6][32];
+    } s;
+    float rec[32][REC_WORDS];
+  } u;
   float mom[32][6];    // query-centred moment (normalised)
   float momM[32][6];   // mean-centred moment (normalised), only when needed
-  float rec[32][REC_WORDS];
   int cnt[32];
   int gidq[32];
 };
@@ -57,18 +63,25 @@ __device__ __forceinline__ float cover2_of(int R, float cell) {
   return (float)(rs * rs * (1.0 - 1e-6));
 }
 
+// gap (in cells, >= 0) between the query at fractional offset f of its cell and the cell d cells
+// away; gaps below 2e-3 cells count as 0 so fp rounding of f can never prune a real neighbour
+__device__ __forceinline__ float cell_gap(int d, float f) {
+  float gp = d > 0 ? (float)d - f : (d < 0 ? f - (float)d - 1.f : 0.f);
+  return gp < 2e-3f ? 0.f : gp;
+}
+
 // Ordered second moment about (cx,cy,cz) of the m neighbours whose keys sit in list[0..m)
 // (registers for m <= 32 via `regkey`, shared memory otherwise).  Lanes 0..5 return
-// c00,c01,c02,c11,c12,c22 (already divided by m); accumulation order is PCL's.
+// c00,c01,c02,c11,c12,c22 (already divided by m); accumulation order is PCL's (SURVEY A.2).
 template <bool FROM_SMEM>
-__device__ __forceinline__ float ordered_moment(const float4* __restrict__ sorted, const u64* list, u64 regkey, int m,
-                                                float cx, float cy, float cz, float (*prod)[32], int lane) {
+__device__ __noinline__ float ordered_moment(const float4* __restrict__ sorted, const uint32_t* __restrict__ inv, const u64* list,
+                                             u64 regkey, int m, float cx, float cy, float cz, float (*prod)[32], int lane) {
   float acc = 0.f;
   for (int base = 0; base < m; base += 32) {
     int j = base + lane;
     if (j < m) {
       u64 key = FROM_SMEM ? list[j] : regkey;
-      float4 p = __ldg(&sorted[(uint32_t)key]);
+      float4 p = __ldg(&sorted[__ldg(&inv[(uint32_t)key])]);
       float px = __fsub_rn(p.x, cx), py = __fsub_rn(p.y, cy), pz = __fsub_rn(p.z, cz);
       prod[0][lane] = __fmul_rn(px, px);  // c00
       prod[1][lane] = __fmul_rn(py, px);  // c01
@@ -80,6 +93,7 @@ __device__ __forceinline__ float ordered_moment(const float4* __restrict__ sorte
     __syncwarp();
     if (lane < 6) {
       int cnt = min(32, m - base);
+#pragma unroll 4
       for (int t = 0; t < cnt; ++t) acc = __fadd_rn(acc, prod[lane][t]);
     }
     __syncwarp();
@@ -90,14 +104,14 @@ __device__ __forceinline__ float ordered_moment(const float4* __restrict__ sorte
 
 // fp32 running-sum centroid in list order (pcl::compute3DCentroid); result on every lane
 template <bool FROM_SMEM>
-__device__ __forceinline__ void ordered_centroid(const float4* __restrict__ sorted, const u64* list, u64 regkey, int m,
-                                                 float (*prod)[32], int lane, float& cx, float& cy, float& cz) {
+__device__ __noinline__ void ordered_centroid(const float4* __restrict__ sorted, const uint32_t* __restrict__ inv, const u64* list,
+                                              u64 regkey, int m, float (*prod)[32], int lane, float& cx, float& cy, float& cz) {
   float acc = 0.f;
   for (int base = 0; base < m; base += 32) {
     int j = base + lane;
     if (j < m) {
       u64 key = FROM_SMEM ? list[j] : regkey;
-      float4 p = __ldg(&sorted[(uint32_t)key]);
+      float4 p = __ldg(&sorted[__ldg(&inv[(uint32_t)key])]);
       prod[0][lane] = p.x;
       prod[1][lane] = p.y;
       prod[2][lane] = p.z;
@@ -115,6 +129,120 @@ __device__ __forceinline__ void ordered_centroid(const float4* __restrict__ sort
   cz = __shfl_sync(PCP_FULL, acc, 2);
 }
 
+// Per-query search state of a warp.
+struct Search {
+  u64 best;         // k-NN: ascending best list, one key per lane
+  u64 thr;          // k-NN: key of the current k-th best (INF until k candidates were merged)
+  int cnt;          // entries waiting in the shared buffer (k-NN) / hits so far (radius)
+};
+
+// Scan every cell of the block of half-width R around (c0,c1,c2) that is NOT in the block of
+// half-width Rp (Rp < 0: nothing scanned yet).  `bound2` prunes rows and clips runs by their
+// distance to the query (radius: r2; k-NN: the current k-th distance or +inf).
+template <int MODE>
+__device__ __forceinline__ void scan_shell(const KArgs& a, WarpSmem<MODE>* ws, Search& st, const float4 Q, int c0, int c1, int c2,
+                                           float f0, float f1, float f2, int Rp, int R, float bound2, int lane, uint32_t dirs) {
+  const GridDesc& g = a.g;
+  const float4* __restrict__ sorted = a.sorted;
+  const unsigned lt_mask = (1u << lane) - 1u;
+  const int lo1 = max(c1 - R, 0), hi1 = min(c1 + R, g.dim[1] - 1), n1 = hi1 - lo1 + 1;
+  const int lo2 = max(c2 - R, 0), hi2 = min(c2 + R, g.dim[2] - 1), n2 = hi2 - lo2 + 1;
+  const int nrows = n1 * n2;
+  const int lo0 = max(c0 - R, 0), hi0 = min(c0 + R, g.dim[0] - 1);
+  const bool prune = bound2 < 3.0e38f;
+  const float inv_c2 = prune ? (float)(g.inv_cell * g.inv_cell) * bound2 * 1.0002f : 0.f;  // bound in cells^2, widened
+  for (int rb = 0; rb < nrows; rb += 32) {
+    const int r = rb + lane;
+    // up to two runs per row: [bA, eA) and [bB, eB) in sorted positions
+    uint32_t bA = 0, eA = 0, bB = 0, eB = 0;
+    if (r < nrows) {
+      const int o2 = r / n1, o1 = r - o2 * n1;
+      int e1 = c1 + o1, e2 = c2 + o2;  // start at the query's own row, wrap to the low side
+      if (e1 > hi1) e1 -= n1;
+      if (e2 > hi2) e2 -= n2;
+      const int d1 = e1 - c1, d2 = e2 - c2;
+      int xlo = lo0, xhi = hi0;
+      bool keep = true;
+      if (prune) {
+        float g1 = cell_gap(d1, f1), g2 = cell_gap(d2, f2);
+        float rest = inv_c2 - (g1 * g1 + g2 * g2) * 0.9998f;
+        keep = rest >= 0.f;
+        if (keep) {
+          float hx = sqrtf(rest) + 4e-3f;  // cells; offsets taken relative to c0 to stay exact
+          xlo = max(xlo, c0 + (int)floorf(f0 - hx));
+          xhi = min(xhi, c0 + (int)floorf(f0 + hx));
+        }
+      }
+      if (keep && xlo <= xhi) {
+        const uint32_t base = ((uint32_t)e2 * (uint32_t)g.dim[1] + (uint32_t)e1) * (uint32_t)g.dim[0];
+        const bool inner = Rp >= 0 && abs(d1) <= Rp && abs(d2) <= Rp;
+        if (!inner) {
+          bA = __ldg(&a.E[base + xlo]);
+          eA = __ldg(&a.E[base + xhi + 1]);
+        } else {
+          const int ahi = min(xhi, c0 - Rp - 1), blo = max(xlo, c0 + Rp + 1);
+          if (xlo <= ahi) {
+            bA = __ldg(&a.E[base + xlo]);
+            eA = __ldg(&a.E[base + ahi + 1]);
+          }
+          if (blo <= xhi) {
+            bB = __ldg(&a.E[base + blo]);
+            eB = __ldg(&a.E[base + xhi + 1]);
+          }
+        }
+      }
+    }
+    // walk the non-empty runs only
+    unsigned mA = __ballot_sync(PCP_FULL, eA > bA), mB = __ballot_sync(PCP_FULL, eB > bB);
+    while (mA | mB) {
+      uint32_t bj, ej;
+      if (mA) {
+        const int j = __ffs(mA) - 1;
+        mA &= mA - 1;
+        bj = __shfl_sync(PCP_FULL, bA, j);
+        ej = __shfl_sync(PCP_FULL, eA, j);
+      } else {
+        const int j = __ffs(mB) - 1;
+        mB &= mB - 1;
+        bj = __shfl_sync(PCP_FULL, bB, j);
+        ej = __shfl_sync(PCP_FULL, eB, j);
+      }
+      for (uint32_t cb = bj; cb < ej; cb += 32) {
+        const uint32_t cp = cb + lane;
+        bool pass = false;
+        u64 key = 0;
+        if (cp < ej) {
+          const float4 P = __ldg(&sorted[cp]);
+          const float d2v = dist2_nofma(Q.x, Q.y, Q.z, P);
+          key = ((u64)__float_as_uint(d2v) << 32) | (u64)__float_as_uint(P.w);
+          pass = MODE == 0 ? key < st.thr : d2v < a.sp.r2;
+        }
+        const unsigned m = __ballot_sync(PCP_FULL, pass);
+        if (m == 0) continue;
+        const int off = st.cnt + __popc(m & lt_mask);
+        if (MODE == 0) {
+          if (pass) ws->u.s.buf[off] = key;
+          st.cnt += __popc(m);
+          __syncwarp();
+          if (st.cnt >= 32) {
+            u64 v = warp_sort32(ws->u.s.buf[lane], dirs);
+            st.best = warp_merge32(st.best, v, lane, dirs);
+            st.thr = shfl_u64(st.best, a.sp.k - 1);
+            u64 rem = (lane + 32 < st.cnt) ? ws->u.s.buf[lane + 32] : 0ull;
+            __syncwarp();
+            if (lane + 32 < st.cnt) ws->u.s.buf[lane] = rem;
+            st.cnt -= 32;
+            __syncwarp();
+          }
+        } else {
+          if (pass && off < RADIUS_CAP) ws->u.s.buf[off] = key;
+          st.cnt += __popc(m);
+        }
+      }
+    }
+  }
+}
+
 template <int MODE>
 __global__ void __launch_bounds__(WARPS * 32) search_pca_kernel(KArgs a) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -130,128 +258,93 @@ __global__ void __launch_bounds__(WARPS * 32) search_pca_kernel(KArgs a) {
   const bool need_m = sp.normals != nullptr || (sp.out != nullptr && sp.center_mode == PCP_CENTER_MEAN);
   const int nq = (int)min((int64_t)32, a.n - pos0);
   const int my_slot = lane < nq ? a.slot[pos0 + lane] : -1;
-  const unsigned lt_mask = (1u << lane) - 1u;
+  const uint32_t dirs = bitonic_dirs(lane);
+  const int max_dim = max(g.dim[0], max(g.dim[1], g.dim[2]));
 
+#pragma unroll 1
   for (int q = 0; q < nq; ++q) {
     const int slot_q = __shfl_sync(PCP_FULL, my_slot, q);
     if (slot_q < 0) continue;  // halo point: neighbour only
     const int64_t pq = pos0 + q;
     const float4 Q = __ldg(&sorted[pq]);
     const uint32_t cid = __ldg(&a.keys[pq]);
-    int n_nb = 0;          // neighbour count of this query
-    u64 best = PCP_KEY_INF;  // k-NN: sorted best list, one per lane
+    int n_nb = 0;
     bool overflow = false;
+    Search st;
+    st.best = PCP_KEY_INF;
+    st.thr = PCP_KEY_INF;
+    st.cnt = 0;
     if (cid < g.n_cells) {
       const int c0 = (int)(cid % (uint32_t)g.dim[0]);
       const uint32_t tq = cid / (uint32_t)g.dim[0];
       const int c1 = (int)(tq % (uint32_t)g.dim[1]);
       const int c2 = (int)(tq / (uint32_t)g.dim[1]);
-      int R = sp.R0;
-      for (;;) {
-        best = PCP_KEY_INF;
-        u64 thr = PCP_KEY_INF;
-        uint32_t thr_hi = 0xFFFFFFFFu;
-        int cnt = 0;  // entries in ws->buf
-        // stencil rows (axes 1 and 2), clipped to the grid; enumeration starts at the query's own row
-        const int lo1 = max(c1 - R, 0), hi1 = min(c1 + R, g.dim[1] - 1), n1 = hi1 - lo1 + 1;
-        const int lo2 = max(c2 - R, 0), hi2 = min(c2 + R, g.dim[2] - 1), n2 = hi2 - lo2 + 1;
-        const int nrows = n1 * n2;
-        const int lo0 = max(c0 - R, 0), hi0 = min(c0 + R, g.dim[0] - 1);
-        for (int rb = 0; rb < nrows; rb += 32) {
-          const int r = rb + lane;
-          uint32_t rbeg = 0, rend = 0;
-          if (r < nrows) {
-            int o1 = r % n1, o2 = r / n1;
-            int e1 = lo1 + (c1 - lo1 + o1) % n1, e2 = lo2 + (c2 - lo2 + o2) % n2;
-            uint32_t base = ((uint32_t)e2 * (uint32_t)g.dim[1] + (uint32_t)e1) * (uint32_t)g.dim[0];
-            rbeg = __ldg(&a.E[base + lo0]);
-            rend = __ldg(&a.E[base + hi0 + 1]);
+      // fractional position inside the own cell (same double arithmetic as the key kernel)
+      const float qc[3] = {Q.x, Q.y, Q.z};
+      float f0 = (float)(((double)qc[g.ax[0]] - g.origin[g.ax[0]]) * g.inv_cell - (double)c0);
+      float f1 = (float)(((double)qc[g.ax[1]] - g.origin[g.ax[1]]) * g.inv_cell - (double)c1);
+      float f2 = (float)(((double)qc[g.ax[2]] - g.origin[g.ax[2]]) * g.inv_cell - (double)c2);
+      f0 = fminf(fmaxf(f0, 0.f), 1.f);
+      f1 = fminf(fmaxf(f1, 0.f), 1.f);
+      f2 = fminf(fmaxf(f2, 0.f), 1.f);
+      if (MODE == 1) {
+        scan_shell<MODE>(a, ws, st, Q, c0, c1, c2, f0, f1, f2, -1, sp.R0, sp.r2, lane, dirs);
+        __syncwarp();
+        n_nb = st.cnt;
+        overflow = st.cnt > RADIUS_CAP;
+      } else {
+        int Rp = -1, R = sp.R0;
+#pragma unroll 1
+        for (;;) {
+          const u64 kth0 = shfl_u64(st.best, sp.k - 1);
+          const float bound = kth0 != PCP_KEY_INF ? __uint_as_float((uint32_t)(kth0 >> 32)) : 3.4e38f;
+          scan_shell<MODE>(a, ws, st, Q, c0, c1, c2, f0, f1, f2, Rp, R, bound, lane, dirs);
+          if (st.cnt > 0) {
+            u64 v = warp_sort32(lane < st.cnt ? ws->u.s.buf[lane] : PCP_KEY_INF, dirs);
+            st.best = warp_merge32(st.best, v, lane, dirs);
+            st.thr = shfl_u64(st.best, sp.k - 1);
+            st.cnt = 0;
+            __syncwarp();
           }
-          const int nr = min(32, nrows - rb);
-          for (int j = 0; j < nr; ++j) {
-            const uint32_t bj = __shfl_sync(PCP_FULL, rbeg, j), ej = __shfl_sync(PCP_FULL, rend, j);
-            for (uint32_t cb = bj; cb < ej; cb += 32) {
-              const uint32_t cp = cb + lane;
-              bool pass = false;
-              u64 key = 0;
-              if (cp < ej) {
-                float4 P = __ldg(&sorted[cp]);
-                float d2 = dist2_nofma(Q.x, Q.y, Q.z, P);
-                uint32_t d2b = __float_as_uint(d2);
-                key = ((u64)d2b << 32) | cp;
-                if (MODE == 0) pass = d2b < thr_hi || (d2b == thr_hi && key_less(key, thr, sorted));
-                else pass = d2 < sp.r2;
-              }
-              const unsigned m = __ballot_sync(PCP_FULL, pass);
-              if (m == 0) continue;
-              const int off = cnt + __popc(m & lt_mask);
-              if (MODE == 0) {
-                if (pass) ws->buf[off] = key;
-                cnt += __popc(m);
-                __syncwarp();
-                if (cnt >= 32) {
-                  u64 v = warp_sort32(ws->buf[lane], lane, sorted);
-                  best = warp_merge32(best, v, lane, sorted);
-                  thr = shfl_u64(best, sp.k - 1);
-                  thr_hi = (uint32_t)(thr >> 32);
-                  u64 rem = (lane + 32 < cnt) ? ws->buf[lane + 32] : 0ull;
-                  __syncwarp();
-                  if (lane + 32 < cnt) ws->buf[lane] = rem;
-                  cnt -= 32;
-                  __syncwarp();
-                }
-              } else {
-                if (pass && off < RADIUS_CAP) ws->buf[off] = key;
-                cnt += __popc(m);
-              }
-            }
+          const u64 kth = st.thr;
+          const bool found = kth != PCP_KEY_INF;
+          const bool whole = (c0 - R <= 0) && (c0 + R >= g.dim[0] - 1) && (c1 - R <= 0) && (c1 + R >= g.dim[1] - 1) &&
+                             (c2 - R <= 0) && (c2 + R >= g.dim[2] - 1);
+          if (whole) break;
+          int Rn;
+          if (found) {
+            const float dk = __uint_as_float((uint32_t)(kth >> 32));
+            if (dk <= cover2_of(R, g.cell)) break;
+            Rn = (int)fmin(ceil(sqrt((double)dk) * (1.0 + 2e-6) * g.inv_cell + 2e-6), 1.0e9);
+            Rn = max(R + 1, Rn);
+          } else {
+            Rn = 2 * R;
           }
+          Rp = R;
+          R = min(Rn, max_dim);
         }
-        if (MODE == 1) {
-          __syncwarp();
-          n_nb = cnt;
-          overflow = cnt > RADIUS_CAP;
-          break;
-        }
-        if (cnt > 0) {
-          u64 v = warp_sort32(lane < cnt ? ws->buf[lane] : PCP_KEY_INF, lane, sorted);
-          best = warp_merge32(best, v, lane, sorted);
-          __syncwarp();
-        }
-        const u64 kth = shfl_u64(best, sp.k - 1);
-        const bool found = kth != PCP_KEY_INF;
-        const bool whole = (c0 - R <= 0) && (c0 + R >= g.dim[0] - 1) && (c1 - R <= 0) && (c1 + R >= g.dim[1] - 1) &&
-                           (c2 - R <= 0) && (c2 + R >= g.dim[2] - 1);
-        if (whole) break;
-        if (found) {
-          const float dk = __uint_as_float((uint32_t)(kth >> 32));
-          if (dk <= cover2_of(R, g.cell)) break;
-          int Rn = (int)fmin(ceil(sqrt((double)dk) * (1.0 + 2e-6) * g.inv_cell + 2e-6), 1.0e9);
-          R = max(R + 1, Rn);
-        } else {
-          R = 2 * R;
-        }
-        R = min(R, max(g.dim[0], max(g.dim[1], g.dim[2])));
+        n_nb = __popc(__ballot_sync(PCP_FULL, lane < sp.k && st.best != PCP_KEY_INF));
       }
-      if (MODE == 0) n_nb = __popc(__ballot_sync(PCP_FULL, lane < sp.k && best != PCP_KEY_INF));
     }
 
     // ---- ordered neighbour list -> outputs
-    const int gid_q = __float_as_int(Q.w);
-    bool valid = !overflow && (MODE == 0 ? n_nb > 0 : n_nb >= sp.min_pts);
+    const int ord_q = __float_as_int(Q.w);
+    const int gid_q = a.gid_of_ord ? __ldg(&a.gid_of_ord[ord_q]) : ord_q;
+    const bool valid = !overflow && (MODE == 0 ? n_nb > 0 : n_nb >= sp.min_pts);
+    u64* buf = ws->u.s.buf;
     if (MODE == 1 && !overflow && n_nb > 0 && (valid || sp.nn_idx != nullptr)) {
       // sort the hits by (d2, index)
       if (n_nb <= 32) {
-        best = warp_sort32(lane < n_nb ? ws->buf[lane] : PCP_KEY_INF, lane, sorted);
+        st.best = warp_sort32(lane < n_nb ? buf[lane] : PCP_KEY_INF, dirs);
         __syncwarp();
-        if (lane < n_nb) ws->buf[lane] = best;
+        if (lane < n_nb) buf[lane] = st.best;
         __syncwarp();
       } else {
         int m2 = 64;
         while (m2 < n_nb) m2 <<= 1;
-        for (int t = n_nb + lane; t < m2; t += 32) ws->buf[t] = PCP_KEY_INF;
+        for (int t = n_nb + lane; t < m2; t += 32) buf[t] = PCP_KEY_INF;
         __syncwarp();
-        smem_sort_pow2(ws->buf, m2, lane, sorted);
+        smem_sort_pow2(buf, m2, lane);
       }
     }
     if (MODE == 1 && overflow && sp.overflow_flag && lane == 0) atomicExch(sp.overflow_flag, 1);
@@ -259,29 +352,31 @@ __global__ void __launch_bounds__(WARPS * 32) search_pca_kernel(KArgs a) {
     if (sp.nn_idx != nullptr && !overflow) {
       if (MODE == 0) {
         if (lane < sp.k) {
-          int64_t o = (int64_t)slot_q * sp.k + lane;
-          bool has = lane < n_nb;
-          sp.nn_idx[o] = has ? __float_as_int(__ldg(&sorted[(uint32_t)best].w)) : -1;
-          if (sp.nn_d2) sp.nn_d2[o] = has ? __uint_as_float((uint32_t)(best >> 32)) : INFINITY;
+          const int64_t o = (int64_t)slot_q * sp.k + lane;
+          const bool has = lane < n_nb;
+          const int ord = (int)(uint32_t)st.best;
+          sp.nn_idx[o] = has ? (a.gid_of_ord ? __ldg(&a.gid_of_ord[ord]) : ord) : -1;
+          if (sp.nn_d2) sp.nn_d2[o] = has ? __uint_as_float((uint32_t)(st.best >> 32)) : INFINITY;
         }
       } else if (sp.offsets) {
-        int64_t o = sp.offsets[slot_q];
+        const int64_t o = sp.offsets[slot_q];
         for (int t = lane; t < n_nb; t += 32) {
-          u64 key = ws->buf[t];
-          sp.nn_idx[o + t] = __float_as_int(__ldg(&sorted[(uint32_t)key].w));
+          const u64 key = buf[t];
+          const int ord = (int)(uint32_t)key;
+          sp.nn_idx[o + t] = a.gid_of_ord ? __ldg(&a.gid_of_ord[ord]) : ord;
           if (sp.nn_d2) sp.nn_d2[o + t] = __uint_as_float((uint32_t)(key >> 32));
         }
       }
     }
     if (valid && (need_q || need_m)) {
       if (need_q) {
-        float c = ordered_moment<MODE == 1>(sorted, ws->buf, best, n_nb, Q.x, Q.y, Q.z, ws->prod, lane);
+        float c = ordered_moment<MODE == 1>(sorted, a.inv, buf, st.best, n_nb, Q.x, Q.y, Q.z, ws->u.s.prod, lane);
         if (lane < 6) ws->mom[q][lane] = c;
       }
       if (need_m) {
         float mx, my, mz;
-        ordered_centroid<MODE == 1>(sorted, ws->buf, best, n_nb, ws->prod, lane, mx, my, mz);
-        float c = ordered_moment<MODE == 1>(sorted, ws->buf, best, n_nb, mx, my, mz, ws->prod, lane);
+        ordered_centroid<MODE == 1>(sorted, a.inv, buf, st.best, n_nb, ws->u.s.prod, lane, mx, my, mz);
+        float c = ordered_moment<MODE == 1>(sorted, a.inv, buf, st.best, n_nb, mx, my, mz, ws->u.s.prod, lane);
         if (lane < 6) ws->momM[q][lane] = c;
       }
     }
@@ -298,7 +393,7 @@ __global__ void __launch_bounds__(WARPS * 32) search_pca_kernel(KArgs a) {
     const int c = ws->cnt[lane];
     const bool valid = c >= 0;
     const int n_nb = valid ? c : -c - 1;
-    float* rec = ws->rec[lane];
+    float* rec = ws->u.rec[lane];
 #pragma unroll
     for (int w = 0; w < REC_WORDS; ++w) rec[w] = 0.f;
     rec[12] = __int_as_float(ws->gidq[lane]);
@@ -347,7 +442,7 @@ __global__ void __launch_bounds__(WARPS * 32) search_pca_kernel(KArgs a) {
     float* outw = reinterpret_cast<float*>(sp.out);
     for (int r = 0; r < nq; ++r) {
       int s = __shfl_sync(PCP_FULL, my_slot, r);
-      if (s >= 0 && lane < REC_WORDS) outw[(int64_t)s * REC_WORDS + lane] = ws->rec[r][lane];
+      if (s >= 0 && lane < REC_WORDS) outw[(int64_t)s * REC_WORDS + lane] = ws->u.rec[r][lane];
     }
   }
 }
@@ -360,6 +455,8 @@ int pcp_search_launch(pcp_ctx* ctx, const SearchParams& sp) {
   a.keys = (const uint32_t*)ctx->keys_sorted.p;
   a.slot = (const int32_t*)ctx->sorted_slot.p;
   a.E = (const uint32_t*)ctx->cell_end.p;
+  a.inv = (const uint32_t*)ctx->inv_pos.p;
+  a.gid_of_ord = ctx->d_gid ? (const int32_t*)ctx->gid_sorted.p : nullptr;
   a.g = ctx->grid;
   a.n = ctx->n;
   a.sp = sp;
