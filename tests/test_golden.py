@@ -1,0 +1,61 @@
+"""Golden vectors (tests/golden/golden_small.npz, made by tests/golden/make_golden.py from the oracle):
+the oracle must keep reproducing them (CPU suite) and the CUDA path must match them (GPU suite)."""
+import os
+
+import numpy as np
+import pytest
+
+from parity import check_features
+
+G = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "golden_small.npz"))
+
+
+def _feat(oracle, raw):
+    return np.ascontiguousarray(raw).view(oracle.FEATURE_DTYPE).reshape(-1)
+
+
+def test_oracle_reproduces_golden(oracle):
+    t = oracle.KdTree(G["urban"])
+    idx, d2 = t.knn_all(20)
+    np.testing.assert_array_equal(idx, G["urban_knn20_idx"])
+    np.testing.assert_array_equal(d2.view(np.uint32), G["urban_knn20_d2"].view(np.uint32))
+    off, ridx, _ = t.radius_all(0.5)
+    np.testing.assert_array_equal(off, G["urban_r05_off"])
+    np.testing.assert_array_equal(ridx, G["urban_r05_idx"])
+    f, valid = oracle.radius_pca_cloud(G["urban"], 0.5, 13, True, nthreads=1)
+    assert f.tobytes() == G["urban_r05_pca"].tobytes()
+    assert oracle.knn_pca_cloud(G["frame"], 10, 0).tobytes() == G["frame_knn10_pca"].tobytes()
+    rng, pti, _, lr = oracle.ring_project(G["ring_in"])
+    np.testing.assert_array_equal(pti, G["ring_index"])
+    assert lr == int(G["ring_long"])
+
+
+@pytest.mark.gpu
+def test_cuda_matches_golden(pcp, oracle):
+    pcp.set_cloud(G["urban"])
+    pcp.build_grid(0.0, 20)
+    idx, d2 = pcp.knn_neighbors(20)
+    np.testing.assert_array_equal(idx, G["urban_knn20_idx"])
+    np.testing.assert_array_equal(d2.view(np.uint32), G["urban_knn20_d2"].view(np.uint32))
+    check_features(pcp.knn_pca(20), _feat(oracle, G["urban_knn20_pca"]), None, "golden knn20")
+    pcp.build_grid(0.5001, 0)
+    off, ridx, rd2 = pcp.radius_neighbors(0.5)
+    np.testing.assert_array_equal(off, G["urban_r05_off"])
+    np.testing.assert_array_equal(ridx, G["urban_r05_idx"])
+    np.testing.assert_array_equal(rd2.view(np.uint32), G["urban_r05_d2"].view(np.uint32))
+    got = pcp.radius_pca(0.5, 13, 0, True)
+    ref, valid = _feat(oracle, G["urban_r05_pca"]), G["urban_r05_valid"]
+    check_features(got, ref, valid, "golden radius")
+    first = int(np.argmax(valid))
+    stale = (~valid.astype(bool)) & (np.arange(valid.size) > first)
+    check_features(got[stale], ref[stale], None, "golden radius stale")
+    pcp.set_cloud(G["frame"])
+    pcp.build_grid(0.0, 10)
+    idx, _ = pcp.knn_neighbors(10)
+    np.testing.assert_array_equal(idx, G["frame_knn10_idx"])
+    check_features(pcp.knn_pca(10), _feat(oracle, G["frame_knn10_pca"]), None, "golden frame knn10")
+    pcp.set_cloud(G["ring_in"])
+    rng, pti, lr = pcp.ring_project()
+    np.testing.assert_array_equal(pti[0], G["ring_index"])
+    np.testing.assert_array_equal(rng[0].view(np.uint32), G["ring_range"].view(np.uint32))
+    assert int(lr[0]) == int(G["ring_long"])

@@ -41,20 +41,3 @@ def test_ring_batch(pcp, oracle):
         np.testing.assert_array_equal(pti[f], rpti)
         np.testing.assert_array_equal(rng[f].view(np.uint32), rrng.view(np.uint32))
         assert int(lr[f]) == rlr
-
-
-def test_ring_calib_xml_matches_constants(tmp_path):
-    """A 16db.xml-shaped calibration yields the constants of include/ringProjection.h:16-20."""
-    vert = [-15, 1, -13, 3, -11, 5, -9, 7, -7, 9, -5, 11, -3, 13, -1, 15]
-    items = "".join(f"<item>{1 if i < 16 else 0}</item>" for i in range(64))
-    px = "".join(f"<item><px><id_>{i}</id_><rotCorrection_>0</rotCorrection_><vertCorrection_>{vert[i % 16] if i < 32 else 0}"
-                 f"</vertCorrection_></px></item>" for i in range(64))
-    xml = f"<boost_serialization><DB><distLSB_>0.2</distLSB_><enabled_><count>64</count>{items}</enabled_><points_>{px}</points_></DB></boost_serialization>"
-    p = tmp_path / "db.xml"
-    p.write_text(xml)
-    c = capi.ring_calib_from_xml(str(p))
-    d = capi.ring_calib_default()
-    assert (c.n_scan, c.horizon_scan) == (16, 1800) == (d.n_scan, d.horizon_scan)
-    assert c.ang_res_y == d.ang_res_y == 2.0 and c.ang_bottom == d.ang_bottom
-    assert abs(c.dist_lsb_cm - 0.2) < 1e-7
-    assert list(c.vert_deg)[:16] == vert == list(d.vert_deg)[:16]

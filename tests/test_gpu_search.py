@@ -68,3 +68,25 @@ def test_radius_strict_boundary(pcp, oracle):
     np.testing.assert_array_equal(off, roff)
     np.testing.assert_array_equal(idx, ridx)
     assert 20 not in idx[off[0]:off[1]]
+
+
+def test_sharded_global_ids_tie_break(pcp, oracle):
+    """A shard = own points first, halo after, arbitrary global ids: results (indices, order, tie
+    breaks) must equal the unsharded run restricted to the own points."""
+    import torch
+
+    pts = _cloud("lattice", 3000, 3)  # exact ties everywhere
+    n = pts.shape[0]
+    perm = np.random.default_rng(0).permutation(n)  # local order: shuffled; first 1000 = own points
+    local = np.ascontiguousarray(pts[perm])
+    d_pts = torch.from_numpy(local).cuda()
+    d_gid = torch.from_numpy(perm.astype(np.int32)).cuda()
+    n_own = 1000
+    pcp.set_cloud_device(d_pts.data_ptr(), n, d_gid.data_ptr(), n_own, keep=(d_pts, d_gid))
+    pcp.build_grid(0.0, 20)
+    idx, d2 = pcp.knn_neighbors(20)
+    ridx, rd2 = oracle.KdTree(pts).knn_all(20)
+    np.testing.assert_array_equal(idx, ridx[perm[:n_own]])
+    np.testing.assert_array_equal(d2.view(np.uint32), rd2[perm[:n_own]].view(np.uint32))
+    feat = pcp.knn_pca(20)
+    np.testing.assert_array_equal(feat["ptID"], perm[:n_own])

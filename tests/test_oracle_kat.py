@@ -1,0 +1,150 @@
+"""CPU: pins of the oracle (parity is otherwise unpinned — the reference ships no fixtures):
+brute force vs kd-tree, analytic known-answer cases, layout sizes, reference quirks Q3-Q7."""
+import numpy as np
+import pytest
+
+from pointcloudprocessing_b200 import synth
+
+
+def test_layout_sizes(oracle):
+    from pointcloudprocessing_b200 import capi
+
+    assert oracle.FEATURE_DTYPE.itemsize == 68 == capi.FEATURE_DTYPE.itemsize  # include/pcaAnalysis.h:34-45
+    assert [oracle.FEATURE_DTYPE.fields[f][1] for f in ("la", "v1", "ptID", "ptNum", "lineStruc")] == [0, 12, 48, 52, 56]
+
+
+@pytest.mark.parametrize("k", [1, 10, 20, 30])
+def test_kdtree_knn_equals_brute(oracle, k):
+    pts = synth.urban(21, 6000, extent=20.0)
+    idx, d2 = oracle.KdTree(pts).knn_all(k)
+    for q in range(0, 6000, 97):
+        bi, bd = oracle.knn_brute(pts, q, k)
+        np.testing.assert_array_equal(idx[q], bi)
+        np.testing.assert_array_equal(d2[q].view(np.uint32), bd.view(np.uint32))
+    assert (idx[:, 0] == np.arange(6000)).all()  # the query is its own nearest neighbour (Q5)
+
+
+@pytest.mark.parametrize("r", [0.3, 0.5, 2.0])
+def test_kdtree_radius_equals_brute(oracle, r):
+    pts = synth.urban(22, 5000, extent=20.0)
+    off, idx, d2 = oracle.KdTree(pts).radius_all(r)
+    for q in range(0, 5000, 83):
+        bi, bd = oracle.radius_brute(pts, q, r)
+        np.testing.assert_array_equal(idx[off[q]:off[q + 1]], bi)
+        np.testing.assert_array_equal(d2[off[q]:off[q + 1]].view(np.uint32), bd.view(np.uint32))
+
+
+def test_ties_broken_by_index(oracle):
+    """Duplicates and lattice points: (d2, index) order, first k of it."""
+    pts = np.zeros((10, 4), np.float32)
+    pts[5:, 0] = 1.0
+    idx, d2 = oracle.knn_brute(pts, 7, 7)
+    assert idx.tolist() == [5, 6, 7, 8, 9, 0, 1]
+    assert d2.tolist() == [0, 0, 0, 0, 0, 1, 1]
+    tidx, _ = oracle.KdTree(pts).knn_all(7)
+    assert tidx[7].tolist() == idx.tolist()
+
+
+def test_radius_is_strict_and_squared_in_double(oracle):
+    """Q6: r2 = (float)((double)r*(double)r); membership d2 < r2."""
+    r = np.float32(0.1)
+    assert oracle.radius2(float(r)) == float(np.float32(np.float64(r) * np.float64(r)))
+    pts = np.zeros((3, 4), np.float32)
+    pts[1, 0] = 0.5
+    pts[2, 0] = np.nextafter(np.float32(0.5), np.float32(0))
+    idx, _ = oracle.radius_brute(pts, 0, 0.5)
+    assert idx.tolist() == [0, 2]
+
+
+def test_covariance_about_query_not_mean(oracle):
+    """Q2: second moment about the given centre, divisor n (not n−1), PCL accumulation order."""
+    pts = np.array([[1, 2, 3, 0], [2, 2, 3, 0], [1, 4, 3, 0], [1, 2, 7, 0]], np.float32)
+    Cm = oracle.covariance_about(pts, [0, 1, 2, 3], pts[0, :3])
+    np.testing.assert_array_equal(Cm, np.diag([1 / 4, 4 / 4, 16 / 4]).astype(np.float32))
+
+
+def test_eigen_known_answers(oracle):
+    ev, Q, _ = oracle.eigen_sym3_qr(np.diag([3.0, 1.0, 2.0]))
+    assert ev.tolist() == [1.0, 2.0, 3.0]  # ascending (Q3)
+    assert np.allclose(np.abs(Q), np.array([[0, 0, 1], [1, 0, 0], [0, 1, 0]]))
+    ev, Q, _ = oracle.eigen_sym3_qr(np.zeros((3, 3)))
+    assert ev.tolist() == [0, 0, 0] and np.allclose(Q, np.eye(3))
+    rng = np.random.default_rng(0)
+    for _ in range(300):
+        A = rng.normal(size=(3, 3)) * rng.choice([1e-3, 1.0, 1e3])
+        S = (A @ A.T).astype(np.float32)
+        ev, Q, it = oracle.eigen_sym3_qr(S)
+        w = np.linalg.eigvalsh(S.astype(np.float64))
+        assert np.abs(ev - w).max() <= 1.5e-6 * np.abs(w).max()  # fp32 QR: a few ulps of λmax
+        assert np.allclose(Q.T @ Q, np.eye(3), atol=2e-6) and it <= 90
+        assert np.abs(S.astype(np.float64) @ Q - Q * ev).max() <= 2e-6 * np.abs(w).max()
+
+
+def test_planar_patch_and_features(oracle):
+    """Plane z = 0 lattice, spacing s: λ = {0, Σx²/n, Σy²/n}; v1 = ±z; the reference's features divide
+    by sqrt of the SMALLEST λ (Q3), so they are inf/nan on an exact plane."""
+    g = (np.arange(-3, 4) * 0.1).astype(np.float32)
+    x, y = np.meshgrid(g, g, indexing="ij")
+    pts = np.stack([x.ravel(), y.ravel(), 0 * x.ravel(), 0 * x.ravel()], 1).astype(np.float32)
+    f, valid = oracle.radius_pca_cloud(pts, 10.0, 13, True)
+    c = f[24]  # centre point: all 49 points are neighbours
+    assert valid.all() and c["ptNum"] == 49 and c["ptID"] == 24
+    m = float((g.astype(np.float64) ** 2).sum() * 7 / 49)
+    assert abs(c["la"][0]) < 1e-8 and np.allclose(c["la"][1:], m, rtol=1e-5)
+    assert abs(abs(c["v1"][2]) - 1) < 1e-6
+    s = oracle.structure_features(1.0, 4.0, 9.0)
+    assert s.tolist() == [-1.0, -1.0, 3.0]  # (√λ1−√λ2)/√λ1, (√λ2−√λ3)/√λ1, √λ3/√λ1
+
+
+def test_min_pts_gate_and_stale_records(oracle):
+    """Q4: < 13 neighbours keeps only ptID/ptNum; with the carry the payload is the last valid one's."""
+    rng = np.random.default_rng(3)
+    dense = rng.normal(0, 0.05, (40, 3))
+    sparse = rng.uniform(5, 50, (10, 3))
+    xyz = np.concatenate([sparse[:3], dense, sparse[3:]]).astype(np.float32)
+    pts = np.column_stack([xyz, np.zeros(len(xyz), np.float32)]).astype(np.float32)
+    f, valid = oracle.radius_pca_cloud(pts, 0.5, 13, True)
+    assert not valid[:3].any() and valid[3:43].all() and not valid[43:].any()
+    assert (f["ptID"] == np.arange(len(pts))).all() and (f["ptNum"][43:] == 1).all()
+    assert not f["la"][:3].any()  # leading records: zero-filled
+    for i in range(43, len(pts)):
+        assert f["la"][i].tobytes() == f["la"][42].tobytes() and f["scatterStruc"][i] == f["scatterStruc"][42]
+    f12, v12 = oracle.radius_pca_cloud(pts[3:15], 10.0, 13, False)
+    f13, v13 = oracle.radius_pca_cloud(pts[3:16], 10.0, 13, False)
+    assert not v12.any() and v13.all()  # exactly 12 vs 13 neighbours
+    fa, _ = oracle.radius_pca_cloud(pts, 0.5, 13, True, nthreads=1)
+    fb, _ = oracle.radius_pca_cloud(pts, 0.5, 13, True, nthreads=4)
+    assert fa.tobytes() == fb.tobytes()  # the parallel baseline equals the faithful sequential loop
+
+
+def test_pcl_eigen33_smallest_pair(oracle):
+    rng = np.random.default_rng(1)
+    for _ in range(100):
+        A = rng.normal(size=(3, 3))
+        S = (A @ A.T + 0.1 * np.eye(3)).astype(np.float32)
+        ev, v = oracle.pcl_eigen33(S)
+        w, V = np.linalg.eigh(S.astype(np.float64))
+        assert abs(ev - w[0]) < 2e-5 * w[2] and abs(abs(v @ V[:, 0]) - 1) < 1e-3
+
+
+def test_ring_projection_known_cells(oracle):
+    """Beam −15° lands in row 0, +15° in row 15; azimuth along +y is column 900 - round(-90/0.2)... =
+    the reference formula col = −round((h−90)/0.2) + 900 with h = atan2(x, y) in degrees."""
+    d = 10.0
+    pts = []
+    for v in (-15, 1, 15):
+        for az in (0.0, 90.0, 180.0, 270.0):
+            a, e = np.deg2rad(az), np.deg2rad(v)
+            pts.append([d * np.cos(e) * np.sin(a), d * np.cos(e) * np.cos(a), d * np.sin(e), 0])
+    pts = np.array(pts, np.float32)
+    rng, pti, tag, lr = oracle.ring_project(pts)
+    rows = {-15: 0, 1: 8, 15: 15}
+    cols = {0.0: 1350, 90.0: 900, 180.0: 450, 270.0: 0}
+    i = 0
+    for v in (-15, 1, 15):
+        for az in (0.0, 90.0, 180.0, 270.0):
+            assert pti[rows[v], cols[az]] == i, (v, az)
+            assert abs(rng[rows[v], cols[az]] - d) < 1e-4
+            i += 1
+    assert (pti >= 0).sum() == 12 and lr == 0
+    assert rng[3, 3] == np.finfo(np.float32).max
