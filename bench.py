@@ -152,7 +152,8 @@ def main():
     ap.add_argument("--points", type=int, default=1_000_000, help="points per GPU")
     ap.add_argument("--k", type=int, default=20)
     ap.add_argument("--cell", type=float, default=0.0)
-    ap.add_argument("--cpu-sample", type=int, default=250_000)
+    ap.add_argument("--cpu-sample", type=int, default=1_000_000)
+    ap.add_argument("--halo", type=float, default=6.0, help="slab halo width in metres (N > 1)")
     ap.add_argument("--no-cpu", action="store_true")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
@@ -170,11 +171,22 @@ def main():
     torch.cuda.set_device(local)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    from pointcloudprocessing_b200 import sharding
+
     n, k = args.points, args.k
     pts = make_cloud(n, rank)
+    L = 200.0 * (n / 1e6) ** 0.5
+    halo = args.halo
+    if world > 1:
+        # weak scaling: rank r owns the slab x in [r*L, (r+1)*L) of a world*L x L scan; neighbours
+        # exchange the strips within `halo` of the shared faces every step (NCCL send/recv)
+        pts[:, 0] = np.clip(pts[:, 0], 0.0, L - 1e-3) + np.float32(rank * L)
+    lo, hi = rank * L, (rank + 1) * L
     p = capi.Pcp(local)  # raises if libpcp.so / the GPU is missing: no fallback
     stream = torch.cuda.ExternalStream(p.stream, device=local)
     d_pts = torch.from_numpy(pts).cuda(local)
+    d_gid = (torch.arange(n, dtype=torch.int32, device=local) + rank * n) if world > 1 else None
+    d_kth = torch.empty(n, dtype=torch.float32, device=local)
     d_out = torch.empty(n * 68, dtype=torch.uint8, device=local)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=local)  # > 126 MB L2
     h_in = torch.from_numpy(pts).pin_memory()
@@ -186,12 +198,35 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
+    keep = {}
+
+    def shard_step(src_pts):
+        # halo exchange + sharded hand-over; torch/NCCL work is ordered on the library's stream
+        with torch.cuda.stream(stream):
+            p_all, g_all, n_own = sharding.exchange_halo(src_pts, d_gid, 0, lo, hi, halo, rank, world)
+        keep["shard"] = (p_all, g_all)
+        p.set_cloud_device(p_all.data_ptr(), p_all.shape[0], g_all.data_ptr(), n_own)
+        p.build_grid(args.cell, k)
+        p.knn_pca(k, capi.CENTER_QUERY, out_device=d_out.data_ptr(), kth_device=d_kth.data_ptr())
+
     def step_device():
+        if world > 1:
+            return shard_step(d_pts)
         p.set_cloud_device(d_pts.data_ptr(), n)
         p.build_grid(args.cell, k)
         p.knn_pca(k, capi.CENTER_QUERY, out_device=d_out.data_ptr())
 
+    d_stage = torch.empty_like(d_pts)
+
     def step_e2e():
+        if world > 1:
+            with torch.cuda.stream(stream):
+                d_stage.copy_(h_in, non_blocking=True)
+            shard_step(d_stage)
+            with torch.cuda.stream(stream):
+                h_out.copy_(d_out, non_blocking=True)
+            p.synchronize()
+            return
         p.set_cloud_host_ptr(h_in.data_ptr(), n, 16)
         p.build_grid(args.cell, k)
         p.knn_pca(k, capi.CENTER_QUERY, out_host_ptr=h_out.data_ptr())
@@ -199,6 +234,13 @@ def main():
     for _ in range(max(args.warmup, 3)):
         step_device()
     p.synchronize()
+    halo_unproven = 0
+    if world > 1:
+        # prove the halo was wide enough for every own query (k-th distance inside the covered region)
+        with torch.cuda.stream(stream):
+            halo_unproven = sharding.knn_halo_violations(d_pts, d_kth, 0, lo, hi, halo, rank, world)
+        if halo_unproven:
+            raise SystemExit(f"rank {rank}: halo {halo} m too narrow for {halo_unproven} queries; raise --halo")
 
     # ---- device-resident timing: CUDA events on the library's stream, L2 flushed between steps
     sampler = ClockSampler(local)
@@ -245,7 +287,9 @@ def main():
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": f"urban_{n}pts_knn_k{k}_pca (configs[2] shape, metric's k)", "points_per_gpu": n, "k": k,
                    "order": "random", "l2": "flushed between steps (256 MiB fill, untimed)",
-                   "step": "bbox+keys+radix sort+cell table+fused search/moment/eigen, 68 B records"},
+                   "step": "bbox+keys+radix sort+cell table+fused search/moment/eigen, 68 B records",
+                   "sharding": "single cloud" if world == 1 else
+                   f"x-slabs of one {world}x{L:.0f} m x {L:.0f} m scan, halo {halo} m exchanged every step (NCCL send/recv), global-index tie-break"},
         "clocks": clocks,
         "e2e": {"value": total_pts / (e2e_ms * 1e-3), "unit": "points/s", "h2d_bytes_per_step": 16 * n, "d2h_bytes_per_step": 68 * n},
         "gpu_launches": int(launches),
@@ -259,14 +303,27 @@ def main():
 
         threads = O.num_threads()
         v1, m1, _ = run_cpu(pts, k, 1, args.cpu_sample // 4)
-        vall, mall, dt = run_cpu(pts, k, threads, args.cpu_sample)
+        best = None
+        for _ in range(3):
+            r_ = run_cpu(pts, k, threads, args.cpu_sample)
+            best = r_ if best is None or r_[0] > best[0] else best
+        vall, mall, dt = best
         line["cpu_baseline"] = {"value": vall, "unit": "points/s", "cores": threads, "kind": "port", "value_1core": v1,
                                 "sample": f"spatial tile of {mall} points (all cores, {dt:.1f} s) / {m1} points (1 core) of the same cloud"}
     if rank == 0:
         print(json.dumps(line), flush=True)
-    p.close()
+    # orderly teardown: tensors that lived on the library's stream go first, then the stream itself
+    p.synchronize()
+    keep.clear()
+    del d_stage, d_pts, d_out, d_kth, flush, d_gid
+    torch.cuda.synchronize()
+    torch.cuda.empty_cache()
     if world > 1:
+        dist.barrier()
         dist.destroy_process_group()
+    p.close()
+    sys.stdout.flush()
+    os._exit(0)
 
 
 if __name__ == "__main__":

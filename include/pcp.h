@@ -152,6 +152,11 @@ PCP_API int pcp_radius_pca(pcp_ctx* ctx, float radius, int min_pts, int center_m
  * |λmin / trace|, normal flipped toward the viewpoint (0,0,0). */
 PCP_API int pcp_knn_pca(pcp_ctx* ctx, int k, int center_mode, pcp_feature68* out,
                         pcp_normal16* normals, int out_is_device);
+/* Same, plus kth_d2[i] = squared distance of point i's k-th neighbour (+inf when the cloud holds
+ * fewer than k points): a tile-sharded caller uses it to prove its halo was wide enough (a query
+ * is safe when kth_d2 <= squared distance to the nearest un-covered tile face). */
+PCP_API int pcp_knn_pca_kth(pcp_ctx* ctx, int k, int center_mode, pcp_feature68* out,
+                            pcp_normal16* normals, float* kth_d2, int out_is_device);
 
 /* ---- neighbour lists (verification and the consumers: mean-shift, DBSCAN) ----------
  * Replace `kdtree.nearestKSearch` / `kdtree.radiusSearch` call sites

@@ -40,7 +40,7 @@ EXPORTS = (
     "pcp_create", "pcp_destroy", "pcp_last_error", "pcp_version", "pcp_stream", "pcp_synchronize",
     "pcp_last_timings", "pcp_launch_count", "pcp_set_cloud_host", "pcp_set_cloud_device",
     "pcp_set_cloud_device_sharded", "pcp_build_grid", "pcp_grid_info", "pcp_radius_pca", "pcp_knn_pca",
-    "pcp_knn_neighbors", "pcp_radius_neighbors", "pcp_segment_pca", "pcp_ring_calib_default",
+    "pcp_knn_pca_kth", "pcp_knn_neighbors", "pcp_radius_neighbors", "pcp_segment_pca", "pcp_ring_calib_default",
     "pcp_ring_calib_from_xml", "pcp_ring_project",
 )
 
@@ -92,6 +92,7 @@ def load() -> C.CDLL:
         "pcp_grid_info": (i32, [vp, vp, vp, vp]),
         "pcp_radius_pca": (i32, [vp, f32, i32, i32, i32, vp, i32]),
         "pcp_knn_pca": (i32, [vp, i32, i32, vp, vp, i32]),
+        "pcp_knn_pca_kth": (i32, [vp, i32, i32, vp, vp, vp, i32]),
         "pcp_knn_neighbors": (i32, [vp, i32, vp, vp, i32]),
         "pcp_radius_neighbors": (i32, [vp, f32, vp, vp, vp, vp, i32]),
         "pcp_segment_pca": (i32, [vp, vp, vp, vp, i64, vp]),
@@ -221,9 +222,9 @@ class Pcp:
         return out
 
     def knn_pca(self, k: int, center_mode: int = CENTER_QUERY, want_normals: bool = False, out_device: Optional[int] = None,
-                normals_device: Optional[int] = None, out_host_ptr: Optional[int] = None):
+                normals_device: Optional[int] = None, out_host_ptr: Optional[int] = None, kth_device: Optional[int] = None):
         if out_device is not None or normals_device is not None:
-            self._ck(self.lib.pcp_knn_pca(self.h, k, center_mode, out_device, normals_device, 1))
+            self._ck(self.lib.pcp_knn_pca_kth(self.h, k, center_mode, out_device, normals_device, kth_device, 1))
             return None
         if out_host_ptr is not None:
             self._ck(self.lib.pcp_knn_pca(self.h, k, center_mode, out_host_ptr, None, 0))

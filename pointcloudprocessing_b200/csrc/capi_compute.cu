@@ -91,6 +91,11 @@ PCP_API int pcp_radius_pca(pcp_ctx* ctx, float radius, int min_pts, int center_m
 }
 
 PCP_API int pcp_knn_pca(pcp_ctx* ctx, int k, int center_mode, pcp_feature68* out, pcp_normal16* normals, int out_is_device) {
+  return pcp_knn_pca_kth(ctx, k, center_mode, out, normals, nullptr, out_is_device);
+}
+
+PCP_API int pcp_knn_pca_kth(pcp_ctx* ctx, int k, int center_mode, pcp_feature68* out, pcp_normal16* normals, float* kth_d2,
+                            int out_is_device) {
   int rc = require_grid(ctx, "pcp_knn_pca");
   if (rc) return rc;
   if (k < 1 || k > PCP_MAX_K) return pcp_fail(ctx, PCP_ERR_K_UNSUPPORTED, "pcp_knn_pca: k outside [1, PCP_MAX_K]");
@@ -105,10 +110,12 @@ PCP_API int pcp_knn_pca(pcp_ctx* ctx, int k, int center_mode, pcp_feature68* out
   sp.center_mode = center_mode;
   if ((rc = pick_out(ctx, ctx->out_feat, out, out_is_device, (size_t)nq, &sp.out))) return rc;
   if ((rc = pick_out(ctx, ctx->out_norm, normals, out_is_device, (size_t)nq, &sp.normals))) return rc;
+  if ((rc = pick_out(ctx, ctx->out_d2, kth_d2, out_is_device, (size_t)nq, &sp.kth_d2))) return rc;
   if ((rc = pcp_search_launch(ctx, sp))) return rc;
   pcp_tic(ctx, PCP_T_D2H);
   if ((rc = copy_back(ctx, out, sp.out, out_is_device, (size_t)nq))) return rc;
   if ((rc = copy_back(ctx, normals, sp.normals, out_is_device, (size_t)nq))) return rc;
+  if ((rc = copy_back(ctx, kth_d2, sp.kth_d2, out_is_device, (size_t)nq))) return rc;
   pcp_toc(ctx, PCP_T_D2H);
   if (!out_is_device) PCP_CUDA(cudaStreamSynchronize(ctx->stream));
   return PCP_OK;

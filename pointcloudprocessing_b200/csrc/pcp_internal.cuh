@@ -94,6 +94,7 @@ struct SearchParams {
   float* nn_d2;
   int32_t* counts;    // radius: per-query neighbour count (may be null)
   const int64_t* offsets; // radius CSR offsets for nn_idx / nn_d2
+  float* kth_d2;      // k-NN: squared distance of the k-th neighbour per output slot (may be null)
   uint8_t* valid;     // per output slot: 1 when the record was computed (may be null)
   int* overflow_flag; // device int: set when a radius neighbourhood exceeded the warp buffer
 };

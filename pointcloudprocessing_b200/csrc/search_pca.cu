@@ -349,6 +349,8 @@ __global__ void __launch_bounds__(WARPS * 32) search_pca_kernel(KArgs a) {
     }
     if (MODE == 1 && overflow && sp.overflow_flag && lane == 0) atomicExch(sp.overflow_flag, 1);
     if (MODE == 1 && sp.counts && lane == 0) sp.counts[slot_q] = n_nb;
+    if (MODE == 0 && sp.kth_d2 && lane == 0)
+      sp.kth_d2[slot_q] = n_nb >= sp.k ? __uint_as_float((uint32_t)(st.thr >> 32)) : INFINITY;
     if (sp.nn_idx != nullptr && !overflow) {
       if (MODE == 0) {
         if (lane < sp.k) {

@@ -1,0 +1,183 @@
+// pcaAnalysis.cpp — the reference's pcaAnalysist methods re-implemented as a thin adapter over the
+// pcp_* C-ABI (include/pcp.h → libpcp.so, CUDA sm_100a).  Replaces src/pcaAnalysis.cpp:11-148.
+// Host work here is packing and hand-over only; there is no CPU compute path: when the GPU or the
+// library is unavailable every method returns false and prints the pcp error once.
+#include "pcaAnalysis.h"
+
+#include <cstdint>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+
+#include "pcp.h"
+
+namespace {
+
+// one device context per host thread (the reference class is stateless and re-entrant)
+struct ThreadCtx {
+  pcp_ctx* ctx = nullptr;
+  const void* cloud_ptr = nullptr;  // identity of the cloud currently resident on the device
+  size_t cloud_n = 0;
+  uint64_t cloud_sig = 0;
+  bool failed = false;
+  ~ThreadCtx() {
+    if (ctx) pcp_destroy(ctx);
+  }
+};
+
+ThreadCtx& tls() {
+  static thread_local ThreadCtx t;
+  return t;
+}
+
+pcp_ctx* context() {
+  ThreadCtx& t = tls();
+  if (t.ctx || t.failed) return t.ctx;
+  const char* dev = std::getenv("PCP_DEVICE");
+  int rc = pcp_create(&t.ctx, dev ? std::atoi(dev) : 0);
+  if (rc != PCP_OK) {
+    std::fprintf(stderr, "pcaAnalysist: pcp_create failed (%d): no sm_100 GPU / libpcp; there is no CPU path\n", rc);
+    t.failed = true;
+    t.ctx = nullptr;
+  }
+  return t.ctx;
+}
+
+bool fail(pcp_ctx* ctx, const char* where, int rc) {
+  std::fprintf(stderr, "pcaAnalysist::%s: pcp error %d: %s\n", where, rc, pcp_last_error(ctx));
+  return false;
+}
+
+// cheap identity of a cloud: address, size and a hash over 64 sampled points
+uint64_t signature(const pcXYZI& c) {
+  uint64_t h = 1469598103934665603ull;
+  const size_t n = c.points.size();
+  const size_t step = n > 64 ? n / 64 : 1;
+  for (size_t i = 0; i < n; i += step) {
+    uint32_t w[3];
+    std::memcpy(w, &c.points[i].x, 12);
+    for (int k = 0; k < 3; ++k) h = (h ^ w[k]) * 1099511628211ull;
+  }
+  return h;
+}
+
+// upload unless this very cloud is already resident
+int ensure_cloud(pcp_ctx* ctx, const pcXYZI& c) {
+  ThreadCtx& t = tls();
+  const uint64_t sig = signature(c);
+  if (t.cloud_ptr == c.points.data() && t.cloud_n == c.points.size() && t.cloud_sig == sig) return PCP_OK;
+  int rc = pcp_set_cloud_host(ctx, c.points.data(), (int64_t)c.points.size(), (int)sizeof(pcl::PointXYZI));
+  if (rc == PCP_OK) {
+    t.cloud_ptr = c.points.data();
+    t.cloud_n = c.points.size();
+    t.cloud_sig = sig;
+  } else {
+    t.cloud_ptr = nullptr;
+  }
+  return rc;
+}
+
+void to_feature(const pcp_feature68& r, pcaAnalysist::pcaFeature& f) {
+  static_assert(sizeof(pcp_feature68) == sizeof(pcaAnalysist::pcaFeature), "layout");
+  std::memcpy(&f, &r, sizeof(r));
+}
+
+}  // namespace
+
+bool pcaAnalysist::calculatePCAofPointCloud(pcXYZIptr inputCloud, float radius, std::vector<pcaFeature>& pcaFeaofCloud) {
+  if (!inputCloud || inputCloud->points.empty()) return true;
+  pcp_ctx* ctx = context();
+  if (!ctx) return false;
+  int rc = ensure_cloud(ctx, *inputCloud);
+  if (rc) return fail(ctx, "calculatePCAofPointCloud", rc);
+  // cell edge = radius: the 27-cell stencil is exact for the radius search (src/pcaAnalysis.cpp:25)
+  if ((rc = pcp_build_grid(ctx, radius * 1.0001f, 0))) return fail(ctx, "calculatePCAofPointCloud", rc);
+  const size_t n = inputCloud->points.size(), old = pcaFeaofCloud.size();
+  pcaFeaofCloud.resize(old + n);  // appended, never cleared
+  // gate 13 (:50), PCA about the query point (:53-55), stale-record carry (:16,:26,:39)
+  rc = pcp_radius_pca(ctx, radius, 13, PCP_CENTER_QUERY, 1, reinterpret_cast<pcp_feature68*>(pcaFeaofCloud.data() + old), 0);
+  if (rc) {
+    pcaFeaofCloud.resize(old);
+    return fail(ctx, "calculatePCAofPointCloud", rc);
+  }
+  return true;
+}
+
+bool pcaAnalysist::calculatePCAofPoint(pcXYZIptr inputCloud, int i, std::vector<int> neighborIndices, pcaFeature& ptFeature) {
+  ptFeature.ptID = i;
+  ptFeature.ptNum = (int)neighborIndices.size();
+  if (ptFeature.ptNum < 13) return true;  // src/pcaAnalysis.cpp:50-51: everything else stays as it was
+  pcp_ctx* ctx = context();
+  if (!ctx || !inputCloud) return false;
+  int rc = ensure_cloud(ctx, *inputCloud);
+  if (rc) return fail(ctx, "calculatePCAofPoint", rc);
+  const pcl::PointXYZI& q = inputCloud->points[(size_t)i];
+  const float centre[3] = {q.x, q.y, q.z};
+  const int64_t offs[2] = {0, (int64_t)neighborIndices.size()};
+  pcp_feature68 r;
+  if ((rc = pcp_segment_pca(ctx, centre, offs, neighborIndices.data(), 1, &r))) return fail(ctx, "calculatePCAofPoint", rc);
+  // this overload sets λ and vectors only (:72-86); the features are the caller's (:29-31)
+  const float l1 = ptFeature.lineStruc, l2 = ptFeature.planeStruc, l3 = ptFeature.scatterStruc;
+  to_feature(r, ptFeature);
+  ptFeature.ptID = i;
+  ptFeature.lineStruc = l1;
+  ptFeature.planeStruc = l2;
+  ptFeature.scatterStruc = l3;
+  return true;
+}
+
+bool pcaAnalysist::calculatePCAofPoint(pcXYZIptr inputCloud, pcl::PointXYZI centro, std::vector<int> neighborIndices,
+                                       pcaAnalysist::pcaFeature& ptFeature) {
+  pcp_ctx* ctx = context();
+  if (!ctx || !inputCloud) return false;
+  int rc = ensure_cloud(ctx, *inputCloud);
+  if (rc) return fail(ctx, "calculatePCAofPoint(centro)", rc);
+  const float centre[3] = {centro.x, centro.y, centro.z};
+  const int64_t offs[2] = {0, (int64_t)neighborIndices.size()};
+  pcp_feature68 r;
+  if ((rc = pcp_segment_pca(ctx, centre, offs, neighborIndices.data(), 1, &r))) return fail(ctx, "calculatePCAofPoint(centro)", rc);
+  const int id = ptFeature.ptID;  // not touched by this overload (src/pcaAnalysis.cpp:92)
+  to_feature(r, ptFeature);
+  ptFeature.ptID = id;
+  return true;
+}
+
+bool pcaAnalysist::getMiniBoundingBox(pcXYZIptr inputCloud) {
+  if (!inputCloud || inputCloud->points.empty()) return true;
+  pcp_ctx* ctx = context();
+  if (!ctx) return false;
+  int rc = ensure_cloud(ctx, *inputCloud);
+  if (rc) return fail(ctx, "getMiniBoundingBox", rc);
+  // pcl::compute3DCentroid: fp32 running sum / n (src/pcaAnalysis.cpp:125-126)
+  const size_t n = inputCloud->points.size();
+  float sx = 0.f, sy = 0.f, sz = 0.f;
+  for (const pcl::PointXYZI& p : inputCloud->points) {
+    sx += p.x;
+    sy += p.y;
+    sz += p.z;
+  }
+  const float centre[3] = {sx / (float)n, sy / (float)n, sz / (float)n};
+  std::vector<int> all(n);
+  for (size_t i = 0; i < n; ++i) all[i] = (int)i;
+  const int64_t offs[2] = {0, (int64_t)n};
+  pcp_feature68 r;
+  if ((rc = pcp_segment_pca(ctx, centre, offs, all.data(), 1, &r))) return fail(ctx, "getMiniBoundingBox", rc);
+  // right-handed frame col2 = col0 × col1 (:133), rigid transform, extents (:137-146); like the
+  // reference the result is not returned to the caller
+  const float* a = r.v1;
+  const float* b = r.v2;
+  const float c[3] = {a[1] * b[2] - a[2] * b[1], a[2] * b[0] - a[0] * b[2], a[0] * b[1] - a[1] * b[0]};
+  float lo[3] = {3.4e38f, 3.4e38f, 3.4e38f}, hi[3] = {-3.4e38f, -3.4e38f, -3.4e38f};
+  for (const pcl::PointXYZI& p : inputCloud->points) {
+    const float d[3] = {p.x - centre[0], p.y - centre[1], p.z - centre[2]};
+    const float t[3] = {a[0] * d[0] + a[1] * d[1] + a[2] * d[2], b[0] * d[0] + b[1] * d[1] + b[2] * d[2],
+                        c[0] * d[0] + c[1] * d[1] + c[2] * d[2]};
+    for (int k = 0; k < 3; ++k) {
+      lo[k] = t[k] < lo[k] ? t[k] : lo[k];
+      hi[k] = t[k] > hi[k] ? t[k] : hi[k];
+    }
+  }
+  (void)lo;
+  (void)hi;
+  return true;
+}
