@@ -24,6 +24,13 @@
 #include "pcp_internal.cuh"
 #include "search_common.cuh"
 
+#ifdef PCP_STATS
+__device__ unsigned long long g_stats[8];
+#define STAT(i, v) do { if (lane == 0) atomicAdd(&g_stats[i], (unsigned long long)(v)); } while (0)
+#else
+#define STAT(i, v) do { } while (0)
+#endif
+
 namespace {
 
 constexpr int WARPS = 8;            // warps per CTA
@@ -49,6 +56,7 @@ struct WarpSmem {
     struct S {
       u64 buf[MODE == 0 ? 64 : RADIUS_CAP];
       float prod[6][32];
+      uint2 runs[32];  // (first sorted position, virtual offset) of the non-empty runs of a row chunk
     } s;
     float rec[32][REC_WORDS];
   } u;
@@ -144,7 +152,7 @@ __device__ __forceinline__ void scan_shell(const KArgs& a, WarpSmem<MODE>* ws, S
                                            float f0, float f1, float f2, int Rp, int R, float bound2, int lane, uint32_t dirs) {
   const GridDesc& g = a.g;
   const float4* __restrict__ sorted = a.sorted;
-  const unsigned lt_mask = (1u << lane) - 1u;
+  const unsigned lt_mask = (1u << lane) - 1u, le_mask = (2u << lane) - 1u;
   const int lo1 = max(c1 - R, 0), hi1 = min(c1 + R, g.dim[1] - 1), n1 = hi1 - lo1 + 1;
   const int lo2 = max(c2 - R, 0), hi2 = min(c2 + R, g.dim[2] - 1), n2 = hi2 - lo2 + 1;
   const int nrows = n1 * n2;
@@ -192,41 +200,58 @@ __device__ __forceinline__ void scan_shell(const KArgs& a, WarpSmem<MODE>* ws, S
         }
       }
     }
-    // walk the non-empty runs only
-    unsigned mA = __ballot_sync(PCP_FULL, eA > bA), mB = __ballot_sync(PCP_FULL, eB > bB);
-    while (mA | mB) {
-      uint32_t bj, ej;
-      if (mA) {
-        const int j = __ffs(mA) - 1;
-        mA &= mA - 1;
-        bj = __shfl_sync(PCP_FULL, bA, j);
-        ej = __shfl_sync(PCP_FULL, eA, j);
-      } else {
-        const int j = __ffs(mB) - 1;
-        mB &= mB - 1;
-        bj = __shfl_sync(PCP_FULL, bB, j);
-        ej = __shfl_sync(PCP_FULL, eB, j);
+    // Flatten the non-empty runs of this row chunk into ONE virtual sequence so that every
+    // 32-candidate step uses all lanes (stencil rows are often short): run descriptors are
+    // compacted by rank into shared memory, and each step maps lane -> (run, offset) with one
+    // warp OR-reduce of the run-start bits and a popc.
+#pragma unroll
+    for (int half = 0; half < 2; ++half) {
+      const uint32_t rbeg = half == 0 ? bA : bB;
+      const uint32_t len = half == 0 ? eA - bA : eB - bB;
+      const unsigned ne = __ballot_sync(PCP_FULL, len > 0);
+      if (ne == 0) continue;
+      uint32_t inc = len;  // inclusive prefix of the run lengths
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t t = __shfl_up_sync(PCP_FULL, inc, o);
+        if (lane >= o) inc += t;
       }
-      for (uint32_t cb = bj; cb < ej; cb += 32) {
-        const uint32_t cp = cb + lane;
+      const uint32_t total = __shfl_sync(PCP_FULL, inc, 31);
+      const uint32_t myoff = inc - len;
+      if (len > 0) ws->u.s.runs[__popc(ne & lt_mask)] = make_uint2(rbeg, myoff);
+      __syncwarp();
+      STAT(2, __popc(ne));
+      uint32_t starts_before = 0;
+      for (uint32_t t0 = 0; t0 < total; t0 += 32) {
+        STAT(3, 1);
+        STAT(4, min(32u, total - t0));
+        const uint32_t rel = myoff - t0;  // wraps for runs that started earlier
+        const unsigned smask = __reduce_or_sync(PCP_FULL, (len > 0 && rel < 32u) ? (1u << rel) : 0u);
+        const uint32_t v = t0 + lane;
+        const bool live = v < total;
+        const int ridx = (int)starts_before + __popc(smask & le_mask) - 1;
+        starts_before += __popc(smask);
         bool pass = false;
         u64 key = 0;
-        if (cp < ej) {
-          const float4 P = __ldg(&sorted[cp]);
+        if (live) {
+          const uint2 rd = ws->u.s.runs[ridx];
+          const float4 P = __ldg(&sorted[rd.x + (v - rd.y)]);
           const float d2v = dist2_nofma(Q.x, Q.y, Q.z, P);
           key = ((u64)__float_as_uint(d2v) << 32) | (u64)__float_as_uint(P.w);
           pass = MODE == 0 ? key < st.thr : d2v < a.sp.r2;
         }
         const unsigned m = __ballot_sync(PCP_FULL, pass);
         if (m == 0) continue;
+        STAT(5, __popc(m));
         const int off = st.cnt + __popc(m & lt_mask);
         if (MODE == 0) {
           if (pass) ws->u.s.buf[off] = key;
           st.cnt += __popc(m);
           __syncwarp();
           if (st.cnt >= 32) {
-            u64 v = warp_sort32(ws->u.s.buf[lane], dirs);
-            st.best = warp_merge32(st.best, v, lane, dirs);
+            STAT(6, 1);
+            u64 v32 = warp_sort32(ws->u.s.buf[lane], dirs);
+            st.best = warp_merge32(st.best, v32, lane, dirs);
             st.thr = shfl_u64(st.best, a.sp.k - 1);
             u64 rem = (lane + 32 < st.cnt) ? ws->u.s.buf[lane + 32] : 0ull;
             __syncwarp();
@@ -239,6 +264,7 @@ __device__ __forceinline__ void scan_shell(const KArgs& a, WarpSmem<MODE>* ws, S
           st.cnt += __popc(m);
         }
       }
+      __syncwarp();  // runs[] is rewritten by the next half / row chunk
     }
   }
 }
@@ -260,12 +286,17 @@ __global__ void __launch_bounds__(WARPS * 32) search_pca_kernel(KArgs a) {
   const int my_slot = lane < nq ? a.slot[pos0 + lane] : -1;
   const uint32_t dirs = bitonic_dirs(lane);
   const int max_dim = max(g.dim[0], max(g.dim[1], g.dim[2]));
+  // lane j remembers query j of the tile and, once solved, its k-th distance: later queries seed
+  // their threshold from them (triangle inequality: d_k(q) <= d_k(q_j) + |q − q_j|)
+  const float4 myP = lane < nq ? __ldg(&sorted[pos0 + lane]) : make_float4(0.f, 0.f, 0.f, 0.f);
+  float my_dk = 3.4e38f;
 
 #pragma unroll 1
   for (int q = 0; q < nq; ++q) {
     const int slot_q = __shfl_sync(PCP_FULL, my_slot, q);
     if (slot_q < 0) continue;  // halo point: neighbour only
     const int64_t pq = pos0 + q;
+    STAT(0, 1);
     const float4 Q = __ldg(&sorted[pq]);
     const uint32_t cid = __ldg(&a.keys[pq]);
     int n_nb = 0;
@@ -294,20 +325,41 @@ __global__ void __launch_bounds__(WARPS * 32) search_pca_kernel(KArgs a) {
         overflow = st.cnt > RADIUS_CAP;
       } else {
         int Rp = -1, R = sp.R0;
+        // seed: the tightest upper bound on this query's k-th distance from the solved queries of
+        // the tile; with it the first pass already filters and prunes like a radius search
+        float bound = 3.4e38f;
+        {
+          float bj = 3.4e38f;
+          if (lane < q && my_dk < 3.0e38f) {
+            float dx = Q.x - myP.x, dy = Q.y - myP.y, dz = Q.z - myP.z;
+            bj = sqrtf(my_dk) + sqrtf(dx * dx + dy * dy + dz * dz);
+          }
+#pragma unroll
+          for (int o = 16; o > 0; o >>= 1) bj = fminf(bj, __shfl_xor_sync(PCP_FULL, bj, o));
+          // a seed is only worth taking from a nearby query (tiles cross row ends): ignore it when
+          // it would widen the first stencil beyond 2 cells
+          const float rs = bj * 1.00001f * (float)g.inv_cell + 1e-5f;
+          if (rs <= 2.0f) {
+            bound = bj * bj * 1.00002f;
+            st.thr = ((u64)__float_as_uint(bound) << 32) | 0xFFFFFFFFull;
+            R = min(max(R, (int)ceilf(rs)), max_dim);
+          }
+        }
 #pragma unroll 1
         for (;;) {
-          const u64 kth0 = shfl_u64(st.best, sp.k - 1);
-          const float bound = kth0 != PCP_KEY_INF ? __uint_as_float((uint32_t)(kth0 >> 32)) : 3.4e38f;
+          STAT(1, 1);
           scan_shell<MODE>(a, ws, st, Q, c0, c1, c2, f0, f1, f2, Rp, R, bound, lane, dirs);
           if (st.cnt > 0) {
+            STAT(7, 1);
             u64 v = warp_sort32(lane < st.cnt ? ws->u.s.buf[lane] : PCP_KEY_INF, dirs);
             st.best = warp_merge32(st.best, v, lane, dirs);
-            st.thr = shfl_u64(st.best, sp.k - 1);
             st.cnt = 0;
             __syncwarp();
           }
-          const u64 kth = st.thr;
+          const u64 kth = shfl_u64(st.best, sp.k - 1);
+          if (kth < st.thr) st.thr = kth;
           const bool found = kth != PCP_KEY_INF;
+          if (found) bound = __uint_as_float((uint32_t)(kth >> 32));
           const bool whole = (c0 - R <= 0) && (c0 + R >= g.dim[0] - 1) && (c1 - R <= 0) && (c1 + R >= g.dim[1] - 1) &&
                              (c2 - R <= 0) && (c2 + R >= g.dim[2] - 1);
           if (whole) break;
@@ -324,6 +376,9 @@ __global__ void __launch_bounds__(WARPS * 32) search_pca_kernel(KArgs a) {
           R = min(Rn, max_dim);
         }
         n_nb = __popc(__ballot_sync(PCP_FULL, lane < sp.k && st.best != PCP_KEY_INF));
+        const u64 kfin = shfl_u64(st.best, sp.k - 1);
+        if (lane == q && kfin != PCP_KEY_INF) my_dk = __uint_as_float((uint32_t)(kfin >> 32));
+        st.thr = kfin;
       }
     }
 
@@ -450,6 +505,16 @@ __global__ void __launch_bounds__(WARPS * 32) search_pca_kernel(KArgs a) {
 }
 
 }  // namespace
+
+#ifdef PCP_STATS
+extern "C" __attribute__((visibility("default"))) int pcp_debug_stats(unsigned long long* out) {
+  unsigned long long z[8] = {0};
+  cudaDeviceSynchronize();
+  cudaMemcpyFromSymbol(out, g_stats, sizeof(z));
+  cudaMemcpyToSymbol(g_stats, z, sizeof(z));
+  return 0;
+}
+#endif
 
 int pcp_search_launch(pcp_ctx* ctx, const SearchParams& sp) {
   KArgs a;
