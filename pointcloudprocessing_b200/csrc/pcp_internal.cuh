@@ -98,5 +98,6 @@ struct SearchParams {
   uint8_t* valid;     // per output slot: 1 when the record was computed (may be null)
   int* overflow_flag; // device int: set when a radius neighbourhood exceeded the warp buffer
 };
-int pcp_search_launch(pcp_ctx* ctx, const SearchParams& sp);
+int pcp_search_launch(pcp_ctx* ctx, const SearchParams& sp);  // radius (and the v3 warp-per-query k-NN, A/B only)
+int pcp_knn_launch(pcp_ctx* ctx, const SearchParams& sp);     // k-NN, one thread per query (knn_pca.cu)
 int pcp_carry_forward_impl(pcp_ctx* ctx, pcp_feature68* d_out, const uint8_t* d_valid, int64_t n);

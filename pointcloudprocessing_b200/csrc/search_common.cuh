@@ -11,6 +11,8 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include "pcp_internal.cuh"
+
 typedef unsigned long long u64;
 #define PCP_KEY_INF 0xFFFFFFFFFFFFFFFFull
 #define PCP_FULL 0xffffffffu
@@ -92,3 +94,31 @@ __device__ __forceinline__ void smem_sort_pow2(u64* buf, int m, int lane) {
     }
   }
 }
+
+// kernel arguments shared by the radius (search_pca.cu) and k-NN (knn_pca.cu) kernels
+struct KArgs {
+  const float4* sorted;       // cell-ordered points, .w = ord bits
+  const uint32_t* keys;       // cell id per sorted position
+  const int32_t* slot;        // output slot per sorted position (−1 = halo)
+  const uint32_t* E;          // E[c] = #points with cell id < c
+  const uint32_t* inv;        // ord -> sorted position
+  const int32_t* gid_of_ord;  // ord -> global id (null = identity)
+  GridDesc g;
+  int64_t n;
+  SearchParams sp;
+};
+
+
+// squared radius around any point of the query cell that the block of half-width R is guaranteed to cover
+__device__ __forceinline__ float cover2_of(int R, float cell) {
+  double rs = ((double)R - 1e-6) * (double)cell;
+  return (float)(rs * rs * (1.0 - 1e-6));
+}
+
+// gap (in cells, >= 0) between the query at fractional offset f of its cell and the cell d cells
+// away; gaps below 2e-3 cells count as 0 so fp rounding of f can never prune a real neighbour
+__device__ __forceinline__ float cell_gap(int d, float f) {
+  float gp = d > 0 ? (float)d - f : (d < 0 ? f - (float)d - 1.f : 0.f);
+  return gp < 2e-3f ? 0.f : gp;
+}
+

@@ -19,6 +19,7 @@
 // of ONE query, so the fp64 Jacobi work is fully lane-parallel.
 #include <cfloat>
 #include <cmath>
+#include <cstdlib>
 
 #include "eigen3.cuh"
 #include "pcp_internal.cuh"
@@ -37,18 +38,6 @@ constexpr int WARPS = 8;            // warps per CTA
 constexpr int RADIUS_CAP = 512;     // radius mode: neighbours kept per query in shared memory
 constexpr int REC_WORDS = 17;       // 68-byte record
 
-struct KArgs {
-  const float4* sorted;       // cell-ordered points, .w = ord bits
-  const uint32_t* keys;       // cell id per sorted position
-  const int32_t* slot;        // output slot per sorted position (−1 = halo)
-  const uint32_t* E;          // E[c] = #points with cell id < c
-  const uint32_t* inv;        // ord -> sorted position
-  const int32_t* gid_of_ord;  // ord -> global id (null = identity)
-  GridDesc g;
-  int64_t n;
-  SearchParams sp;
-};
-
 // shared memory of one warp; the record staging area reuses the search buffers (disjoint phases)
 template <int MODE>
 struct WarpSmem {
@@ -65,18 +54,6 @@ struct WarpSmem {
   int cnt[32];
   int gidq[32];
 };
-
-__device__ __forceinline__ float cover2_of(int R, float cell) {
-  double rs = ((double)R - 1e-6) * (double)cell;
-  return (float)(rs * rs * (1.0 - 1e-6));
-}
-
-// gap (in cells, >= 0) between the query at fractional offset f of its cell and the cell d cells
-// away; gaps below 2e-3 cells count as 0 so fp rounding of f can never prune a real neighbour
-__device__ __forceinline__ float cell_gap(int d, float f) {
-  float gp = d > 0 ? (float)d - f : (d < 0 ? f - (float)d - 1.f : 0.f);
-  return gp < 2e-3f ? 0.f : gp;
-}
 
 // Ordered second moment about (cx,cy,cz) of the m neighbours whose keys sit in list[0..m)
 // (registers for m <= 32 via `regkey`, shared memory otherwise).  Lanes 0..5 return
@@ -517,6 +494,11 @@ extern "C" __attribute__((visibility("default"))) int pcp_debug_stats(unsigned l
 #endif
 
 int pcp_search_launch(pcp_ctx* ctx, const SearchParams& sp) {
+  if (sp.mode == 0) {
+    // PCP_KNN_IMPL selects the k-NN kernel for A/B timing: "tq" = thread-per-query walk (knn_pca.cu)
+    const char* impl = getenv("PCP_KNN_IMPL");
+    if (impl && impl[0] == 't' && impl[1] == 'q') return pcp_knn_launch(ctx, sp);
+  }
   KArgs a;
   a.sorted = (const float4*)ctx->sorted_pts.p;
   a.keys = (const uint32_t*)ctx->keys_sorted.p;

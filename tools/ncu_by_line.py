@@ -5,7 +5,11 @@ src_csv, sass_txt, kname = sys.argv[1:4]
 rows = list(csv.reader(open(src_csv)))
 hdr = rows[1]
 ci = hdr.index("Instructions Executed"); cs = hdr.index("Source"); cst = hdr.index("# Samples")
-ncu = [(r[cs].strip(), int(r[ci] or 0), int(r[cst] or 0)) for r in rows[2:] if len(r) > ci]
+body = []
+for r in rows[2:]:
+    if r and r[0] == "Kernel Name": break  # a second captured launch starts here
+    body.append(r)
+ncu = [(r[cs].strip(), int(r[ci] or 0), int(r[cst] or 0)) for r in body if len(r) > ci]
 # parse nvdisasm: within the function section, track "//## File "...", line N" markers (inlined-at chains too)
 lines = open(sass_txt).read().split("\n")
 infunc = False; cur = None; sass = []; prev_marker = False
