@@ -72,9 +72,10 @@ def load() -> C.CDLL:
     global _lib
     if _lib is not None:
         return _lib
-    if not os.path.exists(LIB_PATH):
-        raise ImportError(f"{LIB_PATH} is missing: run `python -c 'import __graft_entry__ as g; g.build()'`")
-    lib = C.CDLL(LIB_PATH)
+    path = os.environ.get("PCP_LIB", LIB_PATH)  # PCP_LIB: a debug build of the same library (stats counters)
+    if not os.path.exists(path):
+        raise ImportError(f"{path} is missing: run `python -c 'import __graft_entry__ as g; g.build()'`")
+    lib = C.CDLL(path)
     vp, i32, i64, f32 = C.c_void_p, C.c_int, C.c_int64, C.c_float
     sig = {
         "pcp_create": (i32, [C.POINTER(vp), i32]),

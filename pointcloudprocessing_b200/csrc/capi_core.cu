@@ -82,7 +82,7 @@ PCP_API int pcp_destroy(pcp_ctx* ctx) {
   if (!ctx) return PCP_OK;
   cudaSetDevice(ctx->device);
   cudaStreamSynchronize(ctx->stream);
-  DevBuf* bufs[] = {&ctx->own_cloud, &ctx->bbox, &ctx->keys_in, &ctx->keys_sorted, &ctx->vals_in, &ctx->vals_sorted,
+  DevBuf* bufs[] = {&ctx->work_list, &ctx->work_count, &ctx->own_cloud, &ctx->bbox, &ctx->keys_in, &ctx->keys_sorted, &ctx->vals_in, &ctx->vals_sorted,
                     &ctx->sort_tmp, &ctx->sorted_pts, &ctx->inv_pos, &ctx->gid_sorted, &ctx->gid_tmp, &ctx->ord_of_li, &ctx->li_of_ord, &ctx->sorted_slot, &ctx->cell_end, &ctx->scan_tmp, &ctx->out_feat,
                     &ctx->out_norm, &ctx->out_idx, &ctx->out_d2, &ctx->out_counts, &ctx->flags, &ctx->valid,
                     &ctx->last_valid, &ctx->staging, &ctx->ring_range, &ctx->ring_idx, &ctx->ring_long,

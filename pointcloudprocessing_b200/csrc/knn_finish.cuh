@@ -1,0 +1,158 @@
+// knn_finish.cuh — what every k-NN kernel does once a lane holds its query's ordered neighbour list:
+// optional list / k-th distance outputs, the second moment in the reference's accumulation order
+// (pcl::computeCovarianceMatrixNormalized), the eigen-solve (eigen3.cuh), the structure
+// features (src/pcaAnalysis.cpp:29-31), the PCL-twin normal + curvature (src/smoothing.cpp:236-248),
+// and the coalesced 68-byte record write.  Must be called by all 32 lanes of the warp.
+#pragma once
+#include "eigen3.cuh"
+#include "search_common.cuh"
+
+// best[0..n_nb) = this lane's neighbours ascending by (d2, index) as keys bits(d2) << 32 | ord;
+// my_slot < 0: the lane has no query.  rec_all = 32 x 17 floats of warp-private shared memory that no
+// lane still uses for anything else.
+__device__ __forceinline__ void knn_finish(const KArgs& a, u64 (&best)[32], const int n_nb, const float4 Q, const int my_slot,
+                                           float (*rec_all)[17], const int lane) {
+  const SearchParams& sp = a.sp;
+  const int k = sp.k;
+  // ---- neighbour list -> outputs (each lane for its own query)
+  const float4* __restrict__ sorted = a.sorted;
+  const uint32_t* __restrict__ inv = a.inv;
+  const int ord_q = __float_as_int(Q.w);
+  const int gid_q = (my_slot >= 0 && a.gid_of_ord) ? __ldg(&a.gid_of_ord[ord_q]) : ord_q;
+  const bool valid = my_slot >= 0 && n_nb > 0;
+  if (my_slot >= 0) {
+    if (sp.kth_d2) {
+      // best[] is ascending, so its k-th entry is the maximum of the first k (a max-reduction keeps
+      // best[] in registers; an indexed read would push the whole array to local memory)
+      u64 kth = 0;
+#pragma unroll
+      for (int j = 0; j < 32; ++j)
+        if (j < k && best[j] > kth) kth = best[j];
+      sp.kth_d2[my_slot] = n_nb >= k ? __uint_as_float((uint32_t)(kth >> 32)) : INFINITY;
+    }
+    if (sp.nn_idx != nullptr) {
+      const int64_t o = (int64_t)my_slot * k;
+#pragma unroll
+      for (int j = 0; j < 32; ++j) {
+        if (j < k) {
+          const bool has = j < n_nb;
+          const int ord = (int)(uint32_t)best[j];
+          sp.nn_idx[o + j] = has ? (a.gid_of_ord ? __ldg(&a.gid_of_ord[ord]) : ord) : -1;
+          if (sp.nn_d2) sp.nn_d2[o + j] = has ? __uint_as_float((uint32_t)(best[j] >> 32)) : INFINITY;
+        }
+      }
+    }
+  }
+  const bool need_q = sp.out != nullptr && sp.center_mode == PCP_CENTER_QUERY;
+  const bool need_m = sp.normals != nullptr || (sp.out != nullptr && sp.center_mode == PCP_CENTER_MEAN);
+  float mq[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f}, mm[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  if (valid && (need_q || need_m)) {
+    // sorted positions of the neighbours, in list order (the moment re-reads coordinates from them)
+    uint32_t npos[32];
+#pragma unroll
+    for (int j = 0; j < 32; ++j) npos[j] = j < n_nb ? __ldg(&inv[(uint32_t)best[j]]) : 0u;
+    const float fn = (float)n_nb;
+    if (need_q) {
+      // pcl::computeCovarianceMatrixNormalized about the query: six fp32 chains in list order
+#pragma unroll
+      for (int j = 0; j < 32; ++j) {
+        if (j < n_nb) {
+          const float4 P = __ldg(&sorted[npos[j]]);
+          const float px = __fsub_rn(P.x, Q.x), py = __fsub_rn(P.y, Q.y), pz = __fsub_rn(P.z, Q.z);
+          mq[0] = __fadd_rn(mq[0], __fmul_rn(px, px));
+          mq[1] = __fadd_rn(mq[1], __fmul_rn(py, px));
+          mq[2] = __fadd_rn(mq[2], __fmul_rn(pz, px));
+          mq[3] = __fadd_rn(mq[3], __fmul_rn(py, py));
+          mq[4] = __fadd_rn(mq[4], __fmul_rn(py, pz));
+          mq[5] = __fadd_rn(mq[5], __fmul_rn(pz, pz));
+        }
+      }
+#pragma unroll
+      for (int c = 0; c < 6; ++c) mq[c] = __fdiv_rn(mq[c], fn);
+    }
+    if (need_m) {
+      // pcl::compute3DCentroid (fp32 running sums in list order), then the moment about it
+      float sx = 0.f, sy = 0.f, sz = 0.f;
+#pragma unroll
+      for (int j = 0; j < 32; ++j) {
+        if (j < n_nb) {
+          const float4 P = __ldg(&sorted[npos[j]]);
+          sx = __fadd_rn(sx, P.x);
+          sy = __fadd_rn(sy, P.y);
+          sz = __fadd_rn(sz, P.z);
+        }
+      }
+      const float cx = __fdiv_rn(sx, fn), cy = __fdiv_rn(sy, fn), cz = __fdiv_rn(sz, fn);
+#pragma unroll
+      for (int j = 0; j < 32; ++j) {
+        if (j < n_nb) {
+          const float4 P = __ldg(&sorted[npos[j]]);
+          const float px = __fsub_rn(P.x, cx), py = __fsub_rn(P.y, cy), pz = __fsub_rn(P.z, cz);
+          mm[0] = __fadd_rn(mm[0], __fmul_rn(px, px));
+          mm[1] = __fadd_rn(mm[1], __fmul_rn(py, px));
+          mm[2] = __fadd_rn(mm[2], __fmul_rn(pz, px));
+          mm[3] = __fadd_rn(mm[3], __fmul_rn(py, py));
+          mm[4] = __fadd_rn(mm[4], __fmul_rn(py, pz));
+          mm[5] = __fadd_rn(mm[5], __fmul_rn(pz, pz));
+        }
+      }
+#pragma unroll
+      for (int c = 0; c < 6; ++c) mm[c] = __fdiv_rn(mm[c], fn);
+    }
+  }
+
+  // ---- eigen + features, staged as 68-byte records (the search columns are dead now)
+  __syncwarp();
+  if (my_slot >= 0) {
+    float* rec = rec_all[lane];
+#pragma unroll
+    for (int w = 0; w < 17; ++w) rec[w] = 0.f;
+    rec[12] = __int_as_float(gid_q);
+    rec[13] = __int_as_float(n_nb);
+    Sym3Eig eq;
+    bool have_q = false;
+    if (valid && sp.out != nullptr) {
+      sym3_eigen(sp.center_mode == PCP_CENTER_QUERY ? mq : mm, eq);
+      have_q = true;
+      rec[0] = eq.val[0]; rec[1] = eq.val[1]; rec[2] = eq.val[2];
+#pragma unroll
+      for (int c = 0; c < 3; ++c)
+#pragma unroll
+        for (int r = 0; r < 3; ++r) rec[3 + 3 * c + r] = eq.vec[c][r];
+      // src/pcaAnalysis.cpp:29-31 in fp32 on the ascending eigenvalues
+      const float s1 = __fsqrt_rn(eq.val[0]), s2 = __fsqrt_rn(eq.val[1]), s3 = __fsqrt_rn(eq.val[2]);
+      rec[14] = __fdiv_rn(__fsub_rn(s1, s2), s1);
+      rec[15] = __fdiv_rn(__fsub_rn(s2, s3), s1);
+      rec[16] = __fdiv_rn(s3, s1);
+    }
+    if (sp.normals != nullptr) {
+      pcp_normal16 nrm;
+      if (!valid || n_nb < 3) {
+        nrm.nx = nrm.ny = nrm.nz = nrm.curvature = __int_as_float(0x7FC00000);
+      } else {
+        Sym3Eig em;
+        if (have_q && sp.center_mode == PCP_CENTER_MEAN) em = eq;
+        else sym3_eigen(mm, em);
+        const float tr = mm[0] + mm[3] + mm[5];
+        float nx = em.vec[0][0], ny = em.vec[0][1], nz = em.vec[0][2];
+        // flipNormalTowardsViewpoint with viewpoint (0,0,0)
+        const float cs = (0.f - Q.x) * nx + (0.f - Q.y) * ny + (0.f - Q.z) * nz;
+        if (cs < 0.f) { nx = -nx; ny = -ny; nz = -nz; }
+        nrm.nx = nx; nrm.ny = ny; nrm.nz = nz;
+        nrm.curvature = tr != 0.f ? fabsf(em.val[0] / tr) : 0.f;
+      }
+      sp.normals[my_slot] = nrm;
+    }
+    if (sp.valid) sp.valid[my_slot] = valid ? 1 : 0;
+  }
+  __syncwarp();
+  // ---- lanes 0..16 write one contiguous 68-byte record per step
+  if (sp.out != nullptr) {
+    float* outw = reinterpret_cast<float*>(sp.out);
+#pragma unroll 4
+    for (int r = 0; r < 32; ++r) {
+      const int s = __shfl_sync(PCP_FULL, my_slot, r);
+      if (s >= 0 && lane < 17) outw[(int64_t)s * 17 + lane] = rec_all[r][lane];
+    }
+  }
+}

@@ -1,0 +1,310 @@
+// knn_tile.cu — k-NN + PCA fast path: one warp per TILE of 32 consecutive cell-sorted queries, the
+// tile's candidate set staged ONCE in shared memory, one lane per query, uniform control flow.
+//
+// Replaces, per point, nearestKSearch + computeCovarianceMatrixNormalized + SelfAdjointEigenSolver
+// + the structure features (src/smoothing.cpp:239-246, src/pcaAnalysis.cpp:44-87, :29-31).
+//
+// The 32 queries of a tile lie in one stencil row of the grid (consecutive points of the cell-sorted
+// array), so the union of their (2R+1)^3 stencils is (2R+1)^2 contiguous runs of that array.  The warp
+// copies those runs into shared memory as float4 (coalesced global reads, every point read once per
+// tile instead of once per query) and then every lane runs the SAME loop over the staged candidates
+// (broadcast LDS.128, no divergence, unrolled):
+//   pass 1  d2 (FLANN L2_Simple arithmetic, no FMA) -> 64 linear bins over [0, cover^2) in the lane's
+//           own histogram column (bin 64 = beyond the radius the stencil is guaranteed to cover);
+//   scan    the bin holding the k-th smallest; the lane succeeds when that bin is inside the cover
+//           radius and at most 32 candidates lie at or below it;
+//   pass 2  candidates at or below the bin are appended as keys bits(d2)<<32 | ord to the lane's column;
+//   sort    32-input odd-even merge network on registers -> the (d2, index) order of the reference;
+//   then the ordered moment, the fp64 Jacobi eigen-solve and the 68-byte record, all per lane.
+// Lanes that do not succeed (sparse neighbourhood: k-th neighbour beyond the cover radius; a tile that
+// crosses a row end; an over-full bin) are appended to a work list that the warp-per-query kernel of
+// search_pca.cu finishes with its expanding-shell search.  Results are identical either way.
+#include <cfloat>
+#include <cmath>
+#include <cstdlib>
+
+#include "eigen3.cuh"
+#include "pcp_internal.cuh"
+#include "search_common.cuh"
+#include "knn_finish.cuh"
+
+#ifdef PCP_STATS
+__device__ unsigned long long g_tile_stats[16];
+#define TSTAT(i, v) atomicAdd(&g_tile_stats[i], (unsigned long long)(v))
+#else
+#define TSTAT(i, v) do { } while (0)
+#endif
+
+namespace {
+
+constexpr int TA_WARPS = 4;        // warps per CTA
+constexpr int TA_CH = 256;         // staged candidates per chunk
+constexpr int TA_BINS = 64;        // linear d2 bins inside the cover radius (+1 overflow bin)
+constexpr int TA_CAP = 32;         // candidates a lane can hold (sorting-network width)
+constexpr int TA_REC_WORDS = 17;   // 68-byte record
+constexpr int TA_MAXROWS = 64;     // stencil rows of a tile: (2R+1)^2 <= 49, R <= 3
+
+struct __align__(16) TaSmem {
+  float4 cand[TA_CH];                    // staged candidates of the current chunk
+  union U {
+    uint32_t hist[TA_BINS + 1][32];      // pass 1: hist[bin][lane]
+    u64 pend[TA_CAP][32];                // pass 2: pend[j][lane]
+    float rec[32][TA_REC_WORDS];         // record staging
+  } u;
+  uint32_t run_beg[TA_MAXROWS];          // first sorted position of each stencil row's run
+  uint32_t run_off[TA_MAXROWS + 1];      // exclusive prefix of the run lengths
+};
+
+// fractional position of Q inside its cell c along the x/y/z axis `ax`, clamped to [0,1] (same double
+// arithmetic as the key kernel; selects instead of dynamic indexing keep the arguments in the constant bank)
+__device__ __forceinline__ float frac_of(const GridDesc& g, int ax, const float4 Q, int c) {
+  const double v = ax == 0 ? (double)Q.x : (ax == 1 ? (double)Q.y : (double)Q.z);
+  const double o = ax == 0 ? g.origin[0] : (ax == 1 ? g.origin[1] : g.origin[2]);
+  return fminf(fmaxf((float)((v - o) * g.inv_cell - (double)c), 0.f), 1.f);
+}
+
+// copies candidates [cb, cb + cnt) of the tile's virtual candidate sequence (the stencil rows' runs laid
+// end to end) into sm.cand: row by row, the 32 lanes reading consecutive float4 of the run
+__device__ __forceinline__ void stage_chunk(const float4* __restrict__ sorted, TaSmem& sm, int nrows, uint32_t cb, int cnt,
+                                            int lane) {
+  const uint32_t ce = cb + (uint32_t)cnt;
+#pragma unroll 1
+  for (int r = 0; r < nrows; ++r) {
+    const uint32_t off = sm.run_off[r], end = sm.run_off[r + 1];
+    const uint32_t lo = max(off, cb), hi = min(end, ce);
+    if (lo >= hi) continue;
+    const float4* __restrict__ src = sorted + sm.run_beg[r] - off;  // src[v] = candidate v
+#pragma unroll 1
+    for (uint32_t v = lo + (uint32_t)lane; v < hi; v += 32) sm.cand[v - cb] = __ldg(&src[v]);
+  }
+  __syncwarp();
+}
+
+__global__ void __launch_bounds__(TA_WARPS * 32) knn_tile_kernel(KArgs a, int R0, float grow, uint32_t* __restrict__ work_count,
+                                                                 uint32_t* __restrict__ work_list) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  TaSmem& sm = reinterpret_cast<TaSmem*>(smem_raw)[threadIdx.x >> 5];
+  const int lane = threadIdx.x & 31;
+  const int64_t pos0 = ((int64_t)blockIdx.x * TA_WARPS + (threadIdx.x >> 5)) * 32;
+  if (pos0 >= a.n) return;  // whole warp
+  const int64_t p = pos0 + lane;
+  const GridDesc& g = a.g;
+  const SearchParams& sp = a.sp;
+  const float4* __restrict__ sorted = a.sorted;
+  const int k = sp.k;
+  const int my_slot = p < a.n ? __ldg(&a.slot[p]) : -1;  // -1: tail lane or halo point (neighbour only)
+  const float4 Q = p < a.n ? __ldg(&sorted[p]) : make_float4(0.f, 0.f, 0.f, 0.f);
+  const uint32_t cid = p < a.n ? __ldg(&a.keys[p]) : g.n_cells;
+  const bool active = my_slot >= 0;
+  const bool finite = active && cid < g.n_cells;
+  uint32_t* const hcol = &sm.u.hist[0][lane];
+  u64* const pcol = &sm.u.pend[0][lane];
+
+  // ---- tile geometry: the stencil row of the first searchable lane; lanes of other rows are deferred
+  const unsigned fin_mask = __ballot_sync(PCP_FULL, finite);
+  bool ok = false;
+  int nrows = 0, R = R0;
+  float cover_cells = 1.f;
+  uint32_t total = 0;
+  if (fin_mask != 0) {
+    const uint32_t cid0 = __shfl_sync(PCP_FULL, cid, __ffs(fin_mask) - 1);
+    const uint32_t row0 = cid0 / (uint32_t)g.dim[0];
+    const bool in_row = finite && cid / (uint32_t)g.dim[0] == row0;
+    const int c0 = (int)(cid - row0 * (uint32_t)g.dim[0]);
+    const int c1 = (int)(row0 % (uint32_t)g.dim[1]), c2 = (int)(row0 / (uint32_t)g.dim[1]);
+    const int c0min = __reduce_min_sync(PCP_FULL, in_row ? c0 : 0x7fffffff);
+    const int c0max = __reduce_max_sync(PCP_FULL, in_row ? c0 : -1);
+    // Stencil half-width of the tile: the smallest R (<= 3) whose union of cells is expected to hold k
+    // points inside the cover radius R*cell (flat-density guess: disk area / union area).  A wrong
+    // guess costs time, never correctness: lanes whose k-th neighbour is not covered are deferred.
+    const int span = c0max - c0min + 1;
+    uint32_t beg0 = 0, len0 = 0, beg1 = 0, len1 = 0, off0 = 0, off1 = 0;
+#pragma unroll 1
+    for (;;) {
+      const int xlo = max(c0min - R, 0), xhi = min(c0max + R, g.dim[0] - 1);
+      const int lo1 = max(c1 - R, 0), n1 = min(c1 + R, g.dim[1] - 1) - lo1 + 1;
+      const int lo2 = max(c2 - R, 0), n2 = min(c2 + R, g.dim[2] - 1) - lo2 + 1;
+      nrows = n1 * n2;
+      beg0 = len0 = beg1 = len1 = 0;
+      if (lane < nrows) {
+        const int o2 = lane / n1, o1 = lane - o2 * n1;
+        const uint32_t base = ((uint32_t)(lo2 + o2) * (uint32_t)g.dim[1] + (uint32_t)(lo1 + o1)) * (uint32_t)g.dim[0];
+        beg0 = __ldg(&a.E[base + xlo]);
+        len0 = __ldg(&a.E[base + xhi + 1]) - beg0;
+      }
+      if (lane + 32 < nrows) {
+        const int o2 = (lane + 32) / n1, o1 = (lane + 32) - o2 * n1;
+        const uint32_t base = ((uint32_t)(lo2 + o2) * (uint32_t)g.dim[1] + (uint32_t)(lo1 + o1)) * (uint32_t)g.dim[0];
+        beg1 = __ldg(&a.E[base + xlo]);
+        len1 = __ldg(&a.E[base + xhi + 1]) - beg1;
+      }
+      uint32_t inc0 = len0, inc1 = len1;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t t0 = __shfl_up_sync(PCP_FULL, inc0, o), t1 = __shfl_up_sync(PCP_FULL, inc1, o);
+        if (lane >= o) {
+          inc0 += t0;
+          inc1 += t1;
+        }
+      }
+      const uint32_t tot0 = __shfl_sync(PCP_FULL, inc0, 31);
+      total = tot0 + __shfl_sync(PCP_FULL, inc1, 31);
+      off0 = inc0 - len0;
+      off1 = tot0 + inc1 - len1;
+      const bool whole = xlo == 0 && xhi == g.dim[0] - 1 && n1 == g.dim[1] && n2 == g.dim[2];
+      const float frac = 3.14159f * (float)(R * R) / (float)((span + 2 * R) * (2 * R + 1));
+      if (R >= 3 || whole || (float)total * frac >= grow * (float)k) break;
+      ++R;
+    }
+    {
+      const int xlo = max(c0min - R, 0), xhi = min(c0max + R, g.dim[0] - 1);
+      const float f0 = frac_of(g, g.ax[0], Q, c0), f1 = frac_of(g, g.ax[1], Q, c1), f2 = frac_of(g, g.ax[2], Q, c2);
+      const float inf = 3.0e18f;
+      const float m0a = xlo > 0 ? (float)(c0 - xlo) + f0 : inf, m0b = xhi < g.dim[0] - 1 ? (float)(xhi + 1 - c0) - f0 : inf;
+      const float m1a = c1 - R > 0 ? (float)R + f1 : inf, m1b = c1 + R < g.dim[1] - 1 ? (float)(R + 1) - f1 : inf;
+      const float m2a = c2 - R > 0 ? (float)R + f2 : inf, m2b = c2 + R < g.dim[2] - 1 ? (float)(R + 1) - f2 : inf;
+      cover_cells = fminf(fminf(fminf(m0a, m0b), fminf(m1a, m1b)), fminf(m2a, m2b)) - 2e-3f;
+    }
+    sm.run_beg[lane] = beg0;
+    sm.run_off[lane] = off0;
+    sm.run_beg[lane + 32] = beg1;
+    sm.run_off[lane + 32] = off1;
+    ok = in_row;
+  }
+  __syncwarp();
+
+  // ---- pass 1: histogram of d2 over the staged candidates
+  // Radius around THIS query that the union of cells is guaranteed to cover: its distance to the
+  // nearest face of the union block that still has cells behind it (a face on the grid boundary has no
+  // points beyond it), minus 2e-3 cells for the rounding of the fractional position.
+  const float cover2 = cover_cells * cover_cells * g.cell * g.cell * (1.f - 1e-6f);
+  const float Sb = (float)TA_BINS / cover2;
+#pragma unroll
+  for (int b = 0; b <= TA_BINS; ++b) hcol[b * 32] = 0;
+  const bool resident = total <= (uint32_t)TA_CH;  // one chunk: staged once, used by both passes
+#pragma unroll 1
+  for (uint32_t cb = 0; cb < total; cb += TA_CH) {
+    const int cnt = (int)min((uint32_t)TA_CH, total - cb);
+    stage_chunk(sorted, sm, nrows, cb, cnt, lane);
+    // four candidates per step: the loads and the distance arithmetic of a group are independent, and
+    // the histogram update is a fire-and-forget shared atomic (own column: no conflicts, no read-back)
+    int j = 0;
+#pragma unroll 1
+    for (; j + 4 <= cnt; j += 4) {
+      const float4 P0 = sm.cand[j], P1 = sm.cand[j + 1], P2 = sm.cand[j + 2], P3 = sm.cand[j + 3];
+      const int b0 = __float2int_rz(fminf(dist2_nofma(Q.x, Q.y, Q.z, P0) * Sb, (float)TA_BINS));
+      const int b1 = __float2int_rz(fminf(dist2_nofma(Q.x, Q.y, Q.z, P1) * Sb, (float)TA_BINS));
+      const int b2 = __float2int_rz(fminf(dist2_nofma(Q.x, Q.y, Q.z, P2) * Sb, (float)TA_BINS));
+      const int b3 = __float2int_rz(fminf(dist2_nofma(Q.x, Q.y, Q.z, P3) * Sb, (float)TA_BINS));
+      atomicAdd(&hcol[b0 * 32], 1u);
+      atomicAdd(&hcol[b1 * 32], 1u);
+      atomicAdd(&hcol[b2 * 32], 1u);
+      atomicAdd(&hcol[b3 * 32], 1u);
+    }
+    for (; j < cnt; ++j) {
+      const int b0 = __float2int_rz(fminf(dist2_nofma(Q.x, Q.y, Q.z, sm.cand[j]) * Sb, (float)TA_BINS));
+      atomicAdd(&hcol[b0 * 32], 1u);
+    }
+    __syncwarp();
+  }
+  // ---- the bin holding the k-th smallest, and how many candidates lie at or below it
+  int cum = 0, bstar = -1, cum_star = 0;
+#pragma unroll 8
+  for (int b = 0; b < TA_BINS; ++b) {
+    cum += (int)hcol[b * 32];
+    if (bstar < 0 && cum >= k) {
+      bstar = b;
+      cum_star = cum;
+    }
+  }
+  TSTAT(4, (finite && !ok) ? 1 : 0);                              // deferred: other stencil row
+  TSTAT(5, (ok && bstar < 0) ? 1 : 0);                            // deferred: k-th beyond the cover radius
+  TSTAT(6, (ok && bstar >= 0 && cum_star > TA_CAP) ? 1 : 0);      // deferred: threshold bin too full
+  ok = ok && bstar >= 0 && cum_star <= TA_CAP;
+  // a lane that is not ok collects nothing; it goes to the work list below
+  const float thr_bin = ok ? (float)(bstar + 1) : -1.f;
+  __syncwarp();
+
+  // ---- pass 2: collect the candidates at or below the threshold bin (same d2 arithmetic, same bins)
+  u64* wp = pcol;  // next free entry of this lane's column
+#pragma unroll 1
+  for (uint32_t cb = 0; cb < total; cb += TA_CH) {
+    const int n_ch = (int)min((uint32_t)TA_CH, total - cb);
+    if (!resident) stage_chunk(sorted, sm, nrows, cb, n_ch, lane);
+    int j = 0;
+#pragma unroll 1
+    for (; j + 4 <= n_ch; j += 4) {
+      const float4 P0 = sm.cand[j], P1 = sm.cand[j + 1], P2 = sm.cand[j + 2], P3 = sm.cand[j + 3];
+      const float e0 = dist2_nofma(Q.x, Q.y, Q.z, P0), e1 = dist2_nofma(Q.x, Q.y, Q.z, P1);
+      const float e2 = dist2_nofma(Q.x, Q.y, Q.z, P2), e3 = dist2_nofma(Q.x, Q.y, Q.z, P3);
+      if (e0 * Sb < thr_bin) { *wp = ((u64)__float_as_uint(e0) << 32) | (u64)__float_as_uint(P0.w); wp += 32; }
+      if (e1 * Sb < thr_bin) { *wp = ((u64)__float_as_uint(e1) << 32) | (u64)__float_as_uint(P1.w); wp += 32; }
+      if (e2 * Sb < thr_bin) { *wp = ((u64)__float_as_uint(e2) << 32) | (u64)__float_as_uint(P2.w); wp += 32; }
+      if (e3 * Sb < thr_bin) { *wp = ((u64)__float_as_uint(e3) << 32) | (u64)__float_as_uint(P3.w); wp += 32; }
+    }
+    for (; j < n_ch; ++j) {
+      const float4 P0 = sm.cand[j];
+      const float e0 = dist2_nofma(Q.x, Q.y, Q.z, P0);
+      if (e0 * Sb < thr_bin) { *wp = ((u64)__float_as_uint(e0) << 32) | (u64)__float_as_uint(P0.w); wp += 32; }
+    }
+    __syncwarp();
+  }
+  const int cnt = (int)(wp - pcol) >> 5;
+  TSTAT(0, finite ? 1 : 0);
+  TSTAT(1, (finite && !ok) ? 1 : 0);
+  TSTAT(2, lane == 0 ? total : 0);
+  TSTAT(3, ok ? cnt : 0);
+  // ---- deferred lanes -> work list (sorted positions), finished by the expanding-shell kernel
+  {
+    const bool defer = finite && !ok;
+    const unsigned dm = __ballot_sync(PCP_FULL, defer);
+    if (dm != 0) {
+      uint32_t base = 0;
+      if (lane == 0) base = atomicAdd(work_count, (uint32_t)__popc(dm));
+      base = __shfl_sync(PCP_FULL, base, 0);
+      if (defer) work_list[base + __popc(dm & ((1u << lane) - 1u))] = (uint32_t)p;
+    }
+  }
+  // ---- order the collected keys by (d2, index)
+  u64 best[TA_CAP];
+#pragma unroll
+  for (int j = 0; j < TA_CAP; ++j) best[j] = j < cnt ? pcol[j * 32] : PCP_KEY_INF;
+  sort32_regs(best);
+  const int n_nb = ok ? k : 0;
+  const bool emit = active && (ok || !finite);  // non-finite queries get their empty record here
+  __syncwarp();
+  knn_finish(a, best, n_nb, Q, emit ? my_slot : -1, sm.u.rec, lane);
+}
+
+}  // namespace
+
+#ifdef PCP_STATS
+extern "C" __attribute__((visibility("default"))) int pcp_debug_tile_stats(unsigned long long* out) {
+  unsigned long long z[16] = {0};
+  cudaDeviceSynchronize();
+  cudaMemcpyFromSymbol(out, g_tile_stats, sizeof(z));
+  cudaMemcpyToSymbol(g_tile_stats, z, sizeof(z));
+  return 0;
+}
+#endif
+
+// Launches the tile kernel over the whole cloud; deferred queries are left in ctx->work_list /
+// ctx->work_count (device) for pcp_search_launch_worklist.
+int pcp_knn_tile_launch(pcp_ctx* ctx, const SearchParams& sp, const KArgs& a) {
+  int rc;
+  if ((rc = pcp_reserve(ctx, ctx->work_list, (size_t)ctx->n * sizeof(uint32_t)))) return rc;
+  if ((rc = pcp_reserve(ctx, ctx->work_count, sizeof(uint32_t)))) return rc;
+  PCP_CUDA(cudaMemsetAsync(ctx->work_count.p, 0, sizeof(uint32_t), ctx->stream));
+  const int64_t tiles = (ctx->n + 31) / 32;
+  const int blocks = (int)((tiles + TA_WARPS - 1) / TA_WARPS);
+  const size_t smem = sizeof(TaSmem) * TA_WARPS;
+  PCP_CUDA(cudaFuncSetAttribute(knn_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  // the stencil of a tile grows while the expected number of points inside its cover radius is below
+  // grow*k (tuning hook: PCP_KNN_RGROW)
+  float grow = 0.f;  // measured on the urban cloud: growing wide sparse tiles costs more than deferring their lanes
+  if (const char* e = getenv("PCP_KNN_RGROW")) grow = (float)atof(e);
+  knn_tile_kernel<<<blocks, TA_WARPS * 32, smem, ctx->stream>>>(a, sp.R0, grow, (uint32_t*)ctx->work_count.p,
+                                                                 (uint32_t*)ctx->work_list.p);
+  PCP_LAUNCH_CHECK("knn_tile_kernel");
+  return PCP_OK;
+}

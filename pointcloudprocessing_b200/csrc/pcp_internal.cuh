@@ -55,6 +55,7 @@ struct pcp_ctx {
   DevBuf scan_tmp;
 
   // outputs / scratch
+  DevBuf work_list, work_count;  // k-NN queries deferred by the tile kernel (sorted positions)
   DevBuf out_feat, out_norm, out_idx, out_d2, out_counts, flags, valid, last_valid, staging;
   DevBuf ring_range, ring_idx, ring_long, ring_offsets, ring_key;
 };
@@ -99,5 +100,7 @@ struct SearchParams {
   int* overflow_flag; // device int: set when a radius neighbourhood exceeded the warp buffer
 };
 int pcp_search_launch(pcp_ctx* ctx, const SearchParams& sp);  // radius (and the v3 warp-per-query k-NN, A/B only)
+struct KArgs;
+int pcp_knn_tile_launch(pcp_ctx* ctx, const SearchParams& sp, const KArgs& a);  // k-NN tile kernel (knn_tile.cu)
 int pcp_knn_launch(pcp_ctx* ctx, const SearchParams& sp);     // k-NN, one thread per query (knn_pca.cu)
 int pcp_carry_forward_impl(pcp_ctx* ctx, pcp_feature68* d_out, const uint8_t* d_valid, int64_t n);

@@ -122,3 +122,5 @@ __device__ __forceinline__ float cell_gap(int d, float f) {
   return gp < 2e-3f ? 0.f : gp;
 }
 
+
+#include "sortnet32.cuh"

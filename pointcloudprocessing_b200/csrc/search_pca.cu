@@ -246,33 +246,28 @@ __device__ __forceinline__ void scan_shell(const KArgs& a, WarpSmem<MODE>* ws, S
   }
 }
 
+// One tile: lane l holds the sorted position `my_pos` of query l (valid for l < nq); the warp solves the
+// nq queries one after the other and writes their outputs.
 template <int MODE>
-__global__ void __launch_bounds__(WARPS * 32) search_pca_kernel(KArgs a) {
-  extern __shared__ __align__(16) unsigned char smem_raw[];
-  WarpSmem<MODE>* ws = reinterpret_cast<WarpSmem<MODE>*>(smem_raw) + (threadIdx.x >> 5);
-  const int lane = threadIdx.x & 31;
-  const int64_t tile = (int64_t)blockIdx.x * WARPS + (threadIdx.x >> 5);
-  const int64_t pos0 = tile * 32;
-  if (pos0 >= a.n) return;
+__device__ __forceinline__ void search_tile(const KArgs& a, WarpSmem<MODE>* ws, const int lane, const int64_t my_pos, const int nq) {
   const float4* __restrict__ sorted = a.sorted;
   const GridDesc& g = a.g;
   const SearchParams& sp = a.sp;
   const bool need_q = sp.out != nullptr && sp.center_mode == PCP_CENTER_QUERY;
   const bool need_m = sp.normals != nullptr || (sp.out != nullptr && sp.center_mode == PCP_CENTER_MEAN);
-  const int nq = (int)min((int64_t)32, a.n - pos0);
-  const int my_slot = lane < nq ? a.slot[pos0 + lane] : -1;
+  const int my_slot = lane < nq ? a.slot[my_pos] : -1;
   const uint32_t dirs = bitonic_dirs(lane);
   const int max_dim = max(g.dim[0], max(g.dim[1], g.dim[2]));
   // lane j remembers query j of the tile and, once solved, its k-th distance: later queries seed
   // their threshold from them (triangle inequality: d_k(q) <= d_k(q_j) + |q − q_j|)
-  const float4 myP = lane < nq ? __ldg(&sorted[pos0 + lane]) : make_float4(0.f, 0.f, 0.f, 0.f);
+  const float4 myP = lane < nq ? __ldg(&sorted[my_pos]) : make_float4(0.f, 0.f, 0.f, 0.f);
   float my_dk = 3.4e38f;
 
 #pragma unroll 1
   for (int q = 0; q < nq; ++q) {
     const int slot_q = __shfl_sync(PCP_FULL, my_slot, q);
     if (slot_q < 0) continue;  // halo point: neighbour only
-    const int64_t pq = pos0 + q;
+    const int64_t pq = __shfl_sync(PCP_FULL, my_pos, q);
     STAT(0, 1);
     const float4 Q = __ldg(&sorted[pq]);
     const uint32_t cid = __ldg(&a.keys[pq]);
@@ -458,7 +453,7 @@ __global__ void __launch_bounds__(WARPS * 32) search_pca_kernel(KArgs a) {
         else sym3_eigen(ws->momM[lane], em);
         const float* M = ws->momM[lane];
         float tr = M[0] + M[3] + M[5];
-        float4 P = __ldg(&sorted[pos0 + lane]);
+        float4 P = myP;
         float nx = em.vec[0][0], ny = em.vec[0][1], nz = em.vec[0][2];
         // flipNormalTowardsViewpoint with viewpoint (0,0,0)
         float cs = (0.f - P.x) * nx + (0.f - P.y) * ny + (0.f - P.z) * nz;
@@ -481,6 +476,36 @@ __global__ void __launch_bounds__(WARPS * 32) search_pca_kernel(KArgs a) {
   }
 }
 
+// every point of the cloud: tile t = sorted positions [32 t, 32 t + 32)
+template <int MODE>
+__global__ void __launch_bounds__(WARPS * 32, 3) search_pca_kernel(KArgs a) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  WarpSmem<MODE>* ws = reinterpret_cast<WarpSmem<MODE>*>(smem_raw) + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  const int64_t pos0 = ((int64_t)blockIdx.x * WARPS + (threadIdx.x >> 5)) * 32;
+  if (pos0 >= a.n) return;
+  search_tile<MODE>(a, ws, lane, pos0 + lane, (int)min((int64_t)32, a.n - pos0));
+}
+
+// the queries a faster kernel deferred: work_list[0 .. *work_count) are sorted positions; warps take
+// tiles of 32 list entries grid-stride (the count is only known on the device)
+template <int MODE>
+__global__ void __launch_bounds__(WARPS * 32, 3) search_pca_worklist_kernel(KArgs a, const uint32_t* __restrict__ work_count,
+                                                                         const uint32_t* __restrict__ work_list) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  WarpSmem<MODE>* ws = reinterpret_cast<WarpSmem<MODE>*>(smem_raw) + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  const int64_t n_items = (int64_t)*work_count;
+  const int64_t stride = (int64_t)gridDim.x * WARPS * 32;
+#pragma unroll 1
+  for (int64_t i0 = ((int64_t)blockIdx.x * WARPS + (threadIdx.x >> 5)) * 32; i0 < n_items; i0 += stride) {
+    const int nq = (int)min((int64_t)32, n_items - i0);
+    const int64_t my_pos = lane < nq ? (int64_t)work_list[i0 + lane] : 0;
+    search_tile<MODE>(a, ws, lane, my_pos, nq);
+    __syncwarp();
+  }
+}
+
 }  // namespace
 
 #ifdef PCP_STATS
@@ -494,11 +519,13 @@ extern "C" __attribute__((visibility("default"))) int pcp_debug_stats(unsigned l
 #endif
 
 int pcp_search_launch(pcp_ctx* ctx, const SearchParams& sp) {
-  if (sp.mode == 0) {
-    // PCP_KNN_IMPL selects the k-NN kernel for A/B timing: "tq" = thread-per-query walk (knn_pca.cu)
-    const char* impl = getenv("PCP_KNN_IMPL");
-    if (impl && impl[0] == 't' && impl[1] == 'q') return pcp_knn_launch(ctx, sp);
-  }
+  // PCP_KNN_IMPL selects the k-NN kernel for A/B timing: default = tile kernel (knn_tile.cu) + this
+  // file's warp-per-query kernel for the queries it defers; "v3" = warp-per-query for every point;
+  // "tq" = thread-per-query walk (knn_pca.cu).  All three give identical results.
+  const char* impl = getenv("PCP_KNN_IMPL");
+  const bool use_tq = sp.mode == 0 && impl && impl[0] == 't' && impl[1] == 'q';
+  const bool use_v3 = sp.mode == 0 && impl && impl[0] == 'v' && impl[1] == '3';
+  if (use_tq) return pcp_knn_launch(ctx, sp);
   KArgs a;
   a.sorted = (const float4*)ctx->sorted_pts.p;
   a.keys = (const uint32_t*)ctx->keys_sorted.p;
@@ -512,7 +539,15 @@ int pcp_search_launch(pcp_ctx* ctx, const SearchParams& sp) {
   const int64_t tiles = (ctx->n + 31) / 32;
   const int blocks = (int)((tiles + WARPS - 1) / WARPS);
   pcp_tic(ctx, PCP_T_SEARCH_PCA);
-  if (sp.mode == 0) {
+  if (sp.mode == 0 && !use_v3) {
+    int rc = pcp_knn_tile_launch(ctx, sp, a);
+    if (rc) return rc;
+    size_t smem = sizeof(WarpSmem<0>) * WARPS;
+    PCP_CUDA(cudaFuncSetAttribute(search_pca_worklist_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const int wl_blocks = blocks < 148 * 4 ? blocks : 148 * 4;
+    search_pca_worklist_kernel<0><<<wl_blocks, WARPS * 32, smem, ctx->stream>>>(a, (const uint32_t*)ctx->work_count.p,
+                                                                                (const uint32_t*)ctx->work_list.p);
+  } else if (sp.mode == 0) {
     size_t smem = sizeof(WarpSmem<0>) * WARPS;
     PCP_CUDA(cudaFuncSetAttribute(search_pca_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     search_pca_kernel<0><<<blocks, WARPS * 32, smem, ctx->stream>>>(a);
