@@ -43,13 +43,19 @@ constexpr int TA_BINS = 64;        // linear d2 bins inside the cover radius (+1
 constexpr int TA_CAP = 32;         // candidates a lane can hold (sorting-network width)
 constexpr int TA_REC_WORDS = 17;   // 68-byte record
 constexpr int TA_MAXROWS = 64;     // stencil rows of a tile: (2R+1)^2 <= 49, R <= 3
+constexpr int TA_MAXR = 3;
+constexpr int TA_MAXGROUPS = 1;    // stencil rows (row groups) served per tile by default; lanes of further rows are
+                                   // deferred (measured: a second pass for a few lanes costs more than deferring them)
 
 struct __align__(16) TaSmem {
   float4 cand[TA_CH];                    // staged candidates of the current chunk
+  // One 32-bit column per lane, two uses: pass 1 counts into hist[bin][lane] (bin 64 = beyond the cover
+  // radius); pass 2 stores candidate j's key as lo word plane[j][lane] and hi word plane[32 + j][lane].
+  // Both live in the lane's OWN column, so a lane of a later row group can histogram while the lanes
+  // already served keep their candidates.  The record staging reuses the space at the end.
   union U {
-    uint32_t hist[TA_BINS + 1][32];      // pass 1: hist[bin][lane]
-    u64 pend[TA_CAP][32];                // pass 2: pend[j][lane]
-    float rec[32][TA_REC_WORDS];         // record staging
+    uint32_t plane[TA_BINS + 1][32];
+    float rec[32][TA_REC_WORDS];
   } u;
   uint32_t run_beg[TA_MAXROWS];          // first sorted position of each stencil row's run
   uint32_t run_off[TA_MAXROWS + 1];      // exclusive prefix of the run lengths
@@ -80,7 +86,60 @@ __device__ __forceinline__ void stage_chunk(const float4* __restrict__ sorted, T
   __syncwarp();
 }
 
-__global__ void __launch_bounds__(TA_WARPS * 32) knn_tile_kernel(KArgs a, int R0, float grow, uint32_t* __restrict__ work_count,
+// One row group of a tile: the lanes whose query lies in stencil row `row0`.  Looks up the (2R+1)^2 runs
+// of the union of their stencils, writes them to sm.run_*, and returns the number of candidates;
+// cover_cells = radius (in cells) around THIS lane's query that the union is guaranteed to cover: its
+// distance to the nearest face of the union block that still has cells behind it (a face on the grid
+// boundary has no points beyond it), minus 2e-3 cells for the rounding of the fractional position.
+__device__ __forceinline__ uint32_t tile_setup(const KArgs& a, TaSmem& sm, const int lane, const int R, const int c0min,
+                                               const int c0max, const int c1, const int c2, const int c0, const float4 Q,
+                                               int& nrows, bool& whole, float& cover_cells) {
+  const GridDesc& g = a.g;
+  const int xlo = max(c0min - R, 0), xhi = min(c0max + R, g.dim[0] - 1);
+  const int lo1 = max(c1 - R, 0), n1 = min(c1 + R, g.dim[1] - 1) - lo1 + 1;
+  const int lo2 = max(c2 - R, 0), n2 = min(c2 + R, g.dim[2] - 1) - lo2 + 1;
+  nrows = n1 * n2;
+  uint32_t beg0 = 0, len0 = 0, beg1 = 0, len1 = 0;
+  if (lane < nrows) {
+    const int o2 = lane / n1, o1 = lane - o2 * n1;
+    const uint32_t base = ((uint32_t)(lo2 + o2) * (uint32_t)g.dim[1] + (uint32_t)(lo1 + o1)) * (uint32_t)g.dim[0];
+    beg0 = __ldg(&a.E[base + xlo]);
+    len0 = __ldg(&a.E[base + xhi + 1]) - beg0;
+  }
+  if (lane + 32 < nrows) {
+    const int o2 = (lane + 32) / n1, o1 = (lane + 32) - o2 * n1;
+    const uint32_t base = ((uint32_t)(lo2 + o2) * (uint32_t)g.dim[1] + (uint32_t)(lo1 + o1)) * (uint32_t)g.dim[0];
+    beg1 = __ldg(&a.E[base + xlo]);
+    len1 = __ldg(&a.E[base + xhi + 1]) - beg1;
+  }
+  uint32_t inc0 = len0, inc1 = len1;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const uint32_t t0 = __shfl_up_sync(PCP_FULL, inc0, o), t1 = __shfl_up_sync(PCP_FULL, inc1, o);
+    if (lane >= o) {
+      inc0 += t0;
+      inc1 += t1;
+    }
+  }
+  const uint32_t tot0 = __shfl_sync(PCP_FULL, inc0, 31);
+  const uint32_t total = tot0 + __shfl_sync(PCP_FULL, inc1, 31);
+  __syncwarp();
+  sm.run_beg[lane] = beg0;
+  sm.run_off[lane] = inc0 - len0;
+  sm.run_beg[lane + 32] = beg1;
+  sm.run_off[lane + 32] = tot0 + inc1 - len1;
+  __syncwarp();
+  whole = xlo == 0 && xhi == g.dim[0] - 1 && n1 == g.dim[1] && n2 == g.dim[2];
+  const float f0 = frac_of(g, g.ax[0], Q, c0), f1 = frac_of(g, g.ax[1], Q, c1), f2 = frac_of(g, g.ax[2], Q, c2);
+  const float inf = 3.0e18f;
+  const float m0a = xlo > 0 ? (float)(c0 - xlo) + f0 : inf, m0b = xhi < g.dim[0] - 1 ? (float)(xhi + 1 - c0) - f0 : inf;
+  const float m1a = c1 - R > 0 ? (float)R + f1 : inf, m1b = c1 + R < g.dim[1] - 1 ? (float)(R + 1) - f1 : inf;
+  const float m2a = c2 - R > 0 ? (float)R + f2 : inf, m2b = c2 + R < g.dim[2] - 1 ? (float)(R + 1) - f2 : inf;
+  cover_cells = fminf(fminf(fminf(m0a, m0b), fminf(m1a, m1b)), fminf(m2a, m2b)) - 2e-3f;
+  return total;
+}
+
+__global__ void __launch_bounds__(TA_WARPS * 32, 4) knn_tile_kernel(KArgs a, int R0, float grow, int max_groups, uint32_t* __restrict__ work_count,
                                                                  uint32_t* __restrict__ work_list) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   TaSmem& sm = reinterpret_cast<TaSmem*>(smem_raw)[threadIdx.x >> 5];
@@ -97,163 +156,127 @@ __global__ void __launch_bounds__(TA_WARPS * 32) knn_tile_kernel(KArgs a, int R0
   const uint32_t cid = p < a.n ? __ldg(&a.keys[p]) : g.n_cells;
   const bool active = my_slot >= 0;
   const bool finite = active && cid < g.n_cells;
-  uint32_t* const hcol = &sm.u.hist[0][lane];
-  u64* const pcol = &sm.u.pend[0][lane];
+  uint32_t* const hcol = &sm.u.plane[0][lane];
+  uint32_t* wp = hcol;       // next free entry of this lane's candidate column (lo word; hi word 32 rows on)
+  const uint32_t my_row = cid / (uint32_t)g.dim[0];
+  const int c0 = (int)(cid - my_row * (uint32_t)g.dim[0]);
+  bool pending = finite;     // not yet served by a row group
+  bool ok = false;           // the lane's k nearest are in its column
 
-  // ---- tile geometry: the stencil row of the first searchable lane; lanes of other rows are deferred
-  const unsigned fin_mask = __ballot_sync(PCP_FULL, finite);
-  bool ok = false;
-  int nrows = 0, R = R0;
-  float cover_cells = 1.f;
-  uint32_t total = 0;
-  if (fin_mask != 0) {
-    const uint32_t cid0 = __shfl_sync(PCP_FULL, cid, __ffs(fin_mask) - 1);
-    const uint32_t row0 = cid0 / (uint32_t)g.dim[0];
-    const bool in_row = finite && cid / (uint32_t)g.dim[0] == row0;
-    const int c0 = (int)(cid - row0 * (uint32_t)g.dim[0]);
+  // ---- a tile usually lies in ONE stencil row; where it crosses row ends, each row is a group of its own
+#pragma unroll 1
+  for (int grp = 0; grp < max_groups; ++grp) {
+    const unsigned pmask = __ballot_sync(PCP_FULL, pending);
+    if (pmask == 0) break;
+    const uint32_t row0 = __shfl_sync(PCP_FULL, my_row, __ffs(pmask) - 1);
+    const bool in_grp = pending && my_row == row0;
+    pending = pending && !in_grp;
     const int c1 = (int)(row0 % (uint32_t)g.dim[1]), c2 = (int)(row0 / (uint32_t)g.dim[1]);
-    const int c0min = __reduce_min_sync(PCP_FULL, in_row ? c0 : 0x7fffffff);
-    const int c0max = __reduce_max_sync(PCP_FULL, in_row ? c0 : -1);
-    // Stencil half-width of the tile: the smallest R (<= 3) whose union of cells is expected to hold k
-    // points inside the cover radius R*cell (flat-density guess: disk area / union area).  A wrong
-    // guess costs time, never correctness: lanes whose k-th neighbour is not covered are deferred.
-    const int span = c0max - c0min + 1;
-    uint32_t beg0 = 0, len0 = 0, beg1 = 0, len1 = 0, off0 = 0, off1 = 0;
+    const int c0min = __reduce_min_sync(PCP_FULL, in_grp ? c0 : 0x7fffffff);
+    const int c0max = __reduce_max_sync(PCP_FULL, in_grp ? c0 : -1);
+    int R = R0, nrows = 0, bstar = -1, cum_star = 0;
+    uint32_t total = 0;
+    float Sb = 0.f;
+    // ---- pass 1 (+ on-demand growth of the stencil): histogram of d2 over the staged candidates
 #pragma unroll 1
     for (;;) {
-      const int xlo = max(c0min - R, 0), xhi = min(c0max + R, g.dim[0] - 1);
-      const int lo1 = max(c1 - R, 0), n1 = min(c1 + R, g.dim[1] - 1) - lo1 + 1;
-      const int lo2 = max(c2 - R, 0), n2 = min(c2 + R, g.dim[2] - 1) - lo2 + 1;
-      nrows = n1 * n2;
-      beg0 = len0 = beg1 = len1 = 0;
-      if (lane < nrows) {
-        const int o2 = lane / n1, o1 = lane - o2 * n1;
-        const uint32_t base = ((uint32_t)(lo2 + o2) * (uint32_t)g.dim[1] + (uint32_t)(lo1 + o1)) * (uint32_t)g.dim[0];
-        beg0 = __ldg(&a.E[base + xlo]);
-        len0 = __ldg(&a.E[base + xhi + 1]) - beg0;
-      }
-      if (lane + 32 < nrows) {
-        const int o2 = (lane + 32) / n1, o1 = (lane + 32) - o2 * n1;
-        const uint32_t base = ((uint32_t)(lo2 + o2) * (uint32_t)g.dim[1] + (uint32_t)(lo1 + o1)) * (uint32_t)g.dim[0];
-        beg1 = __ldg(&a.E[base + xlo]);
-        len1 = __ldg(&a.E[base + xhi + 1]) - beg1;
-      }
-      uint32_t inc0 = len0, inc1 = len1;
+      bool whole;
+      float cover_cells;
+      total = tile_setup(a, sm, lane, R, c0min, c0max, c1, c2, c0, Q, nrows, whole, cover_cells);
+      Sb = (float)TA_BINS / (cover_cells * cover_cells * g.cell * g.cell * (1.f - 1e-6f));
+      if (in_grp) {
 #pragma unroll
-      for (int o = 1; o < 32; o <<= 1) {
-        const uint32_t t0 = __shfl_up_sync(PCP_FULL, inc0, o), t1 = __shfl_up_sync(PCP_FULL, inc1, o);
-        if (lane >= o) {
-          inc0 += t0;
-          inc1 += t1;
+        for (int b = 0; b <= TA_BINS; ++b) hcol[b * 32] = 0;
+      }
+#pragma unroll 1
+      for (uint32_t cb = 0; cb < total; cb += TA_CH) {
+        const int cnt = (int)min((uint32_t)TA_CH, total - cb);
+        stage_chunk(sorted, sm, nrows, cb, cnt, lane);
+        // four candidates per step: the loads and the distance arithmetic of a group are independent, and
+        // the histogram update is a fire-and-forget shared atomic (own column: no conflicts, no read-back)
+        int j = 0;
+#pragma unroll 1
+        for (; j + 4 <= cnt; j += 4) {
+          const float4 P0 = sm.cand[j], P1 = sm.cand[j + 1], P2 = sm.cand[j + 2], P3 = sm.cand[j + 3];
+          const int b0 = __float2int_rz(fminf(dist2_nofma(Q.x, Q.y, Q.z, P0) * Sb, (float)TA_BINS));
+          const int b1 = __float2int_rz(fminf(dist2_nofma(Q.x, Q.y, Q.z, P1) * Sb, (float)TA_BINS));
+          const int b2 = __float2int_rz(fminf(dist2_nofma(Q.x, Q.y, Q.z, P2) * Sb, (float)TA_BINS));
+          const int b3 = __float2int_rz(fminf(dist2_nofma(Q.x, Q.y, Q.z, P3) * Sb, (float)TA_BINS));
+          if (in_grp) {
+            atomicAdd(&hcol[b0 * 32], 1u);
+            atomicAdd(&hcol[b1 * 32], 1u);
+            atomicAdd(&hcol[b2 * 32], 1u);
+            atomicAdd(&hcol[b3 * 32], 1u);
+          }
+        }
+        for (; j < cnt; ++j) {
+          const int b0 = __float2int_rz(fminf(dist2_nofma(Q.x, Q.y, Q.z, sm.cand[j]) * Sb, (float)TA_BINS));
+          if (in_grp) atomicAdd(&hcol[b0 * 32], 1u);
+        }
+        __syncwarp();
+      }
+      // the bin holding the k-th smallest, and how many candidates lie at or below it
+      int cum = 0;
+      bstar = -1;
+      if (in_grp) {
+#pragma unroll 8
+        for (int b = 0; b < TA_BINS; ++b) {
+          cum += (int)hcol[b * 32];
+          if (bstar < 0 && cum >= k) {
+            bstar = b;
+            cum_star = cum;
+          }
         }
       }
-      const uint32_t tot0 = __shfl_sync(PCP_FULL, inc0, 31);
-      total = tot0 + __shfl_sync(PCP_FULL, inc1, 31);
-      off0 = inc0 - len0;
-      off1 = tot0 + inc1 - len1;
-      const bool whole = xlo == 0 && xhi == g.dim[0] - 1 && n1 == g.dim[1] && n2 == g.dim[2];
-      const float frac = 3.14159f * (float)(R * R) / (float)((span + 2 * R) * (2 * R + 1));
-      if (R >= 3 || whole || (float)total * frac >= grow * (float)k) break;
+      // lanes whose k-th neighbour lies beyond the cover radius: widen the stencil when a pass over the
+      // wider union costs less than finishing them one by one (~2000 vs ~28 instructions per unit)
+      const int n_unc = __popc(__ballot_sync(PCP_FULL, in_grp && bstar < 0));
+      if (n_unc == 0 || R >= TA_MAXR || whole) break;
+      const int span = c0max - c0min + 1;
+      const float wider = (float)total * (float)((span + 2 * R + 2) * (2 * R + 3)) / (float)((span + 2 * R) * (2 * R + 1));
+      if ((float)n_unc * grow < wider) break;
+      TSTAT(7, lane == 0 ? 1 : 0);
       ++R;
     }
-    {
-      const int xlo = max(c0min - R, 0), xhi = min(c0max + R, g.dim[0] - 1);
-      const float f0 = frac_of(g, g.ax[0], Q, c0), f1 = frac_of(g, g.ax[1], Q, c1), f2 = frac_of(g, g.ax[2], Q, c2);
-      const float inf = 3.0e18f;
-      const float m0a = xlo > 0 ? (float)(c0 - xlo) + f0 : inf, m0b = xhi < g.dim[0] - 1 ? (float)(xhi + 1 - c0) - f0 : inf;
-      const float m1a = c1 - R > 0 ? (float)R + f1 : inf, m1b = c1 + R < g.dim[1] - 1 ? (float)(R + 1) - f1 : inf;
-      const float m2a = c2 - R > 0 ? (float)R + f2 : inf, m2b = c2 + R < g.dim[2] - 1 ? (float)(R + 1) - f2 : inf;
-      cover_cells = fminf(fminf(fminf(m0a, m0b), fminf(m1a, m1b)), fminf(m2a, m2b)) - 2e-3f;
-    }
-    sm.run_beg[lane] = beg0;
-    sm.run_off[lane] = off0;
-    sm.run_beg[lane + 32] = beg1;
-    sm.run_off[lane + 32] = off1;
-    ok = in_row;
-  }
-  __syncwarp();
-
-  // ---- pass 1: histogram of d2 over the staged candidates
-  // Radius around THIS query that the union of cells is guaranteed to cover: its distance to the
-  // nearest face of the union block that still has cells behind it (a face on the grid boundary has no
-  // points beyond it), minus 2e-3 cells for the rounding of the fractional position.
-  const float cover2 = cover_cells * cover_cells * g.cell * g.cell * (1.f - 1e-6f);
-  const float Sb = (float)TA_BINS / cover2;
-#pragma unroll
-  for (int b = 0; b <= TA_BINS; ++b) hcol[b * 32] = 0;
-  const bool resident = total <= (uint32_t)TA_CH;  // one chunk: staged once, used by both passes
-#pragma unroll 1
-  for (uint32_t cb = 0; cb < total; cb += TA_CH) {
-    const int cnt = (int)min((uint32_t)TA_CH, total - cb);
-    stage_chunk(sorted, sm, nrows, cb, cnt, lane);
-    // four candidates per step: the loads and the distance arithmetic of a group are independent, and
-    // the histogram update is a fire-and-forget shared atomic (own column: no conflicts, no read-back)
-    int j = 0;
-#pragma unroll 1
-    for (; j + 4 <= cnt; j += 4) {
-      const float4 P0 = sm.cand[j], P1 = sm.cand[j + 1], P2 = sm.cand[j + 2], P3 = sm.cand[j + 3];
-      const int b0 = __float2int_rz(fminf(dist2_nofma(Q.x, Q.y, Q.z, P0) * Sb, (float)TA_BINS));
-      const int b1 = __float2int_rz(fminf(dist2_nofma(Q.x, Q.y, Q.z, P1) * Sb, (float)TA_BINS));
-      const int b2 = __float2int_rz(fminf(dist2_nofma(Q.x, Q.y, Q.z, P2) * Sb, (float)TA_BINS));
-      const int b3 = __float2int_rz(fminf(dist2_nofma(Q.x, Q.y, Q.z, P3) * Sb, (float)TA_BINS));
-      atomicAdd(&hcol[b0 * 32], 1u);
-      atomicAdd(&hcol[b1 * 32], 1u);
-      atomicAdd(&hcol[b2 * 32], 1u);
-      atomicAdd(&hcol[b3 * 32], 1u);
-    }
-    for (; j < cnt; ++j) {
-      const int b0 = __float2int_rz(fminf(dist2_nofma(Q.x, Q.y, Q.z, sm.cand[j]) * Sb, (float)TA_BINS));
-      atomicAdd(&hcol[b0 * 32], 1u);
-    }
+    TSTAT(2, lane == 0 ? total : 0);
+    TSTAT(5, (in_grp && bstar < 0) ? 1 : 0);                          // deferred: k-th beyond the cover radius
+    TSTAT(6, (in_grp && bstar >= 0 && cum_star > TA_CAP) ? 1 : 0);    // deferred: threshold bin too full
+    const bool grp_ok = in_grp && bstar >= 0 && cum_star <= TA_CAP;
+    const float thr_bin = grp_ok ? (float)(bstar + 1) : -1.f;  // other lanes collect nothing
     __syncwarp();
-  }
-  // ---- the bin holding the k-th smallest, and how many candidates lie at or below it
-  int cum = 0, bstar = -1, cum_star = 0;
-#pragma unroll 8
-  for (int b = 0; b < TA_BINS; ++b) {
-    cum += (int)hcol[b * 32];
-    if (bstar < 0 && cum >= k) {
-      bstar = b;
-      cum_star = cum;
-    }
-  }
-  TSTAT(4, (finite && !ok) ? 1 : 0);                              // deferred: other stencil row
-  TSTAT(5, (ok && bstar < 0) ? 1 : 0);                            // deferred: k-th beyond the cover radius
-  TSTAT(6, (ok && bstar >= 0 && cum_star > TA_CAP) ? 1 : 0);      // deferred: threshold bin too full
-  ok = ok && bstar >= 0 && cum_star <= TA_CAP;
-  // a lane that is not ok collects nothing; it goes to the work list below
-  const float thr_bin = ok ? (float)(bstar + 1) : -1.f;
-  __syncwarp();
-
-  // ---- pass 2: collect the candidates at or below the threshold bin (same d2 arithmetic, same bins)
-  u64* wp = pcol;  // next free entry of this lane's column
+    // ---- pass 2: collect the candidates at or below the threshold bin (same d2 arithmetic, same bins)
+    if (__any_sync(PCP_FULL, grp_ok)) {
+      const bool resident = total <= (uint32_t)TA_CH;  // one chunk: still staged from pass 1
 #pragma unroll 1
-  for (uint32_t cb = 0; cb < total; cb += TA_CH) {
-    const int n_ch = (int)min((uint32_t)TA_CH, total - cb);
-    if (!resident) stage_chunk(sorted, sm, nrows, cb, n_ch, lane);
-    int j = 0;
+      for (uint32_t cb = 0; cb < total; cb += TA_CH) {
+        const int n_ch = (int)min((uint32_t)TA_CH, total - cb);
+        if (!resident) stage_chunk(sorted, sm, nrows, cb, n_ch, lane);
+        int j = 0;
 #pragma unroll 1
-    for (; j + 4 <= n_ch; j += 4) {
-      const float4 P0 = sm.cand[j], P1 = sm.cand[j + 1], P2 = sm.cand[j + 2], P3 = sm.cand[j + 3];
-      const float e0 = dist2_nofma(Q.x, Q.y, Q.z, P0), e1 = dist2_nofma(Q.x, Q.y, Q.z, P1);
-      const float e2 = dist2_nofma(Q.x, Q.y, Q.z, P2), e3 = dist2_nofma(Q.x, Q.y, Q.z, P3);
-      if (e0 * Sb < thr_bin) { *wp = ((u64)__float_as_uint(e0) << 32) | (u64)__float_as_uint(P0.w); wp += 32; }
-      if (e1 * Sb < thr_bin) { *wp = ((u64)__float_as_uint(e1) << 32) | (u64)__float_as_uint(P1.w); wp += 32; }
-      if (e2 * Sb < thr_bin) { *wp = ((u64)__float_as_uint(e2) << 32) | (u64)__float_as_uint(P2.w); wp += 32; }
-      if (e3 * Sb < thr_bin) { *wp = ((u64)__float_as_uint(e3) << 32) | (u64)__float_as_uint(P3.w); wp += 32; }
+        for (; j + 4 <= n_ch; j += 4) {
+          const float4 P0 = sm.cand[j], P1 = sm.cand[j + 1], P2 = sm.cand[j + 2], P3 = sm.cand[j + 3];
+          const float e0 = dist2_nofma(Q.x, Q.y, Q.z, P0), e1 = dist2_nofma(Q.x, Q.y, Q.z, P1);
+          const float e2 = dist2_nofma(Q.x, Q.y, Q.z, P2), e3 = dist2_nofma(Q.x, Q.y, Q.z, P3);
+          if (e0 * Sb < thr_bin) { wp[0] = __float_as_uint(P0.w); wp[1024] = __float_as_uint(e0); wp += 32; }
+          if (e1 * Sb < thr_bin) { wp[0] = __float_as_uint(P1.w); wp[1024] = __float_as_uint(e1); wp += 32; }
+          if (e2 * Sb < thr_bin) { wp[0] = __float_as_uint(P2.w); wp[1024] = __float_as_uint(e2); wp += 32; }
+          if (e3 * Sb < thr_bin) { wp[0] = __float_as_uint(P3.w); wp[1024] = __float_as_uint(e3); wp += 32; }
+        }
+        for (; j < n_ch; ++j) {
+          const float4 P0 = sm.cand[j];
+          const float e0 = dist2_nofma(Q.x, Q.y, Q.z, P0);
+          if (e0 * Sb < thr_bin) { wp[0] = __float_as_uint(P0.w); wp[1024] = __float_as_uint(e0); wp += 32; }
+        }
+        __syncwarp();
+      }
     }
-    for (; j < n_ch; ++j) {
-      const float4 P0 = sm.cand[j];
-      const float e0 = dist2_nofma(Q.x, Q.y, Q.z, P0);
-      if (e0 * Sb < thr_bin) { *wp = ((u64)__float_as_uint(e0) << 32) | (u64)__float_as_uint(P0.w); wp += 32; }
-    }
-    __syncwarp();
+    ok = ok || grp_ok;
   }
-  const int cnt = (int)(wp - pcol) >> 5;
+  const int cnt = (int)(wp - hcol) >> 5;
   TSTAT(0, finite ? 1 : 0);
   TSTAT(1, (finite && !ok) ? 1 : 0);
-  TSTAT(2, lane == 0 ? total : 0);
   TSTAT(3, ok ? cnt : 0);
+  TSTAT(4, pending ? 1 : 0);  // deferred: more row groups in the tile than the kernel serves
   // ---- deferred lanes -> work list (sorted positions), finished by the expanding-shell kernel
   {
     const bool defer = finite && !ok;
@@ -268,7 +291,7 @@ __global__ void __launch_bounds__(TA_WARPS * 32) knn_tile_kernel(KArgs a, int R0
   // ---- order the collected keys by (d2, index)
   u64 best[TA_CAP];
 #pragma unroll
-  for (int j = 0; j < TA_CAP; ++j) best[j] = j < cnt ? pcol[j * 32] : PCP_KEY_INF;
+  for (int j = 0; j < TA_CAP; ++j) best[j] = j < cnt ? (((u64)hcol[(32 + j) * 32] << 32) | (u64)hcol[j * 32]) : PCP_KEY_INF;
   sort32_regs(best);
   const int n_nb = ok ? k : 0;
   const bool emit = active && (ok || !finite);  // non-finite queries get their empty record here
@@ -299,11 +322,13 @@ int pcp_knn_tile_launch(pcp_ctx* ctx, const SearchParams& sp, const KArgs& a) {
   const int blocks = (int)((tiles + TA_WARPS - 1) / TA_WARPS);
   const size_t smem = sizeof(TaSmem) * TA_WARPS;
   PCP_CUDA(cudaFuncSetAttribute(knn_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  // the stencil of a tile grows while the expected number of points inside its cover radius is below
-  // grow*k (tuning hook: PCP_KNN_RGROW)
-  float grow = 0.f;  // measured on the urban cloud: growing wide sparse tiles costs more than deferring their lanes
+  // a tile's stencil is widened when (uncovered lanes) * grow exceeds the size of the wider union
+  // (tuning hook: PCP_KNN_RGROW; 0 = never widen)
+  float grow = 0.f;  // ~ instructions per deferred query / instructions per staged candidate
   if (const char* e = getenv("PCP_KNN_RGROW")) grow = (float)atof(e);
-  knn_tile_kernel<<<blocks, TA_WARPS * 32, smem, ctx->stream>>>(a, sp.R0, grow, (uint32_t*)ctx->work_count.p,
+  int max_groups = TA_MAXGROUPS;  // stencil rows served per tile (tuning hook: PCP_KNN_GROUPS)
+  if (const char* e = getenv("PCP_KNN_GROUPS")) max_groups = atoi(e);
+  knn_tile_kernel<<<blocks, TA_WARPS * 32, smem, ctx->stream>>>(a, sp.R0, grow, max_groups, (uint32_t*)ctx->work_count.p,
                                                                  (uint32_t*)ctx->work_list.p);
   PCP_LAUNCH_CHECK("knn_tile_kernel");
   return PCP_OK;
