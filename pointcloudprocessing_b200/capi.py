@@ -41,7 +41,7 @@ EXPORTS = (
     "pcp_last_timings", "pcp_launch_count", "pcp_set_cloud_host", "pcp_set_cloud_device",
     "pcp_set_cloud_device_sharded", "pcp_build_grid", "pcp_grid_info", "pcp_radius_pca", "pcp_knn_pca",
     "pcp_knn_pca_kth", "pcp_knn_neighbors", "pcp_radius_neighbors", "pcp_segment_pca", "pcp_ring_calib_default",
-    "pcp_ring_calib_from_xml", "pcp_ring_project",
+    "pcp_ring_calib_from_xml", "pcp_ring_project", "pcp_set_host_async",
 )
 
 
@@ -86,6 +86,7 @@ def load() -> C.CDLL:
         "pcp_synchronize": (i32, [vp]),
         "pcp_last_timings": (i32, [vp, vp, i32]),
         "pcp_launch_count": (i64, [vp]),
+        "pcp_set_host_async": (i32, [vp, i32]),
         "pcp_set_cloud_host": (i32, [vp, vp, i64, i32]),
         "pcp_set_cloud_device": (i32, [vp, vp, i64]),
         "pcp_set_cloud_device_sharded": (i32, [vp, vp, vp, i64, i64]),
@@ -176,6 +177,10 @@ class Pcp:
 
     def synchronize(self):
         self._ck(self.lib.pcp_synchronize(self.h))
+
+    def set_host_async(self, enable: bool):
+        """Host-pointer calls only enqueue (pinned buffers, caller synchronises): see pcp_set_host_async."""
+        self._ck(self.lib.pcp_set_host_async(self.h, 1 if enable else 0))
 
     def timings(self) -> dict:
         ms = np.zeros(len(STAGES), np.float32)

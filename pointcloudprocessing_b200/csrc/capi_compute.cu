@@ -117,7 +117,7 @@ PCP_API int pcp_knn_pca_kth(pcp_ctx* ctx, int k, int center_mode, pcp_feature68*
   if ((rc = copy_back(ctx, normals, sp.normals, out_is_device, (size_t)nq))) return rc;
   if ((rc = copy_back(ctx, kth_d2, sp.kth_d2, out_is_device, (size_t)nq))) return rc;
   pcp_toc(ctx, PCP_T_D2H);
-  if (!out_is_device) PCP_CUDA(cudaStreamSynchronize(ctx->stream));
+  if (!out_is_device && !ctx->host_async) PCP_CUDA(cudaStreamSynchronize(ctx->stream));
   return PCP_OK;
 }
 

@@ -105,6 +105,12 @@ PCP_API int pcp_synchronize(pcp_ctx* ctx) {
   return PCP_OK;
 }
 
+PCP_API int pcp_set_host_async(pcp_ctx* ctx, int enable) {
+  if (!ctx) return PCP_ERR_INVALID_ARG;
+  ctx->host_async = enable != 0;
+  return PCP_OK;
+}
+
 PCP_API int pcp_last_timings(pcp_ctx* ctx, float* ms, int n) {
   if (!ctx || !ms) return PCP_ERR_INVALID_ARG;
   PCP_CUDA(cudaStreamSynchronize(ctx->stream));
@@ -133,7 +139,7 @@ PCP_API int pcp_set_cloud_host(pcp_ctx* ctx, const void* pts, int64_t n, int str
     PCP_CUDA(cudaMemcpy2DAsync(ctx->own_cloud.p, 16, pts, (size_t)stride_bytes, 12, (size_t)n, cudaMemcpyHostToDevice, ctx->stream));
   }
   pcp_toc(ctx, PCP_T_H2D);
-  PCP_CUDA(cudaStreamSynchronize(ctx->stream));
+  if (!ctx->host_async) PCP_CUDA(cudaStreamSynchronize(ctx->stream));
   return PCP_OK;
 }
 

@@ -31,6 +31,7 @@ struct pcp_ctx {
   int device = 0;
   cudaStream_t stream = nullptr;
   std::string err;
+  bool host_async = false;  // pcp_set_host_async: host-pointer calls only enqueue
   int64_t launches = 0;
   float t_ms[PCP_T_COUNT] = {0};
   cudaEvent_t ev[2 * PCP_T_COUNT] = {nullptr};
