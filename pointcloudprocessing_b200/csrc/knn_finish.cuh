@@ -9,9 +9,10 @@
 
 // best[0..n_nb) = this lane's neighbours ascending by (d2, index) as keys bits(d2) << 32 | ord;
 // my_slot < 0: the lane has no query.  rec_all = 32 x 17 floats of warp-private shared memory that no
-// lane still uses for anything else.
+// lane still uses for anything else; col = 32 words (stride col_stride) of the lane's own shared memory,
+// free once best[] is in registers (it may overlap rec_all: the records are staged after the moments).
 __device__ __forceinline__ void knn_finish(const KArgs& a, u64 (&best)[32], const int n_nb, const float4 Q, const int my_slot,
-                                           float (*rec_all)[17], const int lane) {
+                                           float (*rec_all)[17], uint32_t* col, const int col_stride, const int lane) {
   const SearchParams& sp = a.sp;
   const int k = sp.k;
   // ---- neighbour list -> outputs (each lane for its own query)
@@ -47,25 +48,25 @@ __device__ __forceinline__ void knn_finish(const KArgs& a, u64 (&best)[32], cons
   const bool need_m = sp.normals != nullptr || (sp.out != nullptr && sp.center_mode == PCP_CENTER_MEAN);
   float mq[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f}, mm[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
   if (valid && (need_q || need_m)) {
-    // sorted positions of the neighbours, in list order (the moment re-reads coordinates from them)
-    uint32_t npos[32];
+    // The list moves to the lane's shared-memory column so the moment loops can be ROLLED (three loops
+    // unrolled 32 times were a quarter of the kernel's code and cost instruction-cache misses):
+    // col[j] = sorted position of neighbour j, from which the coordinates are re-read.
 #pragma unroll
-    for (int j = 0; j < 32; ++j) npos[j] = j < n_nb ? __ldg(&inv[(uint32_t)best[j]]) : 0u;
+    for (int j = 0; j < 32; ++j)
+      if (j < n_nb) col[j * col_stride] = __ldg(&inv[(uint32_t)best[j]]);
     const float fn = (float)n_nb;
     if (need_q) {
       // pcl::computeCovarianceMatrixNormalized about the query: six fp32 chains in list order
-#pragma unroll
-      for (int j = 0; j < 32; ++j) {
-        if (j < n_nb) {
-          const float4 P = __ldg(&sorted[npos[j]]);
-          const float px = __fsub_rn(P.x, Q.x), py = __fsub_rn(P.y, Q.y), pz = __fsub_rn(P.z, Q.z);
-          mq[0] = __fadd_rn(mq[0], __fmul_rn(px, px));
-          mq[1] = __fadd_rn(mq[1], __fmul_rn(py, px));
-          mq[2] = __fadd_rn(mq[2], __fmul_rn(pz, px));
-          mq[3] = __fadd_rn(mq[3], __fmul_rn(py, py));
-          mq[4] = __fadd_rn(mq[4], __fmul_rn(py, pz));
-          mq[5] = __fadd_rn(mq[5], __fmul_rn(pz, pz));
-        }
+#pragma unroll 2
+      for (int j = 0; j < n_nb; ++j) {
+        const float4 P = __ldg(&sorted[col[j * col_stride]]);
+        const float px = __fsub_rn(P.x, Q.x), py = __fsub_rn(P.y, Q.y), pz = __fsub_rn(P.z, Q.z);
+        mq[0] = __fadd_rn(mq[0], __fmul_rn(px, px));
+        mq[1] = __fadd_rn(mq[1], __fmul_rn(py, px));
+        mq[2] = __fadd_rn(mq[2], __fmul_rn(pz, px));
+        mq[3] = __fadd_rn(mq[3], __fmul_rn(py, py));
+        mq[4] = __fadd_rn(mq[4], __fmul_rn(py, pz));
+        mq[5] = __fadd_rn(mq[5], __fmul_rn(pz, pz));
       }
 #pragma unroll
       for (int c = 0; c < 6; ++c) mq[c] = __fdiv_rn(mq[c], fn);
@@ -73,28 +74,24 @@ __device__ __forceinline__ void knn_finish(const KArgs& a, u64 (&best)[32], cons
     if (need_m) {
       // pcl::compute3DCentroid (fp32 running sums in list order), then the moment about it
       float sx = 0.f, sy = 0.f, sz = 0.f;
-#pragma unroll
-      for (int j = 0; j < 32; ++j) {
-        if (j < n_nb) {
-          const float4 P = __ldg(&sorted[npos[j]]);
-          sx = __fadd_rn(sx, P.x);
-          sy = __fadd_rn(sy, P.y);
-          sz = __fadd_rn(sz, P.z);
-        }
+#pragma unroll 2
+      for (int j = 0; j < n_nb; ++j) {
+        const float4 P = __ldg(&sorted[col[j * col_stride]]);
+        sx = __fadd_rn(sx, P.x);
+        sy = __fadd_rn(sy, P.y);
+        sz = __fadd_rn(sz, P.z);
       }
       const float cx = __fdiv_rn(sx, fn), cy = __fdiv_rn(sy, fn), cz = __fdiv_rn(sz, fn);
-#pragma unroll
-      for (int j = 0; j < 32; ++j) {
-        if (j < n_nb) {
-          const float4 P = __ldg(&sorted[npos[j]]);
-          const float px = __fsub_rn(P.x, cx), py = __fsub_rn(P.y, cy), pz = __fsub_rn(P.z, cz);
-          mm[0] = __fadd_rn(mm[0], __fmul_rn(px, px));
-          mm[1] = __fadd_rn(mm[1], __fmul_rn(py, px));
-          mm[2] = __fadd_rn(mm[2], __fmul_rn(pz, px));
-          mm[3] = __fadd_rn(mm[3], __fmul_rn(py, py));
-          mm[4] = __fadd_rn(mm[4], __fmul_rn(py, pz));
-          mm[5] = __fadd_rn(mm[5], __fmul_rn(pz, pz));
-        }
+#pragma unroll 2
+      for (int j = 0; j < n_nb; ++j) {
+        const float4 P = __ldg(&sorted[col[j * col_stride]]);
+        const float px = __fsub_rn(P.x, cx), py = __fsub_rn(P.y, cy), pz = __fsub_rn(P.z, cz);
+        mm[0] = __fadd_rn(mm[0], __fmul_rn(px, px));
+        mm[1] = __fadd_rn(mm[1], __fmul_rn(py, px));
+        mm[2] = __fadd_rn(mm[2], __fmul_rn(pz, px));
+        mm[3] = __fadd_rn(mm[3], __fmul_rn(py, py));
+        mm[4] = __fadd_rn(mm[4], __fmul_rn(py, pz));
+        mm[5] = __fadd_rn(mm[5], __fmul_rn(pz, pz));
       }
 #pragma unroll
       for (int c = 0; c < 6; ++c) mm[c] = __fdiv_rn(mm[c], fn);

@@ -38,7 +38,7 @@ __device__ unsigned long long g_tile_stats[16];
 namespace {
 
 constexpr int TA_WARPS = 4;        // warps per CTA
-constexpr int TA_CH = 256;         // staged candidates per chunk
+constexpr int TA_CH = 128;         // staged candidates per chunk
 constexpr int TA_BINS = 64;        // linear d2 bins inside the cover radius (+1 overflow bin)
 constexpr int TA_CAP = 32;         // candidates a lane can hold (sorting-network width)
 constexpr int TA_REC_WORDS = 17;   // 68-byte record
@@ -139,7 +139,7 @@ __device__ __forceinline__ uint32_t tile_setup(const KArgs& a, TaSmem& sm, const
   return total;
 }
 
-__global__ void __launch_bounds__(TA_WARPS * 32, 4) knn_tile_kernel(KArgs a, int R0, float grow, int max_groups, uint32_t* __restrict__ work_count,
+__global__ void __launch_bounds__(TA_WARPS * 32, 5) knn_tile_kernel(KArgs a, int R0, float grow, int max_groups, uint32_t* __restrict__ work_count,
                                                                  uint32_t* __restrict__ work_list) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   TaSmem& sm = reinterpret_cast<TaSmem*>(smem_raw)[threadIdx.x >> 5];
@@ -296,7 +296,7 @@ __global__ void __launch_bounds__(TA_WARPS * 32, 4) knn_tile_kernel(KArgs a, int
   const int n_nb = ok ? k : 0;
   const bool emit = active && (ok || !finite);  // non-finite queries get their empty record here
   __syncwarp();
-  knn_finish(a, best, n_nb, Q, emit ? my_slot : -1, sm.u.rec, lane);
+  knn_finish(a, best, n_nb, Q, emit ? my_slot : -1, sm.u.rec, hcol, 32, lane);
 }
 
 }  // namespace
