@@ -195,7 +195,7 @@ __global__ void __launch_bounds__(TA_WARPS * 32, 5) knn_tile_kernel(KArgs a, int
         // four candidates per step: the loads and the distance arithmetic of a group are independent, and
         // the histogram update is a fire-and-forget shared atomic (own column: no conflicts, no read-back)
         int j = 0;
-#pragma unroll 1
+#pragma unroll 2
         for (; j + 4 <= cnt; j += 4) {
           const float4 P0 = sm.cand[j], P1 = sm.cand[j + 1], P2 = sm.cand[j + 2], P3 = sm.cand[j + 3];
           const int b0 = __float2int_rz(fminf(dist2_nofma(Q.x, Q.y, Q.z, P0) * Sb, (float)TA_BINS));
@@ -247,12 +247,52 @@ __global__ void __launch_bounds__(TA_WARPS * 32, 5) knn_tile_kernel(KArgs a, int
     // ---- pass 2: collect the candidates at or below the threshold bin (same d2 arithmetic, same bins)
     if (__any_sync(PCP_FULL, grp_ok)) {
       const bool resident = total <= (uint32_t)TA_CH;  // one chunk: still staged from pass 1
+      // A candidate farther from the bounding box of the served queries than the largest threshold
+      // distance is nobody's neighbour: each chunk is compacted in place (one candidate per lane, ballot
+      // + rank) before the per-lane loop, which then runs over about half of it.
+      const float big = 3.0e38f;
+      float bx0 = grp_ok ? Q.x : big, bx1 = grp_ok ? Q.x : -big, by0 = grp_ok ? Q.y : big, by1 = grp_ok ? Q.y : -big;
+      float bz0 = grp_ok ? Q.z : big, bz1 = grp_ok ? Q.z : -big;
+      float tmax = grp_ok ? thr_bin / Sb : 0.f;
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        bx0 = fminf(bx0, __shfl_xor_sync(PCP_FULL, bx0, o));
+        bx1 = fmaxf(bx1, __shfl_xor_sync(PCP_FULL, bx1, o));
+        by0 = fminf(by0, __shfl_xor_sync(PCP_FULL, by0, o));
+        by1 = fmaxf(by1, __shfl_xor_sync(PCP_FULL, by1, o));
+        bz0 = fminf(bz0, __shfl_xor_sync(PCP_FULL, bz0, o));
+        bz1 = fmaxf(bz1, __shfl_xor_sync(PCP_FULL, bz1, o));
+        tmax = fmaxf(tmax, __shfl_xor_sync(PCP_FULL, tmax, o));
+      }
+      tmax *= 1.001f;  // slack for the rounding of thr_bin / Sb and of the box distance
 #pragma unroll 1
       for (uint32_t cb = 0; cb < total; cb += TA_CH) {
-        const int n_ch = (int)min((uint32_t)TA_CH, total - cb);
+        int n_ch = (int)min((uint32_t)TA_CH, total - cb);
         if (!resident) stage_chunk(sorted, sm, nrows, cb, n_ch, lane);
-        int j = 0;
+        {
+          int kept = 0;
 #pragma unroll 1
+          for (int i0 = 0; i0 < n_ch; i0 += 32) {
+            const int i = i0 + lane;
+            float4 P = make_float4(0.f, 0.f, 0.f, 0.f);
+            bool keep = false;
+            if (i < n_ch) {
+              P = sm.cand[i];
+              const float dx = fmaxf(fmaxf(bx0 - P.x, P.x - bx1), 0.f), dy = fmaxf(fmaxf(by0 - P.y, P.y - by1), 0.f);
+              const float dz = fmaxf(fmaxf(bz0 - P.z, P.z - bz1), 0.f);
+              keep = dx * dx + dy * dy + dz * dz <= tmax;
+            }
+            const unsigned km = __ballot_sync(PCP_FULL, keep);
+            __syncwarp();  // every lane has read its candidate before any slot is overwritten
+            if (keep) sm.cand[kept + __popc(km & ((1u << lane) - 1u))] = P;
+            kept += __popc(km);
+          }
+          __syncwarp();
+          TSTAT(8, lane == 0 ? kept : 0);
+          n_ch = kept;
+        }
+        int j = 0;
+#pragma unroll 2
         for (; j + 4 <= n_ch; j += 4) {
           const float4 P0 = sm.cand[j], P1 = sm.cand[j + 1], P2 = sm.cand[j + 2], P3 = sm.cand[j + 3];
           const float e0 = dist2_nofma(Q.x, Q.y, Q.z, P0), e1 = dist2_nofma(Q.x, Q.y, Q.z, P1);
