@@ -101,10 +101,14 @@ PCP_API int pcp_synchronize(pcp_ctx* ctx);
 /* Pipelining across clouds (frame batches): with `enable` != 0, pcp_set_cloud_host and pcp_knn_pca[_kth]
  * with host outputs only ENQUEUE their copies and kernels on the ctx stream and return; the caller must
  * pass page-locked host memory, keep it untouched until pcp_synchronize, and may drive a second ctx
- * meanwhile so that one cloud's result copy overlaps the next cloud's upload and search.  Off by default
+ * meanwhile so that one cloud's result copy overlaps the next cloud's upload and search (pcp_ring_project
+ * with host outputs follows the same rule).  Off by default
  * (the reference's calls are synchronous, src/pcaAnalysis.cpp:11-42).  pcp_build_grid still waits for
  * the bounding box (it sizes the grid on the host), pcp_radius_pca for its overflow flag. */
 PCP_API int pcp_set_host_async(pcp_ctx* ctx, int enable);
+/* Page-locked host buffers for that mode (cudaHostAlloc / cudaFreeHost); NULL when the allocation fails. */
+PCP_API void* pcp_alloc_pinned(size_t bytes);
+PCP_API void pcp_free_pinned(void* p);
 /* Copies the PCP_T_COUNT stage times of the last build/compute calls into ms[0..n). */
 PCP_API int pcp_last_timings(pcp_ctx* ctx, float* ms, int n);
 /* Number of kernel launches issued by this ctx since creation. */

@@ -41,8 +41,29 @@ EXPORTS = (
     "pcp_last_timings", "pcp_launch_count", "pcp_set_cloud_host", "pcp_set_cloud_device",
     "pcp_set_cloud_device_sharded", "pcp_build_grid", "pcp_grid_info", "pcp_radius_pca", "pcp_knn_pca",
     "pcp_knn_pca_kth", "pcp_knn_neighbors", "pcp_radius_neighbors", "pcp_segment_pca", "pcp_ring_calib_default",
-    "pcp_ring_calib_from_xml", "pcp_ring_project", "pcp_set_host_async",
+    "pcp_ring_calib_from_xml", "pcp_ring_project", "pcp_set_host_async", "pcp_alloc_pinned", "pcp_free_pinned",
 )
+
+
+class PinnedArray:
+    """numpy view over page-locked host memory from pcp_alloc_pinned (freed with the object)."""
+
+    def __init__(self, shape, dtype):
+        dtype = np.dtype(dtype)
+        nbytes = int(np.prod(shape)) * dtype.itemsize
+        self._lib = load()
+        self._ptr = self._lib.pcp_alloc_pinned(max(nbytes, 1))
+        if not self._ptr:
+            raise MemoryError(f"pcp_alloc_pinned({nbytes}) failed")
+        buf = (C.c_uint8 * max(nbytes, 1)).from_address(self._ptr)
+        self.array = np.frombuffer(buf, dtype=np.uint8, count=nbytes).view(dtype).reshape(shape)
+        self.ptr = self._ptr
+
+    def __del__(self):
+        if getattr(self, "_ptr", None):
+            self.array = None
+            self._lib.pcp_free_pinned(self._ptr)
+            self._ptr = None
 
 
 class RingCalib(C.Structure):
@@ -87,6 +108,8 @@ def load() -> C.CDLL:
         "pcp_last_timings": (i32, [vp, vp, i32]),
         "pcp_launch_count": (i64, [vp]),
         "pcp_set_host_async": (i32, [vp, i32]),
+        "pcp_alloc_pinned": (vp, [C.c_size_t]),
+        "pcp_free_pinned": (None, [vp]),
         "pcp_set_cloud_host": (i32, [vp, vp, i64, i32]),
         "pcp_set_cloud_device": (i32, [vp, vp, i64]),
         "pcp_set_cloud_device_sharded": (i32, [vp, vp, vp, i64, i64]),

@@ -317,7 +317,7 @@ PCP_API int pcp_ring_project(pcp_ctx* ctx, const pcp_ring_calib* calib, const in
   if ((rc = copy_back(ctx, range_img, d_range, out_is_device, cells))) return rc;
   if ((rc = copy_back(ctx, pt_index, d_index, out_is_device, cells))) return rc;
   if ((rc = copy_back(ctx, long_range, d_long, out_is_device, (size_t)n_frames))) return rc;
-  if (!out_is_device) PCP_CUDA(cudaStreamSynchronize(ctx->stream));
+  if (!out_is_device && !ctx->host_async) PCP_CUDA(cudaStreamSynchronize(ctx->stream));
   return PCP_OK;
 }
 

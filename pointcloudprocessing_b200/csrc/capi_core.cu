@@ -105,6 +105,19 @@ PCP_API int pcp_synchronize(pcp_ctx* ctx) {
   return PCP_OK;
 }
 
+// page-locked host memory for the asynchronous host-pointer calls (plain cudaHostAlloc; no ctx needed)
+PCP_API void* pcp_alloc_pinned(size_t bytes) {
+  void* p = nullptr;
+  if (cudaHostAlloc(&p, bytes ? bytes : 1, cudaHostAllocDefault) != cudaSuccess) {
+    cudaGetLastError();
+    return nullptr;
+  }
+  return p;
+}
+PCP_API void pcp_free_pinned(void* p) {
+  if (p) cudaFreeHost(p);
+}
+
 PCP_API int pcp_set_host_async(pcp_ctx* ctx, int enable) {
   if (!ctx) return PCP_ERR_INVALID_ARG;
   ctx->host_async = enable != 0;

@@ -10,7 +10,8 @@ VLP16_VERT_DEG = np.array([-15, 1, -13, 3, -11, 5, -9, 7, -7, 9, -5, 11, -3, 13,
 
 def urban(seed: int, n: int, extent: float = 200.0, order: str = "random") -> np.ndarray:
     """50 % ground (σz 0.02), 25 % façades on a 20 m lattice (0-15 m high, σ 0.02), 15 % vegetation
-    blobs (σ 1.5 m), 10 % uniform clutter 0-10 m."""
+    blobs (σ 1.5 m), 10 % uniform clutter 0-10 m.  order: "random" permutation, "scan" (by azimuth) or
+    anything else = as generated (class by class)."""
     rng = np.random.default_rng(seed)
     n_g = n // 2
     n_f = n // 4
