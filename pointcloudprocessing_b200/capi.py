@@ -289,6 +289,10 @@ class Pcp:
         self._ck(self.lib.pcp_segment_pca(self.h, centres.ctypes.data, offsets.ctypes.data, idx.ctypes.data, nseg, out.ctypes.data))
         return out
 
+    def ring_project_host_ptr(self, calib: RingCalib, range_ptr: int, index_ptr: int, long_ptr: int):
+        """One frame = the whole current cloud, outputs to raw (page-locked) host pointers."""
+        self._ck(self.lib.pcp_ring_project(self.h, C.byref(calib), None, 1, range_ptr, index_ptr, long_ptr, 0))
+
     def ring_project(self, calib: Optional[RingCalib] = None, frame_offsets: Optional[np.ndarray] = None,
                      range_device: Optional[int] = None, index_device: Optional[int] = None, long_device: Optional[int] = None):
         calib = calib or ring_calib_default()

@@ -1,0 +1,85 @@
+"""Frame batches (BASELINE configs[1] and configs[4]): per VLP-16 frame, ring projection
+(`RingProjector::projectPointCloud`, src/ringProjection.cpp:24-81) + k-NN PCA features
+(the pcaAnalysis path with the lidarOdometry-sized k = 10), many frames in flight.
+
+Frames are independent units: no halo, no collective.  One process drives `n_ctx` contexts
+of the C-ABI round-robin in `pcp_set_host_async` mode with page-locked buffers, so one frame's result
+copy and the next frames' upload, grid build and search overlap on the GPU; across GPUs the frames are
+split into contiguous blocks (`sharding.frame_shard`).  No torch here: numpy + ctypes over libpcp.so.
+"""
+from __future__ import annotations
+
+from typing import List, Optional, Sequence
+
+import numpy as np
+
+from . import capi
+
+
+class FramePipeline:
+    def __init__(self, device: int = 0, n_ctx: int = 4, max_points: int = 32768, calib: Optional[capi.RingCalib] = None):
+        self.calib = calib or capi.ring_calib_default()
+        self.cells = self.calib.n_scan * self.calib.horizon_scan
+        self.ctx = [capi.Pcp(device) for _ in range(n_ctx)]
+        self.max_points = max_points
+        self.slots = []
+        for c in self.ctx:
+            c.set_host_async(True)
+            self.slots.append({
+                "pts": capi.PinnedArray((max_points, 4), np.float32),
+                "feat": capi.PinnedArray((max_points,), capi.FEATURE_DTYPE),
+                "range": capi.PinnedArray((self.cells,), np.float32),
+                "index": capi.PinnedArray((self.cells,), np.int32),
+                "long": capi.PinnedArray((1,), np.int32),
+                "frame": -1, "n": 0,
+            })
+
+    def close(self):
+        for c in self.ctx:
+            c.close()
+        self.ctx, self.slots = [], []
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    def _collect(self, i: int, out: list, copy: bool):
+        s = self.slots[i]
+        if s["frame"] < 0:
+            return
+        self.ctx[i].synchronize()
+        n = s["n"]
+        if copy:
+            out[s["frame"]] = {
+                "features": s["feat"].array[:n].copy(),
+                "range": s["range"].array.reshape(self.calib.n_scan, self.calib.horizon_scan).copy(),
+                "index": s["index"].array.reshape(self.calib.n_scan, self.calib.horizon_scan).copy(),
+                "long_range": int(s["long"].array[0]),
+            }
+        s["frame"] = -1
+
+    def run(self, frames: Sequence[np.ndarray], k: int = 10, cell: float = 0.0, ring: bool = True, keep: bool = True) -> List[dict]:
+        """frames[f] = (n_f, 4) float32 x,y,z,intensity in firing order.  Returns one dict per frame
+        (features = n_f pcaFeature records, range / index = the 16x1800 images, long_range) — or, with
+        keep=False, only runs the work (throughput measurements)."""
+        out: List[Optional[dict]] = [None] * len(frames)
+        nc = len(self.ctx)
+        for f, fr in enumerate(frames):
+            i = f % nc
+            self._collect(i, out, keep)  # the slot's previous frame is complete; its buffers are free
+            c, s = self.ctx[i], self.slots[i]
+            n = fr.shape[0]
+            if n > self.max_points:
+                raise ValueError(f"frame {f} has {n} points; pipeline was sized for {self.max_points}")
+            s["pts"].array[:n] = fr
+            s["frame"], s["n"] = f, n
+            c.set_cloud_host_ptr(s["pts"].ptr, n, 16)
+            if ring:
+                c.ring_project_host_ptr(self.calib, s["range"].ptr, s["index"].ptr, s["long"].ptr)
+            c.build_grid(cell, k)
+            c.knn_pca(k, capi.CENTER_QUERY, out_host_ptr=s["feat"].ptr)
+        for i in range(nc):
+            self._collect(i, out, keep)
+        return out
