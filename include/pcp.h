@@ -132,6 +132,19 @@ PCP_API int pcp_set_cloud_device(pcp_ctx* ctx, const void* d_xyzi, int64_t n);
 PCP_API int pcp_set_cloud_device_sharded(pcp_ctx* ctx, const void* d_xyzi, const int32_t* d_global_id,
                                          int64_t n, int64_t n_query);
 
+/* ---- slab sharding: halo classification ----------------------------------------------
+ * Multi-GPU form of the loop at src/pcaAnalysis.cpp:18-40 (the reference is one process):
+ * a rank owns the slab [lo_face, hi_face) along `axis` (0/1/2 = x/y/z) and gives each slab neighbour
+ * its points within `h` of the shared face.  Appends every own point with coord < lo_face + h to the
+ * "lo" buffer and every point with coord >= hi_face - h to the "hi" buffer (float4 + global index,
+ * `cap` entries each, device memory), pads the unused tails with non-finite points (global index
+ * INT32_MAX), which no search ever returns, and leaves the true counts in d_counts[0..1] (a count
+ * above cap means the buffer was too small: points were dropped).  d_global_id may be NULL (identity).
+ * Enqueues on the ctx stream; no host synchronisation. */
+PCP_API int pcp_halo_pack(pcp_ctx* ctx, const void* d_xyzi, const int32_t* d_global_id, int64_t n, int axis, float lo_face,
+                          float hi_face, float h, int64_t cap, void* d_lo_pts, int32_t* d_lo_gid, void* d_hi_pts,
+                          int32_t* d_hi_gid, uint32_t* d_counts);
+
 /* ---- index build ------------------------------------------------------------------
  * Replaces the FLANN KDTreeSingleIndex build inside setInputCloud (src/pcaAnalysis.cpp:15):
  * bbox reduce → cell keys → radix sort → cell table (prefix scan).  `cell` > 0 is the

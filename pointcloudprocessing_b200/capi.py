@@ -41,7 +41,7 @@ EXPORTS = (
     "pcp_last_timings", "pcp_launch_count", "pcp_set_cloud_host", "pcp_set_cloud_device",
     "pcp_set_cloud_device_sharded", "pcp_build_grid", "pcp_grid_info", "pcp_radius_pca", "pcp_knn_pca",
     "pcp_knn_pca_kth", "pcp_knn_neighbors", "pcp_radius_neighbors", "pcp_segment_pca", "pcp_ring_calib_default",
-    "pcp_ring_calib_from_xml", "pcp_ring_project", "pcp_set_host_async", "pcp_alloc_pinned", "pcp_free_pinned",
+    "pcp_ring_calib_from_xml", "pcp_ring_project", "pcp_set_host_async", "pcp_alloc_pinned", "pcp_free_pinned", "pcp_halo_pack",
 )
 
 
@@ -110,6 +110,7 @@ def load() -> C.CDLL:
         "pcp_set_host_async": (i32, [vp, i32]),
         "pcp_alloc_pinned": (vp, [C.c_size_t]),
         "pcp_free_pinned": (None, [vp]),
+        "pcp_halo_pack": (i32, [vp, vp, vp, i64, i32, f32, f32, f32, i64, vp, vp, vp, vp, vp]),
         "pcp_set_cloud_host": (i32, [vp, vp, i64, i32]),
         "pcp_set_cloud_device": (i32, [vp, vp, i64]),
         "pcp_set_cloud_device_sharded": (i32, [vp, vp, vp, i64, i64]),
@@ -200,6 +201,12 @@ class Pcp:
 
     def synchronize(self):
         self._ck(self.lib.pcp_synchronize(self.h))
+
+    def halo_pack(self, d_pts: int, d_gid: Optional[int], n: int, axis: int, lo_face: float, hi_face: float, h: float, cap: int,
+                  d_lo_pts: int, d_lo_gid: int, d_hi_pts: int, d_hi_gid: int, d_counts: int):
+        """Device pointers throughout; see pcp_halo_pack."""
+        self._ck(self.lib.pcp_halo_pack(self.h, d_pts, d_gid, n, axis, lo_face, hi_face, h, cap, d_lo_pts, d_lo_gid, d_hi_pts,
+                                        d_hi_gid, d_counts))
 
     def set_host_async(self, enable: bool):
         """Host-pointer calls only enqueue (pinned buffers, caller synchronises): see pcp_set_host_async."""

@@ -107,3 +107,68 @@ def knn_halo_violations(own_pts: torch.Tensor, kth_d2: torch.Tensor, axis: int, 
 def radius_halo_width(radius: float) -> float:
     """Radius search: a halo of r (plus rounding slack) is exact."""
     return float(radius) * (1.0 + 1e-5) + 1e-6
+
+
+class SlabExchange:
+    """Fixed-capacity halo exchange of one slab rank, with NO host synchronisation per step.
+
+    Persistent device buffers hold `own ‖ halo-from-low-neighbour ‖ halo-from-high-neighbour`
+    (n_own + 2·cap points; unused entries are non-finite padding that the grid ignores).  A step is:
+    `pcp_halo_pack` (one classification kernel into the two send buffers) → one grouped NCCL
+    send/recv per neighbour straight into the halo regions → `pcp_set_cloud_device_sharded`.  Sizes
+    never depend on data, so nothing has to reach the host before the grid build is enqueued; the true
+    strip sizes stay in `counts` (device) and `check()` verifies them once, outside the hot loop."""
+
+    INT_MAX = 0x7FFFFFFF
+
+    def __init__(self, pcp, n_own: int, cap: int, device, rank: int, world: int, axis: int, lo: float, hi: float, h: float,
+                 group=None):
+        self.pcp, self.n_own, self.cap, self.rank, self.world = pcp, n_own, cap, rank, world
+        self.axis, self.lo, self.hi, self.h, self.group = axis, float(lo), float(hi), float(h), group
+        n_all = n_own + 2 * cap
+        self.buf_pts = torch.full((n_all, 4), float("nan"), dtype=torch.float32, device=device)
+        self.buf_pts[:, 3] = 0
+        self.buf_gid = torch.full((n_all,), self.INT_MAX, dtype=torch.int32, device=device)
+        self.send_pts = [torch.empty((cap, 4), dtype=torch.float32, device=device) for _ in range(2)]
+        self.send_gid = [torch.empty((cap,), dtype=torch.int32, device=device) for _ in range(2)]
+        self.counts = torch.zeros(2, dtype=torch.int32, device=device)
+
+    @property
+    def own_pts(self) -> torch.Tensor:
+        return self.buf_pts[: self.n_own]
+
+    @property
+    def own_gid(self) -> torch.Tensor:
+        return self.buf_gid[: self.n_own]
+
+    def halo_region(self, side: int):
+        a = self.n_own + side * self.cap
+        return self.buf_pts[a: a + self.cap], self.buf_gid[a: a + self.cap]
+
+    def pack(self):
+        self.pcp.halo_pack(self.own_pts.data_ptr(), self.own_gid.data_ptr(), self.n_own, self.axis, self.lo, self.hi, self.h,
+                           self.cap, self.send_pts[0].data_ptr(), self.send_gid[0].data_ptr(), self.send_pts[1].data_ptr(),
+                           self.send_gid[1].data_ptr(), self.counts.data_ptr())
+
+    def step(self):
+        """Enqueue pack + exchange + hand-over on the CURRENT torch stream (use the library's stream)."""
+        self.pack()
+        ops = []
+        for side, nb in ((0, self.rank - 1), (1, self.rank + 1)):
+            if nb < 0 or nb >= self.world:
+                continue
+            rp, rg = self.halo_region(side)
+            ops += [dist.P2POp(dist.isend, self.send_pts[side], nb, self.group), dist.P2POp(dist.isend, self.send_gid[side], nb, self.group),
+                    dist.P2POp(dist.irecv, rp, nb, self.group), dist.P2POp(dist.irecv, rg, nb, self.group)]
+        if ops:
+            for w in dist.batch_isend_irecv(ops):
+                w.wait()
+        self.pcp.set_cloud_device(self.buf_pts.data_ptr(), self.buf_pts.shape[0], self.buf_gid.data_ptr(), self.n_own,
+                                  keep=(self.buf_pts, self.buf_gid))
+
+    def check(self):
+        """Host check (synchronises): did both strips fit their buffers?"""
+        c = self.counts.tolist()
+        if max(c) > self.cap:
+            raise RuntimeError(f"rank {self.rank}: halo strips of {c} points exceed the capacity {self.cap}")
+        return c
