@@ -34,6 +34,20 @@ def peaks():
     return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
 
 
+def ncu_traffic(n: int):
+    """DRAM bytes per launch of the search stage (dram__bytes_read.sum + dram__bytes_write.sum of its two
+    kernels) from the committed `ncu --set full` capture of this workload; null for any other size."""
+    path = os.path.join(ROOT, "profiles", "r01b_knn_tile_and_worklist_ncu_summary.txt")
+    if n != 1_000_000 or not os.path.exists(path):
+        return None
+    total = 0.0
+    with open(path) as f:
+        for line in f:
+            if line.startswith("dram__bytes_read.sum [Mbyte]") or line.startswith("dram__bytes_write.sum [Mbyte]"):
+                total += float(line.split("=")[1]) * 1e6
+    return total or None
+
+
 class ClockSampler:
     """Samples SM clock and throttle reasons through NVML while the timed region runs."""
 
@@ -336,7 +350,7 @@ def main():
         "e2e": {"value": total_pts / (e2e_ms * 1e-3), "unit": "points/s", "h2d_bytes_per_step": 16 * n, "d2h_bytes_per_step": 68 * n,
                 "mode": e2e_mode, "sequential_value": total_pts / e2e_seq_s},
         "gpu_launches": int(launches),
-        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": ncu_traffic(n),
                      "kernel": "knn_tile_kernel + search_pca_worklist_kernel<0> (one stage: the tile kernel serves ~90 % of the queries, the work-list kernel the rest)", "bytes_per_point": ALGO_BYTES_PER_POINT, "peak_source": peak_src,
                      "kernel_ms": kern_avg_s * 1e3,
                      "note": "k-NN selection is issue-bound (≈1.5-3 kFLOP + top-k per point), far below the HBM roof by construction"},

@@ -47,12 +47,28 @@ __global__ void __launch_bounds__(256) bbox_kernel(const float4* __restrict__ pt
       hi[d] = fmaxf(hi[d], __shfl_xor_sync(0xffffffffu, hi[d], o));
     }
   }
-  if ((threadIdx.x & 31) == 0) {
+  // block-level combine, then six atomics per block (thousands of warps hammering six words was
+  // most of this kernel's time)
+  __shared__ float s_lo[8][3], s_hi[8][3];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (lane == 0) {
 #pragma unroll
     for (int d = 0; d < 3; ++d) {
-      atomicMin(bbox + d, enc_ordered(lo[d]));
-      atomicMax(bbox + 3 + d, enc_ordered(hi[d]));
+      s_lo[warp][d] = lo[d];
+      s_hi[warp][d] = hi[d];
     }
+  }
+  __syncthreads();
+  if (threadIdx.x < 3) {
+    const int d = threadIdx.x;
+    float l = s_lo[0][d], h = s_hi[0][d];
+#pragma unroll
+    for (int w = 1; w < 8; ++w) {
+      l = fminf(l, s_lo[w][d]);
+      h = fmaxf(h, s_hi[w][d]);
+    }
+    atomicMin(bbox + d, enc_ordered(l));
+    atomicMax(bbox + 3 + d, enc_ordered(h));
   }
 }
 
@@ -141,7 +157,7 @@ int pcp_grid_build_impl(pcp_ctx* ctx, float cell, int k_hint) {
   bbox_init_kernel<<<1, 32, 0, st>>>((uint32_t*)ctx->bbox.p);
   PCP_LAUNCH_CHECK("bbox_init_kernel");
   {
-    int blocks = (int)std::min<int64_t>((n + 255) / 256, 148 * 8);
+    int blocks = (int)std::min<int64_t>((n + 255) / 256, 148 * 4);
     bbox_kernel<<<blocks, 256, 0, st>>>(ctx->d_cloud, n, (uint32_t*)ctx->bbox.p);
     PCP_LAUNCH_CHECK("bbox_kernel");
   }

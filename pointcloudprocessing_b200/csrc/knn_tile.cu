@@ -168,7 +168,12 @@ __global__ void __launch_bounds__(TA_WARPS * 32, 5) knn_tile_kernel(KArgs a, int
   for (int grp = 0; grp < max_groups; ++grp) {
     const unsigned pmask = __ballot_sync(PCP_FULL, pending);
     if (pmask == 0) break;
-    const uint32_t row0 = __shfl_sync(PCP_FULL, my_row, __ffs(pmask) - 1);
+    // the group's row: the one most pending lanes share (a tile that crosses a row end keeps its larger part)
+    const unsigned peers = __match_any_sync(PCP_FULL, pending ? my_row : 0xFFFFFFFFu);
+    const int votes = pending ? __popc(peers) : 0;
+    const int best_votes = __reduce_max_sync(PCP_FULL, votes);
+    const unsigned lead = __ballot_sync(PCP_FULL, pending && votes == best_votes);
+    const uint32_t row0 = __shfl_sync(PCP_FULL, my_row, __ffs(lead) - 1);
     const bool in_grp = pending && my_row == row0;
     pending = pending && !in_grp;
     const int c1 = (int)(row0 % (uint32_t)g.dim[1]), c2 = (int)(row0 / (uint32_t)g.dim[1]);

@@ -3,12 +3,13 @@
 (the pcaAnalysis path with the lidarOdometry-sized k = 10), many frames in flight.
 
 Frames are independent units: no halo, no collective.  One process drives `n_ctx` contexts
-of the C-ABI round-robin in `pcp_set_host_async` mode with page-locked buffers, so one frame's result
-copy and the next frames' upload, grid build and search overlap on the GPU; across GPUs the frames are
+of the C-ABI, one host thread each, with page-locked buffers, so the frames of different contexts
+overlap on the GPU (upload, grid build, search, result copy) and on the host (launch latency); across GPUs the frames are
 split into contiguous blocks (`sharding.frame_shard`).  No torch here: numpy + ctypes over libpcp.so.
 """
 from __future__ import annotations
 
+import threading
 from typing import List, Optional, Sequence
 
 import numpy as np
@@ -66,20 +67,41 @@ class FramePipeline:
         keep=False, only runs the work (throughput measurements)."""
         out: List[Optional[dict]] = [None] * len(frames)
         nc = len(self.ctx)
-        for f, fr in enumerate(frames):
-            i = f % nc
-            self._collect(i, out, keep)  # the slot's previous frame is complete; its buffers are free
+
+        def worker(i: int):
+            # context i serves frames i, i + nc, ...; each context has its own host thread (the C-ABI
+            # calls release the GIL), so the per-frame launch latency and the grid build's wait for the
+            # bounding box overlap across contexts
             c, s = self.ctx[i], self.slots[i]
-            n = fr.shape[0]
-            if n > self.max_points:
-                raise ValueError(f"frame {f} has {n} points; pipeline was sized for {self.max_points}")
-            s["pts"].array[:n] = fr
-            s["frame"], s["n"] = f, n
-            c.set_cloud_host_ptr(s["pts"].ptr, n, 16)
-            if ring:
-                c.ring_project_host_ptr(self.calib, s["range"].ptr, s["index"].ptr, s["long"].ptr)
-            c.build_grid(cell, k)
-            c.knn_pca(k, capi.CENTER_QUERY, out_host_ptr=s["feat"].ptr)
-        for i in range(nc):
-            self._collect(i, out, keep)
+            for f in range(i, len(frames), nc):
+                fr = frames[f]
+                n = fr.shape[0]
+                if n > self.max_points:
+                    raise ValueError(f"frame {f} has {n} points; pipeline was sized for {self.max_points}")
+                s["pts"].array[:n] = fr
+                s["frame"], s["n"] = f, n
+                c.set_cloud_host_ptr(s["pts"].ptr, n, 16)
+                if ring:
+                    c.ring_project_host_ptr(self.calib, s["range"].ptr, s["index"].ptr, s["long"].ptr)
+                c.build_grid(cell, k)
+                c.knn_pca(k, capi.CENTER_QUERY, out_host_ptr=s["feat"].ptr)
+                self._collect(i, out, keep)
+
+        if nc == 1:
+            worker(0)
+        else:
+            threads = [threading.Thread(target=self._guard, args=(worker, i)) for i in range(nc)]
+            self._errors = []
+            for t in threads:
+                t.start()
+            for t in threads:
+                t.join()
+            if self._errors:
+                raise self._errors[0]
         return out
+
+    def _guard(self, fn, i):
+        try:
+            fn(i)
+        except BaseException as e:  # re-raised by run() in the calling thread
+            self._errors.append(e)
