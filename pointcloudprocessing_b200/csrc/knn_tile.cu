@@ -39,22 +39,24 @@ namespace {
 
 constexpr int TA_WARPS = 4;        // warps per CTA
 constexpr int TA_CH = 128;         // staged candidates per chunk
-constexpr int TA_BINS = 64;        // linear d2 bins inside the cover radius (+1 overflow bin)
-constexpr int TA_CAP = 32;         // candidates a lane can hold (sorting-network width)
+// CAP (template parameter, 24 or 32) = candidates a lane can hold = width of the sorting network;
+// the histogram has BINS = 2*CAP - 1 linear d2 bins inside the cover radius + 1 overflow bin, so that it
+// occupies exactly the rows the candidate keys use afterwards.
 constexpr int TA_REC_WORDS = 17;   // 68-byte record
 constexpr int TA_MAXROWS = 64;     // stencil rows of a tile: (2R+1)^2 <= 49, R <= 3
 constexpr int TA_MAXR = 3;
 constexpr int TA_MAXGROUPS = 1;    // stencil rows (row groups) served per tile by default; lanes of further rows are
                                    // deferred (measured: a second pass for a few lanes costs more than deferring them)
 
+template <int CAP>
 struct __align__(16) TaSmem {
   float4 cand[TA_CH];                    // staged candidates of the current chunk
   // One 32-bit column per lane, two uses: pass 1 counts into hist[bin][lane] (bin 64 = beyond the cover
-  // radius); pass 2 stores candidate j's key as lo word plane[j][lane] and hi word plane[32 + j][lane].
+  // radius, BINS = 2*CAP-1); pass 2 stores candidate j's key as lo word plane[j][lane] and hi word plane[CAP + j][lane].
   // Both live in the lane's OWN column, so a lane of a later row group can histogram while the lanes
   // already served keep their candidates.  The record staging reuses the space at the end.
   union U {
-    uint32_t plane[TA_BINS + 1][32];
+    uint32_t plane[2 * CAP][32];
     float rec[32][TA_REC_WORDS];
   } u;
   uint32_t run_beg[TA_MAXROWS];          // first sorted position of each stencil row's run
@@ -71,7 +73,8 @@ __device__ __forceinline__ float frac_of(const GridDesc& g, int ax, const float4
 
 // copies candidates [cb, cb + cnt) of the tile's virtual candidate sequence (the stencil rows' runs laid
 // end to end) into sm.cand: row by row, the 32 lanes reading consecutive float4 of the run
-__device__ __forceinline__ void stage_chunk(const float4* __restrict__ sorted, TaSmem& sm, int nrows, uint32_t cb, int cnt,
+template <int CAP>
+__device__ __forceinline__ void stage_chunk(const float4* __restrict__ sorted, TaSmem<CAP>& sm, int nrows, uint32_t cb, int cnt,
                                             int lane) {
   const uint32_t ce = cb + (uint32_t)cnt;
 #pragma unroll 1
@@ -91,7 +94,8 @@ __device__ __forceinline__ void stage_chunk(const float4* __restrict__ sorted, T
 // cover_cells = radius (in cells) around THIS lane's query that the union is guaranteed to cover: its
 // distance to the nearest face of the union block that still has cells behind it (a face on the grid
 // boundary has no points beyond it), minus 2e-3 cells for the rounding of the fractional position.
-__device__ __forceinline__ uint32_t tile_setup(const KArgs& a, TaSmem& sm, const int lane, const int R, const int c0min,
+template <int CAP>
+__device__ __forceinline__ uint32_t tile_setup(const KArgs& a, TaSmem<CAP>& sm, const int lane, const int R, const int c0min,
                                                const int c0max, const int c1, const int c2, const int c0, const float4 Q,
                                                int& nrows, bool& whole, float& cover_cells) {
   const GridDesc& g = a.g;
@@ -139,10 +143,12 @@ __device__ __forceinline__ uint32_t tile_setup(const KArgs& a, TaSmem& sm, const
   return total;
 }
 
-__global__ void __launch_bounds__(TA_WARPS * 32, 5) knn_tile_kernel(KArgs a, int R0, float grow, int max_groups, uint32_t* __restrict__ work_count,
+template <int CAP>
+__global__ void __launch_bounds__(TA_WARPS * 32, CAP == 24 ? 6 : 5) knn_tile_kernel(KArgs a, int R0, float grow, int max_groups, uint32_t* __restrict__ work_count,
                                                                  uint32_t* __restrict__ work_list) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  TaSmem& sm = reinterpret_cast<TaSmem*>(smem_raw)[threadIdx.x >> 5];
+  constexpr int BINS = 2 * CAP - 1;
+  TaSmem<CAP>& sm = reinterpret_cast<TaSmem<CAP>*>(smem_raw)[threadIdx.x >> 5];
   const int lane = threadIdx.x & 31;
   const int64_t pos0 = ((int64_t)blockIdx.x * TA_WARPS + (threadIdx.x >> 5)) * 32;
   if (pos0 >= a.n) return;  // whole warp
@@ -157,7 +163,7 @@ __global__ void __launch_bounds__(TA_WARPS * 32, 5) knn_tile_kernel(KArgs a, int
   const bool active = my_slot >= 0;
   const bool finite = active && cid < g.n_cells;
   uint32_t* const hcol = &sm.u.plane[0][lane];
-  uint32_t* wp = hcol;       // next free entry of this lane's candidate column (lo word; hi word 32 rows on)
+  uint32_t* wp = hcol;       // next free entry of this lane's candidate column (lo word; hi word CAP rows on)
   const uint32_t my_row = cid / (uint32_t)g.dim[0];
   const int c0 = (int)(cid - my_row * (uint32_t)g.dim[0]);
   bool pending = finite;     // not yet served by a row group
@@ -188,10 +194,10 @@ __global__ void __launch_bounds__(TA_WARPS * 32, 5) knn_tile_kernel(KArgs a, int
       bool whole;
       float cover_cells;
       total = tile_setup(a, sm, lane, R, c0min, c0max, c1, c2, c0, Q, nrows, whole, cover_cells);
-      Sb = (float)TA_BINS / (cover_cells * cover_cells * g.cell * g.cell * (1.f - 1e-6f));
+      Sb = (float)BINS / (cover_cells * cover_cells * g.cell * g.cell * (1.f - 1e-6f));
       if (in_grp) {
 #pragma unroll
-        for (int b = 0; b <= TA_BINS; ++b) hcol[b * 32] = 0;
+        for (int b = 0; b <= BINS; ++b) hcol[b * 32] = 0;
       }
 #pragma unroll 1
       for (uint32_t cb = 0; cb < total; cb += TA_CH) {
@@ -203,10 +209,10 @@ __global__ void __launch_bounds__(TA_WARPS * 32, 5) knn_tile_kernel(KArgs a, int
 #pragma unroll 2
         for (; j + 4 <= cnt; j += 4) {
           const float4 P0 = sm.cand[j], P1 = sm.cand[j + 1], P2 = sm.cand[j + 2], P3 = sm.cand[j + 3];
-          const int b0 = __float2int_rz(fminf(dist2_nofma(Q.x, Q.y, Q.z, P0) * Sb, (float)TA_BINS));
-          const int b1 = __float2int_rz(fminf(dist2_nofma(Q.x, Q.y, Q.z, P1) * Sb, (float)TA_BINS));
-          const int b2 = __float2int_rz(fminf(dist2_nofma(Q.x, Q.y, Q.z, P2) * Sb, (float)TA_BINS));
-          const int b3 = __float2int_rz(fminf(dist2_nofma(Q.x, Q.y, Q.z, P3) * Sb, (float)TA_BINS));
+          const int b0 = __float2int_rz(fminf(dist2_nofma(Q.x, Q.y, Q.z, P0) * Sb, (float)BINS));
+          const int b1 = __float2int_rz(fminf(dist2_nofma(Q.x, Q.y, Q.z, P1) * Sb, (float)BINS));
+          const int b2 = __float2int_rz(fminf(dist2_nofma(Q.x, Q.y, Q.z, P2) * Sb, (float)BINS));
+          const int b3 = __float2int_rz(fminf(dist2_nofma(Q.x, Q.y, Q.z, P3) * Sb, (float)BINS));
           if (in_grp) {
             atomicAdd(&hcol[b0 * 32], 1u);
             atomicAdd(&hcol[b1 * 32], 1u);
@@ -215,7 +221,7 @@ __global__ void __launch_bounds__(TA_WARPS * 32, 5) knn_tile_kernel(KArgs a, int
           }
         }
         for (; j < cnt; ++j) {
-          const int b0 = __float2int_rz(fminf(dist2_nofma(Q.x, Q.y, Q.z, sm.cand[j]) * Sb, (float)TA_BINS));
+          const int b0 = __float2int_rz(fminf(dist2_nofma(Q.x, Q.y, Q.z, sm.cand[j]) * Sb, (float)BINS));
           if (in_grp) atomicAdd(&hcol[b0 * 32], 1u);
         }
         __syncwarp();
@@ -225,7 +231,7 @@ __global__ void __launch_bounds__(TA_WARPS * 32, 5) knn_tile_kernel(KArgs a, int
       bstar = -1;
       if (in_grp) {
 #pragma unroll 8
-        for (int b = 0; b < TA_BINS; ++b) {
+        for (int b = 0; b < BINS; ++b) {
           cum += (int)hcol[b * 32];
           if (bstar < 0 && cum >= k) {
             bstar = b;
@@ -245,8 +251,8 @@ __global__ void __launch_bounds__(TA_WARPS * 32, 5) knn_tile_kernel(KArgs a, int
     }
     TSTAT(2, lane == 0 ? total : 0);
     TSTAT(5, (in_grp && bstar < 0) ? 1 : 0);                          // deferred: k-th beyond the cover radius
-    TSTAT(6, (in_grp && bstar >= 0 && cum_star > TA_CAP) ? 1 : 0);    // deferred: threshold bin too full
-    const bool grp_ok = in_grp && bstar >= 0 && cum_star <= TA_CAP;
+    TSTAT(6, (in_grp && bstar >= 0 && cum_star > CAP) ? 1 : 0);    // deferred: threshold bin too full
+    const bool grp_ok = in_grp && bstar >= 0 && cum_star <= CAP;
     const float thr_bin = grp_ok ? (float)(bstar + 1) : -1.f;  // other lanes collect nothing
     __syncwarp();
     // ---- pass 2: collect the candidates at or below the threshold bin (same d2 arithmetic, same bins)
@@ -302,15 +308,15 @@ __global__ void __launch_bounds__(TA_WARPS * 32, 5) knn_tile_kernel(KArgs a, int
           const float4 P0 = sm.cand[j], P1 = sm.cand[j + 1], P2 = sm.cand[j + 2], P3 = sm.cand[j + 3];
           const float e0 = dist2_nofma(Q.x, Q.y, Q.z, P0), e1 = dist2_nofma(Q.x, Q.y, Q.z, P1);
           const float e2 = dist2_nofma(Q.x, Q.y, Q.z, P2), e3 = dist2_nofma(Q.x, Q.y, Q.z, P3);
-          if (e0 * Sb < thr_bin) { wp[0] = __float_as_uint(P0.w); wp[1024] = __float_as_uint(e0); wp += 32; }
-          if (e1 * Sb < thr_bin) { wp[0] = __float_as_uint(P1.w); wp[1024] = __float_as_uint(e1); wp += 32; }
-          if (e2 * Sb < thr_bin) { wp[0] = __float_as_uint(P2.w); wp[1024] = __float_as_uint(e2); wp += 32; }
-          if (e3 * Sb < thr_bin) { wp[0] = __float_as_uint(P3.w); wp[1024] = __float_as_uint(e3); wp += 32; }
+          if (e0 * Sb < thr_bin) { wp[0] = __float_as_uint(P0.w); wp[CAP * 32] = __float_as_uint(e0); wp += 32; }
+          if (e1 * Sb < thr_bin) { wp[0] = __float_as_uint(P1.w); wp[CAP * 32] = __float_as_uint(e1); wp += 32; }
+          if (e2 * Sb < thr_bin) { wp[0] = __float_as_uint(P2.w); wp[CAP * 32] = __float_as_uint(e2); wp += 32; }
+          if (e3 * Sb < thr_bin) { wp[0] = __float_as_uint(P3.w); wp[CAP * 32] = __float_as_uint(e3); wp += 32; }
         }
         for (; j < n_ch; ++j) {
           const float4 P0 = sm.cand[j];
           const float e0 = dist2_nofma(Q.x, Q.y, Q.z, P0);
-          if (e0 * Sb < thr_bin) { wp[0] = __float_as_uint(P0.w); wp[1024] = __float_as_uint(e0); wp += 32; }
+          if (e0 * Sb < thr_bin) { wp[0] = __float_as_uint(P0.w); wp[CAP * 32] = __float_as_uint(e0); wp += 32; }
         }
         __syncwarp();
       }
@@ -334,10 +340,14 @@ __global__ void __launch_bounds__(TA_WARPS * 32, 5) knn_tile_kernel(KArgs a, int
     }
   }
   // ---- order the collected keys by (d2, index)
-  u64 best[TA_CAP];
+  u64 keys[CAP];
 #pragma unroll
-  for (int j = 0; j < TA_CAP; ++j) best[j] = j < cnt ? (((u64)hcol[(32 + j) * 32] << 32) | (u64)hcol[j * 32]) : PCP_KEY_INF;
-  sort32_regs(best);
+  for (int j = 0; j < CAP; ++j) keys[j] = j < cnt ? (((u64)hcol[(CAP + j) * 32] << 32) | (u64)hcol[j * 32]) : PCP_KEY_INF;
+  if (CAP == 24) sort24_regs(reinterpret_cast<u64(&)[24]>(keys));
+  else sort32_regs(reinterpret_cast<u64(&)[32]>(keys));
+  u64 best[32];
+#pragma unroll
+  for (int j = 0; j < 32; ++j) best[j] = j < CAP ? keys[j < CAP ? j : 0] : PCP_KEY_INF;
   const int n_nb = ok ? k : 0;
   const bool emit = active && (ok || !finite);  // non-finite queries get their empty record here
   __syncwarp();
@@ -365,16 +375,27 @@ int pcp_knn_tile_launch(pcp_ctx* ctx, const SearchParams& sp, const KArgs& a) {
   PCP_CUDA(cudaMemsetAsync(ctx->work_count.p, 0, sizeof(uint32_t), ctx->stream));
   const int64_t tiles = (ctx->n + 31) / 32;
   const int blocks = (int)((tiles + TA_WARPS - 1) / TA_WARPS);
-  const size_t smem = sizeof(TaSmem) * TA_WARPS;
-  PCP_CUDA(cudaFuncSetAttribute(knn_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   // a tile's stencil is widened when (uncovered lanes) * grow exceeds the size of the wider union
-  // (tuning hook: PCP_KNN_RGROW; 0 = never widen)
-  float grow = 0.f;  // ~ instructions per deferred query / instructions per staged candidate
+  // (tuning hook: PCP_KNN_RGROW; 0 = never widen: measured slower on the urban cloud)
+  float grow = 0.f;
   if (const char* e = getenv("PCP_KNN_RGROW")) grow = (float)atof(e);
   int max_groups = TA_MAXGROUPS;  // stencil rows served per tile (tuning hook: PCP_KNN_GROUPS)
   if (const char* e = getenv("PCP_KNN_GROUPS")) max_groups = atoi(e);
-  knn_tile_kernel<<<blocks, TA_WARPS * 32, smem, ctx->stream>>>(a, sp.R0, grow, max_groups, (uint32_t*)ctx->work_count.p,
-                                                                 (uint32_t*)ctx->work_list.p);
+  // 32-entry lanes by default; PCP_KNN_CAP=24 selects 24-entry lanes for k <= 20 (smaller network, 77
+  // registers, 6 CTAs/SM) — measured SLOWER on the urban cloud (1.82 vs 1.63 ms): its 47 bins leave more
+  // lanes with an over-full threshold bin than the extra occupancy pays for
+  const char* capenv = getenv("PCP_KNN_CAP");
+  if (sp.k <= 20 && capenv && capenv[0] == '2') {
+    const size_t smem = sizeof(TaSmem<24>) * TA_WARPS;
+    PCP_CUDA(cudaFuncSetAttribute(knn_tile_kernel<24>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    knn_tile_kernel<24><<<blocks, TA_WARPS * 32, smem, ctx->stream>>>(a, sp.R0, grow, max_groups, (uint32_t*)ctx->work_count.p,
+                                                                      (uint32_t*)ctx->work_list.p);
+  } else {
+    const size_t smem = sizeof(TaSmem<32>) * TA_WARPS;
+    PCP_CUDA(cudaFuncSetAttribute(knn_tile_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    knn_tile_kernel<32><<<blocks, TA_WARPS * 32, smem, ctx->stream>>>(a, sp.R0, grow, max_groups, (uint32_t*)ctx->work_count.p,
+                                                                      (uint32_t*)ctx->work_list.p);
+  }
   PCP_LAUNCH_CHECK("knn_tile_kernel");
   return PCP_OK;
 }
