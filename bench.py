@@ -169,6 +169,7 @@ def main():
     ap.add_argument("--cpu-sample", type=int, default=1_000_000)
     ap.add_argument("--halo", type=float, default=6.0, help="slab halo width in metres (N > 1)")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--e2e-contexts", type=int, default=3, help="C-ABI contexts in flight for the end-to-end figure (N = 1)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -293,25 +294,26 @@ def main():
     p.synchronize()
     e2e_seq_s = time.perf_counter() - t0
     barrier()
-    # (b) pipelined: two contexts in pcp_set_host_async mode, step s+1's upload + grid + search overlap
-    # step s's 68 MB result copy; every step still uploads its cloud and downloads its records
+    # (b) pipelined: several contexts in pcp_set_host_async mode, the next steps' upload + grid + search
+    # overlap a step's 68 MB result copy; every step still uploads its cloud and downloads its records
     e2e_s = e2e_seq_s
     e2e_mode = "sequential, 1 context"
     if world == 1:
-        p2 = capi.Pcp(local)
-        ctxs = [p, p2]
-        h_outs = [h_out, torch.empty(n * 68, dtype=torch.uint8).pin_memory()]
+        extra = [capi.Pcp(local) for _ in range(args.e2e_contexts - 1)]
+        ctxs = [p] + extra
+        nctx = len(ctxs)
+        h_outs = [h_out] + [torch.empty(n * 68, dtype=torch.uint8).pin_memory() for _ in extra]
         for c in ctxs:
             c.set_host_async(True)
 
         def step_async(s):
-            c = ctxs[s & 1]
+            c = ctxs[s % nctx]
             c.synchronize()  # its previous cloud (step s-2) is complete; buffers may be reused
             c.set_cloud_host_ptr(h_in.data_ptr(), n, 16)
             c.build_grid(args.cell, k)
-            c.knn_pca(k, capi.CENTER_QUERY, out_host_ptr=h_outs[s & 1].data_ptr())
+            c.knn_pca(k, capi.CENTER_QUERY, out_host_ptr=h_outs[s % nctx].data_ptr())
 
-        for s in range(4):
+        for s in range(2 * nctx):
             step_async(s)
         for c in ctxs:
             c.synchronize()
@@ -322,10 +324,11 @@ def main():
         for c in ctxs:
             c.synchronize()
         e2e_s = time.perf_counter() - t0
-        e2e_mode = "2 contexts double-buffered (pcp_set_host_async), each step = H2D cloud + grid + search + D2H records"
+        e2e_mode = f"{nctx} contexts in flight (pcp_set_host_async), each step = H2D cloud + grid + search + D2H records"
         for c in ctxs:
             c.set_host_async(False)
-        p2.close()
+        for c in extra:
+            c.close()
         barrier()
 
     t = torch.tensor([dev_ms, e2e_s * 1e3, kern_ms], dtype=torch.float64, device=local)
