@@ -8,10 +8,11 @@
 #include "search_common.cuh"
 
 // best[0..n_nb) = this lane's neighbours ascending by (d2, index) as keys bits(d2) << 32 | ord;
-// my_slot < 0: the lane has no query.  rec_all = 32 x 17 floats of warp-private shared memory that no
+// my_slot < 0: the lane has no query; min_valid = fewest neighbours for which the PCA is computed (1 for k-NN).  rec_all = 32 x 17 floats of warp-private shared memory that no
 // lane still uses for anything else; col = 32 words (stride col_stride) of the lane's own shared memory,
 // free once best[] is in registers (it may overlap rec_all: the records are staged after the moments).
-__device__ __forceinline__ void knn_finish(const KArgs& a, u64 (&best)[32], const int n_nb, const float4 Q, const int my_slot,
+__device__ __forceinline__ void knn_finish(const KArgs& a, u64 (&best)[32], const int n_nb, const int min_valid, const float4 Q,
+                                           const int my_slot,
                                            float (*rec_all)[17], uint32_t* col, const int col_stride, const int lane) {
   const SearchParams& sp = a.sp;
   const int k = sp.k;
@@ -20,7 +21,7 @@ __device__ __forceinline__ void knn_finish(const KArgs& a, u64 (&best)[32], cons
   const uint32_t* __restrict__ inv = a.inv;
   const int ord_q = __float_as_int(Q.w);
   const int gid_q = (my_slot >= 0 && a.gid_of_ord) ? __ldg(&a.gid_of_ord[ord_q]) : ord_q;
-  const bool valid = my_slot >= 0 && n_nb > 0;
+  const bool valid = my_slot >= 0 && n_nb >= min_valid;  // radius search: the reference's 13-neighbour gate (src/pcaAnalysis.cpp:50)
   if (my_slot >= 0) {
     if (sp.kth_d2) {
       // best[] is ascending, so its k-th entry is the maximum of the first k (a max-reduction keeps

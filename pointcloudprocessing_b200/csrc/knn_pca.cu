@@ -389,7 +389,7 @@ __global__ void __launch_bounds__(TQ_WARPS * 32) knn_pca_kernel(KArgs a, int for
   }
   const int n_nb = have < k ? have : k;
 
-  knn_finish(a, best, n_nb, Q, my_slot, sm.rec, reinterpret_cast<uint32_t*>(pcol), 64, lane);
+  knn_finish(a, best, n_nb, 1, Q, my_slot, sm.rec, reinterpret_cast<uint32_t*>(pcol), 64, lane);
 }
 
 }  // namespace

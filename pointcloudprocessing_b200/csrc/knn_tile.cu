@@ -143,7 +143,9 @@ __device__ __forceinline__ uint32_t tile_setup(const KArgs& a, TaSmem<CAP>& sm, 
   return total;
 }
 
-template <int CAP>
+// MODE 0: k nearest (two passes: histogram select, then collect).  MODE 1: radius search — membership is
+// d2 < r2 itself, so there is no selection pass; a lane is served when its neighbourhood fits its column.
+template <int CAP, int MODE>
 __global__ void __launch_bounds__(TA_WARPS * 32, CAP == 24 ? 6 : 5) knn_tile_kernel(KArgs a, int R0, float grow, int max_groups, uint32_t* __restrict__ work_count,
                                                                  uint32_t* __restrict__ work_list) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -188,6 +190,14 @@ __global__ void __launch_bounds__(TA_WARPS * 32, CAP == 24 ? 6 : 5) knn_tile_ker
     int R = R0, nrows = 0, bstar = -1, cum_star = 0;
     uint32_t total = 0;
     float Sb = 0.f;
+    if (MODE == 1) {
+      // radius: the stencil of half-width R0 covers the radius by construction (stencil_for_radius)
+      bool whole;
+      float cover_cells;
+      total = tile_setup(a, sm, lane, R, c0min, c0max, c1, c2, c0, Q, nrows, whole, cover_cells);
+      Sb = 1.f;
+      bstar = 0;
+    } else {
     // ---- pass 1 (+ on-demand growth of the stencil): histogram of d2 over the staged candidates
 #pragma unroll 1
     for (;;) {
@@ -249,15 +259,19 @@ __global__ void __launch_bounds__(TA_WARPS * 32, CAP == 24 ? 6 : 5) knn_tile_ker
       TSTAT(7, lane == 0 ? 1 : 0);
       ++R;
     }
+    }
     TSTAT(2, lane == 0 ? total : 0);
     TSTAT(5, (in_grp && bstar < 0) ? 1 : 0);                          // deferred: k-th beyond the cover radius
     TSTAT(6, (in_grp && bstar >= 0 && cum_star > CAP) ? 1 : 0);    // deferred: threshold bin too full
-    const bool grp_ok = in_grp && bstar >= 0 && cum_star <= CAP;
-    const float thr_bin = grp_ok ? (float)(bstar + 1) : -1.f;  // other lanes collect nothing
+    bool grp_ok = in_grp && bstar >= 0 && cum_star <= CAP;
+    // the collect test is d2 * Sb < thr_bin: the bin bound (k-NN) or, with Sb = 1, r2 itself (radius: strict
+    // d2 < r2 as FLANN's RadiusResultSet); other lanes collect nothing
+    const float thr_bin = grp_ok ? (MODE == 1 ? sp.r2 : (float)(bstar + 1)) : -1.f;
+    uint32_t* const wend = hcol + CAP * 32;
     __syncwarp();
     // ---- pass 2: collect the candidates at or below the threshold bin (same d2 arithmetic, same bins)
     if (__any_sync(PCP_FULL, grp_ok)) {
-      const bool resident = total <= (uint32_t)TA_CH;  // one chunk: still staged from pass 1
+      const bool resident = MODE == 0 && total <= (uint32_t)TA_CH;  // one chunk: still staged from pass 1
       // A candidate farther from the bounding box of the served queries than the largest threshold
       // distance is nobody's neighbour: each chunk is compacted in place (one candidate per lane, ballot
       // + rank) before the per-lane loop, which then runs over about half of it.
@@ -308,19 +322,20 @@ __global__ void __launch_bounds__(TA_WARPS * 32, CAP == 24 ? 6 : 5) knn_tile_ker
           const float4 P0 = sm.cand[j], P1 = sm.cand[j + 1], P2 = sm.cand[j + 2], P3 = sm.cand[j + 3];
           const float e0 = dist2_nofma(Q.x, Q.y, Q.z, P0), e1 = dist2_nofma(Q.x, Q.y, Q.z, P1);
           const float e2 = dist2_nofma(Q.x, Q.y, Q.z, P2), e3 = dist2_nofma(Q.x, Q.y, Q.z, P3);
-          if (e0 * Sb < thr_bin) { wp[0] = __float_as_uint(P0.w); wp[CAP * 32] = __float_as_uint(e0); wp += 32; }
-          if (e1 * Sb < thr_bin) { wp[0] = __float_as_uint(P1.w); wp[CAP * 32] = __float_as_uint(e1); wp += 32; }
-          if (e2 * Sb < thr_bin) { wp[0] = __float_as_uint(P2.w); wp[CAP * 32] = __float_as_uint(e2); wp += 32; }
-          if (e3 * Sb < thr_bin) { wp[0] = __float_as_uint(P3.w); wp[CAP * 32] = __float_as_uint(e3); wp += 32; }
+          if (e0 * Sb < thr_bin) { if (MODE == 0 || wp < wend) { wp[0] = __float_as_uint(P0.w); wp[CAP * 32] = __float_as_uint(e0); } wp += 32; }
+          if (e1 * Sb < thr_bin) { if (MODE == 0 || wp < wend) { wp[0] = __float_as_uint(P1.w); wp[CAP * 32] = __float_as_uint(e1); } wp += 32; }
+          if (e2 * Sb < thr_bin) { if (MODE == 0 || wp < wend) { wp[0] = __float_as_uint(P2.w); wp[CAP * 32] = __float_as_uint(e2); } wp += 32; }
+          if (e3 * Sb < thr_bin) { if (MODE == 0 || wp < wend) { wp[0] = __float_as_uint(P3.w); wp[CAP * 32] = __float_as_uint(e3); } wp += 32; }
         }
         for (; j < n_ch; ++j) {
           const float4 P0 = sm.cand[j];
           const float e0 = dist2_nofma(Q.x, Q.y, Q.z, P0);
-          if (e0 * Sb < thr_bin) { wp[0] = __float_as_uint(P0.w); wp[CAP * 32] = __float_as_uint(e0); wp += 32; }
+          if (e0 * Sb < thr_bin) { if (MODE == 0 || wp < wend) { wp[0] = __float_as_uint(P0.w); wp[CAP * 32] = __float_as_uint(e0); } wp += 32; }
         }
         __syncwarp();
       }
     }
+    if (MODE == 1) grp_ok = grp_ok && wp <= wend;  // a larger neighbourhood than the column holds: deferred
     ok = ok || grp_ok;
   }
   const int cnt = (int)(wp - hcol) >> 5;
@@ -348,10 +363,10 @@ __global__ void __launch_bounds__(TA_WARPS * 32, CAP == 24 ? 6 : 5) knn_tile_ker
   u64 best[32];
 #pragma unroll
   for (int j = 0; j < 32; ++j) best[j] = j < CAP ? keys[j < CAP ? j : 0] : PCP_KEY_INF;
-  const int n_nb = ok ? k : 0;
+  const int n_nb = ok ? (MODE == 1 ? cnt : k) : 0;
   const bool emit = active && (ok || !finite);  // non-finite queries get their empty record here
   __syncwarp();
-  knn_finish(a, best, n_nb, Q, emit ? my_slot : -1, sm.u.rec, hcol, 32, lane);
+  knn_finish(a, best, n_nb, MODE == 1 ? sp.min_pts : 1, Q, emit ? my_slot : -1, sm.u.rec, hcol, 32, lane);
 }
 
 }  // namespace
@@ -385,16 +400,20 @@ int pcp_knn_tile_launch(pcp_ctx* ctx, const SearchParams& sp, const KArgs& a) {
   // registers, 6 CTAs/SM) — measured SLOWER on the urban cloud (1.82 vs 1.63 ms): its 47 bins leave more
   // lanes with an over-full threshold bin than the extra occupancy pays for
   const char* capenv = getenv("PCP_KNN_CAP");
-  if (sp.k <= 20 && capenv && capenv[0] == '2') {
+  uint32_t* wc = (uint32_t*)ctx->work_count.p;
+  uint32_t* wl = (uint32_t*)ctx->work_list.p;
+  if (sp.mode == 1) {
+    const size_t smem = sizeof(TaSmem<32>) * TA_WARPS;
+    PCP_CUDA(cudaFuncSetAttribute(knn_tile_kernel<32, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    knn_tile_kernel<32, 1><<<blocks, TA_WARPS * 32, smem, ctx->stream>>>(a, sp.R0, 0.f, max_groups, wc, wl);
+  } else if (sp.k <= 20 && capenv && capenv[0] == '2') {
     const size_t smem = sizeof(TaSmem<24>) * TA_WARPS;
-    PCP_CUDA(cudaFuncSetAttribute(knn_tile_kernel<24>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    knn_tile_kernel<24><<<blocks, TA_WARPS * 32, smem, ctx->stream>>>(a, sp.R0, grow, max_groups, (uint32_t*)ctx->work_count.p,
-                                                                      (uint32_t*)ctx->work_list.p);
+    PCP_CUDA(cudaFuncSetAttribute(knn_tile_kernel<24, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    knn_tile_kernel<24, 0><<<blocks, TA_WARPS * 32, smem, ctx->stream>>>(a, sp.R0, grow, max_groups, wc, wl);
   } else {
     const size_t smem = sizeof(TaSmem<32>) * TA_WARPS;
-    PCP_CUDA(cudaFuncSetAttribute(knn_tile_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    knn_tile_kernel<32><<<blocks, TA_WARPS * 32, smem, ctx->stream>>>(a, sp.R0, grow, max_groups, (uint32_t*)ctx->work_count.p,
-                                                                      (uint32_t*)ctx->work_list.p);
+    PCP_CUDA(cudaFuncSetAttribute(knn_tile_kernel<32, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    knn_tile_kernel<32, 0><<<blocks, TA_WARPS * 32, smem, ctx->stream>>>(a, sp.R0, grow, max_groups, wc, wl);
   }
   PCP_LAUNCH_CHECK("knn_tile_kernel");
   return PCP_OK;

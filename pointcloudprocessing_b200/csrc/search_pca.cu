@@ -539,14 +539,35 @@ int pcp_search_launch(pcp_ctx* ctx, const SearchParams& sp) {
   const int64_t tiles = (ctx->n + 31) / 32;
   const int blocks = (int)((tiles + WARPS - 1) / WARPS);
   pcp_tic(ctx, PCP_T_SEARCH_PCA);
-  if (sp.mode == 0 && !use_v3) {
+  // radius + PCA records (no neighbour lists requested) also starts in the tile kernel when the
+  // neighbourhoods are expected to be small: lanes hold up to 32 neighbours, larger ones go to the
+  // warp-per-query kernel.  Measured on B200: mean 8.7 neighbours -> 0.82 vs 0.99 ms per 1 M points, mean 32 ->
+  // 3.2 vs 2.4 ms, so the switch is a surface-density guess n*pi*r^2 / (two largest extents) <= 40
+  // (the urban clouds hold ~0.4 of that guess).  PCP_RADIUS_IMPL=tile|v3 forces either.
+  const char* rimpl = getenv("PCP_RADIUS_IMPL");
+  bool radius_tile = false;
+  if (sp.mode == 1 && sp.out != nullptr && sp.counts == nullptr && sp.nn_idx == nullptr) {
+    const double area = (double)ctx->grid.dim[2] * (double)ctx->grid.dim[0] * (double)ctx->grid.cell * (double)ctx->grid.cell;
+    const double guess = (double)ctx->n * 3.14159265 * (double)sp.r2 / (area > 0.0 ? area : 1.0);
+    radius_tile = guess <= 40.0;
+    if (rimpl && rimpl[0] == 't') radius_tile = true;
+    if (rimpl && rimpl[0] == 'v') radius_tile = false;
+  }
+  if ((sp.mode == 0 && !use_v3) || radius_tile) {
     int rc = pcp_knn_tile_launch(ctx, sp, a);
     if (rc) return rc;
-    size_t smem = sizeof(WarpSmem<0>) * WARPS;
-    PCP_CUDA(cudaFuncSetAttribute(search_pca_worklist_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const int wl_blocks = blocks < 148 * 4 ? blocks : 148 * 4;
-    search_pca_worklist_kernel<0><<<wl_blocks, WARPS * 32, smem, ctx->stream>>>(a, (const uint32_t*)ctx->work_count.p,
-                                                                                (const uint32_t*)ctx->work_list.p);
+    if (sp.mode == 0) {
+      size_t smem = sizeof(WarpSmem<0>) * WARPS;
+      PCP_CUDA(cudaFuncSetAttribute(search_pca_worklist_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      search_pca_worklist_kernel<0><<<wl_blocks, WARPS * 32, smem, ctx->stream>>>(a, (const uint32_t*)ctx->work_count.p,
+                                                                                  (const uint32_t*)ctx->work_list.p);
+    } else {
+      size_t smem = sizeof(WarpSmem<1>) * WARPS;
+      PCP_CUDA(cudaFuncSetAttribute(search_pca_worklist_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      search_pca_worklist_kernel<1><<<wl_blocks, WARPS * 32, smem, ctx->stream>>>(a, (const uint32_t*)ctx->work_count.p,
+                                                                                  (const uint32_t*)ctx->work_list.p);
+    }
   } else if (sp.mode == 0) {
     size_t smem = sizeof(WarpSmem<0>) * WARPS;
     PCP_CUDA(cudaFuncSetAttribute(search_pca_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

@@ -112,3 +112,30 @@ def test_host_async_pipelining(oracle):
             c.synchronize()
     for got, ref in zip(outs, want):
         assert got.tobytes() == ref.tobytes()
+
+
+@pytest.mark.parametrize("impl", ["tile", "v3"])
+def test_radius_pca_both_kernels(oracle, impl):
+    """radius + PCA records: tile kernel (+ work list for neighbourhoods above 32) and the warp-per-query
+    kernel give the same bytes, equal to the oracle's within the PCA tolerances."""
+    import sys
+    from parity import check_features
+    pts = synth.urban(17, 40000, extent=22.0)  # ~83 pts/m^2: many neighbourhoods above and below 32
+    old = os.environ.get("PCP_RADIUS_IMPL")
+    try:
+        os.environ["PCP_RADIUS_IMPL"] = impl
+        with capi.Pcp(0) as p:
+            p.set_cloud(pts)
+            p.build_grid(0.5005, 0)
+            got = p.radius_pca(0.5, 13, capi.CENTER_QUERY, True)
+            os.environ["PCP_RADIUS_IMPL"] = "v3"
+            ref_gpu = p.radius_pca(0.5, 13, capi.CENTER_QUERY, True)
+    finally:
+        if old is None:
+            os.environ.pop("PCP_RADIUS_IMPL", None)
+        else:
+            os.environ["PCP_RADIUS_IMPL"] = old
+    assert got.tobytes() == ref_gpu.tobytes()
+    ref, valid = oracle.radius_pca_cloud(pts, 0.5, 13, True, nthreads=1)
+    assert (got["ptNum"] > 32).mean() > 0.05 and (got["ptNum"] <= 32).mean() > 0.05
+    check_features(got, ref, valid, f"radius {impl}")
