@@ -78,3 +78,6 @@ __device__ __forceinline__ void sym3_eigen(const float C[6], Sym3Eig& out) {
   out.vec[1][0] = (float)v01; out.vec[1][1] = (float)v11; out.vec[1][2] = (float)v21;
   out.vec[2][0] = (float)v02; out.vec[2][1] = (float)v12; out.vec[2][2] = (float)v22;
 }
+
+// One shared copy of the solver for the kernels that would otherwise inline it several times.
+static __device__ __noinline__ void sym3_eigen_call(const float C[6], Sym3Eig& out) { sym3_eigen(C, out); }

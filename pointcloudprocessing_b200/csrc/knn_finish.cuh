@@ -7,13 +7,15 @@
 #include "eigen3.cuh"
 #include "search_common.cuh"
 
-// best[0..n_nb) = this lane's neighbours ascending by (d2, index) as keys bits(d2) << 32 | ord;
-// my_slot < 0: the lane has no query; min_valid = fewest neighbours for which the PCA is computed (1 for k-NN).  rec_all = 32 x 17 floats of warp-private shared memory that no
-// lane still uses for anything else; col = 32 words (stride col_stride) of the lane's own shared memory,
-// free once best[] is in registers (it may overlap rec_all: the records are staged after the moments).
-__device__ __forceinline__ void knn_finish(const KArgs& a, u64 (&best)[32], const int n_nb, const int min_valid, const float4 Q,
-                                           const int my_slot,
-                                           float (*rec_all)[17], uint32_t* col, const int col_stride, const int lane) {
+// lo[j * stride] / hi[j * stride] (j < n_nb) = the two words of neighbour j's key bits(d2) << 32 | ord, ascending
+// by (d2, index), in the lane's OWN shared-memory column (every loop over the list is rolled: code size,
+// not instruction count, is what this stage costs the kernels that inline it); the column is overwritten.
+// my_slot < 0: the lane has no query; min_valid = fewest neighbours for which the PCA is computed (1 for
+// k-NN, the reference's 13 for radius search).  rec_all = 32 x 17 floats of warp-private shared memory;
+// it may overlap the columns: the records are staged after the last read of the list.
+__device__ __forceinline__ void knn_finish(const KArgs& a, uint32_t* lo, const uint32_t* hi, const int stride, const int n_nb,
+                                           const int min_valid, const float4 Q, const int my_slot, float (*rec_all)[17],
+                                           const int lane) {
   const SearchParams& sp = a.sp;
   const int k = sp.k;
   // ---- neighbour list -> outputs (each lane for its own query)
@@ -21,27 +23,17 @@ __device__ __forceinline__ void knn_finish(const KArgs& a, u64 (&best)[32], cons
   const uint32_t* __restrict__ inv = a.inv;
   const int ord_q = __float_as_int(Q.w);
   const int gid_q = (my_slot >= 0 && a.gid_of_ord) ? __ldg(&a.gid_of_ord[ord_q]) : ord_q;
-  const bool valid = my_slot >= 0 && n_nb >= min_valid;  // radius search: the reference's 13-neighbour gate (src/pcaAnalysis.cpp:50)
+  const bool valid = my_slot >= 0 && n_nb >= min_valid;  // radius search: the 13-neighbour gate (src/pcaAnalysis.cpp:50)
   if (my_slot >= 0) {
-    if (sp.kth_d2) {
-      // best[] is ascending, so its k-th entry is the maximum of the first k (a max-reduction keeps
-      // best[] in registers; an indexed read would push the whole array to local memory)
-      u64 kth = 0;
-#pragma unroll
-      for (int j = 0; j < 32; ++j)
-        if (j < k && best[j] > kth) kth = best[j];
-      sp.kth_d2[my_slot] = n_nb >= k ? __uint_as_float((uint32_t)(kth >> 32)) : INFINITY;
-    }
+    if (sp.kth_d2) sp.kth_d2[my_slot] = n_nb >= k ? __uint_as_float(hi[(k - 1) * stride]) : INFINITY;
     if (sp.nn_idx != nullptr) {
       const int64_t o = (int64_t)my_slot * k;
-#pragma unroll
-      for (int j = 0; j < 32; ++j) {
-        if (j < k) {
-          const bool has = j < n_nb;
-          const int ord = (int)(uint32_t)best[j];
-          sp.nn_idx[o + j] = has ? (a.gid_of_ord ? __ldg(&a.gid_of_ord[ord]) : ord) : -1;
-          if (sp.nn_d2) sp.nn_d2[o + j] = has ? __uint_as_float((uint32_t)(best[j] >> 32)) : INFINITY;
-        }
+#pragma unroll 1
+      for (int j = 0; j < k; ++j) {
+        const bool has = j < n_nb;
+        const int ord = has ? (int)lo[j * stride] : 0;
+        sp.nn_idx[o + j] = has ? (a.gid_of_ord ? __ldg(&a.gid_of_ord[ord]) : ord) : -1;
+        if (sp.nn_d2) sp.nn_d2[o + j] = has ? __uint_as_float(hi[j * stride]) : INFINITY;
       }
     }
   }
@@ -49,18 +41,15 @@ __device__ __forceinline__ void knn_finish(const KArgs& a, u64 (&best)[32], cons
   const bool need_m = sp.normals != nullptr || (sp.out != nullptr && sp.center_mode == PCP_CENTER_MEAN);
   float mq[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f}, mm[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
   if (valid && (need_q || need_m)) {
-    // The list moves to the lane's shared-memory column so the moment loops can be ROLLED (three loops
-    // unrolled 32 times were a quarter of the kernel's code and cost instruction-cache misses):
-    // col[j] = sorted position of neighbour j, from which the coordinates are re-read.
-#pragma unroll
-    for (int j = 0; j < 32; ++j)
-      if (j < n_nb) col[j * col_stride] = __ldg(&inv[(uint32_t)best[j]]);
+    // ord -> sorted position, in place (the moment re-reads coordinates from them); eight loads in flight
+#pragma unroll 8
+    for (int j = 0; j < n_nb; ++j) lo[j * stride] = __ldg(&inv[lo[j * stride]]);
     const float fn = (float)n_nb;
     if (need_q) {
       // pcl::computeCovarianceMatrixNormalized about the query: six fp32 chains in list order
-#pragma unroll 2
+#pragma unroll 8
       for (int j = 0; j < n_nb; ++j) {
-        const float4 P = __ldg(&sorted[col[j * col_stride]]);
+        const float4 P = __ldg(&sorted[lo[j * stride]]);
         const float px = __fsub_rn(P.x, Q.x), py = __fsub_rn(P.y, Q.y), pz = __fsub_rn(P.z, Q.z);
         mq[0] = __fadd_rn(mq[0], __fmul_rn(px, px));
         mq[1] = __fadd_rn(mq[1], __fmul_rn(py, px));
@@ -75,17 +64,17 @@ __device__ __forceinline__ void knn_finish(const KArgs& a, u64 (&best)[32], cons
     if (need_m) {
       // pcl::compute3DCentroid (fp32 running sums in list order), then the moment about it
       float sx = 0.f, sy = 0.f, sz = 0.f;
-#pragma unroll 2
+#pragma unroll 8
       for (int j = 0; j < n_nb; ++j) {
-        const float4 P = __ldg(&sorted[col[j * col_stride]]);
+        const float4 P = __ldg(&sorted[lo[j * stride]]);
         sx = __fadd_rn(sx, P.x);
         sy = __fadd_rn(sy, P.y);
         sz = __fadd_rn(sz, P.z);
       }
       const float cx = __fdiv_rn(sx, fn), cy = __fdiv_rn(sy, fn), cz = __fdiv_rn(sz, fn);
-#pragma unroll 2
+#pragma unroll 8
       for (int j = 0; j < n_nb; ++j) {
-        const float4 P = __ldg(&sorted[col[j * col_stride]]);
+        const float4 P = __ldg(&sorted[lo[j * stride]]);
         const float px = __fsub_rn(P.x, cx), py = __fsub_rn(P.y, cy), pz = __fsub_rn(P.z, cz);
         mm[0] = __fadd_rn(mm[0], __fmul_rn(px, px));
         mm[1] = __fadd_rn(mm[1], __fmul_rn(py, px));
@@ -107,37 +96,38 @@ __device__ __forceinline__ void knn_finish(const KArgs& a, u64 (&best)[32], cons
     for (int w = 0; w < 17; ++w) rec[w] = 0.f;
     rec[12] = __int_as_float(gid_q);
     rec[13] = __int_as_float(n_nb);
-    Sym3Eig eq;
-    bool have_q = false;
-    if (valid && sp.out != nullptr) {
-      sym3_eigen(sp.center_mode == PCP_CENTER_QUERY ? mq : mm, eq);
-      have_q = true;
-      rec[0] = eq.val[0]; rec[1] = eq.val[1]; rec[2] = eq.val[2];
+    // one call site of the (noinline) solver on the hot path: the matrix the records need, which is also
+    // the normals' matrix unless query-centred records AND normals were requested
+    const bool want_out = valid && sp.out != nullptr;
+    const bool want_nrm = sp.normals != nullptr && valid && n_nb >= 3;
+    const bool first_is_mean = !want_out || sp.center_mode == PCP_CENTER_MEAN;
+    Sym3Eig e1;
+    if (want_out || want_nrm) sym3_eigen_call(first_is_mean ? mm : mq, e1);
+    if (want_out) {
+      rec[0] = e1.val[0]; rec[1] = e1.val[1]; rec[2] = e1.val[2];
 #pragma unroll
       for (int c = 0; c < 3; ++c)
 #pragma unroll
-        for (int r = 0; r < 3; ++r) rec[3 + 3 * c + r] = eq.vec[c][r];
+        for (int r = 0; r < 3; ++r) rec[3 + 3 * c + r] = e1.vec[c][r];
       // src/pcaAnalysis.cpp:29-31 in fp32 on the ascending eigenvalues
-      const float s1 = __fsqrt_rn(eq.val[0]), s2 = __fsqrt_rn(eq.val[1]), s3 = __fsqrt_rn(eq.val[2]);
+      const float s1 = __fsqrt_rn(e1.val[0]), s2 = __fsqrt_rn(e1.val[1]), s3 = __fsqrt_rn(e1.val[2]);
       rec[14] = __fdiv_rn(__fsub_rn(s1, s2), s1);
       rec[15] = __fdiv_rn(__fsub_rn(s2, s3), s1);
       rec[16] = __fdiv_rn(s3, s1);
     }
     if (sp.normals != nullptr) {
       pcp_normal16 nrm;
-      if (!valid || n_nb < 3) {
+      if (!want_nrm) {
         nrm.nx = nrm.ny = nrm.nz = nrm.curvature = __int_as_float(0x7FC00000);
       } else {
-        Sym3Eig em;
-        if (have_q && sp.center_mode == PCP_CENTER_MEAN) em = eq;
-        else sym3_eigen(mm, em);
+        if (!first_is_mean) sym3_eigen_call(mm, e1);  // records were query-centred: solve the mean-centred moment too
         const float tr = mm[0] + mm[3] + mm[5];
-        float nx = em.vec[0][0], ny = em.vec[0][1], nz = em.vec[0][2];
+        float nx = e1.vec[0][0], ny = e1.vec[0][1], nz = e1.vec[0][2];
         // flipNormalTowardsViewpoint with viewpoint (0,0,0)
         const float cs = (0.f - Q.x) * nx + (0.f - Q.y) * ny + (0.f - Q.z) * nz;
         if (cs < 0.f) { nx = -nx; ny = -ny; nz = -nz; }
         nrm.nx = nx; nrm.ny = ny; nrm.nz = nz;
-        nrm.curvature = tr != 0.f ? fabsf(em.val[0] / tr) : 0.f;
+        nrm.curvature = tr != 0.f ? fabsf(e1.val[0] / tr) : 0.f;
       }
       sp.normals[my_slot] = nrm;
     }
@@ -147,7 +137,7 @@ __device__ __forceinline__ void knn_finish(const KArgs& a, u64 (&best)[32], cons
   // ---- lanes 0..16 write one contiguous 68-byte record per step
   if (sp.out != nullptr) {
     float* outw = reinterpret_cast<float*>(sp.out);
-#pragma unroll 4
+#pragma unroll 1
     for (int r = 0; r < 32; ++r) {
       const int s = __shfl_sync(PCP_FULL, my_slot, r);
       if (s >= 0 && lane < 17) outw[(int64_t)s * 17 + lane] = rec_all[r][lane];

@@ -389,7 +389,9 @@ __global__ void __launch_bounds__(TQ_WARPS * 32) knn_pca_kernel(KArgs a, int for
   }
   const int n_nb = have < k ? have : k;
 
-  knn_finish(a, best, n_nb, 1, Q, my_slot, sm.rec, reinterpret_cast<uint32_t*>(pcol), 64, lane);
+#pragma unroll
+  for (int j = 0; j < TQ_CAP; ++j) pcol[j * 32] = best[j];
+  knn_finish(a, reinterpret_cast<uint32_t*>(pcol), reinterpret_cast<uint32_t*>(pcol) + 1, 64, n_nb, 1, Q, my_slot, sm.rec, lane);
 }
 
 }  // namespace

@@ -39,7 +39,7 @@ namespace {
 
 constexpr int TA_WARPS = 4;        // warps per CTA
 constexpr int TA_CH = 128;         // staged candidates per chunk
-// CAP (template parameter, 24 or 32) = candidates a lane can hold = width of the sorting network;
+// CAP (template parameter: 24 or 32 for k-NN, 32 or 64 for radius search) = candidates a lane can hold = width of the sorting network;
 // the histogram has BINS = 2*CAP - 1 linear d2 bins inside the cover radius + 1 overflow bin, so that it
 // occupies exactly the rows the candidate keys use afterwards.
 constexpr int TA_REC_WORDS = 17;   // 68-byte record
@@ -146,7 +146,7 @@ __device__ __forceinline__ uint32_t tile_setup(const KArgs& a, TaSmem<CAP>& sm, 
 // MODE 0: k nearest (two passes: histogram select, then collect).  MODE 1: radius search — membership is
 // d2 < r2 itself, so there is no selection pass; a lane is served when its neighbourhood fits its column.
 template <int CAP, int MODE>
-__global__ void __launch_bounds__(TA_WARPS * 32, CAP == 24 ? 6 : 5) knn_tile_kernel(KArgs a, int R0, float grow, int max_groups, uint32_t* __restrict__ work_count,
+__global__ void __launch_bounds__(TA_WARPS * 32, CAP == 24 ? 6 : (CAP == 64 ? 3 : 5)) knn_tile_kernel(KArgs a, int R0, float grow, int max_groups, uint32_t* __restrict__ work_count,
                                                                  uint32_t* __restrict__ work_list) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   constexpr int BINS = 2 * CAP - 1;
@@ -359,14 +359,18 @@ __global__ void __launch_bounds__(TA_WARPS * 32, CAP == 24 ? 6 : 5) knn_tile_ker
 #pragma unroll
   for (int j = 0; j < CAP; ++j) keys[j] = j < cnt ? (((u64)hcol[(CAP + j) * 32] << 32) | (u64)hcol[j * 32]) : PCP_KEY_INF;
   if (CAP == 24) sort24_regs(reinterpret_cast<u64(&)[24]>(keys));
-  else sort32_regs(reinterpret_cast<u64(&)[32]>(keys));
-  u64 best[32];
+  else if (CAP == 32) sort32_regs(reinterpret_cast<u64(&)[32]>(keys));
+  else sort64_regs(reinterpret_cast<u64(&)[64]>(keys));
+  // the ordered keys go back to the lane's column: everything after this point walks the list with rolled loops
 #pragma unroll
-  for (int j = 0; j < 32; ++j) best[j] = j < CAP ? keys[j < CAP ? j : 0] : PCP_KEY_INF;
+  for (int j = 0; j < CAP; ++j) {
+    hcol[j * 32] = (uint32_t)keys[j];
+    hcol[(CAP + j) * 32] = (uint32_t)(keys[j] >> 32);
+  }
   const int n_nb = ok ? (MODE == 1 ? cnt : k) : 0;
   const bool emit = active && (ok || !finite);  // non-finite queries get their empty record here
   __syncwarp();
-  knn_finish(a, best, n_nb, MODE == 1 ? sp.min_pts : 1, Q, emit ? my_slot : -1, sm.u.rec, hcol, 32, lane);
+  knn_finish(a, hcol, hcol + CAP * 32, 32, n_nb, MODE == 1 ? sp.min_pts : 1, Q, emit ? my_slot : -1, sm.u.rec, lane);
 }
 
 }  // namespace
@@ -383,7 +387,7 @@ extern "C" __attribute__((visibility("default"))) int pcp_debug_tile_stats(unsig
 
 // Launches the tile kernel over the whole cloud; deferred queries are left in ctx->work_list /
 // ctx->work_count (device) for pcp_search_launch_worklist.
-int pcp_knn_tile_launch(pcp_ctx* ctx, const SearchParams& sp, const KArgs& a) {
+int pcp_knn_tile_launch(pcp_ctx* ctx, const SearchParams& sp, const KArgs& a, int radius_cap) {
   int rc;
   if ((rc = pcp_reserve(ctx, ctx->work_list, (size_t)ctx->n * sizeof(uint32_t)))) return rc;
   if ((rc = pcp_reserve(ctx, ctx->work_count, sizeof(uint32_t)))) return rc;
@@ -402,7 +406,11 @@ int pcp_knn_tile_launch(pcp_ctx* ctx, const SearchParams& sp, const KArgs& a) {
   const char* capenv = getenv("PCP_KNN_CAP");
   uint32_t* wc = (uint32_t*)ctx->work_count.p;
   uint32_t* wl = (uint32_t*)ctx->work_list.p;
-  if (sp.mode == 1) {
+  if (sp.mode == 1 && radius_cap == 64) {
+    const size_t smem = sizeof(TaSmem<64>) * TA_WARPS;
+    PCP_CUDA(cudaFuncSetAttribute(knn_tile_kernel<64, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    knn_tile_kernel<64, 1><<<blocks, TA_WARPS * 32, smem, ctx->stream>>>(a, sp.R0, 0.f, max_groups, wc, wl);
+  } else if (sp.mode == 1) {
     const size_t smem = sizeof(TaSmem<32>) * TA_WARPS;
     PCP_CUDA(cudaFuncSetAttribute(knn_tile_kernel<32, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     knn_tile_kernel<32, 1><<<blocks, TA_WARPS * 32, smem, ctx->stream>>>(a, sp.R0, 0.f, max_groups, wc, wl);

@@ -102,6 +102,6 @@ struct SearchParams {
 };
 int pcp_search_launch(pcp_ctx* ctx, const SearchParams& sp);  // radius (and the v3 warp-per-query k-NN, A/B only)
 struct KArgs;
-int pcp_knn_tile_launch(pcp_ctx* ctx, const SearchParams& sp, const KArgs& a);  // k-NN tile kernel (knn_tile.cu)
+int pcp_knn_tile_launch(pcp_ctx* ctx, const SearchParams& sp, const KArgs& a, int radius_cap);  // k-NN tile kernel (knn_tile.cu)
 int pcp_knn_launch(pcp_ctx* ctx, const SearchParams& sp);     // k-NN, one thread per query (knn_pca.cu)
 int pcp_carry_forward_impl(pcp_ctx* ctx, pcp_feature68* d_out, const uint8_t* d_valid, int64_t n);

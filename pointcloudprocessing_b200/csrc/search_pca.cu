@@ -546,15 +546,19 @@ int pcp_search_launch(pcp_ctx* ctx, const SearchParams& sp) {
   // (the urban clouds hold ~0.4 of that guess).  PCP_RADIUS_IMPL=tile|v3 forces either.
   const char* rimpl = getenv("PCP_RADIUS_IMPL");
   bool radius_tile = false;
+  int radius_cap = 32;
   if (sp.mode == 1 && sp.out != nullptr && sp.counts == nullptr && sp.nn_idx == nullptr) {
     const double area = (double)ctx->grid.dim[2] * (double)ctx->grid.dim[0] * (double)ctx->grid.cell * (double)ctx->grid.cell;
     const double guess = (double)ctx->n * 3.14159265 * (double)sp.r2 / (area > 0.0 ? area : 1.0);
-    radius_tile = guess <= 40.0;
-    if (rimpl && rimpl[0] == 't') radius_tile = true;
+    // lanes of 32 neighbours for sparse neighbourhoods, of 64 for dense ones (configs[3]: ~32 on average),
+    // the warp-per-query kernel alone beyond that
+    radius_tile = guess <= 200.0;
+    radius_cap = guess <= 40.0 ? 32 : 64;
+    if (rimpl && rimpl[0] == 't') { radius_tile = true; radius_cap = rimpl[4] == '6' ? 64 : 32; }  // tile32 / tile64
     if (rimpl && rimpl[0] == 'v') radius_tile = false;
   }
   if ((sp.mode == 0 && !use_v3) || radius_tile) {
-    int rc = pcp_knn_tile_launch(ctx, sp, a);
+    int rc = pcp_knn_tile_launch(ctx, sp, a, radius_cap);
     if (rc) return rc;
     const int wl_blocks = blocks < 148 * 4 ? blocks : 148 * 4;
     if (sp.mode == 0) {

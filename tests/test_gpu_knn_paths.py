@@ -114,7 +114,7 @@ def test_host_async_pipelining(oracle):
         assert got.tobytes() == ref.tobytes()
 
 
-@pytest.mark.parametrize("impl", ["tile", "v3"])
+@pytest.mark.parametrize("impl", ["tile", "tile64", "v3"])
 def test_radius_pca_both_kernels(oracle, impl):
     """radius + PCA records: tile kernel (+ work list for neighbourhoods above 32) and the warp-per-query
     kernel give the same bytes, equal to the oracle's within the PCA tolerances."""
