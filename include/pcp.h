@@ -131,6 +131,16 @@ PCP_API int pcp_set_cloud_device(pcp_ctx* ctx, const void* d_xyzi, int64_t n);
  * unsharded run. */
 PCP_API int pcp_set_cloud_device_sharded(pcp_ctx* ctx, const void* d_xyzi, const int32_t* d_global_id,
                                          int64_t n, int64_t n_query);
+/* Frame batch (BASELINE configs[4]: many VLP-16 frames per launch): declares the current cloud to be
+ * `n_frames` independent clouds laid end to end, frame f = points [frame_offsets[f], frame_offsets[f+1])
+ * (HOST array of n_frames + 1 entries, first 0, last n; n_frames <= 65535).  The next pcp_build_grid
+ * builds ONE segmented grid (cell key = frame ‖ cell over the common bounding box) and every search
+ * stays inside the query's frame, so pcp_knn_pca / pcp_radius_pca / pcp_knn_normals give, per frame,
+ * exactly the records of a separate run on that frame — the reference's per-frame loop
+ * (src/lidarOdometry.cpp:66-76 builds one tree and searches every point of ONE frame) in one launch.  ptID and neighbour
+ * indices count from the start of the batch; the stale-record carry restarts at every
+ * frame.  Reset by the next pcp_set_cloud_*; not available for sharded clouds. */
+PCP_API int pcp_set_frames(pcp_ctx* ctx, const int64_t* frame_offsets, int64_t n_frames);
 
 /* ---- slab sharding: halo classification ----------------------------------------------
  * Multi-GPU form of the loop at src/pcaAnalysis.cpp:18-40 (the reference is one process):

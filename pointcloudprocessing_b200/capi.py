@@ -41,7 +41,7 @@ EXPORTS = (
     "pcp_last_timings", "pcp_launch_count", "pcp_set_cloud_host", "pcp_set_cloud_device",
     "pcp_set_cloud_device_sharded", "pcp_build_grid", "pcp_grid_info", "pcp_radius_pca", "pcp_knn_pca",
     "pcp_knn_pca_kth", "pcp_knn_neighbors", "pcp_radius_neighbors", "pcp_segment_pca", "pcp_ring_calib_default",
-    "pcp_ring_calib_from_xml", "pcp_ring_project", "pcp_set_host_async", "pcp_alloc_pinned", "pcp_free_pinned", "pcp_halo_pack",
+    "pcp_ring_calib_from_xml", "pcp_ring_project", "pcp_set_host_async", "pcp_alloc_pinned", "pcp_free_pinned", "pcp_halo_pack", "pcp_set_frames",
 )
 
 
@@ -114,6 +114,7 @@ def load() -> C.CDLL:
         "pcp_set_cloud_host": (i32, [vp, vp, i64, i32]),
         "pcp_set_cloud_device": (i32, [vp, vp, i64]),
         "pcp_set_cloud_device_sharded": (i32, [vp, vp, vp, i64, i64]),
+        "pcp_set_frames": (i32, [vp, vp, i64]),
         "pcp_build_grid": (i32, [vp, f32, i32]),
         "pcp_grid_info": (i32, [vp, vp, vp, vp]),
         "pcp_radius_pca": (i32, [vp, f32, i32, i32, i32, vp, i32]),
@@ -237,6 +238,11 @@ class Pcp:
         self._ck(self.lib.pcp_set_cloud_device_sharded(self.h, d_ptr, d_gid, n, nq))
         self.n, self.n_query, self._keep = n, nq, keep
 
+    def set_frames(self, frame_offsets: np.ndarray):
+        """The current cloud is len(frame_offsets) - 1 independent clouds laid end to end (pcp_set_frames)."""
+        fo = np.ascontiguousarray(frame_offsets, np.int64)
+        self._ck(self.lib.pcp_set_frames(self.h, fo.ctypes.data, fo.shape[0] - 1))
+
     def build_grid(self, cell: float = 0.0, k_hint: int = 0):
         self._ck(self.lib.pcp_build_grid(self.h, float(cell), int(k_hint)))
 
@@ -296,9 +302,15 @@ class Pcp:
         self._ck(self.lib.pcp_segment_pca(self.h, centres.ctypes.data, offsets.ctypes.data, idx.ctypes.data, nseg, out.ctypes.data))
         return out
 
-    def ring_project_host_ptr(self, calib: RingCalib, range_ptr: int, index_ptr: int, long_ptr: int):
-        """One frame = the whole current cloud, outputs to raw (page-locked) host pointers."""
-        self._ck(self.lib.pcp_ring_project(self.h, C.byref(calib), None, 1, range_ptr, index_ptr, long_ptr, 0))
+    def ring_project_host_ptr(self, calib: RingCalib, range_ptr: int, index_ptr: int, long_ptr: int,
+                              frame_offsets: Optional[np.ndarray] = None):
+        """Outputs to raw (page-locked) host pointers; one frame = the whole current cloud unless
+        frame_offsets (int64, n_frames + 1) is given."""
+        if frame_offsets is None:
+            self._ck(self.lib.pcp_ring_project(self.h, C.byref(calib), None, 1, range_ptr, index_ptr, long_ptr, 0))
+        else:
+            fo = np.ascontiguousarray(frame_offsets, np.int64)
+            self._ck(self.lib.pcp_ring_project(self.h, C.byref(calib), fo.ctypes.data, fo.shape[0] - 1, range_ptr, index_ptr, long_ptr, 0))
 
     def ring_project(self, calib: Optional[RingCalib] = None, frame_offsets: Optional[np.ndarray] = None,
                      range_device: Optional[int] = None, index_device: Optional[int] = None, long_device: Optional[int] = None):

@@ -86,7 +86,7 @@ PCP_API int pcp_destroy(pcp_ctx* ctx) {
                     &ctx->sort_tmp, &ctx->sorted_pts, &ctx->inv_pos, &ctx->gid_sorted, &ctx->gid_tmp, &ctx->ord_of_li, &ctx->li_of_ord, &ctx->sorted_slot, &ctx->cell_end, &ctx->scan_tmp, &ctx->out_feat,
                     &ctx->out_norm, &ctx->out_idx, &ctx->out_d2, &ctx->out_counts, &ctx->flags, &ctx->valid,
                     &ctx->last_valid, &ctx->staging, &ctx->ring_range, &ctx->ring_idx, &ctx->ring_long,
-                    &ctx->ring_offsets, &ctx->ring_key};
+                    &ctx->ring_offsets, &ctx->ring_key, &ctx->frames};
   for (DevBuf* b : bufs) free_buf(*b);
   for (int i = 0; i < 2 * PCP_T_COUNT; ++i)
     if (ctx->ev[i]) cudaEventDestroy(ctx->ev[i]);
@@ -148,6 +148,7 @@ PCP_API int pcp_set_cloud_host(pcp_ctx* ctx, const void* pts, int64_t n, int str
   ctx->grid_ok = false;
   ctx->n = ctx->n_query = n;
   ctx->d_gid = nullptr;
+  ctx->n_frames = 1;
   int rc = pcp_reserve(ctx, ctx->own_cloud, (size_t)std::max<int64_t>(n, 1) * sizeof(float4));
   if (rc) return rc;
   ctx->d_cloud = (const float4*)ctx->own_cloud.p;
@@ -184,6 +185,28 @@ PCP_API int pcp_set_cloud_device_sharded(pcp_ctx* ctx, const void* d_xyzi, const
   ctx->d_gid = d_global_id;
   ctx->n = n;
   ctx->n_query = n_query;
+  ctx->n_frames = 1;
+  return PCP_OK;
+}
+
+// Frame batches: the current cloud is n_frames independent clouds laid end to end; the next pcp_build_grid
+// builds one segmented grid over all of them (searches never cross a frame).
+PCP_API int pcp_set_frames(pcp_ctx* ctx, const int64_t* frame_offsets, int64_t n_frames) {
+  if (!ctx) return PCP_ERR_INVALID_ARG;
+  if (!ctx->d_cloud || ctx->n <= 0) return pcp_fail(ctx, PCP_ERR_NO_CLOUD, "pcp_set_frames: no cloud set");
+  if (!frame_offsets || n_frames < 1 || n_frames > 65535) return pcp_fail(ctx, PCP_ERR_INVALID_ARG, "pcp_set_frames: bad argument");
+  if (ctx->d_gid || ctx->n_query != ctx->n) return pcp_fail(ctx, PCP_ERR_INVALID_ARG, "pcp_set_frames: not available for sharded clouds");
+  if (frame_offsets[0] != 0 || frame_offsets[n_frames] != ctx->n)
+    return pcp_fail(ctx, PCP_ERR_INVALID_ARG, "pcp_set_frames: offsets must start at 0 and end at n");
+  for (int64_t f = 0; f < n_frames; ++f)
+    if (frame_offsets[f + 1] < frame_offsets[f]) return pcp_fail(ctx, PCP_ERR_INVALID_ARG, "pcp_set_frames: offsets must not decrease");
+  PCP_CUDA(cudaSetDevice(ctx->device));
+  ctx->grid_ok = false;
+  ctx->n_frames = n_frames;
+  ctx->h_frames.assign(frame_offsets, frame_offsets + n_frames + 1);
+  int rc = pcp_reserve(ctx, ctx->frames, (size_t)(n_frames + 1) * sizeof(int64_t));
+  if (rc) return rc;
+  PCP_CUDA(cudaMemcpyAsync(ctx->frames.p, ctx->h_frames.data(), (size_t)(n_frames + 1) * sizeof(int64_t), cudaMemcpyHostToDevice, ctx->stream));
   return PCP_OK;
 }
 

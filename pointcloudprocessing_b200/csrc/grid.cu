@@ -93,12 +93,26 @@ __device__ __forceinline__ uint32_t cell_of(const GridDesc& g, float4 p) {
   return id;
 }
 
+// frames != nullptr: frame f holds the points [frames[f], frames[f+1]); its cells follow frame f-1's.
 __global__ void __launch_bounds__(256) keys_kernel(const float4* __restrict__ pts, int64_t n, GridDesc g,
-                                                   uint32_t* __restrict__ keys, int32_t* __restrict__ vals) {
+                                                   const int64_t* __restrict__ frames, uint32_t* __restrict__ keys,
+                                                   int32_t* __restrict__ vals) {
   int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (i >= n) return;
   float4 p = __ldg(pts + i);
-  keys[i] = finite3(p) ? cell_of(g, p) : g.n_cells;
+  uint32_t key = g.n_cells;
+  if (finite3(p)) {
+    key = cell_of(g, p);
+    if (frames) {
+      int lo = 0, hi = g.n_seg;  // last f with frames[f] <= i
+      while (hi - lo > 1) {
+        const int mid = (lo + hi) >> 1;
+        if (__ldg(frames + mid) <= i) lo = mid; else hi = mid;
+      }
+      key += (uint32_t)lo * g.seg_cells;
+    }
+  }
+  keys[i] = key;
   vals[i] = (int32_t)i;
 }
 
@@ -145,6 +159,7 @@ int bits_for(uint32_t v) {
 
 int pcp_grid_build_impl(pcp_ctx* ctx, float cell, int k_hint) {
   const int64_t n = ctx->n;
+  const int n_seg = (int)ctx->n_frames;
   ctx->grid_ok = false;
   if (n <= 0) return pcp_fail(ctx, PCP_ERR_NO_CLOUD, "pcp_build_grid: empty cloud");
   if (n >= (int64_t)0x7FFFFF00) return pcp_fail(ctx, PCP_ERR_INVALID_ARG, "pcp_build_grid: n exceeds int32 indexing");
@@ -190,7 +205,7 @@ int pcp_grid_build_impl(pcp_ctx* ctx, float cell, int k_hint) {
     // uncovered queries beat the larger candidate set) so a 3×3×3 stencil usually covers the k-NN ball.
     double area = std::max(ext[order[0]], 1e-3) * std::max(ext[order[1]], 1e-3);
     int k = k_hint > 0 ? k_hint : 20;
-    cell = (float)std::sqrt(1.9 * k * area / (double)n);
+    cell = (float)std::sqrt(1.9 * k * area / ((double)n / (double)n_seg));  // per frame: the frames share the box
     if (!(cell > 0.f)) cell = 1.f;
   }
   const double max_cells = 1.0e9;
@@ -202,7 +217,12 @@ int pcp_grid_build_impl(pcp_ctx* ctx, float cell, int k_hint) {
       g.dim[a] = (int)cnt;
       total *= cnt;
     }
-    if (total <= max_cells) { g.n_cells = (uint32_t)total; break; }
+    if (total * n_seg <= max_cells) {
+      g.seg_cells = (uint32_t)total;
+      g.n_cells = g.seg_cells * (uint32_t)n_seg;
+      g.n_seg = n_seg;
+      break;
+    }
     if (!auto_cell) return pcp_fail(ctx, PCP_ERR_GRID_TOO_LARGE, "pcp_build_grid: dense cell table above 1e9 cells; use a larger cell");
     cell *= 1.26f;
   }
@@ -243,7 +263,8 @@ int pcp_grid_build_impl(pcp_ctx* ctx, float cell, int k_hint) {
   if ((rc = pcp_reserve(ctx, ctx->cell_end, table_entries * sizeof(uint32_t)))) return rc;
   const int nb = (int)((n + 255) / 256);
   pcp_tic(ctx, PCP_T_KEYS);
-  keys_kernel<<<nb, 256, 0, st>>>(ctx->d_cloud, n, g, (uint32_t*)ctx->keys_in.p, (int32_t*)ctx->vals_in.p);
+  keys_kernel<<<nb, 256, 0, st>>>(ctx->d_cloud, n, g, n_seg > 1 ? (const int64_t*)ctx->frames.p : nullptr, (uint32_t*)ctx->keys_in.p,
+                                  (int32_t*)ctx->vals_in.p);
   PCP_LAUNCH_CHECK("keys_kernel");
   pcp_toc(ctx, PCP_T_KEYS);
 

@@ -96,7 +96,7 @@ __device__ __forceinline__ void stage_chunk(const float4* __restrict__ sorted, T
 // boundary has no points beyond it), minus 2e-3 cells for the rounding of the fractional position.
 template <int CAP>
 __device__ __forceinline__ uint32_t tile_setup(const KArgs& a, TaSmem<CAP>& sm, const int lane, const int R, const int c0min,
-                                               const int c0max, const int c1, const int c2, const int c0, const float4 Q,
+                                               const int c0max, const int c1, const int c2, const int zoff, const int c0, const float4 Q,
                                                int& nrows, bool& whole, float& cover_cells) {
   const GridDesc& g = a.g;
   const int xlo = max(c0min - R, 0), xhi = min(c0max + R, g.dim[0] - 1);
@@ -106,13 +106,13 @@ __device__ __forceinline__ uint32_t tile_setup(const KArgs& a, TaSmem<CAP>& sm, 
   uint32_t beg0 = 0, len0 = 0, beg1 = 0, len1 = 0;
   if (lane < nrows) {
     const int o2 = lane / n1, o1 = lane - o2 * n1;
-    const uint32_t base = ((uint32_t)(lo2 + o2) * (uint32_t)g.dim[1] + (uint32_t)(lo1 + o1)) * (uint32_t)g.dim[0];
+    const uint32_t base = ((uint32_t)(zoff + lo2 + o2) * (uint32_t)g.dim[1] + (uint32_t)(lo1 + o1)) * (uint32_t)g.dim[0];
     beg0 = __ldg(&a.E[base + xlo]);
     len0 = __ldg(&a.E[base + xhi + 1]) - beg0;
   }
   if (lane + 32 < nrows) {
     const int o2 = (lane + 32) / n1, o1 = (lane + 32) - o2 * n1;
-    const uint32_t base = ((uint32_t)(lo2 + o2) * (uint32_t)g.dim[1] + (uint32_t)(lo1 + o1)) * (uint32_t)g.dim[0];
+    const uint32_t base = ((uint32_t)(zoff + lo2 + o2) * (uint32_t)g.dim[1] + (uint32_t)(lo1 + o1)) * (uint32_t)g.dim[0];
     beg1 = __ldg(&a.E[base + xlo]);
     len1 = __ldg(&a.E[base + xhi + 1]) - beg1;
   }
@@ -184,7 +184,9 @@ __global__ void __launch_bounds__(TA_WARPS * 32, CAP == 24 ? 6 : (CAP == 64 ? 3 
     const uint32_t row0 = __shfl_sync(PCP_FULL, my_row, __ffs(lead) - 1);
     const bool in_grp = pending && my_row == row0;
     pending = pending && !in_grp;
-    const int c1 = (int)(row0 % (uint32_t)g.dim[1]), c2 = (int)(row0 / (uint32_t)g.dim[1]);
+    const int c1 = (int)(row0 % (uint32_t)g.dim[1]);
+    int c2 = (int)(row0 / (uint32_t)g.dim[1]);
+    const int zoff = pcp_unfold_z(g, c2);  // frame batches: the frame's first z row; c2 is now frame-local
     const int c0min = __reduce_min_sync(PCP_FULL, in_grp ? c0 : 0x7fffffff);
     const int c0max = __reduce_max_sync(PCP_FULL, in_grp ? c0 : -1);
     int R = R0, nrows = 0, bstar = -1, cum_star = 0;
@@ -194,7 +196,7 @@ __global__ void __launch_bounds__(TA_WARPS * 32, CAP == 24 ? 6 : (CAP == 64 ? 3 
       // radius: the stencil of half-width R0 covers the radius by construction (stencil_for_radius)
       bool whole;
       float cover_cells;
-      total = tile_setup(a, sm, lane, R, c0min, c0max, c1, c2, c0, Q, nrows, whole, cover_cells);
+      total = tile_setup(a, sm, lane, R, c0min, c0max, c1, c2, zoff, c0, Q, nrows, whole, cover_cells);
       Sb = 1.f;
       bstar = 0;
     } else {
@@ -203,7 +205,7 @@ __global__ void __launch_bounds__(TA_WARPS * 32, CAP == 24 ? 6 : (CAP == 64 ? 3 
     for (;;) {
       bool whole;
       float cover_cells;
-      total = tile_setup(a, sm, lane, R, c0min, c0max, c1, c2, c0, Q, nrows, whole, cover_cells);
+      total = tile_setup(a, sm, lane, R, c0min, c0max, c1, c2, zoff, c0, Q, nrows, whole, cover_cells);
       Sb = (float)BINS / (cover_cells * cover_cells * g.cell * g.cell * (1.f - 1e-6f));
       if (in_grp) {
 #pragma unroll

@@ -25,13 +25,24 @@ __global__ void __launch_bounds__(256) valid_index_kernel(const uint8_t* __restr
 }
 
 // one warp per invalid record: lanes 0..16 copy words, keeping ptID (12) and ptNum (13)
+// frame batches (frames != nullptr): every frame is its own reference run, so nothing is carried across
+// a frame start
 __global__ void __launch_bounds__(256) carry_gather_kernel(float* __restrict__ out, const uint8_t* __restrict__ valid,
-                                                           const int* __restrict__ lv, int64_t n) {
+                                                           const int* __restrict__ lv, int64_t n, const int64_t* __restrict__ frames,
+                                                           int n_frames) {
   int64_t i = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
   int lane = threadIdx.x & 31;
   if (i >= n || valid[i]) return;
   int src = lv[i];
   if (src < 0 || lane >= 17 || lane == 12 || lane == 13) return;  // leading records stay zero
+  if (frames) {
+    int lo = 0, hi = n_frames;  // last f with frames[f] <= i
+    while (hi - lo > 1) {
+      const int mid = (lo + hi) >> 1;
+      if (__ldg(frames + mid) <= i) lo = mid; else hi = mid;
+    }
+    if ((int64_t)src < __ldg(frames + lo)) return;
+  }
   out[i * 17 + lane] = out[(int64_t)src * 17 + lane];
 }
 
@@ -102,7 +113,9 @@ int pcp_carry_forward_impl(pcp_ctx* ctx, pcp_feature68* d_out, const uint8_t* d_
   if ((rc = pcp_reserve(ctx, ctx->scan_tmp, tmp))) return rc;
   PCP_CUDA(cub::DeviceScan::InclusiveScan(ctx->scan_tmp.p, tmp, lv, lv, MaxInt(), (int)n, ctx->stream));
   ctx->launches += 2;
-  carry_gather_kernel<<<(unsigned)((n * 32 + 255) / 256), 256, 0, ctx->stream>>>((float*)d_out, d_valid, lv, n);
+  carry_gather_kernel<<<(unsigned)((n * 32 + 255) / 256), 256, 0, ctx->stream>>>((float*)d_out, d_valid, lv, n,
+                                                                                    ctx->n_frames > 1 ? (const int64_t*)ctx->frames.p : nullptr,
+                                                                                    (int)ctx->n_frames);
   PCP_LAUNCH_CHECK("carry_gather_kernel");
   pcp_toc(ctx, PCP_T_CARRY);
   return PCP_OK;

@@ -4,6 +4,7 @@
 #include <stdint.h>
 
 #include <string>
+#include <vector>
 
 #include "pcp.h"
 
@@ -19,8 +20,21 @@ struct GridDesc {
   float cell;         // cell edge
   int ax[3];          // permuted axis -> x/y/z
   int dim[3];         // cells along permuted axes
-  uint32_t n_cells;   // dim0*dim1*dim2; cell id n_cells is the trash cell (non-finite points)
+  uint32_t n_cells;   // n_seg*seg_cells; cell id n_cells is the trash cell (non-finite points)
+  // Segmented grid (frame batches, pcp_set_frames): every frame has its own copy of the dim0×dim1×dim2
+  // box, frame f's cells are ids [f*seg_cells, (f+1)*seg_cells) — the frame is folded into the slowest
+  // cell coordinate (row z' = f*dim2 + c2), so a stencil clamped to [0, dim2) never leaves its frame.
+  uint32_t seg_cells; // dim0*dim1*dim2
+  int n_seg;          // 1 for a plain cloud
 };
+
+// a query's folded slowest coordinate -> (frame row offset, coordinate inside the frame)
+__host__ __device__ __forceinline__ int pcp_unfold_z(const GridDesc& g, int& c2) {
+  if (g.n_seg == 1) return 0;
+  const int f = c2 / g.dim[2];
+  c2 -= f * g.dim[2];
+  return f * g.dim[2];
+}
 
 struct DevBuf {
   void* p = nullptr;
@@ -42,6 +56,9 @@ struct pcp_ctx {
   const int32_t* d_gid = nullptr;  // optional global ids (sharded)
   int64_t n = 0, n_query = 0;
   DevBuf own_cloud;  // when the cloud came from the host
+  int64_t n_frames = 1;            // pcp_set_frames: the cloud is n_frames independent clouds laid end to end
+  std::vector<int64_t> h_frames;   // host copy of the n_frames + 1 offsets
+  DevBuf frames;                   // device copy (int64)
 
   // grid
   bool grid_ok = false;

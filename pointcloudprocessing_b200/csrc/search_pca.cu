@@ -126,7 +126,7 @@ struct Search {
 // distance to the query (radius: r2; k-NN: the current k-th distance or +inf).
 template <int MODE>
 __device__ __forceinline__ void scan_shell(const KArgs& a, WarpSmem<MODE>* ws, Search& st, const float4 Q, int c0, int c1, int c2,
-                                           float f0, float f1, float f2, int Rp, int R, float bound2, int lane, uint32_t dirs) {
+                                           int zoff, float f0, float f1, float f2, int Rp, int R, float bound2, int lane, uint32_t dirs) {
   const GridDesc& g = a.g;
   const float4* __restrict__ sorted = a.sorted;
   const unsigned lt_mask = (1u << lane) - 1u, le_mask = (2u << lane) - 1u;
@@ -159,7 +159,7 @@ __device__ __forceinline__ void scan_shell(const KArgs& a, WarpSmem<MODE>* ws, S
         }
       }
       if (keep && xlo <= xhi) {
-        const uint32_t base = ((uint32_t)e2 * (uint32_t)g.dim[1] + (uint32_t)e1) * (uint32_t)g.dim[0];
+        const uint32_t base = ((uint32_t)(zoff + e2) * (uint32_t)g.dim[1] + (uint32_t)e1) * (uint32_t)g.dim[0];
         const bool inner = Rp >= 0 && abs(d1) <= Rp && abs(d2) <= Rp;
         if (!inner) {
           bA = __ldg(&a.E[base + xlo]);
@@ -261,6 +261,7 @@ __device__ __forceinline__ void search_tile(const KArgs& a, WarpSmem<MODE>* ws, 
   // lane j remembers query j of the tile and, once solved, its k-th distance: later queries seed
   // their threshold from them (triangle inequality: d_k(q) <= d_k(q_j) + |q − q_j|)
   const float4 myP = lane < nq ? __ldg(&sorted[my_pos]) : make_float4(0.f, 0.f, 0.f, 0.f);
+  const uint32_t my_seg = (g.n_seg > 1 && lane < nq) ? __ldg(&a.keys[my_pos]) / g.seg_cells : 0u;  // a seed must come from the same frame
   float my_dk = 3.4e38f;
 
 #pragma unroll 1
@@ -281,7 +282,8 @@ __device__ __forceinline__ void search_tile(const KArgs& a, WarpSmem<MODE>* ws, 
       const int c0 = (int)(cid % (uint32_t)g.dim[0]);
       const uint32_t tq = cid / (uint32_t)g.dim[0];
       const int c1 = (int)(tq % (uint32_t)g.dim[1]);
-      const int c2 = (int)(tq / (uint32_t)g.dim[1]);
+      int c2 = (int)(tq / (uint32_t)g.dim[1]);
+      const int zoff = pcp_unfold_z(g, c2);  // frame batches: first z row of the query's frame; c2 is frame-local
       // fractional position inside the own cell (same double arithmetic as the key kernel)
       const float qc[3] = {Q.x, Q.y, Q.z};
       float f0 = (float)(((double)qc[g.ax[0]] - g.origin[g.ax[0]]) * g.inv_cell - (double)c0);
@@ -291,7 +293,7 @@ __device__ __forceinline__ void search_tile(const KArgs& a, WarpSmem<MODE>* ws, 
       f1 = fminf(fmaxf(f1, 0.f), 1.f);
       f2 = fminf(fmaxf(f2, 0.f), 1.f);
       if (MODE == 1) {
-        scan_shell<MODE>(a, ws, st, Q, c0, c1, c2, f0, f1, f2, -1, sp.R0, sp.r2, lane, dirs);
+        scan_shell<MODE>(a, ws, st, Q, c0, c1, c2, zoff, f0, f1, f2, -1, sp.R0, sp.r2, lane, dirs);
         __syncwarp();
         n_nb = st.cnt;
         overflow = st.cnt > RADIUS_CAP;
@@ -302,7 +304,7 @@ __device__ __forceinline__ void search_tile(const KArgs& a, WarpSmem<MODE>* ws, 
         float bound = 3.4e38f;
         {
           float bj = 3.4e38f;
-          if (lane < q && my_dk < 3.0e38f) {
+          if (lane < q && my_dk < 3.0e38f && my_seg == (g.n_seg > 1 ? cid / g.seg_cells : 0u)) {
             float dx = Q.x - myP.x, dy = Q.y - myP.y, dz = Q.z - myP.z;
             bj = sqrtf(my_dk) + sqrtf(dx * dx + dy * dy + dz * dz);
           }
@@ -320,7 +322,7 @@ __device__ __forceinline__ void search_tile(const KArgs& a, WarpSmem<MODE>* ws, 
 #pragma unroll 1
         for (;;) {
           STAT(1, 1);
-          scan_shell<MODE>(a, ws, st, Q, c0, c1, c2, f0, f1, f2, Rp, R, bound, lane, dirs);
+          scan_shell<MODE>(a, ws, st, Q, c0, c1, c2, zoff, f0, f1, f2, Rp, R, bound, lane, dirs);
           if (st.cnt > 0) {
             STAT(7, 1);
             u64 v = warp_sort32(lane < st.cnt ? ws->u.s.buf[lane] : PCP_KEY_INF, dirs);
@@ -523,7 +525,7 @@ int pcp_search_launch(pcp_ctx* ctx, const SearchParams& sp) {
   // file's warp-per-query kernel for the queries it defers; "v3" = warp-per-query for every point;
   // "tq" = thread-per-query walk (knn_pca.cu).  All three give identical results.
   const char* impl = getenv("PCP_KNN_IMPL");
-  const bool use_tq = sp.mode == 0 && impl && impl[0] == 't' && impl[1] == 'q';
+  const bool use_tq = sp.mode == 0 && impl && impl[0] == 't' && impl[1] == 'q' && ctx->grid.n_seg == 1;  // (no frame batches in the A/B kernel)
   const bool use_v3 = sp.mode == 0 && impl && impl[0] == 'v' && impl[1] == '3';
   if (use_tq) return pcp_knn_launch(ctx, sp);
   KArgs a;
@@ -549,7 +551,7 @@ int pcp_search_launch(pcp_ctx* ctx, const SearchParams& sp) {
   int radius_cap = 32;
   if (sp.mode == 1 && sp.out != nullptr && sp.counts == nullptr && sp.nn_idx == nullptr) {
     const double area = (double)ctx->grid.dim[2] * (double)ctx->grid.dim[0] * (double)ctx->grid.cell * (double)ctx->grid.cell;
-    const double guess = (double)ctx->n * 3.14159265 * (double)sp.r2 / (area > 0.0 ? area : 1.0);
+    const double guess = (double)ctx->n / (double)ctx->grid.n_seg * 3.14159265 * (double)sp.r2 / (area > 0.0 ? area : 1.0);
     // lanes of 32 neighbours for sparse neighbourhoods, of 64 for dense ones (configs[3]: ~32 on average),
     // the warp-per-query kernel alone beyond that
     radius_tile = guess <= 200.0;

@@ -23,3 +23,86 @@ def test_frame_pipeline_matches_oracle(oracle, n_ctx):
         check_features(got[f]["features"], oracle.knn_pca_cloud(fr, 10, 0), None, f"frame {f}")
     for f in range(3):
         assert again[f]["features"].tobytes() == got[f]["features"].tobytes()
+
+
+@pytest.mark.parametrize("n_ctx,batch", [(1, 4), (2, 3), (1, 16)])
+def test_frame_batcher_equals_per_frame_runs(oracle, n_ctx, batch):
+    """One segmented grid over many frames gives, per frame, the bytes of a run on that frame alone."""
+    fr = [synth.vlp16_frame(400 + f, pose_jitter=0.5) for f in range(9)]
+    with frames.FramePipeline(0, n_ctx=1) as pipe:
+        want = pipe.run(fr, k=10, cell=0.7)
+    with frames.FrameBatcher(0, n_ctx=n_ctx, batch=batch) as bat:
+        got = bat.run(fr, k=10, cell=0.7)
+        auto = bat.run(fr, k=10)  # auto cell differs from the per-frame one; the records must not
+    for f in range(len(fr)):
+        for key in ("features", "range", "index"):
+            assert got[f][key].tobytes() == want[f][key].tobytes(), (f, key)
+        assert got[f]["long_range"] == want[f]["long_range"]
+        assert auto[f]["features"].tobytes() == want[f]["features"].tobytes(), f
+    check_features(got[2]["features"], oracle.knn_pca_cloud(fr[2], 10, 0), None, "batched frame 2")
+
+
+def test_segmented_grid_edge_cases(oracle):
+    """Empty frames, frames smaller than k, overlapping frames that must not see each other, and every
+    k-NN kernel path (tile, work list, v3) on a segmented cloud."""
+    import os
+    from pointcloudprocessing_b200 import capi
+    rng = np.random.default_rng(5)
+    base = synth.urban(9, 6000, extent=20.0)
+    parts = [base[:2500], base[:0], base[2500:2507], base[2000:6000], base[:0], base[100:101], base[:2500].copy()]
+    offs = np.concatenate([[0], np.cumsum([p.shape[0] for p in parts])]).astype(np.int64)
+    cloud = np.concatenate(parts)
+    k = 12
+    want = []
+    with capi.Pcp(0) as p:
+        for part in parts:
+            if part.shape[0] == 0:
+                want.append(None)
+                continue
+            p.set_cloud(part)
+            p.build_grid(0.0, k)
+            want.append((p.knn_pca(k), p.knn_neighbors(k)))
+        for impl in ("", "v3"):
+            os.environ["PCP_KNN_IMPL"] = impl
+            try:
+                for cell in (0.0, 0.9, 40.0):
+                    p.set_cloud(cloud)
+                    p.set_frames(offs)
+                    p.build_grid(cell, k)
+                    feat = p.knn_pca(k)
+                    idx, d2 = p.knn_neighbors(k)
+                    for f, part in enumerate(parts):
+                        if want[f] is None:
+                            continue
+                        a, b = int(offs[f]), int(offs[f + 1])
+                        wf, (wi, wd) = want[f]
+                        gf = feat[a:b].copy()
+                        gf["ptID"] -= np.int32(a)
+                        assert gf.tobytes() == wf.tobytes(), (impl, cell, f)
+                        gi = idx[a:b].copy()
+                        gi[gi >= 0] -= a
+                        assert np.array_equal(gi, wi), (impl, cell, f)
+                        assert np.array_equal(d2[a:b].view(np.uint32), wd.view(np.uint32)), (impl, cell, f)
+            finally:
+                os.environ.pop("PCP_KNN_IMPL", None)
+        # radius mode: the stale-record carry restarts at every frame
+        r = 0.6
+        p.set_cloud(cloud)
+        p.set_frames(offs)
+        p.build_grid(r * 1.001, 0)
+        feat = p.radius_pca(r)
+        for f, part in enumerate(parts):
+            if part.shape[0] == 0:
+                continue
+            a, b = int(offs[f]), int(offs[f + 1])
+            p.set_cloud(part)
+            p.build_grid(r * 1.001, 0)
+            wf = p.radius_pca(r)
+            gf = feat[a:b].copy()
+            gf["ptID"] -= np.int32(a)
+            assert gf.tobytes() == wf.tobytes(), ("radius", f)
+        # a new cloud resets the segmentation
+        p.set_cloud(parts[0])
+        p.build_grid(0.0, k)
+        assert p.knn_pca(k).tobytes() == want[0][0].tobytes()
+    check_features(want[3][0], oracle.knn_pca_cloud(parts[3], k, 0), None, "part 3")

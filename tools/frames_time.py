@@ -14,3 +14,13 @@ for n_ctx in (1, 2, 4, 8):
         pipe.run(batch, k=10, keep=False)
         dt = time.perf_counter() - t0
     print(f"n_ctx={n_ctx} frames={nf} points={pts} {nf/dt:.0f} frames/s {pts/dt/1e6:.1f} M points/s", flush=True)
+for n_ctx, bsz in ((1, 32), (2, 32), (2, 64), (3, 64), (2, 128), (3, 128)):
+    if nf < bsz * n_ctx:
+        continue
+    for cell in (0.0, 0.5):
+        with frames.FrameBatcher(0, n_ctx=n_ctx, batch=bsz) as bat:
+            bat.run(batch[: bsz * n_ctx], k=10, cell=cell, keep=False)
+            t0 = time.perf_counter()
+            bat.run(batch, k=10, cell=cell, keep=False)
+            dt = time.perf_counter() - t0
+        print(f"batched n_ctx={n_ctx} batch={bsz} cell={cell} frames={nf} {nf/dt:.0f} frames/s {pts/dt/1e6:.1f} M points/s", flush=True)
