@@ -145,6 +145,24 @@ __global__ void __launch_bounds__(256) invert_kernel(const int32_t* __restrict__
   if (o < n) ord_of_li[li_of_ord[o]] = (int32_t)o;
 }
 
+// Point-weighted histogram of the cell occupancy for the automatic cell size: hist[m] = number of points
+// living in a cell of m points (m clamped to OCC_BINS - 1).  The host takes its median — the occupancy a
+// typical point sees; the mean would be hijacked by a handful of cells holding thousands of returns.
+constexpr int OCC_BINS = 1024;
+__global__ void __launch_bounds__(256) occupancy_kernel(const uint32_t* __restrict__ E, uint32_t n_cells,
+                                                        unsigned long long* __restrict__ hist) {
+  __shared__ uint32_t sh[OCC_BINS];
+  for (int i = threadIdx.x; i < OCC_BINS; i += blockDim.x) sh[i] = 0;
+  __syncthreads();
+  for (uint32_t c = blockIdx.x * blockDim.x + threadIdx.x; c < n_cells; c += gridDim.x * blockDim.x) {
+    const uint32_t m = __ldg(E + c + 1) - __ldg(E + c);
+    if (m) atomicAdd(&sh[min(m, (uint32_t)OCC_BINS - 1)], m);
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < OCC_BINS; i += blockDim.x)
+    if (sh[i]) atomicAdd(hist + i, (unsigned long long)sh[i]);
+}
+
 struct MaxOp {
   __device__ __forceinline__ uint32_t operator()(uint32_t a, uint32_t b) const { return a > b ? a : b; }
 };
@@ -199,15 +217,68 @@ int pcp_grid_build_impl(pcp_ctx* ctx, float cell, int k_hint) {
   g.ax[0] = order[1];
   g.ax[1] = order[2];
   bool auto_cell = !(cell > 0.f);
+  const int kk = k_hint > 0 ? k_hint : 20;
+  const double occ_target = 0.9 * (double)kk;
+  // median of the point-weighted occupancy histogram in ctx->h_occ; 0 when it is empty
+  auto occ_median = [&]() -> int {
+    unsigned long long total = 0, cum = 0;
+    for (int i = 1; i < OCC_BINS; ++i) total += ctx->h_occ[i];
+    if (total == 0) return 0;
+    int med = 1;
+    for (; med < OCC_BINS - 1; ++med) {
+      cum += ctx->h_occ[med];
+      if (2 * cum >= total) break;
+    }
+    return med;
+  };
+  bool learned = false;  // a similar cloud was built before on this context: its cell correction is reused
+  float cell0 = 1.f;     // the first guess
   if (auto_cell) {
     // surface-like density estimate: n points over the two largest extents; aim at about
     // 1.9*k points in an average cell (measured optimum of the tile kernel on the urban cloud: fewer
     // uncovered queries beat the larger candidate set) so a 3×3×3 stencil usually covers the k-NN ball.
     double area = std::max(ext[order[0]], 1e-3) * std::max(ext[order[1]], 1e-3);
-    int k = k_hint > 0 ? k_hint : 20;
-    cell = (float)std::sqrt(1.9 * k * area / ((double)n / (double)n_seg));  // per frame: the frames share the box
-    if (!(cell > 0.f)) cell = 1.f;
+    cell0 = (float)std::sqrt(1.9 * kk * area / ((double)n / (double)n_seg));  // per frame: the frames share the box
+    if (!(cell0 > 0.f)) cell0 = 1.f;
+    learned = ctx->scale_n > 0 && ctx->scale_seg == n_seg && ctx->scale_k == kk && (double)n >= 0.8 * (double)ctx->scale_n &&
+              (double)n <= 1.25 * (double)ctx->scale_n;
+    if (!learned) {
+      ctx->cell_scale = 1.0;
+      ctx->occ_pending = false;
+    } else if (ctx->occ_pending && cudaEventQuery(ctx->occ_ev) == cudaSuccess) {
+      // the occupancy of an earlier build of this stream of clouds has arrived: steer the correction
+      ctx->occ_pending = false;
+      const int med = occ_median();
+      if (med > 0 && ((double)med > 1.6 * occ_target || (double)med < 0.5 * occ_target)) ctx->cell_scale *= std::sqrt(occ_target / (double)med);
+    }
+    cell = (float)((double)cell0 * ctx->cell_scale);
+    if (!(cell > 0.f)) cell = cell0;
+    if (!ctx->h_occ) {
+      PCP_CUDA(cudaHostAlloc((void**)&ctx->h_occ, OCC_BINS * sizeof(unsigned long long), cudaHostAllocDefault));
+      PCP_CUDA(cudaEventCreateWithFlags(&ctx->occ_ev, cudaEventDisableTiming));
+    }
   }
+  // ---- sharded clouds: ord = rank of the global id (ties are broken by global index)
+  if (ctx->d_gid) {
+    if ((rc = pcp_reserve(ctx, ctx->gid_sorted, n * sizeof(int32_t)))) return rc;
+    if ((rc = pcp_reserve(ctx, ctx->gid_tmp, n * sizeof(int32_t)))) return rc;
+    if ((rc = pcp_reserve(ctx, ctx->ord_of_li, n * sizeof(int32_t)))) return rc;
+    if ((rc = pcp_reserve(ctx, ctx->li_of_ord, n * sizeof(int32_t)))) return rc;
+    const int nbi = (int)((n + 255) / 256);
+    iota_kernel<<<nbi, 256, 0, st>>>((int32_t*)ctx->gid_tmp.p, n);
+    PCP_LAUNCH_CHECK("iota_kernel");
+    size_t tb = 0;
+    PCP_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tb, (const uint32_t*)ctx->d_gid, (uint32_t*)ctx->gid_sorted.p,
+                                             (const int32_t*)ctx->gid_tmp.p, (int32_t*)ctx->li_of_ord.p, (int)n, 0, 32, st));
+    if ((rc = pcp_reserve(ctx, ctx->sort_tmp, tb))) return rc;
+    PCP_CUDA(cub::DeviceRadixSort::SortPairs(ctx->sort_tmp.p, tb, (const uint32_t*)ctx->d_gid, (uint32_t*)ctx->gid_sorted.p,
+                                             (const int32_t*)ctx->gid_tmp.p, (int32_t*)ctx->li_of_ord.p, (int)n, 0, 32, st));
+    ctx->launches += 5;
+    invert_kernel<<<nbi, 256, 0, st>>>((const int32_t*)ctx->li_of_ord.p, (int32_t*)ctx->ord_of_li.p, n);
+    PCP_LAUNCH_CHECK("invert_kernel");
+  }
+
+  for (int attempt = 0;; ++attempt) {
   const double max_cells = 1.0e9;
   for (;;) {
     double total = 1.0;
@@ -230,26 +301,6 @@ int pcp_grid_build_impl(pcp_ctx* ctx, float cell, int k_hint) {
   g.inv_cell = 1.0 / (double)cell;
   for (int d = 0; d < 3; ++d) g.origin[d] = lo[d];
   ctx->grid = g;
-
-  // ---- sharded clouds: ord = rank of the global id (ties are broken by global index)
-  if (ctx->d_gid) {
-    if ((rc = pcp_reserve(ctx, ctx->gid_sorted, n * sizeof(int32_t)))) return rc;
-    if ((rc = pcp_reserve(ctx, ctx->gid_tmp, n * sizeof(int32_t)))) return rc;
-    if ((rc = pcp_reserve(ctx, ctx->ord_of_li, n * sizeof(int32_t)))) return rc;
-    if ((rc = pcp_reserve(ctx, ctx->li_of_ord, n * sizeof(int32_t)))) return rc;
-    const int nbi = (int)((n + 255) / 256);
-    iota_kernel<<<nbi, 256, 0, st>>>((int32_t*)ctx->gid_tmp.p, n);
-    PCP_LAUNCH_CHECK("iota_kernel");
-    size_t tb = 0;
-    PCP_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tb, (const uint32_t*)ctx->d_gid, (uint32_t*)ctx->gid_sorted.p,
-                                             (const int32_t*)ctx->gid_tmp.p, (int32_t*)ctx->li_of_ord.p, (int)n, 0, 32, st));
-    if ((rc = pcp_reserve(ctx, ctx->sort_tmp, tb))) return rc;
-    PCP_CUDA(cub::DeviceRadixSort::SortPairs(ctx->sort_tmp.p, tb, (const uint32_t*)ctx->d_gid, (uint32_t*)ctx->gid_sorted.p,
-                                             (const int32_t*)ctx->gid_tmp.p, (int32_t*)ctx->li_of_ord.p, (int)n, 0, 32, st));
-    ctx->launches += 5;
-    invert_kernel<<<nbi, 256, 0, st>>>((const int32_t*)ctx->li_of_ord.p, (int32_t*)ctx->ord_of_li.p, n);
-    PCP_LAUNCH_CHECK("invert_kernel");
-  }
 
   // ---- keys
   if ((rc = pcp_reserve(ctx, ctx->keys_in, n * sizeof(uint32_t)))) return rc;
@@ -295,6 +346,42 @@ int pcp_grid_build_impl(pcp_ctx* ctx, float cell, int k_hint) {
   PCP_CUDA(cub::DeviceScan::InclusiveScan(ctx->scan_tmp.p, scan_bytes, E, E, MaxOp(), (int)table_entries, st));
   ctx->launches += 2;
   pcp_toc(ctx, PCP_T_TABLE);
+  // ---- automatic cell: check the occupancy a typical point sees (point-weighted median of the cell
+  // counts) against ~0.9 k, the measured optimum of the tile kernel on both the urban cloud and VLP-16
+  // frames.  The first guess assumes n points spread evenly over the two largest extents; a cloud that is
+  // dense in places and empty elsewhere (a sensor-centred scan) lands far above the target and is rebuilt
+  // ONCE with cell * sqrt(target / occupancy) (surface-like scaling; a build costs ~2 % of the search).
+  // The correction is remembered: the next cloud of similar size on this context starts from it, and its
+  // own occupancy comes back asynchronously (no host wait), steering the clouds after it.
+  if (!auto_cell) break;
+  {
+    if ((rc = pcp_reserve(ctx, ctx->occ_hist, OCC_BINS * sizeof(unsigned long long)))) return rc;
+    unsigned long long* d_occ = (unsigned long long*)ctx->occ_hist.p;
+    if (learned && ctx->occ_pending) break;  // an earlier measurement is still in flight
+    PCP_CUDA(cudaMemsetAsync(d_occ, 0, OCC_BINS * sizeof(unsigned long long), st));
+    const int ob = (int)std::min<uint64_t>(((uint64_t)g.n_cells + 4095) / 4096, 148 * 2);  // few blocks: each flushes 1024 bins
+    occupancy_kernel<<<ob, 256, 0, st>>>((const uint32_t*)ctx->cell_end.p, g.n_cells, d_occ);
+    PCP_LAUNCH_CHECK("occupancy_kernel");
+    PCP_CUDA(cudaMemcpyAsync(ctx->h_occ, d_occ, OCC_BINS * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
+    if (learned) {
+      PCP_CUDA(cudaEventRecord(ctx->occ_ev, st));
+      ctx->occ_pending = true;
+      break;
+    }
+    PCP_CUDA(cudaStreamSynchronize(st));
+    const int med = occ_median();
+    const bool in_band = med == 0 || ((double)med <= 1.6 * occ_target && (double)med >= 0.5 * occ_target);
+    if (in_band || attempt > 0) {
+      ctx->scale_n = n;
+      ctx->scale_seg = n_seg;
+      ctx->scale_k = kk;
+      ctx->cell_scale = (double)g.cell / (double)cell0;
+      break;
+    }
+    cell = (float)((double)cell * std::sqrt(occ_target / (double)med));
+    if (!(cell > 0.f)) break;
+  }
+  }
   ctx->grid_ok = true;
   return PCP_OK;
 }

@@ -191,7 +191,7 @@ __global__ void __launch_bounds__(TA_WARPS * 32, CAP == 24 ? 6 : (CAP == 64 ? 3 
     const int c0max = __reduce_max_sync(PCP_FULL, in_grp ? c0 : -1);
     int R = R0, nrows = 0, bstar = -1, cum_star = 0;
     uint32_t total = 0;
-    float Sb = 0.f;
+    float Sb = 0.f, noff = 0.f;
     if (MODE == 1) {
       // radius: the stencil of half-width R0 covers the radius by construction (stencil_for_radius)
       bool whole;
@@ -200,17 +200,26 @@ __global__ void __launch_bounds__(TA_WARPS * 32, CAP == 24 ? 6 : (CAP == 64 ? 3 
       Sb = 1.f;
       bstar = 0;
     } else {
-    // ---- pass 1 (+ on-demand growth of the stencil): histogram of d2 over the staged candidates
+    // ---- pass 1 (+ on-demand growth of the stencil): histogram of d2 over the staged candidates.
+    // A lane's bin coordinate is fma(d2, Sb, noff): first BINS linear bins over [0, cover^2); a lane whose
+    // threshold bin holds too many candidates for its column (d_k << cover: dense scan lines next to a
+    // sparse surrounding, e.g. the near field of a VLP-16 frame) gets ONE refinement pass with the window
+    // narrowed to that bin (candidates below the window count in bin 0 and are all collected).
+    bool hist_on = in_grp, fresh = true, refined = false, whole = false;
 #pragma unroll 1
     for (;;) {
-      bool whole;
-      float cover_cells;
-      total = tile_setup(a, sm, lane, R, c0min, c0max, c1, c2, zoff, c0, Q, nrows, whole, cover_cells);
-      Sb = (float)BINS / (cover_cells * cover_cells * g.cell * g.cell * (1.f - 1e-6f));
-      if (in_grp) {
+      if (fresh) {
+        float cover_cells;
+        total = tile_setup(a, sm, lane, R, c0min, c0max, c1, c2, zoff, c0, Q, nrows, whole, cover_cells);
+        Sb = (float)BINS / (cover_cells * cover_cells * g.cell * g.cell * (1.f - 1e-6f));
+        noff = 0.f;
+        hist_on = in_grp;
+      }
+      if (hist_on) {
 #pragma unroll
         for (int b = 0; b <= BINS; ++b) hcol[b * 32] = 0;
       }
+      __syncwarp();
 #pragma unroll 1
       for (uint32_t cb = 0; cb < total; cb += TA_CH) {
         const int cnt = (int)min((uint32_t)TA_CH, total - cb);
@@ -221,11 +230,11 @@ __global__ void __launch_bounds__(TA_WARPS * 32, CAP == 24 ? 6 : (CAP == 64 ? 3 
 #pragma unroll 2
         for (; j + 4 <= cnt; j += 4) {
           const float4 P0 = sm.cand[j], P1 = sm.cand[j + 1], P2 = sm.cand[j + 2], P3 = sm.cand[j + 3];
-          const int b0 = __float2int_rz(fminf(dist2_nofma(Q.x, Q.y, Q.z, P0) * Sb, (float)BINS));
-          const int b1 = __float2int_rz(fminf(dist2_nofma(Q.x, Q.y, Q.z, P1) * Sb, (float)BINS));
-          const int b2 = __float2int_rz(fminf(dist2_nofma(Q.x, Q.y, Q.z, P2) * Sb, (float)BINS));
-          const int b3 = __float2int_rz(fminf(dist2_nofma(Q.x, Q.y, Q.z, P3) * Sb, (float)BINS));
-          if (in_grp) {
+          const uint32_t b0 = __float2uint_rz(fminf(__fmaf_rn(dist2_nofma(Q.x, Q.y, Q.z, P0), Sb, noff), (float)BINS));
+          const uint32_t b1 = __float2uint_rz(fminf(__fmaf_rn(dist2_nofma(Q.x, Q.y, Q.z, P1), Sb, noff), (float)BINS));
+          const uint32_t b2 = __float2uint_rz(fminf(__fmaf_rn(dist2_nofma(Q.x, Q.y, Q.z, P2), Sb, noff), (float)BINS));
+          const uint32_t b3 = __float2uint_rz(fminf(__fmaf_rn(dist2_nofma(Q.x, Q.y, Q.z, P3), Sb, noff), (float)BINS));
+          if (hist_on) {
             atomicAdd(&hcol[b0 * 32], 1u);
             atomicAdd(&hcol[b1 * 32], 1u);
             atomicAdd(&hcol[b2 * 32], 1u);
@@ -233,15 +242,15 @@ __global__ void __launch_bounds__(TA_WARPS * 32, CAP == 24 ? 6 : (CAP == 64 ? 3 
           }
         }
         for (; j < cnt; ++j) {
-          const int b0 = __float2int_rz(fminf(dist2_nofma(Q.x, Q.y, Q.z, sm.cand[j]) * Sb, (float)BINS));
-          if (in_grp) atomicAdd(&hcol[b0 * 32], 1u);
+          const uint32_t b0 = __float2uint_rz(fminf(__fmaf_rn(dist2_nofma(Q.x, Q.y, Q.z, sm.cand[j]), Sb, noff), (float)BINS));
+          if (hist_on) atomicAdd(&hcol[b0 * 32], 1u);
         }
         __syncwarp();
       }
       // the bin holding the k-th smallest, and how many candidates lie at or below it
-      int cum = 0;
-      bstar = -1;
-      if (in_grp) {
+      if (hist_on) {
+        int cum = 0;
+        bstar = -1;
 #pragma unroll 8
         for (int b = 0; b < BINS; ++b) {
           cum += (int)hcol[b * 32];
@@ -249,6 +258,24 @@ __global__ void __launch_bounds__(TA_WARPS * 32, CAP == 24 ? 6 : (CAP == 64 ? 3 
             bstar = b;
             cum_star = cum;
           }
+        }
+      }
+      if (refined) break;
+      {
+        // threshold bin over-full: narrow the lane's window to [bstar - 0.02, bstar + 1.03) old bins and
+        // count again (negative coordinates convert to bin 0; the window holds the k-th by construction)
+        const bool refine = hist_on && bstar >= 0 && cum_star > CAP;
+        if (__any_sync(PCP_FULL, refine)) {
+          TSTAT(9, refine ? 1 : 0);
+          refined = true;
+          fresh = false;
+          hist_on = refine;
+          if (refine) {
+            const float z = (float)BINS * (1.f / 1.05f);
+            noff = -((float)bstar - 0.02f) * z;
+            Sb *= z;
+          }
+          continue;
         }
       }
       // lanes whose k-th neighbour lies beyond the cover radius: widen the stencil when a pass over the
@@ -268,7 +295,7 @@ __global__ void __launch_bounds__(TA_WARPS * 32, CAP == 24 ? 6 : (CAP == 64 ? 3 
     bool grp_ok = in_grp && bstar >= 0 && cum_star <= CAP;
     // the collect test is d2 * Sb < thr_bin: the bin bound (k-NN) or, with Sb = 1, r2 itself (radius: strict
     // d2 < r2 as FLANN's RadiusResultSet); other lanes collect nothing
-    const float thr_bin = grp_ok ? (MODE == 1 ? sp.r2 : (float)(bstar + 1)) : -1.f;
+    const float thr_bin = grp_ok ? (MODE == 1 ? sp.r2 : (float)(bstar + 1)) : -3.0e38f;
     uint32_t* const wend = hcol + CAP * 32;
     __syncwarp();
     // ---- pass 2: collect the candidates at or below the threshold bin (same d2 arithmetic, same bins)
@@ -280,7 +307,7 @@ __global__ void __launch_bounds__(TA_WARPS * 32, CAP == 24 ? 6 : (CAP == 64 ? 3 
       const float big = 3.0e38f;
       float bx0 = grp_ok ? Q.x : big, bx1 = grp_ok ? Q.x : -big, by0 = grp_ok ? Q.y : big, by1 = grp_ok ? Q.y : -big;
       float bz0 = grp_ok ? Q.z : big, bz1 = grp_ok ? Q.z : -big;
-      float tmax = grp_ok ? thr_bin / Sb : 0.f;
+      float tmax = grp_ok ? (thr_bin - noff) / Sb : 0.f;
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) {
         bx0 = fminf(bx0, __shfl_xor_sync(PCP_FULL, bx0, o));
@@ -324,15 +351,15 @@ __global__ void __launch_bounds__(TA_WARPS * 32, CAP == 24 ? 6 : (CAP == 64 ? 3 
           const float4 P0 = sm.cand[j], P1 = sm.cand[j + 1], P2 = sm.cand[j + 2], P3 = sm.cand[j + 3];
           const float e0 = dist2_nofma(Q.x, Q.y, Q.z, P0), e1 = dist2_nofma(Q.x, Q.y, Q.z, P1);
           const float e2 = dist2_nofma(Q.x, Q.y, Q.z, P2), e3 = dist2_nofma(Q.x, Q.y, Q.z, P3);
-          if (e0 * Sb < thr_bin) { if (MODE == 0 || wp < wend) { wp[0] = __float_as_uint(P0.w); wp[CAP * 32] = __float_as_uint(e0); } wp += 32; }
-          if (e1 * Sb < thr_bin) { if (MODE == 0 || wp < wend) { wp[0] = __float_as_uint(P1.w); wp[CAP * 32] = __float_as_uint(e1); } wp += 32; }
-          if (e2 * Sb < thr_bin) { if (MODE == 0 || wp < wend) { wp[0] = __float_as_uint(P2.w); wp[CAP * 32] = __float_as_uint(e2); } wp += 32; }
-          if (e3 * Sb < thr_bin) { if (MODE == 0 || wp < wend) { wp[0] = __float_as_uint(P3.w); wp[CAP * 32] = __float_as_uint(e3); } wp += 32; }
+          if (__fmaf_rn(e0, Sb, noff) < thr_bin) { if (MODE == 0 || wp < wend) { wp[0] = __float_as_uint(P0.w); wp[CAP * 32] = __float_as_uint(e0); } wp += 32; }
+          if (__fmaf_rn(e1, Sb, noff) < thr_bin) { if (MODE == 0 || wp < wend) { wp[0] = __float_as_uint(P1.w); wp[CAP * 32] = __float_as_uint(e1); } wp += 32; }
+          if (__fmaf_rn(e2, Sb, noff) < thr_bin) { if (MODE == 0 || wp < wend) { wp[0] = __float_as_uint(P2.w); wp[CAP * 32] = __float_as_uint(e2); } wp += 32; }
+          if (__fmaf_rn(e3, Sb, noff) < thr_bin) { if (MODE == 0 || wp < wend) { wp[0] = __float_as_uint(P3.w); wp[CAP * 32] = __float_as_uint(e3); } wp += 32; }
         }
         for (; j < n_ch; ++j) {
           const float4 P0 = sm.cand[j];
           const float e0 = dist2_nofma(Q.x, Q.y, Q.z, P0);
-          if (e0 * Sb < thr_bin) { if (MODE == 0 || wp < wend) { wp[0] = __float_as_uint(P0.w); wp[CAP * 32] = __float_as_uint(e0); } wp += 32; }
+          if (__fmaf_rn(e0, Sb, noff) < thr_bin) { if (MODE == 0 || wp < wend) { wp[0] = __float_as_uint(P0.w); wp[CAP * 32] = __float_as_uint(e0); } wp += 32; }
         }
         __syncwarp();
       }
@@ -400,7 +427,12 @@ int pcp_knn_tile_launch(pcp_ctx* ctx, const SearchParams& sp, const KArgs& a, in
   // (tuning hook: PCP_KNN_RGROW; 0 = never widen: measured slower on the urban cloud)
   float grow = 0.f;
   if (const char* e = getenv("PCP_KNN_RGROW")) grow = (float)atof(e);
-  int max_groups = TA_MAXGROUPS;  // stencil rows served per tile (tuning hook: PCP_KNN_GROUPS)
+  // Stencil rows served per tile.  One on big clouds (a second row group costs the urban cloud 5-10 %);
+  // up to four when the rows are short — frame batches: 26 k points over a few hundred rows, where 8-30 %
+  // of the lanes sit in another row than their tile's majority (measured 8.8 -> 7.1 ms per 128 frames).
+  // Tuning hook: PCP_KNN_GROUPS.
+  const double pts_per_row = (double)ctx->n / ((double)ctx->grid.n_seg * (double)ctx->grid.dim[1] * (double)ctx->grid.dim[2]);
+  int max_groups = pts_per_row < 256.0 ? 4 : TA_MAXGROUPS;
   if (const char* e = getenv("PCP_KNN_GROUPS")) max_groups = atoi(e);
   // 32-entry lanes by default; PCP_KNN_CAP=24 selects 24-entry lanes for k <= 20 (smaller network, 77
   // registers, 6 CTAs/SM) — measured SLOWER on the urban cloud (1.82 vs 1.63 ms): its 47 bins leave more

@@ -64,6 +64,13 @@ struct pcp_ctx {
   bool grid_ok = false;
   GridDesc grid;
   DevBuf bbox;        // 6 ordered-uint encodings
+  DevBuf occ_hist;    // automatic cell: point-weighted histogram of the cell occupancy
+  unsigned long long* h_occ = nullptr;  // its page-locked host copy
+  cudaEvent_t occ_ev = nullptr;         // recorded behind an asynchronous copy into h_occ
+  bool occ_pending = false;
+  double cell_scale = 1.0;              // learned correction of the first-guess cell for clouds like the last one
+  int64_t scale_n = 0;
+  int scale_seg = 0, scale_k = 0;
   DevBuf keys_in, keys_sorted, vals_in, vals_sorted, sort_tmp;
   DevBuf sorted_pts;  // float4 {x,y,z, ord bits} in cell order (ord = rank in index order)
   DevBuf inv_pos;     // uint32 ord -> sorted position
