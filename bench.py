@@ -168,6 +168,8 @@ def main():
     ap.add_argument("--cell", type=float, default=0.0)
     ap.add_argument("--cpu-sample", type=int, default=1_000_000)
     ap.add_argument("--halo", type=float, default=6.0, help="slab halo width in metres (N > 1)")
+    ap.add_argument("--halo-impl", default="peer", choices=["peer", "nccl"],
+                    help="N > 1: halo strips by peer stores + flags (pcp_halo_push / pcp_halo_wait) or by NCCL send/recv")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--e2e-contexts", type=int, default=3, help="C-ABI contexts in flight for the end-to-end figure (N = 1)")
     args = ap.parse_args()
@@ -194,7 +196,7 @@ def main():
     halo = args.halo
     if world > 1:
         # weak scaling: rank r owns the slab x in [r*L, (r+1)*L) of a world*L x L scan; neighbours
-        # exchange the strips within `halo` of the shared faces every step (NCCL send/recv)
+        # exchange the strips within `halo` of the shared faces every step (peer stores, or NCCL send/recv)
         pts[:, 0] = np.clip(pts[:, 0], 0.0, L - 1e-3) + np.float32(rank * L)
     lo, hi = rank * L, (rank + 1) * L
     p = capi.Pcp(local)  # raises if libpcp.so / the GPU is missing: no fallback
@@ -218,10 +220,17 @@ def main():
     if world > 1:
         # fixed-capacity halo buffers: own points first, then the two received strips (sharding.SlabExchange)
         cap = max(4096, int(n * min(0.5, 1.6 * halo / L)))
-        ex = sharding.SlabExchange(p, n, cap, local, rank, world, 0, lo, hi, halo)
-        ex.own_pts.copy_(d_pts)
-        ex.own_gid.copy_(d_gid)
+        if args.halo_impl == "peer":
+            # strips are written straight into the neighbours' halo regions (CUDA IPC mappings, NVLink stores)
+            ex = sharding.SlabExchangePeer(p, n, cap, local, rank, world, 0, lo, hi, halo)
+            ex.connect_group()
+            ex.set_own(d_pts, d_gid)
+        else:
+            ex = sharding.SlabExchange(p, n, cap, local, rank, world, 0, lo, hi, halo)
+            ex.own_pts.copy_(d_pts)
+            ex.own_gid.copy_(d_gid)
         torch.cuda.synchronize()
+        dist.barrier()
 
     def shard_step(src_pts):
         # halo classification kernel + grouped NCCL send/recv + sharded hand-over, all enqueued on the
@@ -348,7 +357,11 @@ def main():
                    "order": "random", "l2": "flushed between steps (256 MiB fill, untimed)",
                    "step": "bbox+keys+radix sort+cell table+fused search/moment/eigen, 68 B records",
                    "sharding": "single cloud" if world == 1 else
-                   f"x-slabs of one {world}x{L:.0f} m x {L:.0f} m scan, halo {halo} m exchanged every step (pcp_halo_pack kernel + grouped NCCL send/recv into fixed-capacity buffers, no host sync in the exchange), global-index tie-break"},
+                   f"x-slabs of one {world}x{L:.0f} m x {L:.0f} m scan, halo {halo} m exchanged every step (" +
+                   ("pcp_halo_push: the classification kernel stores the strips straight into the neighbours' halo regions over NVLink and raises their flags; pcp_halo_wait on the receiver; no NCCL, no host sync"
+                    if args.halo_impl == "peer" else
+                    "pcp_halo_pack kernel + grouped NCCL send/recv into fixed-capacity buffers, no host sync in the exchange") +
+                   "), global-index tie-break"},
         "clocks": clocks,
         "e2e": {"value": total_pts / (e2e_ms * 1e-3), "unit": "points/s", "h2d_bytes_per_step": 16 * n, "d2h_bytes_per_step": 68 * n,
                 "mode": e2e_mode, "sequential_value": total_pts / e2e_seq_s},
@@ -375,6 +388,10 @@ def main():
     # orderly teardown: tensors that lived on the library's stream go first, then the stream itself
     p.synchronize()
     keep.clear()
+    if world > 1:
+        dist.barrier()  # nobody unmaps while a neighbour may still store into the mapping
+        if hasattr(ex, "close"):
+            ex.close()
     ex = None
     del d_pts, d_out, d_kth, flush, d_gid
     torch.cuda.synchronize()

@@ -155,6 +155,28 @@ PCP_API int pcp_halo_pack(pcp_ctx* ctx, const void* d_xyzi, const int32_t* d_glo
                           float hi_face, float h, int64_t cap, void* d_lo_pts, int32_t* d_lo_gid, void* d_hi_pts,
                           int32_t* d_hi_gid, uint32_t* d_counts);
 
+/* Peer form of the exchange (no message, no NCCL launch): p_lo_* / p_hi_* point INTO the slab neighbours'
+ * halo regions (memory of another GPU mapped with pcp_peer_open, or plain device memory), so the
+ * classification kernel's stores are the transfer (NVLink peer writes).  When the strips and their padding
+ * are complete, the last block raises *p_lo_flag and *p_hi_flag (either may be NULL) to `epoch` with
+ * system-scope release stores; d_counts as in pcp_halo_pack.  The receiver enqueues pcp_halo_wait before
+ * it reads its halo regions: one thread polls its own flags (either may be NULL) until they reached
+ * `epoch`, and gives up after timeout_ms, leaving 1 in *d_err (device word, zeroed by the caller) instead
+ * of hanging the GPU.  Callers alternate between two sets of halo regions (epoch parity) so that a
+ * neighbour's step t+1 strip never lands in memory step t is still reading. */
+PCP_API int pcp_halo_push(pcp_ctx* ctx, const void* d_xyzi, const int32_t* d_global_id, int64_t n, int axis, float lo_face,
+                          float hi_face, float h, int64_t cap, void* p_lo_pts, int32_t* p_lo_gid, void* p_hi_pts,
+                          int32_t* p_hi_gid, uint32_t* d_counts, uint32_t* p_lo_flag, uint32_t* p_hi_flag, uint32_t epoch);
+PCP_API int pcp_halo_wait(pcp_ctx* ctx, const uint32_t* d_flag_a, const uint32_t* d_flag_b, uint32_t epoch, int timeout_ms,
+                          uint32_t* d_err);
+/* Device memory that other processes of the node can map: cudaMalloc + a 64-byte CUDA IPC handle to send to
+ * them (any transport); pcp_peer_open maps a received handle (peer access enabled lazily), pcp_peer_close
+ * unmaps it, pcp_peer_free releases an own allocation.  open/close/free synchronise the ctx stream. */
+PCP_API int pcp_peer_alloc(pcp_ctx* ctx, size_t bytes, void** d_ptr, void* handle64);
+PCP_API int pcp_peer_free(pcp_ctx* ctx, void* d_ptr);
+PCP_API int pcp_peer_open(pcp_ctx* ctx, const void* handle64, void** d_ptr);
+PCP_API int pcp_peer_close(pcp_ctx* ctx, void* d_ptr);
+
 /* ---- index build ------------------------------------------------------------------
  * Replaces the FLANN KDTreeSingleIndex build inside setInputCloud (src/pcaAnalysis.cpp:15):
  * bbox reduce → cell keys → radix sort → cell table (prefix scan).  `cell` > 0 is the

@@ -42,6 +42,7 @@ EXPORTS = (
     "pcp_set_cloud_device_sharded", "pcp_build_grid", "pcp_grid_info", "pcp_radius_pca", "pcp_knn_pca",
     "pcp_knn_pca_kth", "pcp_knn_neighbors", "pcp_radius_neighbors", "pcp_segment_pca", "pcp_ring_calib_default",
     "pcp_ring_calib_from_xml", "pcp_ring_project", "pcp_set_host_async", "pcp_alloc_pinned", "pcp_free_pinned", "pcp_halo_pack", "pcp_set_frames",
+    "pcp_halo_push", "pcp_halo_wait", "pcp_peer_alloc", "pcp_peer_free", "pcp_peer_open", "pcp_peer_close",
 )
 
 
@@ -111,6 +112,12 @@ def load() -> C.CDLL:
         "pcp_alloc_pinned": (vp, [C.c_size_t]),
         "pcp_free_pinned": (None, [vp]),
         "pcp_halo_pack": (i32, [vp, vp, vp, i64, i32, f32, f32, f32, i64, vp, vp, vp, vp, vp]),
+        "pcp_halo_push": (i32, [vp, vp, vp, i64, i32, f32, f32, f32, i64, vp, vp, vp, vp, vp, vp, vp, C.c_uint32]),
+        "pcp_halo_wait": (i32, [vp, vp, vp, C.c_uint32, i32, vp]),
+        "pcp_peer_alloc": (i32, [vp, C.c_size_t, C.POINTER(vp), vp]),
+        "pcp_peer_free": (i32, [vp, vp]),
+        "pcp_peer_open": (i32, [vp, vp, C.POINTER(vp)]),
+        "pcp_peer_close": (i32, [vp, vp]),
         "pcp_set_cloud_host": (i32, [vp, vp, i64, i32]),
         "pcp_set_cloud_device": (i32, [vp, vp, i64]),
         "pcp_set_cloud_device_sharded": (i32, [vp, vp, vp, i64, i64]),
@@ -208,6 +215,33 @@ class Pcp:
         """Device pointers throughout; see pcp_halo_pack."""
         self._ck(self.lib.pcp_halo_pack(self.h, d_pts, d_gid, n, axis, lo_face, hi_face, h, cap, d_lo_pts, d_lo_gid, d_hi_pts,
                                         d_hi_gid, d_counts))
+
+    def halo_push(self, d_pts: int, d_gid: Optional[int], n: int, axis: int, lo_face: float, hi_face: float, h: float, cap: int,
+                  p_lo_pts: int, p_lo_gid: int, p_hi_pts: int, p_hi_gid: int, d_counts: int, p_lo_flag: Optional[int],
+                  p_hi_flag: Optional[int], epoch: int):
+        self._ck(self.lib.pcp_halo_push(self.h, d_pts, d_gid, n, axis, lo_face, hi_face, h, cap, p_lo_pts, p_lo_gid, p_hi_pts, p_hi_gid,
+                                        d_counts, p_lo_flag, p_hi_flag, epoch))
+
+    def halo_wait(self, d_flag_a: Optional[int], d_flag_b: Optional[int], epoch: int, timeout_ms: int, d_err: int):
+        self._ck(self.lib.pcp_halo_wait(self.h, d_flag_a, d_flag_b, epoch, timeout_ms, d_err))
+
+    def peer_alloc(self, nbytes: int):
+        """-> (device pointer, 64-byte IPC handle)"""
+        ptr = C.c_void_p()
+        handle = C.create_string_buffer(64)
+        self._ck(self.lib.pcp_peer_alloc(self.h, nbytes, C.byref(ptr), handle))
+        return ptr.value, handle.raw
+
+    def peer_free(self, ptr: int):
+        self._ck(self.lib.pcp_peer_free(self.h, ptr))
+
+    def peer_open(self, handle: bytes) -> int:
+        ptr = C.c_void_p()
+        self._ck(self.lib.pcp_peer_open(self.h, C.create_string_buffer(handle, 64), C.byref(ptr)))
+        return ptr.value
+
+    def peer_close(self, ptr: int):
+        self._ck(self.lib.pcp_peer_close(self.h, ptr))
 
     def set_host_async(self, enable: bool):
         """Host-pointer calls only enqueue (pinned buffers, caller synchronises): see pcp_set_host_async."""

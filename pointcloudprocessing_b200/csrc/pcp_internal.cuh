@@ -83,6 +83,7 @@ struct pcp_ctx {
   DevBuf work_list, work_count;  // k-NN queries deferred by the tile kernel (sorted positions)
   DevBuf out_feat, out_norm, out_idx, out_d2, out_counts, flags, valid, last_valid, staging;
   DevBuf ring_range, ring_idx, ring_long, ring_offsets, ring_key;
+  DevBuf halo_done;   // block counter of halo_pad_signal_kernel
 };
 
 int pcp_fail(pcp_ctx* ctx, int status, const char* what, cudaError_t ce = cudaSuccess);

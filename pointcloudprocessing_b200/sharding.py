@@ -172,3 +172,147 @@ class SlabExchange:
         if max(c) > self.cap:
             raise RuntimeError(f"rank {self.rank}: halo strips of {c} points exceed the capacity {self.cap}")
         return c
+
+
+class _DevView:
+    """Zero-copy torch view of raw device memory (the __cuda_array_interface__ protocol)."""
+
+    def __init__(self, ptr: int, shape, typestr: str):
+        self.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": typestr, "data": (int(ptr), False), "version": 2}
+
+
+class SlabExchangePeer:
+    """Halo exchange by peer stores: the classification kernel of `pcp_halo_push` writes a rank's two
+    strips STRAIGHT INTO its slab neighbours' halo regions (their memory mapped over CUDA IPC, NVLink
+    peer writes) and raises a flag there; the receiver's stream only waits for its two flags
+    (`pcp_halo_wait`).  No message, no NCCL kernel, no host synchronisation per step.
+
+    Every rank owns ONE peer-mappable allocation holding two `own ‖ halo ‖ halo` buffers (even / odd
+    epochs, so a neighbour's strip for step t+1 never lands in memory step t still reads), their
+    global-id arrays, four flags, an error word and the two strip counters.  All ranks use the same
+    `cap`.  Set-up: `meta = alloc()`, exchange the metas of all ranks by any transport (here
+    `all_gather_object`), `connect(metas)`; then `step()` per cloud as with SlabExchange."""
+
+    INT_MAX = 0x7FFFFFFF
+
+    def __init__(self, pcp, n_own: int, cap: int, device, rank: int, world: int, axis: int, lo: float, hi: float, h: float,
+                 timeout_ms: int = 2000):
+        import os
+        self.pcp, self.n_own, self.cap, self.rank, self.world = pcp, n_own, cap, rank, world
+        self.axis, self.lo, self.hi, self.h, self.timeout_ms = axis, float(lo), float(hi), float(h), timeout_ms
+        self.device = torch.device("cuda", device) if isinstance(device, int) else torch.device(device)
+        self.n_all = n_own + 2 * cap
+        lay = self.layout(n_own, cap)
+        self.base, self.handle = pcp.peer_alloc(lay["bytes"])
+        self.lay, self.pid, self.epoch = lay, os.getpid(), 0
+        self.peers = {}      # neighbour rank -> (base pointer, layout, opened over IPC?)
+        raw = torch.as_tensor(_DevView(self.base, (lay["bytes"] // 4,), "<u4"), device=self.device)
+        raw.zero_()
+        for b in (0, 1):
+            self.buf_pts(b).fill_(float("nan"))
+            self.buf_pts(b)[:, 3] = 0
+            self.buf_gid(b).fill_(self.INT_MAX)
+        # strips towards a face without a neighbour go nowhere useful: local scratch
+        self.scratch_pts = torch.empty((cap, 4), dtype=torch.float32, device=self.device)
+        self.scratch_gid = torch.empty((cap,), dtype=torch.int32, device=self.device)
+        torch.cuda.synchronize(self.device)
+
+    @staticmethod
+    def layout(n_own: int, cap: int) -> dict:
+        n_all = n_own + 2 * cap
+        pts = [0, n_all * 16]
+        gid = [2 * n_all * 16, 2 * n_all * 16 + n_all * 4]
+        flags = (2 * n_all * 16 + 2 * n_all * 4 + 255) // 256 * 256
+        return {"n_own": n_own, "cap": cap, "n_all": n_all, "pts": pts, "gid": gid, "flags": flags, "err": flags + 16,
+                "counts": flags + 32, "bytes": flags + 64}
+
+    # ---- views / addresses of the own allocation
+    def buf_pts(self, b: int) -> torch.Tensor:
+        return torch.as_tensor(_DevView(self.base + self.lay["pts"][b], (self.n_all, 4), "<f4"), device=self.device)
+
+    def buf_gid(self, b: int) -> torch.Tensor:
+        return torch.as_tensor(_DevView(self.base + self.lay["gid"][b], (self.n_all,), "<i4"), device=self.device)
+
+    @property
+    def own_pts(self) -> torch.Tensor:
+        """Own region of the buffer the NEXT step() uses."""
+        return self.buf_pts(self.epoch & 1)[: self.n_own]
+
+    def set_own(self, pts: torch.Tensor, gid: torch.Tensor):
+        for b in (0, 1):
+            self.buf_pts(b)[: self.n_own].copy_(pts)
+            self.buf_gid(b)[: self.n_own].copy_(gid)
+
+    @staticmethod
+    def _halo_addr(base: int, lay: dict, b: int, side: int):
+        o = lay["n_own"] + side * lay["cap"]
+        return base + lay["pts"][b] + o * 16, base + lay["gid"][b] + o * 4, base + lay["flags"] + (b * 2 + side) * 4
+
+    # ---- set-up
+    def meta(self) -> dict:
+        return {"rank": self.rank, "pid": self.pid, "ptr": self.base, "handle": self.handle, "n_own": self.n_own, "cap": self.cap}
+
+    def connect(self, metas):
+        for m in metas:
+            if m["cap"] != self.cap:
+                raise ValueError("SlabExchangePeer: every rank must use the same halo capacity")
+        for nb in (self.rank - 1, self.rank + 1):
+            if nb < 0 or nb >= self.world:
+                continue
+            m = next(x for x in metas if x["rank"] == nb)
+            same = m["pid"] == self.pid  # two ranks emulated in one process: the pointer is valid as it is
+            base = m["ptr"] if same else self.pcp.peer_open(m["handle"])
+            self.peers[nb] = (base, self.layout(m["n_own"], m["cap"]), not same)
+
+    def connect_group(self, group=None):
+        metas = [None] * self.world
+        dist.all_gather_object(metas, self.meta(), group=group)
+        self.connect(metas)
+        dist.barrier(group=group)
+
+    # ---- per cloud
+    def step(self):
+        """Enqueue push + wait + hand-over on the library's stream."""
+        b = self.epoch & 1
+        self.epoch += 1
+        e = self.epoch
+        tgt = []
+        for nb, side_there in ((self.rank - 1, 1), (self.rank + 1, 0)):
+            if nb in self.peers:
+                base, lay, _ = self.peers[nb]
+                tgt.append(self._halo_addr(base, lay, b, side_there))
+            else:
+                tgt.append((self.scratch_pts.data_ptr(), self.scratch_gid.data_ptr(), None))
+        own_p = self.base + self.lay["pts"][b]
+        own_g = self.base + self.lay["gid"][b]
+        self.pcp.halo_push(own_p, own_g, self.n_own, self.axis, self.lo, self.hi, self.h, self.cap, tgt[0][0], tgt[0][1], tgt[1][0],
+                           tgt[1][1], self.base + self.lay["counts"], tgt[0][2], tgt[1][2], e)
+        fa = self._halo_addr(self.base, self.lay, b, 0)[2] if (self.rank - 1) in self.peers else None
+        fb = self._halo_addr(self.base, self.lay, b, 1)[2] if (self.rank + 1) in self.peers else None
+        self.pcp.halo_wait(fa, fb, e, self.timeout_ms, self.base + self.lay["err"])
+        self.pcp.set_cloud_device(own_p, self.n_all, own_g, self.n_own)
+
+    def halo_region(self, side: int, b: int = None):
+        b = ((self.epoch - 1) & 1) if b is None else b
+        a = self.n_own + side * self.cap
+        return self.buf_pts(b)[a: a + self.cap], self.buf_gid(b)[a: a + self.cap]
+
+    def check(self):
+        """Host check (synchronises): both strips fitted, no wait timed out."""
+        self.pcp.synchronize()
+        raw = torch.as_tensor(_DevView(self.base + self.lay["err"], (8,), "<u4"), device=self.device).tolist()
+        if raw[0]:
+            raise RuntimeError(f"rank {self.rank}: a halo wait timed out (a neighbour never delivered its strip)")
+        c = [raw[4], raw[5]]
+        if max(c) > self.cap:
+            raise RuntimeError(f"rank {self.rank}: halo strips of {c} points exceed the capacity {self.cap}")
+        return c
+
+    def close(self):
+        for nb, (base, _, opened) in self.peers.items():
+            if opened:
+                self.pcp.peer_close(base)
+        self.peers = {}
+        if self.base:
+            self.pcp.peer_free(self.base)
+            self.base = 0

@@ -55,3 +55,67 @@ def test_two_slabs_equal_unsharded(pcp, mode):
         got[g] = np.frombuffer(out.cpu().numpy().tobytes(), dtype=capi.FEATURE_DTYPE)
         ctx.close()
     assert got.tobytes() == want.tobytes()
+
+
+def test_peer_store_exchange_three_slabs():
+    """pcp_halo_push / pcp_halo_wait: three slab ranks emulated on one GPU (one context and stream each; a
+    'peer' pointer is then plain device memory) exchange their strips by direct stores + flags over
+    several epochs and reproduce the unsharded k-NN records bit for bit."""
+    pts = synth.urban(33, 90000, extent=60.0)
+    k = 16
+    with capi.Pcp(0) as full:
+        full.set_cloud(pts)
+        full.build_grid(0.0, k)
+        want = full.knn_pca(k)
+    edges, h, cap = [0.0, 20.0, 40.0, 60.0], 8.0, 32768
+    gid = np.arange(pts.shape[0], dtype=np.int32)
+    masks = [((pts[:, 0] >= edges[r]) | (r == 0)) & ((pts[:, 0] < edges[r + 1]) | (r == 2)) for r in range(3)]
+    assert sum(int(m.sum()) for m in masks) == pts.shape[0]
+    ctxs = [capi.Pcp(0) for _ in range(3)]
+    exs = [sharding.SlabExchangePeer(ctxs[r], int(masks[r].sum()), cap, 0, r, 3, 0, edges[r], edges[r + 1], h) for r in range(3)]
+    metas = [ex.meta() for ex in exs]
+    for r, ex in enumerate(exs):
+        ex.connect(metas)
+        ex.set_own(torch.from_numpy(pts[masks[r]]).cuda(), torch.from_numpy(gid[masks[r]]).cuda())
+    torch.cuda.synchronize()
+    outs = [torch.empty(ex.n_own * 68, dtype=torch.uint8, device="cuda") for ex in exs]
+    for epoch in range(3):  # both buffer parities, flags reused
+        for ex in exs:      # enqueue only: a rank's wait completes when its neighbours' pushes have run
+            ex.step()
+        got = np.zeros(pts.shape[0], capi.FEATURE_DTYPE)
+        for r, (ctx, ex) in enumerate(zip(ctxs, exs)):
+            ctx.build_grid(0.0, k)
+            outs[r].zero_()
+            torch.cuda.synchronize()  # torch's stream and the library's stream are not ordered
+            ctx.knn_pca(k, capi.CENTER_QUERY, out_device=outs[r].data_ptr())
+            ctx.synchronize()
+            got[gid[masks[r]]] = np.frombuffer(outs[r].cpu().numpy().tobytes(), dtype=capi.FEATURE_DTYPE)
+        assert got.tobytes() == want.tobytes(), epoch
+    counts = [ex.check() for ex in exs]
+    assert counts[1][0] > 0 and counts[1][1] > 0
+    # the middle rank's low halo region holds rank 0's high strip: same multiset as the NCCL-path packer's
+    rp, rg = exs[1].halo_region(0)
+    m = rg != sharding.SlabExchangePeer.INT_MAX
+    ids = np.sort(rg[m].cpu().numpy())
+    want_ids = np.sort(gid[masks[0]][pts[masks[0], 0] >= edges[1] - h])
+    assert np.array_equal(ids, want_ids)
+    assert torch.isnan(rp[~m][:, 0]).all()
+    for ex in exs:
+        ex.close()
+    for c in ctxs:
+        c.close()
+
+
+def test_halo_wait_times_out_instead_of_hanging():
+    with capi.Pcp(0) as p:
+        ex = sharding.SlabExchangePeer(p, 1000, 256, 0, 0, 2, 0, 0.0, 10.0, 1.0, timeout_ms=50)
+        other = sharding.SlabExchangePeer(p, 1000, 256, 0, 1, 2, 0, 10.0, 20.0, 1.0, timeout_ms=50)
+        metas = [ex.meta(), other.meta()]
+        ex.connect(metas)
+        pts = torch.rand(1000, 4, device="cuda") * 10.0
+        ex.set_own(pts, torch.arange(1000, dtype=torch.int32, device="cuda"))
+        ex.step()  # rank 1 never pushes: rank 0's wait must give up after 50 ms
+        with pytest.raises(RuntimeError, match="timed out"):
+            ex.check()
+        ex.close()
+        other.close()
