@@ -265,6 +265,35 @@ PCP_API int pcp_ring_project(pcp_ctx* ctx, const pcp_ring_calib* calib, const in
                              int64_t n_frames, float* range_img, int32_t* pt_index,
                              int32_t* long_range, int out_is_device);
 
+/* Constants of the segmentation stage (include/ringProjection.h:21-26). */
+typedef struct pcp_ring_seg_params {
+  int32_t ground_scan_ind;         /* 7      rings tested for ground, bottom-up */
+  float sensor_mount_angle;        /* 0.0    degrees */
+  float segment_theta;             /* 1.0472 growth threshold, radians */
+  int32_t segment_valid_point_num; /* 5 */
+  int32_t segment_valid_line_num;  /* 3 */
+} pcp_ring_seg_params;
+PCP_API int pcp_ring_seg_params_default(pcp_ring_seg_params* prm);
+
+/* RingProjector::fullSegmentation (include/ringProjection.h:174-179) for `n_frames` frames of the current
+ * cloud: projectPointCloud (as pcp_ring_project), then groundRemoval (src/ringProjection.cpp:83-136) and
+ * cloudSegmentation / labelComponents (:138-289), one thread block per frame.  Outputs, per frame, host or
+ * device (range_img, pt_index, long_range as in pcp_ring_project; any of them and of the following may be
+ * NULL except label):
+ *   ground      : n_scan × horizon int8   groundMat: 1 ground, -1 no ring pair, 0 else
+ *   label       : n_scan × horizon int32  labelMat: -1 ground or empty, 1.. valid segments numbered in the
+ *                 raster order of their first pixel, 999999 rejected segments
+ *   col_max_ground : horizon floats       maxGroundrangeOfcol (never initialised upstream: starts at 0)
+ *   above_idx   : n_scan × horizon int32  frame-local indices of the points of cloudaboveGround in the
+ *                 reference's order, padded with -1;  above_count : their number
+ *   n_labels    : number of valid segments (labelCount - 1)
+ * The reference's flood grows right, +255 columns and down only (its neighbour table is unsigned,
+ * include/ringProjection.h:69); that behaviour is kept.  At most 16 rings. */
+PCP_API int pcp_ring_segment(pcp_ctx* ctx, const pcp_ring_calib* calib, const pcp_ring_seg_params* prm,
+                             const int64_t* frame_offsets, int64_t n_frames, float* range_img, int32_t* pt_index,
+                             int32_t* long_range, int8_t* ground, int32_t* label, float* col_max_ground, int32_t* above_idx,
+                             int32_t* above_count, int32_t* n_labels, int out_is_device);
+
 #ifdef __cplusplus
 }
 #endif

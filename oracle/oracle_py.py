@@ -55,6 +55,7 @@ def load() -> C.CDLL:
         "orc_knn_pca_cloud": (None, [vp, i64, i32, i32, vp, vp, i32]),
         "orc_segment_pca": (None, [vp, vp, vp, vp, i64, vp]),
         "orc_ring_project": (i32, [vp, i64, i32, i32, f32, f32, f32, vp, vp, vp]),
+        "orc_ring_segment": (i32, [vp, i32, i32, f32, f32, i32, f32, f32, i32, i32, vp, vp, vp, vp, vp, vp, vp]),
         "orc_num_threads": (i32, []),
     }
     for name, (res, args) in sig.items():
@@ -196,3 +197,23 @@ def ring_project(pts, n_scan=16, horizon=1800, ang_res_x=0.2, ang_res_y=2.0, ang
     lr = load().orc_ring_project(pts.ctypes.data, pts.shape[0], n_scan, horizon, np.float32(ang_res_x), np.float32(ang_res_y),
                                  np.float32(ang_bottom), rng.ctypes.data, pti.ctypes.data, tag.ctypes.data)
     return rng, pti, tag, int(lr)
+
+
+def ring_segment(pts, rng, pti, n_scan=16, horizon=1800, ang_res_x=0.2, ang_res_y=2.0, ground_scan_ind=7, sensor_mount_angle=0.0,
+                 segment_theta=1.0472, valid_point_num=5, valid_line_num=3):
+    """groundRemoval + cloudSegmentation (src/ringProjection.cpp:83-289) on one projected frame.
+    Returns ground (int8 image), label (int32 image), col_max_ground, above_idx (original point indices
+    of the cloud above ground, raster order), n_labels."""
+    pts = _f4(pts)
+    rng = np.ascontiguousarray(rng, np.float32)
+    pti = np.ascontiguousarray(pti, np.int32)
+    ground = np.zeros((n_scan, horizon), np.int8)
+    label = np.zeros((n_scan, horizon), np.int32)
+    colmax = np.zeros(horizon, np.float32)
+    above = np.zeros(n_scan * horizon, np.int32)
+    nl = np.zeros(1, np.int32)
+    na = load().orc_ring_segment(pts.ctypes.data, n_scan, horizon, np.float32(ang_res_x), np.float32(ang_res_y), ground_scan_ind,
+                                 np.float32(sensor_mount_angle), np.float32(segment_theta), valid_point_num, valid_line_num,
+                                 rng.ctypes.data, pti.ctypes.data, ground.ctypes.data, label.ctypes.data, colmax.ctypes.data,
+                                 above.ctypes.data, nl.ctypes.data)
+    return ground, label, colmax, above[:na].copy(), int(nl[0])

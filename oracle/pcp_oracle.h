@@ -86,6 +86,16 @@ int32_t orc_ring_project(const float* xyzi, int64_t n, int n_scan, int horizon, 
                          float ang_res_y, float ang_bottom, float* range_img, int32_t* pt_index,
                          float* full_intensity);
 
+/* RingProjector::groundRemoval + cloudSegmentation + labelComponents (src/ringProjection.cpp:83-289) for one
+ * frame, given its projection.  ground: int8 image (1 ground, -1 no pair, 0 else); label: int32 image
+ * (-1 ground / empty, 1.. valid segments in seed raster order, 999999 rejected); col_max_ground: per column;
+ * above_idx: original indices of the "cloud above ground" in raster order, -1 padded to n_scan*horizon.
+ * Returns the above-ground count; *n_labels = number of valid segments. */
+int32_t orc_ring_segment(const float* xyzi, int n_scan, int horizon, float ang_res_x, float ang_res_y, int ground_scan_ind,
+                         float sensor_mount_angle, float segment_theta, int valid_point_num, int valid_line_num,
+                         const float* range_img, const int32_t* pt_index, int8_t* ground, int32_t* label,
+                         float* col_max_ground, int32_t* above_idx, int32_t* n_labels);
+
 int orc_num_threads(void);
 
 #ifdef __cplusplus

@@ -43,6 +43,7 @@ EXPORTS = (
     "pcp_knn_pca_kth", "pcp_knn_neighbors", "pcp_radius_neighbors", "pcp_segment_pca", "pcp_ring_calib_default",
     "pcp_ring_calib_from_xml", "pcp_ring_project", "pcp_set_host_async", "pcp_alloc_pinned", "pcp_free_pinned", "pcp_halo_pack", "pcp_set_frames",
     "pcp_halo_push", "pcp_halo_wait", "pcp_peer_alloc", "pcp_peer_free", "pcp_peer_open", "pcp_peer_close",
+    "pcp_ring_seg_params_default", "pcp_ring_segment",
 )
 
 
@@ -77,6 +78,16 @@ class RingCalib(C.Structure):
         ("vert_deg", C.c_float * 64),
         ("dist_lsb_cm", C.c_float),
         ("n_enabled", C.c_int32),
+    ]
+
+
+class RingSegParams(C.Structure):
+    _fields_ = [
+        ("ground_scan_ind", C.c_int32),
+        ("sensor_mount_angle", C.c_float),
+        ("segment_theta", C.c_float),
+        ("segment_valid_point_num", C.c_int32),
+        ("segment_valid_line_num", C.c_int32),
     ]
 
 
@@ -133,6 +144,8 @@ def load() -> C.CDLL:
         "pcp_ring_calib_default": (i32, [C.POINTER(RingCalib)]),
         "pcp_ring_calib_from_xml": (i32, [C.c_char_p, C.POINTER(RingCalib)]),
         "pcp_ring_project": (i32, [vp, C.POINTER(RingCalib), vp, i64, vp, vp, vp, i32]),
+        "pcp_ring_seg_params_default": (i32, [C.POINTER(RingSegParams)]),
+        "pcp_ring_segment": (i32, [vp, C.POINTER(RingCalib), C.POINTER(RingSegParams), vp, i64, vp, vp, vp, vp, vp, vp, vp, vp, vp, i32]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(lib, name)
@@ -149,6 +162,14 @@ def _ptr(a) -> Optional[int]:
     if isinstance(a, (int, np.integer)):
         return int(a)
     return a.ctypes.data
+
+
+def ring_seg_params_default() -> "RingSegParams":
+    prm = RingSegParams()
+    st = load().pcp_ring_seg_params_default(C.byref(prm))
+    if st != 0:
+        raise PcpError(st, "pcp_ring_seg_params_default")
+    return prm
 
 
 def ring_calib_default() -> RingCalib:
@@ -345,6 +366,32 @@ class Pcp:
         else:
             fo = np.ascontiguousarray(frame_offsets, np.int64)
             self._ck(self.lib.pcp_ring_project(self.h, C.byref(calib), fo.ctypes.data, fo.shape[0] - 1, range_ptr, index_ptr, long_ptr, 0))
+
+    def ring_segment(self, calib: Optional[RingCalib] = None, prm: Optional["RingSegParams"] = None,
+                     frame_offsets: Optional[np.ndarray] = None) -> dict:
+        """RingProjector::fullSegmentation on the current cloud (one frame, or frame_offsets.shape[0] - 1 frames)."""
+        calib = calib or ring_calib_default()
+        prm = prm or ring_seg_params_default()
+        nf = 1 if frame_offsets is None else frame_offsets.shape[0] - 1
+        fo = None if frame_offsets is None else np.ascontiguousarray(frame_offsets, np.int64)
+        ns, hs = calib.n_scan, calib.horizon_scan
+        out = {
+            "range": np.zeros((nf, ns, hs), np.float32), "index": np.zeros((nf, ns, hs), np.int32), "long_range": np.zeros(nf, np.int32),
+            "ground": np.zeros((nf, ns, hs), np.int8), "label": np.zeros((nf, ns, hs), np.int32),
+            "col_max_ground": np.zeros((nf, hs), np.float32), "above_idx": np.zeros((nf, ns * hs), np.int32),
+            "above_count": np.zeros(nf, np.int32), "n_labels": np.zeros(nf, np.int32),
+        }
+        self._ck(self.lib.pcp_ring_segment(self.h, C.byref(calib), C.byref(prm), _ptr(fo), nf, *[out[key].ctypes.data for key in (
+            "range", "index", "long_range", "ground", "label", "col_max_ground", "above_idx", "above_count", "n_labels")], 0))
+        return out
+
+    def ring_segment_host_ptr(self, calib: RingCalib, prm: "RingSegParams", frame_offsets: np.ndarray, range_ptr: int, index_ptr: int,
+                              long_ptr: int, ground_ptr: int, label_ptr: int, colmax_ptr: int, above_ptr: int, above_count_ptr: int,
+                              n_labels_ptr: int):
+        """pcp_ring_segment with raw (page-locked) host output pointers."""
+        fo = np.ascontiguousarray(frame_offsets, np.int64)
+        self._ck(self.lib.pcp_ring_segment(self.h, C.byref(calib), C.byref(prm), fo.ctypes.data, fo.shape[0] - 1, range_ptr, index_ptr,
+                                           long_ptr, ground_ptr, label_ptr, colmax_ptr, above_ptr, above_count_ptr, n_labels_ptr, 0))
 
     def ring_project(self, calib: Optional[RingCalib] = None, frame_offsets: Optional[np.ndarray] = None,
                      range_device: Optional[int] = None, index_device: Optional[int] = None, long_device: Optional[int] = None):

@@ -3,6 +3,7 @@
 #include <cstdio>
 #include <cstring>
 #include <string>
+#include <type_traits>
 #include <vector>
 
 #include "pcp_internal.cuh"
@@ -11,6 +12,9 @@ int pcp_segment_pca_impl(pcp_ctx* ctx, const float* d_centres, const int64_t* d_
                          pcp_feature68* d_out);
 int pcp_ring_project_impl(pcp_ctx* ctx, const pcp_ring_calib* calib, const int64_t* h_offsets, int64_t n_frames, float* d_range,
                           int32_t* d_index, int32_t* d_long);
+int pcp_ring_segment_impl(pcp_ctx* ctx, const pcp_ring_calib* calib, const pcp_ring_seg_params* prm, const int64_t* d_offsets,
+                          int64_t n_frames, const float* d_range, const int32_t* d_index, int8_t* d_ground, int32_t* d_label,
+                          float* d_colmax, int32_t* d_above, int32_t* d_above_count, int32_t* d_n_labels);
 
 namespace {
 
@@ -317,6 +321,71 @@ PCP_API int pcp_ring_project(pcp_ctx* ctx, const pcp_ring_calib* calib, const in
   if ((rc = copy_back(ctx, range_img, d_range, out_is_device, cells))) return rc;
   if ((rc = copy_back(ctx, pt_index, d_index, out_is_device, cells))) return rc;
   if ((rc = copy_back(ctx, long_range, d_long, out_is_device, (size_t)n_frames))) return rc;
+  if (!out_is_device && !ctx->host_async) PCP_CUDA(cudaStreamSynchronize(ctx->stream));
+  return PCP_OK;
+}
+
+PCP_API int pcp_ring_seg_params_default(pcp_ring_seg_params* prm) {
+  if (!prm) return PCP_ERR_INVALID_ARG;
+  prm->ground_scan_ind = 7;
+  prm->sensor_mount_angle = 0.0f;
+  prm->segment_theta = 1.0472f;
+  prm->segment_valid_point_num = 5;
+  prm->segment_valid_line_num = 3;
+  return PCP_OK;
+}
+
+PCP_API int pcp_ring_segment(pcp_ctx* ctx, const pcp_ring_calib* calib, const pcp_ring_seg_params* prm, const int64_t* frame_offsets,
+                             int64_t n_frames, float* range_img, int32_t* pt_index, int32_t* long_range, int8_t* ground, int32_t* label,
+                             float* col_max_ground, int32_t* above_idx, int32_t* above_count, int32_t* n_labels, int out_is_device) {
+  if (!ctx) return PCP_ERR_INVALID_ARG;
+  if (!ctx->d_cloud || ctx->n <= 0) return pcp_fail(ctx, PCP_ERR_NO_CLOUD, "pcp_ring_segment: no cloud set");
+  if (!calib || !prm || !label || n_frames < 1 || n_frames > 65535 || calib->n_scan < 1 || calib->horizon_scan < 1 ||
+      prm->ground_scan_ind < 0 || prm->ground_scan_ind >= calib->n_scan)
+    return pcp_fail(ctx, PCP_ERR_INVALID_ARG, "pcp_ring_segment: bad argument");
+  if (!frame_offsets && n_frames != 1) return pcp_fail(ctx, PCP_ERR_INVALID_ARG, "pcp_ring_segment: frame_offsets required");
+  if (frame_offsets && (frame_offsets[0] < 0 || frame_offsets[n_frames] > ctx->n))
+    return pcp_fail(ctx, PCP_ERR_INVALID_ARG, "pcp_ring_segment: frame_offsets outside the cloud");
+  PCP_CUDA(cudaSetDevice(ctx->device));
+  const size_t cells = (size_t)calib->n_scan * calib->horizon_scan * (size_t)n_frames;
+  const size_t cols = (size_t)calib->horizon_scan * (size_t)n_frames;
+  // every stage output lives on the device (the caller's buffer when it is a device pointer, else ctx-owned)
+  float *d_range, *d_colmax;
+  int32_t *d_index, *d_long, *d_label, *d_above, *d_acount, *d_nlab;
+  int8_t* d_ground;
+  int rc;
+  auto need = [&](auto*& dev, DevBuf& own, auto* user, size_t count) -> int {
+    using T = std::remove_pointer_t<std::remove_reference_t<decltype(dev)>>;
+    if (user && out_is_device) {
+      dev = user;
+      return PCP_OK;
+    }
+    int r = pcp_reserve(ctx, own, count * sizeof(T));
+    dev = (T*)own.p;
+    return r;
+  };
+  if ((rc = need(d_range, ctx->ring_range, range_img, cells))) return rc;
+  if ((rc = need(d_index, ctx->ring_idx, pt_index, cells))) return rc;
+  if ((rc = need(d_long, ctx->ring_long, long_range, (size_t)n_frames))) return rc;
+  if ((rc = need(d_ground, ctx->seg_ground, ground, cells))) return rc;
+  if ((rc = need(d_label, ctx->seg_label, label, cells))) return rc;
+  if ((rc = need(d_colmax, ctx->seg_colmax, col_max_ground, cols))) return rc;
+  if ((rc = need(d_above, ctx->seg_above, above_idx, cells))) return rc;
+  if ((rc = need(d_acount, ctx->seg_counts, above_count, (size_t)n_frames))) return rc;
+  if ((rc = need(d_nlab, ctx->seg_nlabels, n_labels, (size_t)n_frames))) return rc;
+  if ((rc = pcp_ring_project_impl(ctx, calib, frame_offsets, n_frames, d_range, d_index, d_long))) return rc;
+  if ((rc = pcp_ring_segment_impl(ctx, calib, prm, frame_offsets ? (const int64_t*)ctx->ring_offsets.p : nullptr, n_frames, d_range,
+                                  d_index, d_ground, d_label, d_colmax, d_above, d_acount, d_nlab)))
+    return rc;
+  if ((rc = copy_back(ctx, range_img, d_range, out_is_device, cells))) return rc;
+  if ((rc = copy_back(ctx, pt_index, d_index, out_is_device, cells))) return rc;
+  if ((rc = copy_back(ctx, long_range, d_long, out_is_device, (size_t)n_frames))) return rc;
+  if ((rc = copy_back(ctx, ground, d_ground, out_is_device, cells))) return rc;
+  if ((rc = copy_back(ctx, label, d_label, out_is_device, cells))) return rc;
+  if ((rc = copy_back(ctx, col_max_ground, d_colmax, out_is_device, cols))) return rc;
+  if ((rc = copy_back(ctx, above_idx, d_above, out_is_device, cells))) return rc;
+  if ((rc = copy_back(ctx, above_count, d_acount, out_is_device, (size_t)n_frames))) return rc;
+  if ((rc = copy_back(ctx, n_labels, d_nlab, out_is_device, (size_t)n_frames))) return rc;
   if (!out_is_device && !ctx->host_async) PCP_CUDA(cudaStreamSynchronize(ctx->stream));
   return PCP_OK;
 }

@@ -11,10 +11,6 @@ namespace {
 // `tempFea` lives outside the reference loop, so a record whose neighbourhood is below the
 // gate repeats λ / vectors / features of the last valid lower-index record.  The sequential
 // dependence becomes: last_valid[i] = max-scan of (valid[i] ? i : −1), then a gather.
-struct ValidToIndex {
-  const uint8_t* valid;
-  __device__ __forceinline__ int operator()(int i) const { return valid[i] ? i : -1; }
-};
 struct MaxInt {
   __device__ __forceinline__ int operator()(int a, int b) const { return a > b ? a : b; }
 };

@@ -120,8 +120,10 @@ class FrameBatcher:
     to `FramePipeline` (tests/test_gpu_frames.py)."""
 
     def __init__(self, device: int = 0, n_ctx: int = 2, batch: int = 64, max_points: int = 32768,
-                 calib: Optional[capi.RingCalib] = None):
+                 calib: Optional[capi.RingCalib] = None, segment: bool = False):
         self.calib = calib or capi.ring_calib_default()
+        self.segment = segment  # also run groundRemoval + cloudSegmentation (RingProjector::fullSegmentation)
+        self.seg_prm = capi.ring_seg_params_default()
         self.cells = self.calib.n_scan * self.calib.horizon_scan
         self.batch, self.max_points = batch, max_points
         self.ctx = [capi.Pcp(device) for _ in range(n_ctx)]
@@ -136,6 +138,15 @@ class FrameBatcher:
                 "index": capi.PinnedArray((batch * self.cells,), np.int32),
                 "long": capi.PinnedArray((batch,), np.int32),
             })
+            if segment:
+                self.slots[-1].update({
+                    "ground": capi.PinnedArray((batch * self.cells,), np.int8),
+                    "label": capi.PinnedArray((batch * self.cells,), np.int32),
+                    "colmax": capi.PinnedArray((batch * self.calib.horizon_scan,), np.float32),
+                    "above": capi.PinnedArray((batch * self.cells,), np.int32),
+                    "above_count": capi.PinnedArray((batch,), np.int32),
+                    "n_labels": capi.PinnedArray((batch,), np.int32),
+                })
 
     def close(self):
         for c in self.ctx:
@@ -163,7 +174,10 @@ class FrameBatcher:
             return
         c.set_cloud_host_ptr(s["pts"].ptr, n_all, 16)
         c.set_frames(offs)
-        if ring:
+        if ring and self.segment:
+            c.ring_segment_host_ptr(self.calib, self.seg_prm, offs, s["range"].ptr, s["index"].ptr, s["long"].ptr, s["ground"].ptr,
+                                    s["label"].ptr, s["colmax"].ptr, s["above"].ptr, s["above_count"].ptr, s["n_labels"].ptr)
+        elif ring:
             c.ring_project_host_ptr(self.calib, s["range"].ptr, s["index"].ptr, s["long"].ptr, frame_offsets=offs)
         c.build_grid(cell, k)
         c.knn_pca(k, capi.CENTER_QUERY, out_host_ptr=s["feat"].ptr)
@@ -180,9 +194,17 @@ class FrameBatcher:
                 "index": s["index"].array[j * self.cells:(j + 1) * self.cells].reshape(ns, hs).copy(),
                 "long_range": int(s["long"].array[j]),
             }
+            if ring and self.segment:
+                na = int(s["above_count"].array[j])
+                out[f0 + j].update({
+                    "ground": s["ground"].array[j * self.cells:(j + 1) * self.cells].reshape(ns, hs).copy(),
+                    "label": s["label"].array[j * self.cells:(j + 1) * self.cells].reshape(ns, hs).copy(),
+                    "above_idx": s["above"].array[j * self.cells:j * self.cells + na].copy(),
+                    "n_labels": int(s["n_labels"].array[j]),
+                })
 
     def run(self, frames: Sequence[np.ndarray], k: int = 10, cell: float = 0.0, ring: bool = True, keep: bool = True) -> List[dict]:
-        """Same contract as FramePipeline.run."""
+        """Same contract as FramePipeline.run (plus ground / label / above_idx / n_labels with segment=True)."""
         out: List[Optional[dict]] = [None] * len(frames)
         starts = list(range(0, len(frames), self.batch))
         nc = len(self.ctx)

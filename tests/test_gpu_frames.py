@@ -106,3 +106,16 @@ def test_segmented_grid_edge_cases(oracle):
         p.build_grid(0.0, k)
         assert p.knn_pca(k).tobytes() == want[0][0].tobytes()
     check_features(want[3][0], oracle.knn_pca_cloud(parts[3], k, 0), None, "part 3")
+
+
+def test_frame_batcher_full_segmentation(oracle):
+    """configs[4] end to end per frame: projection + ground removal + segmentation + k-NN PCA in one batch."""
+    fr = [synth.vlp16_frame(500 + f, pose_jitter=0.5) for f in range(5)]
+    with frames.FrameBatcher(0, n_ctx=2, batch=3, segment=True) as bat:
+        got = bat.run(fr, k=10)
+    for f, cloud in enumerate(fr):
+        rrng, rpti, _, _ = oracle.ring_project(cloud)
+        g, lab, cm, above, nl = oracle.ring_segment(cloud, rrng, rpti)
+        assert np.array_equal(got[f]["ground"], g) and np.array_equal(got[f]["label"], lab)
+        assert np.array_equal(got[f]["above_idx"], above) and got[f]["n_labels"] == nl
+    check_features(got[4]["features"], oracle.knn_pca_cloud(fr[4], 10, 0), None, "frame 4")

@@ -148,3 +148,83 @@ def test_ring_projection_known_cells(oracle):
             i += 1
     assert (pti >= 0).sum() == 12 and lr == 0
     assert rng[3, 3] == np.finfo(np.float32).max
+
+
+def _ring_image(pixels, n_scan=16, horizon=1800):
+    """pixels: {(row, col): range}.  Builds the projection outputs directly: one point per filled pixel
+    (coordinates only matter for the ground test; rows >= 8 never take part in it)."""
+    rng = np.full((n_scan, horizon), np.finfo(np.float32).max, np.float32)
+    pti = np.full((n_scan, horizon), -1, np.int32)
+    pts = np.zeros((len(pixels), 4), np.float32)
+    for n, ((r, c), d) in enumerate(sorted(pixels.items())):
+        rng[r, c] = d
+        pti[r, c] = n
+        pts[n] = (d, 0.0, 0.0, 0.0)
+    return pts, rng, pti
+
+
+def test_ring_segment_quirks_by_hand(oracle):
+    """Hand-derived from src/ringProjection.cpp:199-289 with the unsigned neighbour table
+    (include/ringProjection.h:69,119-122): the flood grows right, +255 columns and down, never left or up."""
+    d = np.float32(10.0)
+    # (a) a 6-pixel run on ring 9 plus the pixel below its first pixel: 7 pixels, pushed rows {9, 10} -> only
+    #     two rings counted (the seed's ring 9 counts because OTHER ring-9 pixels were pushed) -> rejected
+    px = {(9, c): d for c in range(100, 106)}
+    px[(10, 100)] = d
+    # (b) the same shape over three rings -> valid (>= 5 points, 3 rings)
+    for c in range(300, 304):
+        px[(9, c)] = d
+    px[(10, 300)] = d
+    px[(11, 300)] = d
+    # (c) far link: (12, 500) reaches (12, 755) although nothing lies between them; 30 more pixels to the
+    #     right of 755 make the segment valid by size
+    px[(12, 500)] = d
+    for c in range(755, 785):
+        px[(12, c)] = d
+    # (d) wrap: (13, 1799) links right to (13, 0), and (13, 1600) links far to (13, 0) — but (13, 0) was
+    #     flooded first as its own seed, so all three stay separate single pixels -> rejected
+    px[(13, 0)] = d
+    px[(13, 1799)] = d
+    px[(13, 1600)] = d
+    # (e) no upward growth: (15, 900) cannot reach (14, 900); raster order visits (14, 900) first and IT grows down
+    px[(14, 900)] = d
+    px[(15, 900)] = d
+    pts, rng, pti = _ring_image(px)
+    g, lab, cm, above, nl = oracle.ring_segment(pts, rng, pti)
+    assert (g == 0).all() or set(np.unique(g)) <= {-1, 0}  # rows 0..7 are empty: no ground anywhere
+    assert (lab[9, 100:106] == 999999).all() and lab[10, 100] == 999999
+    assert lab[9, 300] == 1 and (lab[9, 300:304] == 1).all() and lab[10, 300] == 1 and lab[11, 300] == 1
+    assert lab[12, 500] == 2 and (lab[12, 755:785] == 2).all()
+    assert lab[13, 0] == 999999 and lab[13, 1799] == 999999 and lab[13, 1600] == 999999
+    assert lab[14, 900] == 999999 and lab[15, 900] == 999999  # one 2-pixel segment, rejected
+    assert nl == 2
+    assert (lab[rng == np.finfo(np.float32).max] == -1).all()
+    assert above.shape[0] == 0  # no ground -> maxGroundrangeOfcol stays 0 -> nothing is "above ground"
+
+
+def test_ring_segment_ground_pairs_by_hand(oracle):
+    """groundRemoval (src/ringProjection.cpp:88-114): flat pairs are ground; a missing upper pixel writes -1 over
+    the 1 the previous pair gave; the column's farthest ground range gates cloudaboveGround (:186-189)."""
+    n_scan, horizon = 16, 1800
+    rng = np.full((n_scan, horizon), np.finfo(np.float32).max, np.float32)
+    pti = np.full((n_scan, horizon), -1, np.int32)
+    pts = []
+
+    def put(r, c, x, z):
+        pti[r, c] = len(pts)
+        rng[r, c] = np.float32(np.sqrt(np.float32(x * x + z * z)))
+        pts.append((x, 0.0, z, 0.0))
+
+    put(0, 7, 5.0, -1.8); put(1, 7, 7.0, -1.8); put(2, 7, 9.0, -1.8)      # flat: rows 0,1,2 ground; row 3 empty
+    put(9, 7, 4.0, 1.0)                                                     # an object nearer than the ground: above
+    put(9, 8, 4.0, 1.0)                                                     # no ground in column 8: not above
+    put(0, 20, 5.0, -1.8); put(1, 20, 5.2, 0.5)                             # steep pair: not ground
+    pts = np.asarray(pts, np.float32)
+    g, lab, cm, above, nl = oracle.ring_segment(pts, rng, pti)
+    assert g[0, 7] == 1 and g[1, 7] == 1
+    assert g[2, 7] == -1  # pair (2,3): upper empty -> -1 written over the 1 from pair (1,2)
+    assert g[3, 7] == -1 and g[6, 7] == -1 and g[7, 7] == 0
+    assert g[0, 20] == 0 and g[1, 20] == -1
+    assert lab[0, 7] == -1 and lab[1, 7] == -1 and lab[2, 7] == 999999  # row 2 is free again: a 1-pixel segment
+    assert cm[7] == rng[1, 7] and cm[8] == 0.0
+    assert above.tolist() == [int(pti[9, 7])]
