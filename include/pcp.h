@@ -294,6 +294,30 @@ PCP_API int pcp_ring_segment(pcp_ctx* ctx, const pcp_ring_calib* calib, const pc
                              int32_t* long_range, int8_t* ground, int32_t* label, float* col_max_ground, int32_t* above_idx,
                              int32_t* above_count, int32_t* n_labels, int out_is_device);
 
+/* ---- Velodyne packet decode -------------------------------------------------------------------
+ * Replaces the host-side decode the reference does with its prebuilt lib/libPacketDecoder.so
+ * (PacketDecoder::DecodePacket / ProcessHDLPacket / PushFiringData / SplitFrame, include/PacketDecoder.h:79-121,
+ * driven at src/pcapReader.cpp:79-102): `packets` = n_packets x 1206 bytes (12 blocks of {u16 0xEEFF|0xDDFF,
+ * u16 azimuth in 0.01 deg, 32 x {u16 distance in 2 mm, u8 intensity}}, u32 timestamp, 2 bytes), host or
+ * device.  Per return with a non-zero distance, in arrival order, the optional arrays of `out` (capacity
+ * n_packets * 384 each, host or device, any member may be NULL) receive what PacketDecoder::HDLFrame holds
+ * (include/PacketDecoder.h:84-94), doubles bit-identical to the reference binary's.  frame_offsets (HOST,
+ * max_frames entries): frame f = points [frame_offsets[f], frame_offsets[f+1]); frames 0 .. *n_frames_complete-1
+ * are complete revolutions (what GetFrames() returns), frame *n_frames_complete is the one still being filled.
+ * The decoded points (x, y, z, intensity narrowed to float) become the CURRENT CLOUD of the context with its
+ * non-empty frames declared as by pcp_set_frames, so pcp_ring_project / pcp_ring_segment (pass the same
+ * frame_offsets) / pcp_build_grid / pcp_knn_pca follow without the points ever visiting the host.
+ * Synchronises (the sizes are needed on the host). */
+typedef struct pcp_decoded {
+  double *x, *y, *z, *distance;
+  uint8_t *intensity, *laser_id;
+  uint16_t* azimuth;
+  uint32_t* ms;
+} pcp_decoded;
+PCP_API int pcp_decode_packets(pcp_ctx* ctx, const pcp_ring_calib* calib, const void* packets, int64_t n_packets,
+                               int packets_on_device, const pcp_decoded* out, int out_is_device, int64_t* frame_offsets,
+                               int64_t max_frames, int64_t* n_frames_complete, int64_t* n_points);
+
 #ifdef __cplusplus
 }
 #endif

@@ -55,6 +55,7 @@ def load() -> C.CDLL:
         "orc_knn_pca_cloud": (None, [vp, i64, i32, i32, vp, vp, i32]),
         "orc_segment_pca": (None, [vp, vp, vp, vp, i64, vp]),
         "orc_ring_project": (i32, [vp, i64, i32, i32, f32, f32, f32, vp, vp, vp]),
+        "orc_decode_packets": (i64, [vp, i64, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i64, vp]),
         "orc_ring_segment": (i32, [vp, i32, i32, f32, f32, i32, f32, f32, i32, i32, vp, vp, vp, vp, vp, vp, vp]),
         "orc_num_threads": (i32, []),
     }
@@ -217,3 +218,23 @@ def ring_segment(pts, rng, pti, n_scan=16, horizon=1800, ang_res_x=0.2, ang_res_
                                  rng.ctypes.data, pti.ctypes.data, ground.ctypes.data, label.ctypes.data, colmax.ctypes.data,
                                  above.ctypes.data, nl.ctypes.data)
     return ground, label, colmax, above[:na].copy(), int(nl[0])
+
+
+def decode_packets(packets, vert_deg):
+    """Velodyne packets (n, 1206) uint8 -> dict of per-return arrays + frame_offsets (complete frames first,
+    then the frame in progress) + n_complete.  vert_deg: 64 vertical corrections in degrees (16db.xml)."""
+    pk = np.ascontiguousarray(packets, np.uint8).reshape(-1, 1206)
+    n_max = pk.shape[0] * 384
+    vd = np.ascontiguousarray(vert_deg, np.float32)
+    out = {"x": np.zeros(n_max), "y": np.zeros(n_max), "z": np.zeros(n_max), "distance": np.zeros(n_max),
+           "intensity": np.zeros(n_max, np.uint8), "laser_id": np.zeros(n_max, np.uint8), "azimuth": np.zeros(n_max, np.uint16),
+           "ms": np.zeros(n_max, np.uint32)}
+    max_frames = pk.shape[0] * 12 + 2
+    offs = np.zeros(max_frames, np.int64)
+    nf = np.zeros(1, np.int64)
+    n = load().orc_decode_packets(pk.ctypes.data, pk.shape[0], vd.ctypes.data, *[out[k].ctypes.data for k in (
+        "x", "y", "z", "distance", "intensity", "laser_id", "azimuth", "ms")], offs.ctypes.data, max_frames, nf.ctypes.data)
+    res = {k: v[:n].copy() for k, v in out.items()}
+    res["frame_offsets"] = offs[: int(nf[0]) + 2].copy()
+    res["n_complete"] = int(nf[0])
+    return res

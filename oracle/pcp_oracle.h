@@ -98,6 +98,14 @@ int32_t orc_ring_segment(const float* xyzi, int n_scan, int horizon, float ang_r
 
 int orc_num_threads(void);
 
+/* Velodyne packet decode (lib/libPacketDecoder.so restated, see decoder.cpp): n_packets x 1206 bytes ->
+ * per-return arrays in arrival order (zero distances dropped).  frame_offsets[f] = first point of frame f;
+ * *n_frames = number of COMPLETE frames (the reference's GetFrames()); frame_offsets[*n_frames + 1] = total,
+ * the trailing frame being the one still in progress.  Returns the number of points. */
+int64_t orc_decode_packets(const uint8_t* packets, int64_t n_packets, const float* vert_deg, double* x, double* y, double* z,
+                           double* distance, uint8_t* intensity, uint8_t* laser_id, uint16_t* azimuth, uint32_t* ms,
+                           int64_t* frame_offsets, int64_t max_frames, int64_t* n_frames);
+
 #ifdef __cplusplus
 }
 #endif

@@ -43,7 +43,7 @@ EXPORTS = (
     "pcp_knn_pca_kth", "pcp_knn_neighbors", "pcp_radius_neighbors", "pcp_segment_pca", "pcp_ring_calib_default",
     "pcp_ring_calib_from_xml", "pcp_ring_project", "pcp_set_host_async", "pcp_alloc_pinned", "pcp_free_pinned", "pcp_halo_pack", "pcp_set_frames",
     "pcp_halo_push", "pcp_halo_wait", "pcp_peer_alloc", "pcp_peer_free", "pcp_peer_open", "pcp_peer_close",
-    "pcp_ring_seg_params_default", "pcp_ring_segment",
+    "pcp_ring_seg_params_default", "pcp_ring_segment", "pcp_decode_packets",
 )
 
 
@@ -89,6 +89,11 @@ class RingSegParams(C.Structure):
         ("segment_valid_point_num", C.c_int32),
         ("segment_valid_line_num", C.c_int32),
     ]
+
+
+class Decoded(C.Structure):
+    _fields_ = [("x", C.c_void_p), ("y", C.c_void_p), ("z", C.c_void_p), ("distance", C.c_void_p), ("intensity", C.c_void_p),
+                ("laser_id", C.c_void_p), ("azimuth", C.c_void_p), ("ms", C.c_void_p)]
 
 
 class PcpError(RuntimeError):
@@ -145,6 +150,7 @@ def load() -> C.CDLL:
         "pcp_ring_calib_from_xml": (i32, [C.c_char_p, C.POINTER(RingCalib)]),
         "pcp_ring_project": (i32, [vp, C.POINTER(RingCalib), vp, i64, vp, vp, vp, i32]),
         "pcp_ring_seg_params_default": (i32, [C.POINTER(RingSegParams)]),
+        "pcp_decode_packets": (i32, [vp, C.POINTER(RingCalib), vp, i64, i32, vp, i32, vp, i64, vp, vp]),
         "pcp_ring_segment": (i32, [vp, C.POINTER(RingCalib), C.POINTER(RingSegParams), vp, i64, vp, vp, vp, vp, vp, vp, vp, vp, vp, i32]),
     }
     for name, (res, args) in sig.items():
@@ -366,6 +372,35 @@ class Pcp:
         else:
             fo = np.ascontiguousarray(frame_offsets, np.int64)
             self._ck(self.lib.pcp_ring_project(self.h, C.byref(calib), fo.ctypes.data, fo.shape[0] - 1, range_ptr, index_ptr, long_ptr, 0))
+
+    def decode_packets(self, packets: np.ndarray, calib: Optional[RingCalib] = None, want_arrays: bool = True,
+                       packets_device: Optional[int] = None, n_packets: Optional[int] = None) -> dict:
+        """Velodyne packets ((n, 1206) uint8 on the host, or a device pointer) -> the decoded points become the
+        current cloud (with its frames); returns frame_offsets / n_complete / n_points and, with want_arrays,
+        the per-return arrays of PacketDecoder::HDLFrame."""
+        calib = calib or ring_calib_default()
+        if packets_device is None:
+            pk = np.ascontiguousarray(packets, np.uint8).reshape(-1, 1206)
+            npk, ptr, on_dev = pk.shape[0], pk.ctypes.data, 0
+        else:
+            npk, ptr, on_dev = int(n_packets), packets_device, 1
+        cap = npk * 384
+        max_frames = npk * 12 + 2
+        offs = np.zeros(max_frames, np.int64)
+        nfc, npts = C.c_int64(), C.c_int64()
+        arrays, dec = {}, None
+        if want_arrays:
+            arrays = {"x": np.zeros(cap), "y": np.zeros(cap), "z": np.zeros(cap), "distance": np.zeros(cap),
+                      "intensity": np.zeros(cap, np.uint8), "laser_id": np.zeros(cap, np.uint8), "azimuth": np.zeros(cap, np.uint16),
+                      "ms": np.zeros(cap, np.uint32)}
+            dec = Decoded(**{k: v.ctypes.data for k, v in arrays.items()})
+        self._ck(self.lib.pcp_decode_packets(self.h, C.byref(calib), ptr, npk, on_dev, C.byref(dec) if dec else None, 0, offs.ctypes.data,
+                                             max_frames, C.byref(nfc), C.byref(npts)))
+        n, nc = npts.value, nfc.value
+        self.n = self.n_query = n
+        res = {k: v[:n] for k, v in arrays.items()}
+        res.update({"frame_offsets": offs[: nc + 2].copy(), "n_complete": nc, "n_points": n})
+        return res
 
     def ring_segment(self, calib: Optional[RingCalib] = None, prm: Optional["RingSegParams"] = None,
                      frame_offsets: Optional[np.ndarray] = None) -> dict:

@@ -87,7 +87,7 @@ PCP_API int pcp_destroy(pcp_ctx* ctx) {
                     &ctx->out_norm, &ctx->out_idx, &ctx->out_d2, &ctx->out_counts, &ctx->flags, &ctx->valid,
                     &ctx->last_valid, &ctx->staging, &ctx->ring_range, &ctx->ring_idx, &ctx->ring_long,
                     &ctx->ring_offsets, &ctx->ring_key, &ctx->frames, &ctx->occ_hist, &ctx->halo_done, &ctx->seg_ground, &ctx->seg_label,
-                    &ctx->seg_colmax, &ctx->seg_above, &ctx->seg_counts, &ctx->seg_nlabels};
+                    &ctx->seg_colmax, &ctx->seg_above, &ctx->seg_counts, &ctx->seg_nlabels, &ctx->dec_tables, &ctx->dec_packed, &ctx->dec_out};
   for (DevBuf* b : bufs) free_buf(*b);
   if (ctx->h_occ) cudaFreeHost(ctx->h_occ);
   if (ctx->occ_ev) cudaEventDestroy(ctx->occ_ev);

@@ -84,6 +84,7 @@ struct pcp_ctx {
   DevBuf out_feat, out_norm, out_idx, out_d2, out_counts, flags, valid, last_valid, staging;
   DevBuf ring_range, ring_idx, ring_long, ring_offsets, ring_key;
   DevBuf halo_done;   // block counter of halo_pad_signal_kernel
+  DevBuf dec_tables, dec_packed, dec_out;  // pcp_decode_packets: azimuth cos/sin tables, per-block scan, staged outputs
   DevBuf seg_ground, seg_label, seg_colmax, seg_above, seg_counts, seg_nlabels;  // pcp_ring_segment outputs
 };
 

@@ -59,3 +59,23 @@ def test_cuda_matches_golden(pcp, oracle):
     np.testing.assert_array_equal(pti[0], G["ring_index"])
     np.testing.assert_array_equal(rng[0].view(np.uint32), G["ring_range"].view(np.uint32))
     assert int(lr[0]) == int(G["ring_long"])
+
+
+VERT_16DB = np.array(([-15, 1, -13, 3, -11, 5, -9, 7, -7, 9, -5, 11, -3, 13, -1, 15] * 2) + [0] * 32, np.float32)  # 16db.xml:813-1249
+
+
+@pytest.mark.parametrize("name", ["sweep", "ragged", "upper_bank"])
+def test_decode_oracle_is_pinned_to_the_reference_binary(oracle, name):
+    """tests/golden/decoder_*.npz hold what the reference's own lib/libPacketDecoder.so produced for these
+    packets (oracle/ref_decoder/make_golden.py).  The restated decoder must agree bit for bit, doubles included,
+    and split the frames at the same points."""
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", f"decoder_{name}.npz"))
+    got = oracle.decode_packets(g["packets"], VERT_16DB)
+    nc = got["n_complete"]
+    assert nc == g["frame_offsets"].shape[0] - 1
+    np.testing.assert_array_equal(got["frame_offsets"][: nc + 1], g["frame_offsets"])
+    n = int(g["frame_offsets"][-1])
+    for key in ("x", "y", "z", "distance"):
+        np.testing.assert_array_equal(got[key][:n].view(np.uint64), g[key].view(np.uint64), err_msg=key)
+    for key in ("intensity", "laser_id", "azimuth", "ms"):
+        np.testing.assert_array_equal(got[key][:n], g[key], err_msg=key)
