@@ -358,6 +358,7 @@ int pcp_grid_build_impl(pcp_ctx* ctx, float cell, int k_hint) {
     if ((rc = pcp_reserve(ctx, ctx->occ_hist, OCC_BINS * sizeof(unsigned long long)))) return rc;
     unsigned long long* d_occ = (unsigned long long*)ctx->occ_hist.p;
     if (learned && ctx->occ_pending) break;  // an earlier measurement is still in flight
+    if (learned && (ctx->occ_tick++ & 15) != 0) break;  // steady state: look again every 16th cloud only
     PCP_CUDA(cudaMemsetAsync(d_occ, 0, OCC_BINS * sizeof(unsigned long long), st));
     const int ob = (int)std::min<uint64_t>(((uint64_t)g.n_cells + 4095) / 4096, 148 * 2);  // few blocks: each flushes 1024 bins
     occupancy_kernel<<<ob, 256, 0, st>>>((const uint32_t*)ctx->cell_end.p, g.n_cells, d_occ);

@@ -68,6 +68,7 @@ struct pcp_ctx {
   unsigned long long* h_occ = nullptr;  // its page-locked host copy
   cudaEvent_t occ_ev = nullptr;         // recorded behind an asynchronous copy into h_occ
   bool occ_pending = false;
+  unsigned occ_tick = 0;
   double cell_scale = 1.0;              // learned correction of the first-guess cell for clouds like the last one
   int64_t scale_n = 0;
   int scale_seg = 0, scale_k = 0;
