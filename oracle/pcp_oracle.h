@@ -10,6 +10,9 @@
  * reference tree nor installed in this image, so the upstream arithmetic is restated from
  * the published algorithms and pinned by brute-force cross-checks and analytic known-answer
  * cases (tests/test_oracle_*.py), not by outputs of the reference itself.
+ * Exception — the packet-decode row (orc_decode_packets) IS pinned: the reference's prebuilt
+ * lib/libPacketDecoder.so runs in the build container, oracle/ref_decoder/ drives it, and
+ * tests/golden/decoder_*.npz hold its outputs (tests/test_golden.py).
  *
  * Clouds are packed float4 (x,y,z,intensity), n×4 floats.
  */
