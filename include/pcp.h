@@ -46,7 +46,8 @@ typedef enum pcp_status {
   PCP_ERR_K_UNSUPPORTED = -7,  /* k outside [1, PCP_MAX_K] */
   PCP_ERR_OOM = -8,
   PCP_ERR_IO = -9,             /* calibration file could not be read / parsed */
-  PCP_ERR_NEIGHBOR_OVERFLOW = -10 /* a radius neighbourhood exceeded the per-query on-chip buffer */
+  PCP_ERR_NEIGHBOR_OVERFLOW = -10 /* pcp_radius_neighbors: a neighbour LIST exceeded the 512-entry on-chip buffer (records and normals of such
+                                     neighbourhoods are still computed: unordered double-precision accumulation) */
 } pcp_status;
 
 #define PCP_MAX_K 32

@@ -247,6 +247,45 @@ __device__ __forceinline__ void scan_shell(const KArgs& a, WarpSmem<MODE>* ws, S
 }
 
 // One tile: lane l holds the sorted position `my_pos` of query l (valid for l < nq); the warp solves the
+// Radius neighbourhoods larger than the warp buffer (RADIUS_CAP hits; e.g. r = 3 m on a dense scan,
+// src/lidarOdometry.cpp:76): no list can be kept, so the hits are accumulated where they are found — one
+// walk over the stencil per call, every lane summing its own candidates in DOUBLE, then a warp reduction:
+// count, coordinate sums and the six second moments about (cx, cy, cz).  The reference sums the same
+// terms in fp32 in (d2, index) order; the double sums differ from that by rounding only (well inside the
+// 1e-4 parity bar, and closer to the exact moment).  Used for records / normals, never for neighbour lists.
+__device__ __noinline__ void heavy_moment(const KArgs& a, const float4 Q, int c0, int c1, int c2, int zoff, int R, float r2, double cx,
+                                          double cy, double cz, int lane, double* sums /*3*/, double* mom /*6*/) {
+  const GridDesc& g = a.g;
+  const int lo0 = max(c0 - R, 0), hi0 = min(c0 + R, g.dim[0] - 1);
+  const int lo1 = max(c1 - R, 0), hi1 = min(c1 + R, g.dim[1] - 1);
+  const int lo2 = max(c2 - R, 0), hi2 = min(c2 + R, g.dim[2] - 1);
+  double s[3] = {0, 0, 0}, m[6] = {0, 0, 0, 0, 0, 0};
+  for (int e2 = lo2; e2 <= hi2; ++e2)
+    for (int e1 = lo1; e1 <= hi1; ++e1) {
+      const uint32_t base = ((uint32_t)(zoff + e2) * (uint32_t)g.dim[1] + (uint32_t)e1) * (uint32_t)g.dim[0];
+      const uint32_t b = __ldg(&a.E[base + lo0]), e = __ldg(&a.E[base + hi0 + 1]);
+      for (uint32_t j = b + lane; j < e; j += 32) {
+        const float4 P = __ldg(&a.sorted[j]);
+        if (dist2_nofma(Q.x, Q.y, Q.z, P) < r2) {
+          const double px = (double)P.x - cx, py = (double)P.y - cy, pz = (double)P.z - cz;
+          s[0] += (double)P.x; s[1] += (double)P.y; s[2] += (double)P.z;
+          m[0] += px * px; m[1] += px * py; m[2] += px * pz; m[3] += py * py; m[4] += py * pz; m[5] += pz * pz;
+        }
+      }
+    }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+#pragma unroll
+    for (int t = 0; t < 3; ++t) s[t] += __shfl_xor_sync(PCP_FULL, s[t], o);
+#pragma unroll
+    for (int t = 0; t < 6; ++t) m[t] += __shfl_xor_sync(PCP_FULL, m[t], o);
+  }
+#pragma unroll
+  for (int t = 0; t < 3; ++t) sums[t] = s[t];
+#pragma unroll
+  for (int t = 0; t < 6; ++t) mom[t] = m[t];
+}
+
 // nq queries one after the other and writes their outputs.
 template <int MODE>
 __device__ __forceinline__ void search_tile(const KArgs& a, WarpSmem<MODE>* ws, const int lane, const int64_t my_pos, const int nq) {
@@ -273,7 +312,7 @@ __device__ __forceinline__ void search_tile(const KArgs& a, WarpSmem<MODE>* ws, 
     const float4 Q = __ldg(&sorted[pq]);
     const uint32_t cid = __ldg(&a.keys[pq]);
     int n_nb = 0;
-    bool overflow = false;
+    bool overflow = false, heavy = false;
     Search st;
     st.best = PCP_KEY_INF;
     st.thr = PCP_KEY_INF;
@@ -297,6 +336,25 @@ __device__ __forceinline__ void search_tile(const KArgs& a, WarpSmem<MODE>* ws, 
         __syncwarp();
         n_nb = st.cnt;
         overflow = st.cnt > RADIUS_CAP;
+        if (overflow && sp.nn_idx == nullptr) {
+          // more hits than the buffer holds: unordered double-precision accumulation instead of a list
+          overflow = false;
+          heavy = true;
+          if (n_nb >= sp.min_pts && (need_q || need_m)) {
+            double sums[3], mom[6];
+            const double inv_n = 1.0 / (double)n_nb;
+            if (need_q) {
+              heavy_moment(a, Q, c0, c1, c2, zoff, sp.R0, sp.r2, (double)Q.x, (double)Q.y, (double)Q.z, lane, sums, mom);
+              if (lane < 6) ws->mom[q][lane] = (float)(mom[lane] * inv_n);
+            }
+            if (need_m) {
+              if (!need_q) heavy_moment(a, Q, c0, c1, c2, zoff, sp.R0, sp.r2, 0.0, 0.0, 0.0, lane, sums, mom);
+              const double mx = sums[0] * inv_n, my = sums[1] * inv_n, mz = sums[2] * inv_n;
+              heavy_moment(a, Q, c0, c1, c2, zoff, sp.R0, sp.r2, mx, my, mz, lane, sums, mom);
+              if (lane < 6) ws->momM[q][lane] = (float)(mom[lane] * inv_n);
+            }
+          }
+        }
       } else {
         int Rp = -1, R = sp.R0;
         // seed: the tightest upper bound on this query's k-th distance from the solved queries of
@@ -361,7 +419,7 @@ __device__ __forceinline__ void search_tile(const KArgs& a, WarpSmem<MODE>* ws, 
     const int gid_q = a.gid_of_ord ? __ldg(&a.gid_of_ord[ord_q]) : ord_q;
     const bool valid = !overflow && (MODE == 0 ? n_nb > 0 : n_nb >= sp.min_pts);
     u64* buf = ws->u.s.buf;
-    if (MODE == 1 && !overflow && n_nb > 0 && (valid || sp.nn_idx != nullptr)) {
+    if (MODE == 1 && !overflow && !heavy && n_nb > 0 && (valid || sp.nn_idx != nullptr)) {
       // sort the hits by (d2, index)
       if (n_nb <= 32) {
         st.best = warp_sort32(lane < n_nb ? buf[lane] : PCP_KEY_INF, dirs);
@@ -399,7 +457,7 @@ __device__ __forceinline__ void search_tile(const KArgs& a, WarpSmem<MODE>* ws, 
         }
       }
     }
-    if (valid && (need_q || need_m)) {
+    if (valid && !heavy && (need_q || need_m)) {
       if (need_q) {
         float c = ordered_moment<MODE == 1>(sorted, a.inv, buf, st.best, n_nb, Q.x, Q.y, Q.z, ws->u.s.prod, lane);
         if (lane < 6) ws->mom[q][lane] = c;

@@ -2,7 +2,7 @@
 import numpy as np
 import pytest
 
-from pointcloudprocessing_b200 import synth
+from pointcloudprocessing_b200 import capi, synth
 from pointcloudprocessing_b200.capi import CENTER_MEAN, CENTER_QUERY
 from parity import check_features
 
@@ -132,3 +132,28 @@ def test_eigen_closer_to_fp64_truth(pcp, oracle):
         eo = max(eo, np.abs(ref["la"][i] - w).max() / w.max())
     assert eg < 1.2e-7  # fp32 rounding of the exact value
     assert eg <= eo
+
+
+def test_radius_pca_heavy_neighbourhoods(pcp, oracle):
+    """r = 3 m on a dense scan (the radius src/lidarOdometry.cpp:76 uses): thousands of hits per query, far
+    beyond the 512-entry warp buffer — records come from the unordered double-precision accumulation, counts
+    stay exact, eigen outputs within the parity bar; neighbour LISTS of that size still fail loudly."""
+    pts = synth.urban(8, 40000, extent=30.0)
+    r = 3.0
+    pcp.set_cloud(pts)
+    pcp.build_grid(r * 1.001, 0)
+    got = pcp.radius_pca(r, 13, CENTER_QUERY, True)
+    ref, valid = oracle.radius_pca_cloud(pts, r, 13, True, nthreads=0)
+    assert got["ptNum"].max() > 2000 and (got["ptNum"] > 512).mean() > 0.5
+    assert np.array_equal(got["ptNum"], ref["ptNum"])
+    check_features(got, ref, valid, "radius heavy")
+    with pytest.raises(capi.PcpError):
+        pcp.radius_neighbors(r)
+    # a mix: sparse clutter (short lists, bitwise path) next to dense ground (heavy path) in one launch
+    r = 1.2
+    pcp.build_grid(r * 1.001, 0)
+    got = pcp.radius_pca(r, 13, CENTER_QUERY, True)
+    ref, valid = oracle.radius_pca_cloud(pts, r, 13, True, nthreads=0)
+    assert (got["ptNum"] > 512).any() and (got["ptNum"] < 200).any()
+    assert np.array_equal(got["ptNum"], ref["ptNum"])
+    check_features(got, ref, valid, "radius mixed")
