@@ -24,6 +24,9 @@
 #include <cstdlib>
 
 #include "eigen3.cuh"
+#ifndef PCP_TILE_SYNC
+#define PCP_TILE_SYNC 1
+#endif
 #include "pcp_internal.cuh"
 #include "search_common.cuh"
 #include "knn_finish.cuh"
@@ -383,6 +386,12 @@ __global__ void __launch_bounds__(TA_WARPS * 32, CAP == 24 ? 6 : (CAP == 64 ? 3 
       if (defer) work_list[base + __popc(dm & ((1u << lane) - 1u))] = (uint32_t)p;
     }
   }
+  // The sorting network and the finish stage are ~50 KB of straight-line code walked once per tile: the
+  // warps of a CTA re-align here so that they fetch it together (one miss serves four warps) instead of
+  // evicting each other's lines (PCP_TILE_SYNC=0 at build time to compare).
+#if PCP_TILE_SYNC
+  __syncthreads();
+#endif
   // ---- order the collected keys by (d2, index)
   u64 keys[CAP];
 #pragma unroll
@@ -399,6 +408,9 @@ __global__ void __launch_bounds__(TA_WARPS * 32, CAP == 24 ? 6 : (CAP == 64 ? 3 
   const int n_nb = ok ? (MODE == 1 ? cnt : k) : 0;
   const bool emit = active && (ok || !finite);  // non-finite queries get their empty record here
   __syncwarp();
+#if PCP_TILE_SYNC
+  __syncthreads();
+#endif
   knn_finish(a, hcol, hcol + CAP * 32, 32, n_nb, MODE == 1 ? sp.min_pts : 1, Q, emit ? my_slot : -1, sm.u.rec, lane);
 }
 
