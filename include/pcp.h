@@ -319,6 +319,52 @@ PCP_API int pcp_decode_packets(pcp_ctx* ctx, const pcp_ring_calib* calib, const 
                                int packets_on_device, const pcp_decoded* out, int out_is_device, int64_t* frame_offsets,
                                int64_t max_frames, int64_t* n_frames_complete, int64_t* n_points);
 
+/* ---- lidarOdometry consumers ------------------------------------------------
+ * Per-point neighbour COUNT within `radius` (the query included; FLANN's strict fp32 test
+ * d2 < (float)(r*r)), stopping at `cap` hits when cap > 0: counts[i] = min(count, cap).  This is all the
+ * reference takes from its radiusSearch(i, 3.0) in getRangeAndptIdImage (`size() < 6`,
+ * src/lidarOdometry.cpp:76-78) and from DBSCAN's core test (include/dbscanCLuster.h:282-284).
+ * Needs a grid (any cell size; cell = radius is the cheap choice). */
+PCP_API int pcp_radius_count(pcp_ctx* ctx, float radius, int cap, int32_t* counts, int out_is_device);
+
+typedef struct pcp_odom_params {
+  int32_t n_rows;          /* 16   src/lidarOdometry.cpp:29 */
+  int32_t n_cols;          /* 900  :29 */
+  double vert_res_deg;     /* 2.0  :85 */
+  double hori_res_deg;     /* 0.2  :86 */
+  float radius;            /* 3.0  :76 */
+  int32_t min_neighbors;   /* 6    :77 */
+  int32_t n_blocks;        /* 5    :131 */
+  int32_t half_window;     /* 9    :133,141 */
+  float near_range;        /* 1    :136,143 */
+  int32_t min_valid;       /* 9    :149 */
+  int32_t pick;            /* 3    thresholds sorted[size-3] and sorted[3], :167,170 */
+  int32_t min_block_valid; /* 9    :162 */
+} pcp_odom_params;
+PCP_API int pcp_odom_params_default(pcp_odom_params* prm);
+
+/* lidarOdometryClass::getRangeAndptIdImage (src/lidarOdometry.cpp:21-113) for `n_frames` frames of the current
+ * cloud (frame_offsets: HOST array as in pcp_ring_project, NULL = one frame; for frame batches declare the same
+ * frames with pcp_set_frames BEFORE pcp_build_grid so the neighbour counts stay inside a frame).  Needs a grid.
+ * Per frame, host or device, row-major n_rows x n_cols (the reference's MatrixXf is column-major; contents equal):
+ *   range_img : float, 0 where empty (rangeImg)           ptid_img : float point id, 0 where empty (ptIdImg; may be NULL)
+ *   pt_index  : int32 frame-local id, -1 where empty (may be NULL)
+ *   stats     : per frame {overwritten returns ("losing points num"), occupied cells}   (may be NULL)
+ *   angle_minmax : per frame {vert min, vert max, hori min, hori max} in degrees (doubles; may be NULL)
+ * Where the reference is undefined (row >= n_rows / col >= n_cols writes outside its matrix, int(NaN)) the
+ * point is skipped. */
+PCP_API int pcp_odom_range_image(pcp_ctx* ctx, const pcp_odom_params* prm, const int64_t* frame_offsets, int64_t n_frames,
+                                 float* range_img, float* ptid_img, int32_t* pt_index, int32_t* stats, double* angle_minmax,
+                                 int out_is_device);
+
+/* lidarOdometryClass::calculateSmoothness (src/lidarOdometry.cpp:121-187): range images (n_frames x n_rows x
+ * n_cols floats; host or device per range_is_device; NULL = the device images the last pcp_odom_range_image of
+ * this context produced) -> smooth_img (smoothnessImg; may be NULL) and type_img (ptTypeImg: 0, 1 = among the
+ * three roughest of its block, 2 = below the fourth smallest smoothness of its block), host or device.
+ * Reads past the last column (:141-143 for the last 8 columns) see range 0. */
+PCP_API int pcp_odom_smoothness(pcp_ctx* ctx, const pcp_odom_params* prm, const float* range_img, int range_is_device,
+                                int64_t n_frames, float* smooth_img, float* type_img, int out_is_device);
+
 #ifdef __cplusplus
 }
 #endif

@@ -57,6 +57,9 @@ def load() -> C.CDLL:
         "orc_ring_project": (i32, [vp, i64, i32, i32, f32, f32, f32, vp, vp, vp]),
         "orc_decode_packets": (i64, [vp, i64, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i64, vp]),
         "orc_ring_segment": (i32, [vp, i32, i32, f32, f32, i32, f32, f32, i32, i32, vp, vp, vp, vp, vp, vp, vp]),
+        "orc_odom_range_image": (None, [vp, i64, vp, i32, i32, i32, C.c_double, C.c_double, vp, vp, vp, vp, vp]),
+        "orc_odom_smoothness": (None, [vp, i32, i32, i32, i32, f32, i32, i32, i32, vp, vp]),
+        "orc_atanf_mismatches": (i64, [C.c_uint32, C.c_uint32]),
         "orc_num_threads": (i32, []),
     }
     for name, (res, args) in sig.items():
@@ -115,6 +118,11 @@ class KdTree:
         d2 = np.zeros((self.n, k), np.float32)
         load().orc_kdtree_knn_all(self.h, k, idx.ctypes.data, d2.ctypes.data, nthreads or num_threads())
         return idx, d2
+
+    def radius_counts(self, radius: float, nthreads: int = 0):
+        counts = np.zeros(self.n, np.int32)
+        load().orc_kdtree_radius_counts(self.h, radius2(radius), counts.ctypes.data, nthreads or num_threads())
+        return counts
 
     def radius_all(self, radius: float, nthreads: int = 0):
         r2 = radius2(radius)
@@ -238,3 +246,29 @@ def decode_packets(packets, vert_deg):
     res["frame_offsets"] = offs[: int(nf[0]) + 2].copy()
     res["n_complete"] = int(nf[0])
     return res
+
+
+def odom_range_image(pts, nb_counts, min_neighbors=6, n_rows=16, n_cols=900, vert_res=2.0, hori_res=0.2):
+    """getRangeAndptIdImage (src/lidarOdometry.cpp:21-113) on one frame; nb_counts = radius-search counts (r = 3)."""
+    pts = _f4(pts)
+    cnt = np.ascontiguousarray(nb_counts, np.int32)
+    rng = np.zeros((n_rows, n_cols), np.float32)
+    pid = np.zeros((n_rows, n_cols), np.float32)
+    pti = np.zeros((n_rows, n_cols), np.int32)
+    stats = np.zeros(2, np.int32)
+    mm = np.zeros(4, np.float64)
+    load().orc_odom_range_image(pts.ctypes.data, pts.shape[0], cnt.ctypes.data, min_neighbors, n_rows, n_cols,
+                                C.c_double(vert_res), C.c_double(hori_res), rng.ctypes.data, pid.ctypes.data,
+                                pti.ctypes.data, stats.ctypes.data, mm.ctypes.data)
+    return rng, pid, pti, stats, mm
+
+
+def odom_smoothness(rng, n_blocks=5, half_window=9, near_range=1.0, min_valid=9, pick=3, min_block_valid=9):
+    """calculateSmoothness (src/lidarOdometry.cpp:121-187): (smoothness image, point-type image)."""
+    rng = np.ascontiguousarray(rng, np.float32)
+    n_rows, n_cols = rng.shape
+    sm = np.zeros_like(rng)
+    ty = np.zeros_like(rng)
+    load().orc_odom_smoothness(rng.ctypes.data, n_rows, n_cols, n_blocks, half_window, C.c_float(near_range), min_valid,
+                               pick, min_block_valid, sm.ctypes.data, ty.ctypes.data)
+    return sm, ty

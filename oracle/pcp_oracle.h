@@ -99,6 +99,22 @@ int32_t orc_ring_segment(const float* xyzi, int n_scan, int horizon, float ang_r
                          const float* range_img, const int32_t* pt_index, int8_t* ground, int32_t* label,
                          float* col_max_ground, int32_t* above_idx, int32_t* n_labels);
 
+/* lidarOdometryClass::getRangeAndptIdImage (src/lidarOdometry.cpp:21-113) for one frame, given every point's
+ * radius-search count (r = 3.0 upstream, computed by the caller with orc_kdtree_radius_counts): 16 x 900 range image
+ * and point-id image (both 0 where empty, row-major), pt_index (optional, -1 where empty), stats2 = {overwrites
+ * ("losing points"), occupied cells}, minmax4 = {vert min, vert max, hori min, hori max} in degrees. */
+void orc_odom_range_image(const float* xyzi, int64_t n, const int32_t* nb_counts, int min_neighbors, int n_rows, int n_cols,
+                          double vert_res, double hori_res, float* range_img, float* ptid_img, int32_t* pt_index,
+                          int32_t* stats2, double* minmax4);
+/* lidarOdometryClass::calculateSmoothness (src/lidarOdometry.cpp:121-187): smoothness image and point-type image
+ * (0 none, 1 edge, 2 flat), row-major. */
+void orc_odom_smoothness(const float* range_img, int n_rows, int n_cols, int n_blocks, int half_window, float near_range,
+                         int min_valid, int pick, int min_block_valid, float* smooth_img, float* type_img);
+
+/* inputs (every stride-th float bit pattern from start) where the fdlibm atanf the CUDA path evaluates differs
+ * from this C library's atanf */
+int64_t orc_atanf_mismatches(uint32_t start, uint32_t stride);
+
 int orc_num_threads(void);
 
 /* Velodyne packet decode (lib/libPacketDecoder.so restated, see decoder.cpp): n_packets x 1206 bytes ->

@@ -44,6 +44,7 @@ EXPORTS = (
     "pcp_ring_calib_from_xml", "pcp_ring_project", "pcp_set_host_async", "pcp_alloc_pinned", "pcp_free_pinned", "pcp_halo_pack", "pcp_set_frames",
     "pcp_halo_push", "pcp_halo_wait", "pcp_peer_alloc", "pcp_peer_free", "pcp_peer_open", "pcp_peer_close",
     "pcp_ring_seg_params_default", "pcp_ring_segment", "pcp_decode_packets",
+    "pcp_radius_count", "pcp_odom_params_default", "pcp_odom_range_image", "pcp_odom_smoothness",
 )
 
 
@@ -88,6 +89,15 @@ class RingSegParams(C.Structure):
         ("segment_theta", C.c_float),
         ("segment_valid_point_num", C.c_int32),
         ("segment_valid_line_num", C.c_int32),
+    ]
+
+
+class OdomParams(C.Structure):
+    """pcp_odom_params: the literals of src/lidarOdometry.cpp:21-187."""
+    _fields_ = [
+        ("n_rows", C.c_int32), ("n_cols", C.c_int32), ("vert_res_deg", C.c_double), ("hori_res_deg", C.c_double),
+        ("radius", C.c_float), ("min_neighbors", C.c_int32), ("n_blocks", C.c_int32), ("half_window", C.c_int32),
+        ("near_range", C.c_float), ("min_valid", C.c_int32), ("pick", C.c_int32), ("min_block_valid", C.c_int32),
     ]
 
 
@@ -151,6 +161,10 @@ def load() -> C.CDLL:
         "pcp_ring_project": (i32, [vp, C.POINTER(RingCalib), vp, i64, vp, vp, vp, i32]),
         "pcp_ring_seg_params_default": (i32, [C.POINTER(RingSegParams)]),
         "pcp_decode_packets": (i32, [vp, C.POINTER(RingCalib), vp, i64, i32, vp, i32, vp, i64, vp, vp]),
+        "pcp_radius_count": (i32, [vp, f32, i32, vp, i32]),
+        "pcp_odom_params_default": (i32, [C.POINTER(OdomParams)]),
+        "pcp_odom_range_image": (i32, [vp, C.POINTER(OdomParams), vp, i64, vp, vp, vp, vp, vp, i32]),
+        "pcp_odom_smoothness": (i32, [vp, C.POINTER(OdomParams), vp, i32, i64, vp, vp, i32]),
         "pcp_ring_segment": (i32, [vp, C.POINTER(RingCalib), C.POINTER(RingSegParams), vp, i64, vp, vp, vp, vp, vp, vp, vp, vp, vp, i32]),
     }
     for name, (res, args) in sig.items():
@@ -184,6 +198,14 @@ def ring_calib_default() -> RingCalib:
     if st:
         raise PcpError(st, "pcp_ring_calib_default")
     return c
+
+
+def odom_params_default() -> OdomParams:
+    prm = OdomParams()
+    st = load().pcp_odom_params_default(C.byref(prm))
+    if st:
+        raise PcpError(st, "pcp_odom_params_default")
+    return prm
 
 
 def ring_calib_from_xml(path: str) -> RingCalib:
@@ -443,3 +465,34 @@ class Pcp:
         assert rng.size == cells * nf
         self._ck(self.lib.pcp_ring_project(self.h, C.byref(calib), _ptr(fo), nf, rng.ctypes.data, pti.ctypes.data, lr.ctypes.data, 0))
         return rng, pti, lr
+
+    def radius_count(self, radius: float, cap: int = 0) -> np.ndarray:
+        """Per-point neighbour count within radius (query included), min(count, cap) when cap > 0."""
+        out = np.zeros(self.n_query, np.int32)
+        self._ck(self.lib.pcp_radius_count(self.h, radius, cap, out.ctypes.data, 0))
+        return out
+
+    def odom_range_image(self, prm: Optional[OdomParams] = None, frame_offsets: Optional[np.ndarray] = None) -> dict:
+        """lidarOdometryClass::getRangeAndptIdImage per frame: range / ptid / pt_index images, stats, angle min/max."""
+        prm = prm or odom_params_default()
+        nf = 1 if frame_offsets is None else frame_offsets.shape[0] - 1
+        fo = None if frame_offsets is None else np.ascontiguousarray(frame_offsets, np.int64)
+        shape = (nf, prm.n_rows, prm.n_cols)
+        out = {"range": np.zeros(shape, np.float32), "ptid": np.zeros(shape, np.float32), "pt_index": np.zeros(shape, np.int32),
+               "stats": np.zeros((nf, 2), np.int32), "minmax": np.zeros((nf, 4), np.float64)}
+        self._ck(self.lib.pcp_odom_range_image(self.h, C.byref(prm), _ptr(fo), nf, out["range"].ctypes.data, out["ptid"].ctypes.data,
+                                               out["pt_index"].ctypes.data, out["stats"].ctypes.data, out["minmax"].ctypes.data, 0))
+        return out
+
+    def odom_smoothness(self, range_img: Optional[np.ndarray] = None, prm: Optional[OdomParams] = None, n_frames: Optional[int] = None):
+        """lidarOdometryClass::calculateSmoothness: (smoothness images, point-type images); range_img None = the device
+        images of the last odom_range_image call."""
+        prm = prm or odom_params_default()
+        if range_img is not None:
+            range_img = np.ascontiguousarray(range_img, np.float32).reshape(-1, prm.n_rows, prm.n_cols)
+            n_frames = range_img.shape[0]
+        shape = (int(n_frames), prm.n_rows, prm.n_cols)
+        sm = np.zeros(shape, np.float32)
+        ty = np.zeros(shape, np.float32)
+        self._ck(self.lib.pcp_odom_smoothness(self.h, C.byref(prm), _ptr(range_img), 0, shape[0], sm.ctypes.data, ty.ctypes.data, 0))
+        return sm, ty

@@ -16,6 +16,12 @@ int pcp_ring_segment_impl(pcp_ctx* ctx, const pcp_ring_calib* calib, const pcp_r
                           int64_t n_frames, const float* d_range, const int32_t* d_index, int8_t* d_ground, int32_t* d_label,
                           float* d_colmax, int32_t* d_above, int32_t* d_above_count, int32_t* d_n_labels);
 
+int pcp_radius_count_impl(pcp_ctx* ctx, float r2, int R, int cap, int32_t* d_counts);
+int pcp_odom_range_impl(pcp_ctx* ctx, const pcp_odom_params* prm, const int64_t* d_off, int64_t n_frames, int64_t max_len,
+                        const int32_t* d_counts, float* d_range, float* d_ptid, int32_t* d_index, int32_t* d_stats, double* d_minmax);
+int pcp_odom_smooth_impl(pcp_ctx* ctx, const pcp_odom_params* prm, const float* d_range, int64_t n_frames, float* d_smooth,
+                         float* d_type);
+
 namespace {
 
 int require_grid(pcp_ctx* ctx, const char* who) {
@@ -386,6 +392,131 @@ PCP_API int pcp_ring_segment(pcp_ctx* ctx, const pcp_ring_calib* calib, const pc
   if ((rc = copy_back(ctx, above_idx, d_above, out_is_device, cells))) return rc;
   if ((rc = copy_back(ctx, above_count, d_acount, out_is_device, (size_t)n_frames))) return rc;
   if ((rc = copy_back(ctx, n_labels, d_nlab, out_is_device, (size_t)n_frames))) return rc;
+  if (!out_is_device && !ctx->host_async) PCP_CUDA(cudaStreamSynchronize(ctx->stream));
+  return PCP_OK;
+}
+
+PCP_API int pcp_radius_count(pcp_ctx* ctx, float radius, int cap, int32_t* counts, int out_is_device) {
+  int rc = require_grid(ctx, "pcp_radius_count");
+  if (rc) return rc;
+  if (!(radius > 0.f) || !counts) return pcp_fail(ctx, PCP_ERR_INVALID_ARG, "pcp_radius_count: bad argument");
+  const float r2 = (float)((double)radius * (double)radius);
+  int32_t* d_counts;
+  if ((rc = pick_out(ctx, ctx->odom_counts, counts, out_is_device, (size_t)ctx->n_query, &d_counts))) return rc;
+  if ((rc = pcp_radius_count_impl(ctx, r2, stencil_for_radius(ctx->grid, r2), cap, d_counts))) return rc;
+  if ((rc = copy_back(ctx, counts, d_counts, out_is_device, (size_t)ctx->n_query))) return rc;
+  if (!out_is_device && !ctx->host_async) PCP_CUDA(cudaStreamSynchronize(ctx->stream));
+  return PCP_OK;
+}
+
+PCP_API int pcp_odom_params_default(pcp_odom_params* prm) {
+  if (!prm) return PCP_ERR_INVALID_ARG;
+  prm->n_rows = 16;
+  prm->n_cols = 900;
+  prm->vert_res_deg = 2.0;
+  prm->hori_res_deg = 0.2;
+  prm->radius = 3.0f;
+  prm->min_neighbors = 6;
+  prm->n_blocks = 5;
+  prm->half_window = 9;
+  prm->near_range = 1.0f;
+  prm->min_valid = 9;
+  prm->pick = 3;
+  prm->min_block_valid = 9;
+  return PCP_OK;
+}
+
+static bool odom_params_ok(const pcp_odom_params* p) {
+  return p && p->n_rows >= 1 && p->n_cols >= 32 && p->n_blocks >= 1 && p->n_blocks <= p->n_cols && p->half_window >= 0 &&
+         p->n_cols / p->n_blocks - p->half_window >= 1 && p->n_cols / p->n_blocks - p->half_window <= 256 && p->pick >= 0 &&
+         p->min_block_valid >= 2 * p->pick && p->vert_res_deg > 0 && p->hori_res_deg > 0 && p->radius > 0.f;
+}
+
+PCP_API int pcp_odom_range_image(pcp_ctx* ctx, const pcp_odom_params* prm, const int64_t* frame_offsets, int64_t n_frames,
+                                 float* range_img, float* ptid_img, int32_t* pt_index, int32_t* stats, double* angle_minmax,
+                                 int out_is_device) {
+  int rc = require_grid(ctx, "pcp_odom_range_image");
+  if (rc) return rc;
+  if (!odom_params_ok(prm) || !range_img || n_frames < 1 || n_frames > 65535)
+    return pcp_fail(ctx, PCP_ERR_INVALID_ARG, "pcp_odom_range_image: bad argument");
+  if (ctx->d_gid) return pcp_fail(ctx, PCP_ERR_INVALID_ARG, "pcp_odom_range_image: not defined for shards of a cloud");
+  if (!frame_offsets && n_frames != 1) return pcp_fail(ctx, PCP_ERR_INVALID_ARG, "pcp_odom_range_image: frame_offsets required");
+  if (frame_offsets && (frame_offsets[0] < 0 || frame_offsets[n_frames] > ctx->n))
+    return pcp_fail(ctx, PCP_ERR_INVALID_ARG, "pcp_odom_range_image: frame_offsets outside the cloud");
+  const size_t cells = (size_t)prm->n_rows * prm->n_cols * (size_t)n_frames;
+  int64_t max_len = ctx->n;
+  const int64_t* d_off = nullptr;
+  if (frame_offsets) {
+    max_len = 0;
+    for (int64_t f = 0; f < n_frames; ++f) {
+      if (frame_offsets[f + 1] < frame_offsets[f]) return pcp_fail(ctx, PCP_ERR_INVALID_ARG, "pcp_odom_range_image: offsets decrease");
+      max_len = std::max(max_len, frame_offsets[f + 1] - frame_offsets[f]);
+    }
+    if ((rc = pcp_reserve(ctx, ctx->ring_offsets, (n_frames + 1) * sizeof(int64_t)))) return rc;
+    PCP_CUDA(cudaMemcpyAsync(ctx->ring_offsets.p, frame_offsets, (n_frames + 1) * sizeof(int64_t), cudaMemcpyHostToDevice, ctx->stream));
+    d_off = (const int64_t*)ctx->ring_offsets.p;
+  }
+  float *d_range, *d_ptid;
+  int32_t *d_index, *d_stats;
+  double* d_minmax;
+  auto need = [&](auto*& dev, DevBuf& own, auto* user, size_t count) -> int {
+    using T = std::remove_pointer_t<std::remove_reference_t<decltype(dev)>>;
+    if (user && out_is_device) {
+      dev = user;
+      return PCP_OK;
+    }
+    int r = pcp_reserve(ctx, own, count * sizeof(T));
+    dev = (T*)own.p;
+    return r;
+  };
+  if ((rc = need(d_range, ctx->odom_range, range_img, cells))) return rc;
+  if ((rc = need(d_index, ctx->odom_index, pt_index, cells))) return rc;
+  if ((rc = need(d_stats, ctx->odom_stats, stats, 2 * (size_t)n_frames))) return rc;
+  if ((rc = need(d_minmax, ctx->odom_minmax, angle_minmax, 4 * (size_t)n_frames))) return rc;
+  d_ptid = nullptr;
+  if (ptid_img && (rc = need(d_ptid, ctx->odom_ptid, ptid_img, cells))) return rc;
+  if ((rc = pcp_reserve(ctx, ctx->odom_counts, (size_t)ctx->n * sizeof(int32_t)))) return rc;
+  int32_t* d_counts = (int32_t*)ctx->odom_counts.p;
+  const float r2 = (float)((double)prm->radius * (double)prm->radius);
+  if ((rc = pcp_radius_count_impl(ctx, r2, stencil_for_radius(ctx->grid, r2), prm->min_neighbors, d_counts))) return rc;
+  if ((rc = pcp_odom_range_impl(ctx, prm, d_off, n_frames, max_len, d_counts, d_range, d_ptid, d_index, d_stats, d_minmax))) return rc;
+  ctx->odom_last_range = d_range;
+  ctx->odom_last_frames = n_frames;
+  if ((rc = copy_back(ctx, range_img, d_range, out_is_device, cells))) return rc;
+  if ((rc = copy_back(ctx, ptid_img, d_ptid, out_is_device, cells))) return rc;
+  if ((rc = copy_back(ctx, pt_index, d_index, out_is_device, cells))) return rc;
+  if ((rc = copy_back(ctx, stats, d_stats, out_is_device, 2 * (size_t)n_frames))) return rc;
+  if ((rc = copy_back(ctx, angle_minmax, d_minmax, out_is_device, 4 * (size_t)n_frames))) return rc;
+  if (!out_is_device && !ctx->host_async) PCP_CUDA(cudaStreamSynchronize(ctx->stream));
+  return PCP_OK;
+}
+
+PCP_API int pcp_odom_smoothness(pcp_ctx* ctx, const pcp_odom_params* prm, const float* range_img, int range_is_device,
+                                int64_t n_frames, float* smooth_img, float* type_img, int out_is_device) {
+  if (!ctx) return PCP_ERR_INVALID_ARG;
+  if (!odom_params_ok(prm) || !type_img || n_frames < 1 || n_frames > 65535)
+    return pcp_fail(ctx, PCP_ERR_INVALID_ARG, "pcp_odom_smoothness: bad argument");
+  PCP_CUDA(cudaSetDevice(ctx->device));
+  const size_t cells = (size_t)prm->n_rows * prm->n_cols * (size_t)n_frames;
+  const float* d_range = range_img;
+  int rc;
+  if (!range_img) {
+    if (!ctx->odom_last_range || ctx->odom_last_frames != n_frames)
+      return pcp_fail(ctx, PCP_ERR_INVALID_ARG, "pcp_odom_smoothness: no range images of that many frames in this context");
+    d_range = ctx->odom_last_range;
+  } else if (!range_is_device) {
+    if ((rc = pcp_reserve(ctx, ctx->odom_range, cells * sizeof(float)))) return rc;
+    PCP_CUDA(cudaMemcpyAsync(ctx->odom_range.p, range_img, cells * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+    d_range = (const float*)ctx->odom_range.p;
+    ctx->odom_last_range = d_range;
+    ctx->odom_last_frames = n_frames;
+  }
+  float *d_smooth, *d_type;
+  if ((rc = pick_out(ctx, ctx->odom_smooth, smooth_img, out_is_device, cells, &d_smooth))) return rc;
+  if ((rc = pick_out(ctx, ctx->odom_type, type_img, out_is_device, cells, &d_type))) return rc;
+  if ((rc = pcp_odom_smooth_impl(ctx, prm, d_range, n_frames, d_smooth, d_type))) return rc;
+  if ((rc = copy_back(ctx, smooth_img, d_smooth, out_is_device, cells))) return rc;
+  if ((rc = copy_back(ctx, type_img, d_type, out_is_device, cells))) return rc;
   if (!out_is_device && !ctx->host_async) PCP_CUDA(cudaStreamSynchronize(ctx->stream));
   return PCP_OK;
 }

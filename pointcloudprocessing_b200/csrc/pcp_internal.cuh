@@ -86,6 +86,9 @@ struct pcp_ctx {
   DevBuf ring_range, ring_idx, ring_long, ring_offsets, ring_key;
   DevBuf halo_done;   // block counter of halo_pad_signal_kernel
   DevBuf dec_tables, dec_packed, dec_out;  // pcp_decode_packets: azimuth cos/sin tables, per-block scan, staged outputs
+  DevBuf odom_counts, odom_range, odom_ptid, odom_index, odom_stats, odom_minmax, odom_smooth, odom_type;  // lidarOdometry images
+  const float* odom_last_range = nullptr;  // device images of the last pcp_odom_range_image
+  int64_t odom_last_frames = 0;
   DevBuf seg_ground, seg_label, seg_colmax, seg_above, seg_counts, seg_nlabels;  // pcp_ring_segment outputs
 };
 

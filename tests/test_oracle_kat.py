@@ -228,3 +228,59 @@ def test_ring_segment_ground_pairs_by_hand(oracle):
     assert lab[0, 7] == -1 and lab[1, 7] == -1 and lab[2, 7] == 999999  # row 2 is free again: a 1-pixel segment
     assert cm[7] == rng[1, 7] and cm[8] == 0.0
     assert above.tolist() == [int(pti[9, 7])]
+
+
+# ---- lidarOdometry images (src/lidarOdometry.cpp:21-187) ----
+
+def test_atanf_restatement_equals_libm(oracle):
+    """The CUDA path evaluates atanf with the fdlibm algorithm (odom.cu); the oracle's copy of that algorithm
+    equals this C library's atanf on every sampled bit pattern (all 2^32 were checked once, stride 1)."""
+    assert oracle.load().orc_atanf_mismatches(0, 257) == 0
+    assert oracle.load().orc_atanf_mismatches(0x3E000000, 31) == 0  # a second lattice from the reduction thresholds on
+
+
+def test_odom_range_image_known_cells(oracle):
+    """Four returns on known beams: rows from the vertical angle above the minimum in 2-degree steps, columns
+    from atan(y / x) (NOT atan2: the back half folds onto the front half) above the minimum in 0.2-degree steps."""
+    def pt(v_deg, h_deg, d):
+        v, h = np.radians(v_deg), np.radians(h_deg)
+        return [d * np.cos(v) * np.cos(h), d * np.cos(v) * np.sin(h), d * np.sin(v), 0.0]
+    pts = np.array([pt(-15, -60, 10), pt(-15 + 4.5, -60 + 10.1, 12), pt(1, 0, 5), pt(-15 + 4.5, -60 + 10.1 + 180, 7)], np.float32)
+    cnt = np.full(4, 6, np.int32)
+    rng, pid, pti, stats, mm = oracle.odom_range_image(pts, cnt)
+    assert pti[0, 0] == 0 and pti[8, 300] == 2
+    assert pti[2, 50] == 3          # the point behind the sensor lands in the cell of point 1 and overwrites it
+    assert stats.tolist() == [1, 3]
+    assert abs(mm[0] + 15) < 1e-5 and abs(mm[2] + 60) < 1e-5
+    assert rng[2, 50] == np.float32(7.0) or abs(rng[2, 50] - 7.0) < 1e-5
+    cnt[3] = 5                      # fewer than 6 neighbours: left out, point 1 shows again
+    rng, pid, pti, stats, mm = oracle.odom_range_image(pts, cnt)
+    assert pti[2, 50] == 1 and stats.tolist() == [0, 3] and pid[2, 50] == 1.0
+
+
+def test_odom_smoothness_known_answers(oracle):
+    img = np.full((16, 900), 10.0, np.float32)
+    sm, ty = oracle.odom_smoothness(img)
+    assert (sm == 0).all()
+    # every smoothness ties at 0: `>= sorted[size-3]` holds for all, `< sorted[3]` for none (:167-172);
+    # the first nine columns of each 180-column block are never visited (:133)
+    exp = np.ones((16, 900), np.float32)
+    for b in range(5):
+        exp[:, 180 * b:180 * b + 9] = 0
+    assert np.array_equal(ty, exp)
+    # one spike: the window of 18 pixels [col-9, col+9) that contains it has sum = 17*10 + 30
+    img[4, 100] = 30.0
+    sm, ty = oracle.odom_smoothness(img)
+    assert sm[4, 100] == np.float32(abs((17 * 10.0 + 30.0) - 30.0 * 18) / (18 * 30.0))
+    assert sm[4, 95] == np.float32(abs((17 * 10.0 + 30.0) - 10.0 * 18) / (18 * 10.0))
+    # the window is asymmetric: pixel 100 is inside [col-9, col+9) for col = 92 .. 109
+    assert sm[4, 92] == np.float32(20.0 / 180.0) and sm[4, 109] == np.float32(20.0 / 180.0) and sm[4, 110] == 0 and sm[4, 91] == 0
+    assert ty[4, 100] == 1  # among the three roughest
+    # fewer than ten valid pixels in a block: no types at all there
+    img2 = np.zeros((16, 900), np.float32)
+    img2[0, 20:29] = 5.0   # nine pixels, each sees exactly nine valid ones: nine smoothness values, not > 9 (:162)
+    sm, ty = oracle.odom_smoothness(img2)
+    assert (ty == 0).all() and (sm == 0).all()
+    img2[0, 29] = 5.0      # ten values, all 0: `0 >= sorted[size-3] = 0` marks the whole block, empty pixels too
+    sm, ty = oracle.odom_smoothness(img2)
+    assert (ty[0, 9:180] == 1).all() and (ty[0, :9] == 0).all() and (ty[1:] == 0).all() and (ty[0, 180:] == 0).all()
