@@ -365,6 +365,32 @@ PCP_API int pcp_odom_range_image(pcp_ctx* ctx, const pcp_odom_params* prm, const
 PCP_API int pcp_odom_smoothness(pcp_ctx* ctx, const pcp_odom_params* prm, const float* range_img, int range_is_device,
                                 int64_t n_frames, float* smooth_img, float* type_img, int out_is_device);
 
+/* ---- DBSCAN and mean shift ---------------------------------------------------
+ * DynaTools::clusterDBSCAN's labelling (include/dbscanCLuster.h:256-300) on the current cloud and grid.  The
+ * reference clusters a copy of the cloud with z set to 0 (:264-267): hand that flattened cloud to
+ * pcp_set_cloud_* (the distance is then the planar one).  labels[i] = the reference's state[i]: cluster id 1..
+ * (numbered by their first core point in index order) or -2 for noise; a border point belongs to the
+ * first-seeded cluster that reaches it, and stays noise when its own index precedes that cluster's seed, as in
+ * the reference's sequential walk.  *n_clusters = clusterID (HOST int32).  Synchronises. */
+PCP_API int pcp_dbscan(pcp_ctx* ctx, float radius, int min_pts, int32_t* labels, int32_t* n_clusters, int out_is_device);
+
+/* Per cluster 1..n_clusters of `labels` (host or device per labels_is_device), over the CURRENT cloud (set the
+ * original 3-D cloud again after pcp_dbscan): centroid (pcl::compute3DCentroid), min and max corner
+ * (pcl::getMinMax3D) and member count — what include/dbscanCLuster.h:312-325 derives per cluster; outputs are HOST
+ * arrays (n_clusters x 3 floats each, counts may be NULL).  The centroid is the double-precision mean rounded to
+ * float (the reference adds in fp32 in index order: equal within fp32 rounding of the sum). */
+PCP_API int pcp_cluster_boxes(pcp_ctx* ctx, const int32_t* labels, int labels_is_device, int32_t n_clusters, float* centroid_xyz,
+                              float* min_xyz, float* max_xyz, int32_t* counts);
+
+/* buildingFacadeExtractor::meanShiftClustering (src/buildingFacadeExtraction.cpp:59-132): `iterations` sweeps
+ * (at least one: the reference loop is a do-while) over the current cloud, whose grid (any cell; cell = radius is
+ * the cheap choice) indexes the ORIGINAL positions for every sweep, as the reference's kd-tree does.  The reference
+ * uses radius 2.0 and min_pts 15 (:79-80).  start_xyzi: the positions the first sweep starts from (n x 4 floats,
+ * host or device per start_is_device; NULL = the cloud itself).  out_xyzi: n x 4 floats (x, y, z moved, intensity
+ * kept), host or device; counts (optional): neighbours found by the last sweep.  Not for frame batches. */
+PCP_API int pcp_mean_shift(pcp_ctx* ctx, float radius, int min_pts, int iterations, const void* start_xyzi, int start_is_device,
+                           void* out_xyzi, int32_t* counts, int out_is_device);
+
 #ifdef __cplusplus
 }
 #endif

@@ -60,6 +60,9 @@ def load() -> C.CDLL:
         "orc_odom_range_image": (None, [vp, i64, vp, i32, i32, i32, C.c_double, C.c_double, vp, vp, vp, vp, vp]),
         "orc_odom_smoothness": (None, [vp, i32, i32, i32, i32, f32, i32, i32, i32, vp, vp]),
         "orc_atanf_mismatches": (i64, [C.c_uint32, C.c_uint32]),
+        "orc_dbscan": (i32, [vp, i64, f32, i32, vp]),
+        "orc_cluster_boxes": (None, [vp, i64, vp, i32, vp, vp, vp, vp]),
+        "orc_mean_shift_step": (None, [vp, vp, i64, f32, i32, vp, vp, vp]),
         "orc_num_threads": (i32, []),
     }
     for name, (res, args) in sig.items():
@@ -272,3 +275,34 @@ def odom_smoothness(rng, n_blocks=5, half_window=9, near_range=1.0, min_valid=9,
     load().orc_odom_smoothness(rng.ctypes.data, n_rows, n_cols, n_blocks, half_window, C.c_float(near_range), min_valid,
                                pick, min_block_valid, sm.ctypes.data, ty.ctypes.data)
     return sm, ty
+
+
+def dbscan(pts, radius: float, min_pts: int):
+    """DynaTools::clusterDBSCAN on the given (already flattened) cloud: (state, n_clusters)."""
+    pts = _f4(pts)
+    state = np.zeros(pts.shape[0], np.int32)
+    nc = load().orc_dbscan(pts.ctypes.data, pts.shape[0], radius, min_pts, state.ctypes.data)
+    return state, int(nc)
+
+
+def cluster_boxes(pts, state, n_clusters: int):
+    pts = _f4(pts)
+    state = np.ascontiguousarray(state, np.int32)
+    cen = np.zeros((n_clusters, 3), np.float32)
+    lo = np.zeros((n_clusters, 3), np.float32)
+    hi = np.zeros((n_clusters, 3), np.float32)
+    cnt = np.zeros(n_clusters, np.int32)
+    load().orc_cluster_boxes(pts.ctypes.data, pts.shape[0], state.ctypes.data, n_clusters, cen.ctypes.data, lo.ctypes.data,
+                             hi.ctypes.data, cnt.ctypes.data)
+    return cen, lo, hi, cnt
+
+
+def mean_shift_step(orig, cur, radius: float = 2.0, min_pts: int = 15):
+    """One sweep of meanShiftClustering: (next positions n x 4, shift n x 3, neighbour counts)."""
+    orig, cur = _f4(orig), _f4(cur)
+    nxt = np.zeros_like(cur)
+    shift = np.zeros((cur.shape[0], 3), np.float32)
+    cnt = np.zeros(cur.shape[0], np.int32)
+    load().orc_mean_shift_step(orig.ctypes.data, cur.ctypes.data, cur.shape[0], radius, min_pts, nxt.ctypes.data,
+                               shift.ctypes.data, cnt.ctypes.data)
+    return nxt, shift, cnt

@@ -115,6 +115,17 @@ void orc_odom_smoothness(const float* range_img, int n_rows, int n_cols, int n_b
  * from this C library's atanf */
 int64_t orc_atanf_mismatches(uint32_t start, uint32_t stride);
 
+/* DynaTools::clusterDBSCAN (include/dbscanCLuster.h:256-300) on the cloud it searches in (z zeroed by the caller, as
+ * :264-267): state[i] = cluster id 1.. or -2 (noise).  Returns the number of clusters. */
+int32_t orc_dbscan(const float* xyzi, int64_t n, float radius, int min_pts, int32_t* state);
+/* per cluster: compute3DCentroid, getMinMax3D (:312-325) and the member count */
+void orc_cluster_boxes(const float* xyzi, int64_t n, const int32_t* state, int32_t n_clusters, float* centroid3, float* min3,
+                       float* max3, int32_t* counts);
+/* one sweep of buildingFacadeExtractor::meanShiftClustering (src/buildingFacadeExtraction.cpp:72-123): tree on the
+ * original positions, queries and differences from the current ones.  shift_xyz (n x 3) and counts optional. */
+void orc_mean_shift_step(const float* orig_xyzi, const float* cur_xyzi, int64_t n, float radius, int min_pts, float* next_xyzi,
+                         float* shift_xyz, int32_t* counts);
+
 int orc_num_threads(void);
 
 /* Velodyne packet decode (lib/libPacketDecoder.so restated, see decoder.cpp): n_packets x 1206 bytes ->

@@ -217,6 +217,16 @@ extern "C" int64_t orc_kdtree_radius(const orc_kdtree* t, int64_t q, float r2, i
   return m;
 }
 
+// radius search around an arbitrary position (pcl::KdTreeFLANN::radiusSearch(const PointT&, ...)): indices in
+// (d2, index) order.  C++ linkage: used by consumers.cpp.
+void orc_kdtree_radius_vec(const orc_kdtree* t, const float* q, float r2, std::vector<int32_t>& out) {
+  std::vector<DI> hits;
+  if (t->n > 0) radius_rec(t, 0, q, r2, hits);
+  std::sort(hits.begin(), hits.end());
+  out.resize(hits.size());
+  for (size_t j = 0; j < hits.size(); ++j) out[j] = hits[j].second;
+}
+
 extern "C" int64_t orc_kdtree_knn(const orc_kdtree* t, int64_t q, int k, int32_t* idx, float* d2) {
   MaxHeap heap;
   if (t->n > 0 && k > 0) knn_rec(t, 0, t->cloud + 4 * q, (size_t)k, heap);

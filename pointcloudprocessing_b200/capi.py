@@ -44,6 +44,7 @@ EXPORTS = (
     "pcp_ring_calib_from_xml", "pcp_ring_project", "pcp_set_host_async", "pcp_alloc_pinned", "pcp_free_pinned", "pcp_halo_pack", "pcp_set_frames",
     "pcp_halo_push", "pcp_halo_wait", "pcp_peer_alloc", "pcp_peer_free", "pcp_peer_open", "pcp_peer_close",
     "pcp_ring_seg_params_default", "pcp_ring_segment", "pcp_decode_packets",
+    "pcp_dbscan", "pcp_cluster_boxes", "pcp_mean_shift",
     "pcp_radius_count", "pcp_odom_params_default", "pcp_odom_range_image", "pcp_odom_smoothness",
 )
 
@@ -162,6 +163,9 @@ def load() -> C.CDLL:
         "pcp_ring_seg_params_default": (i32, [C.POINTER(RingSegParams)]),
         "pcp_decode_packets": (i32, [vp, C.POINTER(RingCalib), vp, i64, i32, vp, i32, vp, i64, vp, vp]),
         "pcp_radius_count": (i32, [vp, f32, i32, vp, i32]),
+        "pcp_dbscan": (i32, [vp, f32, i32, vp, vp, i32]),
+        "pcp_cluster_boxes": (i32, [vp, vp, i32, i32, vp, vp, vp, vp]),
+        "pcp_mean_shift": (i32, [vp, f32, i32, i32, vp, i32, vp, vp, i32]),
         "pcp_odom_params_default": (i32, [C.POINTER(OdomParams)]),
         "pcp_odom_range_image": (i32, [vp, C.POINTER(OdomParams), vp, i64, vp, vp, vp, vp, vp, i32]),
         "pcp_odom_smoothness": (i32, [vp, C.POINTER(OdomParams), vp, i32, i64, vp, vp, i32]),
@@ -496,3 +500,29 @@ class Pcp:
         ty = np.zeros(shape, np.float32)
         self._ck(self.lib.pcp_odom_smoothness(self.h, C.byref(prm), _ptr(range_img), 0, shape[0], sm.ctypes.data, ty.ctypes.data, 0))
         return sm, ty
+
+    def dbscan(self, radius: float, min_pts: int):
+        """DynaTools::clusterDBSCAN's state vector on the current (flattened by the caller) cloud: (labels, n_clusters)."""
+        labels = np.zeros(self.n, np.int32)
+        nc = C.c_int32()
+        self._ck(self.lib.pcp_dbscan(self.h, radius, min_pts, labels.ctypes.data, C.addressof(nc), 0))
+        return labels, int(nc.value)
+
+    def cluster_boxes(self, labels: np.ndarray, n_clusters: int):
+        """Per cluster of `labels` over the current cloud: (centroid, min, max, count)."""
+        labels = np.ascontiguousarray(labels, np.int32)
+        cen = np.zeros((n_clusters, 3), np.float32)
+        lo = np.zeros((n_clusters, 3), np.float32)
+        hi = np.zeros((n_clusters, 3), np.float32)
+        cnt = np.zeros(n_clusters, np.int32)
+        self._ck(self.lib.pcp_cluster_boxes(self.h, labels.ctypes.data, 0, n_clusters, cen.ctypes.data, lo.ctypes.data, hi.ctypes.data,
+                                            cnt.ctypes.data))
+        return cen, lo, hi, cnt
+
+    def mean_shift(self, radius: float = 2.0, min_pts: int = 15, iterations: int = 1, start: Optional[np.ndarray] = None):
+        """meanShiftClustering sweeps over the current cloud (grid = the original positions): (positions n x 4, counts)."""
+        st = None if start is None else np.ascontiguousarray(start, np.float32)
+        out = np.zeros((self.n, 4), np.float32)
+        cnt = np.zeros(self.n, np.int32)
+        self._ck(self.lib.pcp_mean_shift(self.h, radius, min_pts, iterations, _ptr(st), 0, out.ctypes.data, cnt.ctypes.data, 0))
+        return out, cnt

@@ -22,6 +22,11 @@ int pcp_odom_range_impl(pcp_ctx* ctx, const pcp_odom_params* prm, const int64_t*
 int pcp_odom_smooth_impl(pcp_ctx* ctx, const pcp_odom_params* prm, const float* d_range, int64_t n_frames, float* d_smooth,
                          float* d_type);
 
+int pcp_dbscan_impl(pcp_ctx* ctx, float r2, int R, int min_pts, int32_t* d_labels, int32_t* d_n_clusters);
+int pcp_cluster_boxes_impl(pcp_ctx* ctx, const int32_t* d_labels, int n_clusters, float* d_centroid, float* d_lo, float* d_hi,
+                           int32_t* d_counts);
+int pcp_mean_shift_impl(pcp_ctx* ctx, const float4* d_cur, float r2, int R, int min_pts, float4* d_next, int32_t* d_counts);
+
 namespace {
 
 int require_grid(pcp_ctx* ctx, const char* who) {
@@ -517,6 +522,85 @@ PCP_API int pcp_odom_smoothness(pcp_ctx* ctx, const pcp_odom_params* prm, const 
   if ((rc = pcp_odom_smooth_impl(ctx, prm, d_range, n_frames, d_smooth, d_type))) return rc;
   if ((rc = copy_back(ctx, smooth_img, d_smooth, out_is_device, cells))) return rc;
   if ((rc = copy_back(ctx, type_img, d_type, out_is_device, cells))) return rc;
+  if (!out_is_device && !ctx->host_async) PCP_CUDA(cudaStreamSynchronize(ctx->stream));
+  return PCP_OK;
+}
+
+PCP_API int pcp_dbscan(pcp_ctx* ctx, float radius, int min_pts, int32_t* labels, int32_t* n_clusters, int out_is_device) {
+  int rc = require_grid(ctx, "pcp_dbscan");
+  if (rc) return rc;
+  if (!(radius > 0.f) || min_pts < 1 || !labels || !n_clusters) return pcp_fail(ctx, PCP_ERR_INVALID_ARG, "pcp_dbscan: bad argument");
+  if (ctx->d_gid) return pcp_fail(ctx, PCP_ERR_INVALID_ARG, "pcp_dbscan: not defined for shards of a cloud");
+  const float r2 = (float)((double)radius * (double)radius);
+  int32_t* d_labels;
+  if ((rc = pick_out(ctx, ctx->db_labels, labels, out_is_device, (size_t)ctx->n, &d_labels))) return rc;
+  if ((rc = pcp_reserve(ctx, ctx->flags, sizeof(int)))) return rc;
+  if ((rc = pcp_dbscan_impl(ctx, r2, stencil_for_radius(ctx->grid, r2), min_pts, d_labels, (int32_t*)ctx->flags.p))) return rc;
+  if ((rc = copy_back(ctx, labels, d_labels, out_is_device, (size_t)ctx->n))) return rc;
+  PCP_CUDA(cudaMemcpyAsync(n_clusters, ctx->flags.p, sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->stream));
+  PCP_CUDA(cudaStreamSynchronize(ctx->stream));
+  return PCP_OK;
+}
+
+PCP_API int pcp_cluster_boxes(pcp_ctx* ctx, const int32_t* labels, int labels_is_device, int32_t n_clusters, float* centroid_xyz,
+                              float* min_xyz, float* max_xyz, int32_t* counts) {
+  if (!ctx) return PCP_ERR_INVALID_ARG;
+  if (!ctx->d_cloud || ctx->n <= 0) return pcp_fail(ctx, PCP_ERR_NO_CLOUD, "pcp_cluster_boxes: no cloud set");
+  if (!labels || n_clusters < 0 || (n_clusters > 0 && (!centroid_xyz || !min_xyz || !max_xyz)))
+    return pcp_fail(ctx, PCP_ERR_INVALID_ARG, "pcp_cluster_boxes: bad argument");
+  if (n_clusters == 0) return PCP_OK;
+  PCP_CUDA(cudaSetDevice(ctx->device));
+  int rc;
+  const int32_t* d_labels = labels;
+  if (!labels_is_device) {
+    if ((rc = pcp_reserve(ctx, ctx->db_labels, (size_t)ctx->n * sizeof(int32_t)))) return rc;
+    PCP_CUDA(cudaMemcpyAsync(ctx->db_labels.p, labels, (size_t)ctx->n * sizeof(int32_t), cudaMemcpyHostToDevice, ctx->stream));
+    d_labels = (const int32_t*)ctx->db_labels.p;
+  }
+  const size_t nc = (size_t)n_clusters;
+  if ((rc = pcp_reserve(ctx, ctx->db_out, nc * 10 * sizeof(float)))) return rc;
+  float* o = (float*)ctx->db_out.p;
+  if ((rc = pcp_cluster_boxes_impl(ctx, d_labels, n_clusters, o, o + 3 * nc, o + 6 * nc, (int32_t*)(o + 9 * nc)))) return rc;
+  PCP_CUDA(cudaMemcpyAsync(centroid_xyz, o, nc * 3 * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+  PCP_CUDA(cudaMemcpyAsync(min_xyz, o + 3 * nc, nc * 3 * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+  PCP_CUDA(cudaMemcpyAsync(max_xyz, o + 6 * nc, nc * 3 * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+  if (counts) PCP_CUDA(cudaMemcpyAsync(counts, o + 9 * nc, nc * sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->stream));
+  PCP_CUDA(cudaStreamSynchronize(ctx->stream));
+  return PCP_OK;
+}
+
+PCP_API int pcp_mean_shift(pcp_ctx* ctx, float radius, int min_pts, int iterations, const void* start_xyzi, int start_is_device,
+                           void* out_xyzi, int32_t* counts, int out_is_device) {
+  int rc = require_grid(ctx, "pcp_mean_shift");
+  if (rc) return rc;
+  if (!(radius > 0.f) || !out_xyzi) return pcp_fail(ctx, PCP_ERR_INVALID_ARG, "pcp_mean_shift: bad argument");
+  if (ctx->d_gid || ctx->grid.n_seg != 1) return pcp_fail(ctx, PCP_ERR_INVALID_ARG, "pcp_mean_shift: single unsharded cloud only");
+  const size_t n = (size_t)ctx->n;
+  const float r2 = (float)((double)radius * (double)radius);
+  const int R = stencil_for_radius(ctx->grid, r2);
+  if (iterations < 1) iterations = 1;  // do { ... } while (times < iterTimes)
+  if ((rc = pcp_reserve(ctx, ctx->ms_a, n * sizeof(float4)))) return rc;
+  if ((rc = pcp_reserve(ctx, ctx->ms_b, n * sizeof(float4)))) return rc;
+  int32_t* d_counts;
+  if ((rc = pick_out(ctx, ctx->odom_counts, counts, out_is_device, n, &d_counts))) return rc;
+  const float4* cur = ctx->d_cloud;
+  if (start_xyzi) {
+    if (start_is_device) {
+      cur = (const float4*)start_xyzi;
+    } else {
+      PCP_CUDA(cudaMemcpyAsync(ctx->ms_b.p, start_xyzi, n * sizeof(float4), cudaMemcpyHostToDevice, ctx->stream));
+      cur = (const float4*)ctx->ms_b.p;
+    }
+  }
+  float4* bufs[2] = {(float4*)ctx->ms_a.p, (float4*)ctx->ms_b.p};
+  for (int it = 0; it < iterations; ++it) {
+    const bool last = it == iterations - 1;
+    float4* nxt = (last && out_is_device) ? (float4*)out_xyzi : bufs[it & 1];
+    if ((rc = pcp_mean_shift_impl(ctx, cur, r2, R, min_pts, nxt, last ? d_counts : nullptr))) return rc;
+    cur = nxt;
+  }
+  if (!out_is_device) PCP_CUDA(cudaMemcpyAsync(out_xyzi, cur, n * sizeof(float4), cudaMemcpyDeviceToHost, ctx->stream));
+  if ((rc = copy_back(ctx, counts, d_counts, out_is_device, n))) return rc;
   if (!out_is_device && !ctx->host_async) PCP_CUDA(cudaStreamSynchronize(ctx->stream));
   return PCP_OK;
 }
