@@ -17,6 +17,23 @@ struct Vector3f {
   float& operator[](int r) { return v[r]; }
   float operator[](int r) const { return v[r]; }
 };
+// column-major dynamic float matrix: the slice of Eigen::MatrixXf that lidarOdometryClass's signatures use
+struct MatrixXf {
+  int r = 0, c = 0;
+  std::vector<float> d;
+  MatrixXf() {}
+  MatrixXf(int rows_, int cols_) : r(rows_), c(cols_), d((std::size_t)rows_ * cols_, 0.f) {}
+  void resize(int rows_, int cols_) {
+    r = rows_;
+    c = cols_;
+    d.assign((std::size_t)rows_ * cols_, 0.f);
+  }
+  static MatrixXf Zero(int rows_, int cols_) { return MatrixXf(rows_, cols_); }
+  int rows() const { return r; }
+  int cols() const { return c; }
+  float& operator()(int i, int j) { return d[(std::size_t)j * r + i]; }
+  float operator()(int i, int j) const { return d[(std::size_t)j * r + i]; }
+};
 }  // namespace Eigen
 
 namespace boost {
@@ -44,6 +61,10 @@ struct PointCloud {
     width = (unsigned)points.size();
   }
   std::size_t size() const { return points.size(); }
+  void clear() {
+    points.clear();
+    width = 0;
+  }
 };
 }  // namespace pcl
 #endif

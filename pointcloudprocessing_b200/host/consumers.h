@@ -1,0 +1,32 @@
+// consumers.h — drop-in declarations of the reference entry points that consume the radius search and the
+// range image next to the PCA stage, with the reference's names and signatures:
+//   lidarOdometry::lidarOdometryClass::getRangeAndptIdImage / calculateSmoothness  (include/lidarOdometry.h:31-33)
+//   DynaTools::clusterDBSCAN                                                       (include/dbscanCLuster.h:256-260)
+//   buildingFacadeExtractor::meanShiftClustering                                   (include/buildingFacadeExtraction.h)
+// Bodies (consumers.cpp) forward to the CUDA path behind include/pcp.h; there is no CPU path.  Differences a
+// caller can observe: the bool methods really return true/false (the reference falls off their ends), nothing
+// is printed to std::cout, and where the reference indexes outside its 16 x 900 matrices the point is skipped.
+#ifndef PCP_HOST_CONSUMERS_H_
+#define PCP_HOST_CONSUMERS_H_
+
+#include "pcaAnalysis.h"  // pcXYZIptr / pcXYZI and the PCL / Eigen types (real or compat)
+
+namespace lidarOdometry {
+class lidarOdometryClass {
+ public:
+  bool getRangeAndptIdImage(pcXYZIptr inputCloud, Eigen::MatrixXf& rangeImg, Eigen::MatrixXf& ptIdImg);
+  bool calculateSmoothness(Eigen::MatrixXf rangeImg, Eigen::MatrixXf& ptTypeImg);
+};
+}  // namespace lidarOdometry
+
+namespace DynaTools {
+int clusterDBSCAN(pcXYZIptr inCloud, double r, int minptNum, pcXYZIptr pcClusterCentos, pcXYZIptr pcClusterMinpts,
+                  pcXYZIptr pcClusterMaxpts);
+}
+
+class buildingFacadeExtractor {
+ public:
+  bool meanShiftClustering(pcXYZIptr inputcloud, int iterTimes);
+};
+
+#endif

@@ -1,0 +1,71 @@
+// consumers_test.cpp — drives the drop-in consumers like a reference caller.  Used by tests/test_gpu_dropin.py:
+//   consumers_test odom  cloud.bin out_range.bin out_ptid.bin out_type.bin     (16 x 900 floats each, row-major)
+//   consumers_test dbscan cloud.bin r minpts out.bin      (int32 clusterID, int32 n_kept, then n_kept x 9 floats)
+//   consumers_test meanshift cloud.bin iters out.bin      (n x 3 floats)
+// cloud.bin: n x 4 float32 (x, y, z, intensity).
+#include <cstdint>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <vector>
+
+#include "consumers.h"
+
+static pcXYZIptr load(const char* path) {
+  pcXYZIptr cloud(new pcXYZI());
+  FILE* f = std::fopen(path, "rb");
+  if (!f) return cloud;
+  float p[4];
+  while (std::fread(p, sizeof(float), 4, f) == 4) cloud->push_back(pcl::PointXYZI(p[0], p[1], p[2], p[3]));
+  std::fclose(f);
+  return cloud;
+}
+
+static void dump(const char* path, const Eigen::MatrixXf& m) {
+  FILE* o = std::fopen(path, "wb");
+  for (int i = 0; i < m.rows(); ++i)
+    for (int j = 0; j < m.cols(); ++j) {
+      const float v = m(i, j);
+      std::fwrite(&v, 4, 1, o);
+    }
+  std::fclose(o);
+}
+
+int main(int argc, char** argv) {
+  if (argc < 4) return 2;
+  pcXYZIptr cloud = load(argv[2]);
+  if (!std::strcmp(argv[1], "odom") && argc >= 6) {
+    lidarOdometry::lidarOdometryClass lo;
+    Eigen::MatrixXf rng, pid, ty;
+    if (!lo.getRangeAndptIdImage(cloud, rng, pid)) return 1;
+    if (!lo.calculateSmoothness(rng, ty)) return 1;
+    dump(argv[3], rng);
+    dump(argv[4], pid);
+    dump(argv[5], ty);
+    return 0;
+  }
+  if (!std::strcmp(argv[1], "dbscan") && argc >= 6) {
+    pcXYZIptr cen(new pcXYZI()), mn(new pcXYZI()), mx(new pcXYZI());
+    const int32_t id = DynaTools::clusterDBSCAN(cloud, std::atof(argv[3]), std::atoi(argv[4]), cen, mn, mx);
+    FILE* o = std::fopen(argv[5], "wb");
+    const int32_t kept = (int32_t)cen->points.size();
+    std::fwrite(&id, 4, 1, o);
+    std::fwrite(&kept, 4, 1, o);
+    for (int32_t c = 0; c < kept; ++c) {
+      const float v[9] = {cen->points[c].x, cen->points[c].y, cen->points[c].z, mn->points[c].x, mn->points[c].y,
+                          mn->points[c].z,  mx->points[c].x,  mx->points[c].y,  mx->points[c].z};
+      std::fwrite(v, 4, 9, o);
+    }
+    std::fclose(o);
+    return 0;
+  }
+  if (!std::strcmp(argv[1], "meanshift") && argc >= 5) {
+    buildingFacadeExtractor bfe;
+    if (!bfe.meanShiftClustering(cloud, std::atoi(argv[3]))) return 1;
+    FILE* o = std::fopen(argv[4], "wb");
+    for (size_t i = 0; i < cloud->points.size(); ++i) std::fwrite(&cloud->points[i].x, 4, 3, o);
+    std::fclose(o);
+    return 0;
+  }
+  return 2;
+}

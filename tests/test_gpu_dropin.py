@@ -47,3 +47,58 @@ def test_class_dropin(tmp_path, oracle):
     assert (sgot["ptID"] == -7).all()  # the centro overload leaves ptID alone (src/pcaAnalysis.cpp:92)
     sref["ptID"] = -7
     check_features(sgot, sref, None, "dropin segments")
+
+
+def _run(args, tmp_path):
+    exe = os.path.join(PKG, "consumers_test")
+    assert os.path.exists(exe), "build the host library first (__graft_entry__.build())"
+    r = subprocess.run([exe] + [str(a) for a in args], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout + r.stderr
+
+
+def test_consumers_dropin_odometry_images(tmp_path, oracle):
+    """lidarOdometryClass::getRangeAndptIdImage + calculateSmoothness through the C++ signatures
+    (include/lidarOdometry.h:31-33), Eigen-style column-major matrices on the caller's side."""
+    fr = synth.vlp16_frame(12)
+    fr.tofile(tmp_path / "cloud.bin")
+    _run(["odom", tmp_path / "cloud.bin", tmp_path / "r.bin", tmp_path / "p.bin", tmp_path / "t.bin"], tmp_path)
+    cnt = oracle.KdTree(fr).radius_counts(3.0)
+    rng, pid, _, _, _ = oracle.odom_range_image(fr, cnt)
+    _, ty = oracle.odom_smoothness(rng)
+    np.testing.assert_array_equal(np.fromfile(tmp_path / "r.bin", np.float32).reshape(16, 900).view(np.uint32), rng.view(np.uint32))
+    np.testing.assert_array_equal(np.fromfile(tmp_path / "p.bin", np.float32).reshape(16, 900), pid)
+    np.testing.assert_array_equal(np.fromfile(tmp_path / "t.bin", np.float32).reshape(16, 900), ty)
+
+
+def test_consumers_dropin_dbscan_and_mean_shift(tmp_path, oracle):
+    """DynaTools::clusterDBSCAN (cluster count + the centroid / min / max lists that pass its size filter,
+    include/dbscanCLuster.h:308-325) and buildingFacadeExtractor::meanShiftClustering through the C++ signatures."""
+    rs = np.random.default_rng(5)
+    blobs = [rs.normal(c, 0.25, (400, 3)) for c in ((2, 2, 1), (8, 3, 1), (5, 9, 1), (12, 12, 1), (15, 4, 1))]
+    wall = np.stack([rs.uniform(0, 18, 3000), np.full(3000, 16.0), rs.uniform(0, 3, 3000)], 1)  # 18 m long: filtered out
+    xyz = np.concatenate(blobs + [wall, rs.uniform(0, 18, (300, 3))], 0)
+    pts = np.ascontiguousarray(np.concatenate([xyz, np.zeros((xyz.shape[0], 1))], 1).astype(np.float32))
+    pts = np.ascontiguousarray(pts[rs.permutation(pts.shape[0])])
+    pts.tofile(tmp_path / "cloud.bin")
+    _run(["dbscan", tmp_path / "cloud.bin", 0.4, 10, tmp_path / "d.bin"], tmp_path)
+    raw = open(tmp_path / "d.bin", "rb").read()
+    cluster_id, kept = struct.unpack("<ii", raw[:8])
+    got = np.frombuffer(raw[8:], np.float32).reshape(kept, 9)
+    flat = pts.copy()
+    flat[:, 2] = 0
+    state, nc = oracle.dbscan(flat, 0.4, 10)
+    assert cluster_id == nc and nc > 3
+    cen, lo, hi, _ = oracle.cluster_boxes(pts, state, nc)
+    ext = hi - lo
+    keep = ~((ext[:, 0] > 4) | (ext[:, 1] > 4) | (ext[:, 2].astype(np.float64) < 0.3))
+    assert kept == int(keep.sum()) and 0 < kept < nc
+    np.testing.assert_array_equal(got[:, 3:6], lo[keep])
+    np.testing.assert_array_equal(got[:, 6:9], hi[keep])
+    assert np.abs(got[:, :3] - cen[keep]).max() < 1e-4
+    _run(["meanshift", tmp_path / "cloud.bin", 2, tmp_path / "m.bin"], tmp_path)
+    moved = np.fromfile(tmp_path / "m.bin", np.float32).reshape(-1, 3)
+    cur = pts
+    for _ in range(2):
+        cur, _, _ = oracle.mean_shift_step(pts, cur, 2.0, 15)
+    err = np.abs(moved - cur[:, :3]).max(1)
+    assert (err > 2e-4).sum() <= 5
