@@ -14,6 +14,10 @@
  * lib/libPacketDecoder.so runs in the build container, oracle/ref_decoder/ drives it, and
  * tests/golden/decoder_*.npz hold its outputs (tests/test_golden.py).
  *
+ * The lidarOdometry images (odom.cpp) and the DBSCAN / mean-shift consumers (consumers.cpp) are restated from the
+ * reference's OWN sources (src/lidarOdometry.cpp, include/dbscanCLuster.h, src/buildingFacadeExtraction.cpp) on top
+ * of the same search; their libm dependency (atanf) is pinned to this image's glibc on all 2^32 inputs.
+ *
  * Clouds are packed float4 (x,y,z,intensity), n×4 floats.
  */
 #ifndef PCP_ORACLE_H_
