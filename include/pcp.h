@@ -50,7 +50,7 @@ typedef enum pcp_status {
                                      neighbourhoods are still computed: unordered double-precision accumulation) */
 } pcp_status;
 
-#define PCP_MAX_K 32
+#define PCP_MAX_K 64 /* k <= 32: the tile / warp-per-query k-NN kernels; 33..64 (SOR k = 60, region growing k = 50 upstream): cover-radius form, same results */
 
 /* Record layout-identical to `pcaAnalysist::pcaFeature` (include/pcaAnalysis.h:34-45):
  * lamda{la1,la2,la3} ascending; vec{v1,v2,v3} as three packed 3-float columns;

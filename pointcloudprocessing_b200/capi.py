@@ -33,7 +33,7 @@ assert FEATURE_DTYPE.itemsize == 68
 
 CENTER_QUERY, CENTER_MEAN = 0, 1
 STAGES = ("bbox", "keys", "sort", "table", "search_pca", "carry", "h2d", "d2h")
-MAX_K = 32
+MAX_K = 64
 
 # every symbol include/pcp.h declares (checked by tests/test_abi.py)
 EXPORTS = (
@@ -362,6 +362,13 @@ class Pcp:
         nrm = np.zeros((self.n_query, 4), np.float32) if want_normals else None
         self._ck(self.lib.pcp_knn_pca(self.h, k, center_mode, out.ctypes.data, _ptr(nrm), 0))
         return (out, nrm) if want_normals else out
+
+    def knn_pca_kth(self, k: int, center_mode: int = CENTER_QUERY):
+        """Records + the squared distance of every query's k-th neighbour (inf when the cloud holds fewer than k)."""
+        out = np.zeros(self.n_query, FEATURE_DTYPE)
+        kth = np.zeros(self.n_query, np.float32)
+        self._ck(self.lib.pcp_knn_pca_kth(self.h, k, center_mode, out.ctypes.data, None, kth.ctypes.data, 0))
+        return out, kth
 
     def knn_neighbors(self, k: int):
         idx = np.zeros((self.n_query, k), np.int32)

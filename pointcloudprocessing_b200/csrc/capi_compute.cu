@@ -62,6 +62,26 @@ int copy_back(pcp_ctx* ctx, T* user, const T* dev, int out_is_device, size_t cou
   return PCP_OK;
 }
 
+// 32 < k <= PCP_MAX_K: the k-NN kernels keep one key per lane, so these run through the radius machinery of
+// the warp-per-query kernel ("k by cover radius", search_pca.cu) — same results, same tie rule
+int knn_wide(pcp_ctx* ctx, SearchParams& sp) {
+  if (sp.k <= 32) return PCP_OK;
+  sp.mode = 1;
+  sp.min_pts = 1;
+  int rc = pcp_reserve(ctx, ctx->flags, sizeof(int));
+  if (rc) return rc;
+  sp.overflow_flag = (int*)ctx->flags.p;
+  PCP_CUDA(cudaMemsetAsync(ctx->flags.p, 0, sizeof(int), ctx->stream));
+  return PCP_OK;
+}
+int knn_wide_check(pcp_ctx* ctx, const char* who) {
+  int h_flag = 0;
+  PCP_CUDA(cudaMemcpyAsync(&h_flag, ctx->flags.p, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+  PCP_CUDA(cudaStreamSynchronize(ctx->stream));
+  if (h_flag) return pcp_fail(ctx, PCP_ERR_NEIGHBOR_OVERFLOW, who);
+  return PCP_OK;
+}
+
 // smallest stencil half-width whose guaranteed coverage (R − 1e-6)·cell holds the radius
 int stencil_for_radius(const GridDesc& g, float r2) {
   double r = std::sqrt((double)r2) * (1.0 + 2e-6);
@@ -123,6 +143,7 @@ PCP_API int pcp_knn_pca_kth(pcp_ctx* ctx, int k, int center_mode, pcp_feature68*
   sp.k = k;
   sp.R0 = 1;
   sp.center_mode = center_mode;
+  if ((rc = knn_wide(ctx, sp))) return rc;
   if ((rc = pick_out(ctx, ctx->out_feat, out, out_is_device, (size_t)nq, &sp.out))) return rc;
   if ((rc = pick_out(ctx, ctx->out_norm, normals, out_is_device, (size_t)nq, &sp.normals))) return rc;
   if ((rc = pick_out(ctx, ctx->out_d2, kth_d2, out_is_device, (size_t)nq, &sp.kth_d2))) return rc;
@@ -132,6 +153,7 @@ PCP_API int pcp_knn_pca_kth(pcp_ctx* ctx, int k, int center_mode, pcp_feature68*
   if ((rc = copy_back(ctx, normals, sp.normals, out_is_device, (size_t)nq))) return rc;
   if ((rc = copy_back(ctx, kth_d2, sp.kth_d2, out_is_device, (size_t)nq))) return rc;
   pcp_toc(ctx, PCP_T_D2H);
+  if (sp.overflow_flag) return knn_wide_check(ctx, "pcp_knn_pca");
   if (!out_is_device && !ctx->host_async) PCP_CUDA(cudaStreamSynchronize(ctx->stream));
   return PCP_OK;
 }
@@ -147,11 +169,13 @@ PCP_API int pcp_knn_neighbors(pcp_ctx* ctx, int k, int32_t* idx, float* d2, int 
   sp.mode = 0;
   sp.k = k;
   sp.R0 = 1;
+  if ((rc = knn_wide(ctx, sp))) return rc;
   if ((rc = pick_out(ctx, ctx->out_idx, idx, out_is_device, cnt, &sp.nn_idx))) return rc;
   if ((rc = pick_out(ctx, ctx->out_d2, d2, out_is_device, cnt, &sp.nn_d2))) return rc;
   if ((rc = pcp_search_launch(ctx, sp))) return rc;
   if ((rc = copy_back(ctx, idx, sp.nn_idx, out_is_device, cnt))) return rc;
   if ((rc = copy_back(ctx, d2, sp.nn_d2, out_is_device, cnt))) return rc;
+  if (sp.overflow_flag) return knn_wide_check(ctx, "pcp_knn_neighbors");
   if (!out_is_device) PCP_CUDA(cudaStreamSynchronize(ctx->stream));
   return PCP_OK;
 }

@@ -215,7 +215,7 @@ __device__ __forceinline__ void scan_shell(const KArgs& a, WarpSmem<MODE>* ws, S
           const float4 P = __ldg(&sorted[rd.x + (v - rd.y)]);
           const float d2v = dist2_nofma(Q.x, Q.y, Q.z, P);
           key = ((u64)__float_as_uint(d2v) << 32) | (u64)__float_as_uint(P.w);
-          pass = MODE == 0 ? key < st.thr : d2v < a.sp.r2;
+          pass = MODE == 0 ? key < st.thr : d2v < bound2;  // radius mode: bound2 = r2 (or the k-by-cover radius of this pass)
         }
         const unsigned m = __ballot_sync(PCP_FULL, pass);
         if (m == 0) continue;
@@ -331,7 +331,43 @@ __device__ __forceinline__ void search_tile(const KArgs& a, WarpSmem<MODE>* ws, 
       f0 = fminf(fmaxf(f0, 0.f), 1.f);
       f1 = fminf(fmaxf(f1, 0.f), 1.f);
       f2 = fminf(fmaxf(f2, 0.f), 1.f);
-      if (MODE == 1) {
+      if (MODE == 1 && sp.k > 0) {
+        // k nearest for 32 < k <= 64 (the best list above holds one key per lane): collect EVERY point inside
+        // a radius the stencil is known to cover, and keep the first k of the sorted hits.  Fewer than k hits:
+        // grow the stencil; more than the buffer holds: bisect the radius between a value known to hold < k
+        // points and the one that overflowed.  Exact, ties included (all points at the k-th distance lie
+        // inside the radius and are ordered by index).
+        int R = sp.R0;
+        float lo2 = 0.f, hi2 = 0.f;
+        overflow = true;
+#pragma unroll 1
+        for (int it = 0; it < 96; ++it) {
+          const bool whole = (c0 - R <= 0) && (c0 + R >= g.dim[0] - 1) && (c1 - R <= 0) && (c1 + R >= g.dim[1] - 1) &&
+                             (c2 - R <= 0) && (c2 + R >= g.dim[2] - 1);
+          const float cov = whole ? 3.0e38f : cover2_of(R, g.cell);
+          const bool bisect = hi2 > 0.f && hi2 <= cov;
+          const float r2q = bisect ? 0.5f * lo2 + 0.5f * hi2 : cov;
+          if (bisect && !(r2q > lo2 && r2q < hi2)) break;  // more than RADIUS_CAP points at one distance: give up
+          st.cnt = 0;
+          __syncwarp();
+          scan_shell<MODE>(a, ws, st, Q, c0, c1, c2, zoff, f0, f1, f2, -1, R, r2q, lane, dirs);
+          __syncwarp();
+          if (st.cnt > RADIUS_CAP) {
+            hi2 = r2q;
+            continue;
+          }
+          if (st.cnt >= sp.k || (whole && !bisect)) {
+            overflow = false;
+            break;
+          }
+          lo2 = r2q;
+          if (!bisect) {  // fewer than k inside the covered radius: widen the stencil (planar density guess)
+            const double want = sqrt((double)cov * 1.6 * (double)sp.k / (double)max(st.cnt, 1)) * g.inv_cell;
+            R = min(max(R + 1, (int)fmin(ceil(want), 1.0e6)), max_dim);
+          }
+        }
+        n_nb = overflow ? 0 : st.cnt;
+      } else if (MODE == 1) {
         scan_shell<MODE>(a, ws, st, Q, c0, c1, c2, zoff, f0, f1, f2, -1, sp.R0, sp.r2, lane, dirs);
         __syncwarp();
         n_nb = st.cnt;
@@ -434,10 +470,13 @@ __device__ __forceinline__ void search_tile(const KArgs& a, WarpSmem<MODE>* ws, 
         smem_sort_pow2(buf, m2, lane);
       }
     }
+    if (MODE == 1 && sp.k > 0 && n_nb > sp.k) n_nb = sp.k;  // k by cover radius: the first k of the sorted hits
     if (MODE == 1 && overflow && sp.overflow_flag && lane == 0) atomicExch(sp.overflow_flag, 1);
     if (MODE == 1 && sp.counts && lane == 0) sp.counts[slot_q] = n_nb;
     if (MODE == 0 && sp.kth_d2 && lane == 0)
       sp.kth_d2[slot_q] = n_nb >= sp.k ? __uint_as_float((uint32_t)(st.thr >> 32)) : INFINITY;
+    if (MODE == 1 && sp.k > 0 && sp.kth_d2 && lane == 0)
+      sp.kth_d2[slot_q] = n_nb >= sp.k ? __uint_as_float((uint32_t)(buf[sp.k - 1] >> 32)) : INFINITY;
     if (sp.nn_idx != nullptr && !overflow) {
       if (MODE == 0) {
         if (lane < sp.k) {
@@ -446,6 +485,15 @@ __device__ __forceinline__ void search_tile(const KArgs& a, WarpSmem<MODE>* ws, 
           const int ord = (int)(uint32_t)st.best;
           sp.nn_idx[o] = has ? (a.gid_of_ord ? __ldg(&a.gid_of_ord[ord]) : ord) : -1;
           if (sp.nn_d2) sp.nn_d2[o] = has ? __uint_as_float((uint32_t)(st.best >> 32)) : INFINITY;
+        }
+      } else if (sp.k > 0) {
+        for (int t = lane; t < sp.k; t += 32) {
+          const int64_t o = (int64_t)slot_q * sp.k + t;
+          const bool has = t < n_nb;
+          const u64 key = has ? buf[t] : 0ull;
+          const int ord = (int)(uint32_t)key;
+          sp.nn_idx[o] = has ? (a.gid_of_ord ? __ldg(&a.gid_of_ord[ord]) : ord) : -1;
+          if (sp.nn_d2) sp.nn_d2[o] = has ? __uint_as_float((uint32_t)(key >> 32)) : INFINITY;
         }
       } else if (sp.offsets) {
         const int64_t o = sp.offsets[slot_q];
@@ -607,7 +655,7 @@ int pcp_search_launch(pcp_ctx* ctx, const SearchParams& sp) {
   const char* rimpl = getenv("PCP_RADIUS_IMPL");
   bool radius_tile = false;
   int radius_cap = 32;
-  if (sp.mode == 1 && sp.out != nullptr && sp.counts == nullptr && sp.nn_idx == nullptr) {
+  if (sp.mode == 1 && sp.k == 0 && sp.out != nullptr && sp.counts == nullptr && sp.nn_idx == nullptr) {
     const double area = (double)ctx->grid.dim[2] * (double)ctx->grid.dim[0] * (double)ctx->grid.cell * (double)ctx->grid.cell;
     const double guess = (double)ctx->n / (double)ctx->grid.n_seg * 3.14159265 * (double)sp.r2 / (area > 0.0 ? area : 1.0);
     // lanes of 32 neighbours for sparse neighbourhoods, of 64 for dense ones (configs[3]: ~32 on average),

@@ -90,3 +90,48 @@ def test_sharded_global_ids_tie_break(pcp, oracle):
     np.testing.assert_array_equal(d2.view(np.uint32), rd2[perm[:n_own]].view(np.uint32))
     feat = pcp.knn_pca(20)
     np.testing.assert_array_equal(feat["ptID"], perm[:n_own])
+
+
+@pytest.mark.parametrize("kind,n,k", [("urban", 20000, 33), ("urban", 20000, 50), ("urban", 30000, 60), ("urban", 20000, 64),
+                                      ("lattice", 4000, 50), ("frame", 25000, 60), ("urban", 50, 64), ("urban", 40, 40)])
+def test_knn_wide_k_bit_exact(pcp, oracle, kind, n, k):
+    """32 < k <= 64 (pcl::StatisticalOutlierRemoval k = 60 src/smoothing.cpp:161-166, region growing k = 50 :256-268):
+    served by the cover-radius form of the warp-per-query kernel; same lists, same tie rule."""
+    pts = _cloud(kind, n, 13)
+    pcp.set_cloud(pts)
+    pcp.build_grid(0.0, k)
+    idx, d2 = pcp.knn_neighbors(k)
+    ridx, rd2 = oracle.KdTree(pts).knn_all(k)
+    np.testing.assert_array_equal(idx, ridx)
+    np.testing.assert_array_equal(d2.view(np.uint32), rd2.view(np.uint32))
+
+
+@pytest.mark.parametrize("cell", [0.15, 0.6, 3.0])
+def test_knn_wide_k_any_cell_and_dense_clumps(pcp, oracle, cell):
+    """Stencil growth (small cells) and radius bisection (a clump of 1500 points inside one cell overflows the
+    512-entry hit buffer at the covered radius) give the same lists."""
+    rs = np.random.default_rng(21)
+    pts = _cloud("urban", 12000, 6)
+    clump = (np.array([20.0, 20.0, 1.0, 0.0], np.float32) + rs.normal(0, 0.02, (1500, 4))).astype(np.float32)
+    pts = np.ascontiguousarray(np.concatenate([pts, clump], 0))
+    pcp.set_cloud(pts)
+    pcp.build_grid(cell, 0)
+    idx, d2 = pcp.knn_neighbors(48)
+    ridx, rd2 = oracle.KdTree(pts).knn_all(48)
+    np.testing.assert_array_equal(idx, ridx)
+    np.testing.assert_array_equal(d2.view(np.uint32), rd2.view(np.uint32))
+
+
+def test_knn_wide_k_pca_records(pcp, oracle):
+    from parity import check_features
+    pts = _cloud("urban", 20000, 17)
+    pcp.set_cloud(pts)
+    pcp.build_grid(0.0, 50)
+    for mode in (0, 1):
+        got, nrm = pcp.knn_pca(50, mode, want_normals=True)
+        ref, rn = oracle.knn_pca_cloud(pts, 50, mode, want_normals=True)
+        check_features(got, ref, None, f"k=50 mode {mode}")
+    kth = pcp.knn_pca_kth(60, 0)[1] if hasattr(pcp, "knn_pca_kth") else None
+    if kth is not None:
+        _, rd2 = oracle.KdTree(pts).knn_all(60)
+        np.testing.assert_array_equal(kth.view(np.uint32), rd2[:, 59].view(np.uint32))
