@@ -391,6 +391,17 @@ PCP_API int pcp_cluster_boxes(pcp_ctx* ctx, const int32_t* labels, int labels_is
 PCP_API int pcp_mean_shift(pcp_ctx* ctx, float radius, int min_pts, int iterations, const void* start_xyzi, int start_is_device,
                            void* out_xyzi, int32_t* counts, int out_is_device);
 
+/* ---- text clouds ---------------------------------------------------------------
+ * Replaces preprocess::txt2pc (src/smoothing.cpp:39-81): `text` = the bytes of an "x y z intensity" file (host or
+ * device per text_is_device), parsed on the device with the reference's stream semantics — one point per line
+ * (empty lines included), a field the line does not supply keeps the previous line's value, a field that does
+ * not parse becomes 0 and ends the line, values are the correctly rounded floats strtof gives (exact for up to
+ * 19 significant digits).  The points become the CURRENT CLOUD of the context; *n_points (HOST) receives their
+ * number and out_xyzi (optional, n x 4 floats, host or device, capacity in points) a copy.  Synchronises.
+ * preprocess::xyz2pc (:83-125) is not offered: it sscanf's a %s into a single char (undefined upstream). */
+PCP_API int pcp_set_cloud_txt(pcp_ctx* ctx, const void* text, int64_t n_bytes, int text_is_device, int64_t* n_points,
+                              float* out_xyzi, int64_t out_capacity, int out_is_device);
+
 #ifdef __cplusplus
 }
 #endif

@@ -63,6 +63,7 @@ def load() -> C.CDLL:
         "orc_dbscan": (i32, [vp, i64, f32, i32, vp]),
         "orc_cluster_boxes": (None, [vp, i64, vp, i32, vp, vp, vp, vp]),
         "orc_mean_shift_step": (None, [vp, vp, i64, f32, i32, vp, vp, vp]),
+        "orc_txt2pc": (i64, [C.c_char_p, i64, vp, i64]),
         "orc_num_threads": (i32, []),
     }
     for name, (res, args) in sig.items():
@@ -306,3 +307,11 @@ def mean_shift_step(orig, cur, radius: float = 2.0, min_pts: int = 15):
     load().orc_mean_shift_step(orig.ctypes.data, cur.ctypes.data, cur.shape[0], radius, min_pts, nxt.ctypes.data,
                                shift.ctypes.data, cnt.ctypes.data)
     return nxt, shift, cnt
+
+
+def txt2pc(text: bytes):
+    """preprocess::txt2pc on an in-memory file: (n_lines, 4) float32."""
+    cap = text.count(b"\n") + 1
+    out = np.zeros((cap, 4), np.float32)
+    n = load().orc_txt2pc(text, len(text), out.ctypes.data, cap)
+    return out[:n].copy()

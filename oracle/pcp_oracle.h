@@ -130,6 +130,10 @@ void orc_cluster_boxes(const float* xyzi, int64_t n, const int32_t* state, int32
 void orc_mean_shift_step(const float* orig_xyzi, const float* cur_xyzi, int64_t n, float radius, int min_pts, float* next_xyzi,
                          float* shift_xyz, int32_t* counts);
 
+/* preprocess::txt2pc (src/smoothing.cpp:39-81): text -> points (x y z intensity per line), the reference's own
+ * stream statements.  Returns the number of lines = points; writes at most `capacity` of them. */
+int64_t orc_txt2pc(const char* text, int64_t n_bytes, float* out_xyzi, int64_t capacity);
+
 int orc_num_threads(void);
 
 /* Velodyne packet decode (lib/libPacketDecoder.so restated, see decoder.cpp): n_packets x 1206 bytes ->

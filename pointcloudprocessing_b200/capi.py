@@ -44,7 +44,7 @@ EXPORTS = (
     "pcp_ring_calib_from_xml", "pcp_ring_project", "pcp_set_host_async", "pcp_alloc_pinned", "pcp_free_pinned", "pcp_halo_pack", "pcp_set_frames",
     "pcp_halo_push", "pcp_halo_wait", "pcp_peer_alloc", "pcp_peer_free", "pcp_peer_open", "pcp_peer_close",
     "pcp_ring_seg_params_default", "pcp_ring_segment", "pcp_decode_packets",
-    "pcp_dbscan", "pcp_cluster_boxes", "pcp_mean_shift",
+    "pcp_dbscan", "pcp_cluster_boxes", "pcp_mean_shift", "pcp_set_cloud_txt",
     "pcp_radius_count", "pcp_odom_params_default", "pcp_odom_range_image", "pcp_odom_smoothness",
 )
 
@@ -164,6 +164,7 @@ def load() -> C.CDLL:
         "pcp_decode_packets": (i32, [vp, C.POINTER(RingCalib), vp, i64, i32, vp, i32, vp, i64, vp, vp]),
         "pcp_radius_count": (i32, [vp, f32, i32, vp, i32]),
         "pcp_dbscan": (i32, [vp, f32, i32, vp, vp, i32]),
+        "pcp_set_cloud_txt": (i32, [vp, vp, i64, i32, vp, vp, i64, i32]),
         "pcp_cluster_boxes": (i32, [vp, vp, i32, i32, vp, vp, vp, vp]),
         "pcp_mean_shift": (i32, [vp, f32, i32, i32, vp, i32, vp, vp, i32]),
         "pcp_odom_params_default": (i32, [C.POINTER(OdomParams)]),
@@ -533,3 +534,13 @@ class Pcp:
         cnt = np.zeros(self.n, np.int32)
         self._ck(self.lib.pcp_mean_shift(self.h, radius, min_pts, iterations, _ptr(st), 0, out.ctypes.data, cnt.ctypes.data, 0))
         return out, cnt
+
+    def set_cloud_txt(self, text: bytes) -> np.ndarray:
+        """preprocess::txt2pc on the device: the parsed points become the current cloud; returns them (n, 4)."""
+        buf = np.frombuffer(text, np.uint8)
+        cap = text.count(b"\n") + 1
+        out = np.zeros((cap, 4), np.float32)
+        n = C.c_int64()
+        self._ck(self.lib.pcp_set_cloud_txt(self.h, buf.ctypes.data if len(text) else None, len(text), 0, C.addressof(n), out.ctypes.data, cap, 0))
+        self.n = self.n_query = int(n.value)
+        return out[: int(n.value)].copy()

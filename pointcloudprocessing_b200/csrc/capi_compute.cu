@@ -27,6 +27,8 @@ int pcp_cluster_boxes_impl(pcp_ctx* ctx, const int32_t* d_labels, int n_clusters
                            int32_t* d_counts);
 int pcp_mean_shift_impl(pcp_ctx* ctx, const float4* d_cur, float r2, int R, int min_pts, float4* d_next, int32_t* d_counts);
 
+int pcp_parse_txt_impl(pcp_ctx* ctx, const unsigned char* d_text, int64_t n_bytes, int64_t* n_lines_out);
+
 namespace {
 
 int require_grid(pcp_ctx* ctx, const char* who) {
@@ -626,6 +628,34 @@ PCP_API int pcp_mean_shift(pcp_ctx* ctx, float radius, int min_pts, int iteratio
   if (!out_is_device) PCP_CUDA(cudaMemcpyAsync(out_xyzi, cur, n * sizeof(float4), cudaMemcpyDeviceToHost, ctx->stream));
   if ((rc = copy_back(ctx, counts, d_counts, out_is_device, n))) return rc;
   if (!out_is_device && !ctx->host_async) PCP_CUDA(cudaStreamSynchronize(ctx->stream));
+  return PCP_OK;
+}
+
+PCP_API int pcp_set_cloud_txt(pcp_ctx* ctx, const void* text, int64_t n_bytes, int text_is_device, int64_t* n_points,
+                              float* out_xyzi, int64_t out_capacity, int out_is_device) {
+  if (!ctx) return PCP_ERR_INVALID_ARG;
+  if (n_bytes < 0 || (n_bytes > 0 && !text) || !n_points || (out_xyzi && out_capacity < 0))
+    return pcp_fail(ctx, PCP_ERR_INVALID_ARG, "pcp_set_cloud_txt: bad argument");
+  PCP_CUDA(cudaSetDevice(ctx->device));
+  *n_points = 0;
+  if (n_bytes == 0) return PCP_OK;
+  int rc;
+  const unsigned char* d_text = (const unsigned char*)text;
+  if (!text_is_device) {
+    if ((rc = pcp_reserve(ctx, ctx->txt_in, (size_t)n_bytes))) return rc;
+    PCP_CUDA(cudaMemcpyAsync(ctx->txt_in.p, text, (size_t)n_bytes, cudaMemcpyHostToDevice, ctx->stream));
+    d_text = (const unsigned char*)ctx->txt_in.p;
+  }
+  int64_t n = 0;
+  if ((rc = pcp_parse_txt_impl(ctx, d_text, n_bytes, &n))) return rc;
+  *n_points = n;
+  if (n > 0 && (rc = pcp_set_cloud_device(ctx, ctx->txt_out.p, n))) return rc;
+  if (out_xyzi) {
+    const size_t m = (size_t)(n < out_capacity ? n : out_capacity);
+    if (m) PCP_CUDA(cudaMemcpyAsync(out_xyzi, ctx->txt_out.p, m * 4 * sizeof(float), out_is_device ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost,
+                                    ctx->stream));
+  }
+  PCP_CUDA(cudaStreamSynchronize(ctx->stream));
   return PCP_OK;
 }
 

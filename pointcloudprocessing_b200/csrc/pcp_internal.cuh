@@ -88,6 +88,7 @@ struct pcp_ctx {
   DevBuf dec_tables, dec_packed, dec_out;  // pcp_decode_packets: azimuth cos/sin tables, per-block scan, staged outputs
   DevBuf odom_counts, odom_range, odom_ptid, odom_index, odom_stats, odom_minmax, odom_smooth, odom_type;  // lidarOdometry images
   DevBuf db_parent, db_root, db_flag, db_rank, db_boxes, db_labels, db_out, ms_a, ms_b;  // DBSCAN / mean shift scratch
+  DevBuf txt_in, txt_rank, txt_starts, txt_vals, txt_last, txt_out;  // pcp_set_cloud_txt
   const float* odom_last_range = nullptr;  // device images of the last pcp_odom_range_image
   int64_t odom_last_frames = 0;
   DevBuf seg_ground, seg_label, seg_colmax, seg_above, seg_counts, seg_nlabels;  // pcp_ring_segment outputs

@@ -153,3 +153,26 @@ bool buildingFacadeExtractor::meanShiftClustering(pcXYZIptr inputcloud, int iter
   }
   return true;
 }
+
+bool preprocess::txt2pc(std::string txtpath, pcXYZI& origiCloud) {
+  FILE* f = std::fopen(txtpath.c_str(), "rb");
+  if (!f) {
+    std::fprintf(stderr, "Wrong txt file! \n");  // (:47-49); the reference still returns true
+    return true;
+  }
+  std::vector<char> text;
+  char chunk[1 << 16];
+  size_t got;
+  while ((got = std::fread(chunk, 1, sizeof(chunk), f)) > 0) text.insert(text.end(), chunk, chunk + got);
+  std::fclose(f);
+  pcp_ctx* ctx = context();
+  if (!ctx) return false;
+  size_t lines = 1;
+  for (char c : text) lines += c == '\n';
+  std::vector<float> pts(4 * lines);
+  int64_t n = 0;
+  const int rc = pcp_set_cloud_txt(ctx, text.data(), (int64_t)text.size(), 0, &n, pts.data(), (int64_t)lines, 0);
+  if (rc) return fail(ctx, "txt2pc", rc);
+  for (int64_t i = 0; i < n; ++i) origiCloud.push_back(pcl::PointXYZI(pts[4 * i], pts[4 * i + 1], pts[4 * i + 2], pts[4 * i + 3]));
+  return true;
+}

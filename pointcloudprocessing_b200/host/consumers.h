@@ -3,11 +3,14 @@
 //   lidarOdometry::lidarOdometryClass::getRangeAndptIdImage / calculateSmoothness  (include/lidarOdometry.h:31-33)
 //   DynaTools::clusterDBSCAN                                                       (include/dbscanCLuster.h:256-260)
 //   buildingFacadeExtractor::meanShiftClustering                                   (include/buildingFacadeExtraction.h)
+//   preprocess::txt2pc                                                             (src/smoothing.cpp:39-81)
 // Bodies (consumers.cpp) forward to the CUDA path behind include/pcp.h; there is no CPU path.  Differences a
 // caller can observe: the bool methods really return true/false (the reference falls off their ends), nothing
 // is printed to std::cout, and where the reference indexes outside its 16 x 900 matrices the point is skipped.
 #ifndef PCP_HOST_CONSUMERS_H_
 #define PCP_HOST_CONSUMERS_H_
+
+#include <string>
 
 #include "pcaAnalysis.h"  // pcXYZIptr / pcXYZI and the PCL / Eigen types (real or compat)
 
@@ -23,6 +26,12 @@ namespace DynaTools {
 int clusterDBSCAN(pcXYZIptr inCloud, double r, int minptNum, pcXYZIptr pcClusterCentos, pcXYZIptr pcClusterMinpts,
                   pcXYZIptr pcClusterMaxpts);
 }
+
+// preprocess::txt2pc (include/smoothing.h, src/smoothing.cpp:39-81): "x y z intensity" text file -> cloud (appended)
+class preprocess {
+ public:
+  bool txt2pc(std::string txtpath, pcXYZI& origiCloud);
+};
 
 class buildingFacadeExtractor {
  public:

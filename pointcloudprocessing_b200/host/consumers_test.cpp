@@ -2,6 +2,7 @@
 //   consumers_test odom  cloud.bin out_range.bin out_ptid.bin out_type.bin     (16 x 900 floats each, row-major)
 //   consumers_test dbscan cloud.bin r minpts out.bin      (int32 clusterID, int32 n_kept, then n_kept x 9 floats)
 //   consumers_test meanshift cloud.bin iters out.bin      (n x 3 floats)
+//   consumers_test txt file.txt out.bin                   (1 + n points x 4 floats; the first is the caller's own)
 // cloud.bin: n x 4 float32 (x, y, z, intensity).
 #include <cstdint>
 #include <cstdio>
@@ -33,7 +34,7 @@ static void dump(const char* path, const Eigen::MatrixXf& m) {
 
 int main(int argc, char** argv) {
   if (argc < 4) return 2;
-  pcXYZIptr cloud = load(argv[2]);
+  pcXYZIptr cloud = std::strcmp(argv[1], "txt") ? load(argv[2]) : pcXYZIptr(new pcXYZI());
   if (!std::strcmp(argv[1], "odom") && argc >= 6) {
     lidarOdometry::lidarOdometryClass lo;
     Eigen::MatrixXf rng, pid, ty;
@@ -55,6 +56,19 @@ int main(int argc, char** argv) {
       const float v[9] = {cen->points[c].x, cen->points[c].y, cen->points[c].z, mn->points[c].x, mn->points[c].y,
                           mn->points[c].z,  mx->points[c].x,  mx->points[c].y,  mx->points[c].z};
       std::fwrite(v, 4, 9, o);
+    }
+    std::fclose(o);
+    return 0;
+  }
+  if (!std::strcmp(argv[1], "txt") && argc >= 4) {  // consumers_test txt file.txt out.bin  (n x 4 floats)
+    preprocess pre;
+    pcXYZI cl;
+    cl.push_back(pcl::PointXYZI(-1.f, -2.f, -3.f, -4.f));  // txt2pc appends
+    if (!pre.txt2pc(argv[2], cl)) return 1;
+    FILE* o = std::fopen(argv[3], "wb");
+    for (size_t i = 0; i < cl.points.size(); ++i) {
+      const float v[4] = {cl.points[i].x, cl.points[i].y, cl.points[i].z, cl.points[i].intensity};
+      std::fwrite(v, 4, 4, o);
     }
     std::fclose(o);
     return 0;

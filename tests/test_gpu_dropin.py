@@ -102,3 +102,15 @@ def test_consumers_dropin_dbscan_and_mean_shift(tmp_path, oracle):
         cur, _, _ = oracle.mean_shift_step(pts, cur, 2.0, 15)
     err = np.abs(moved - cur[:, :3]).max(1)
     assert (err > 2e-4).sum() <= 5
+
+
+def test_consumers_dropin_txt2pc(tmp_path, oracle):
+    """preprocess::txt2pc(path, cloud) through the C++ signature: appends to the caller's cloud."""
+    pts = synth.urban(29, 5000, extent=20.0)
+    text = "".join("%.4f %.4f %.4f %.0f\n" % tuple(p) for p in pts.astype(np.float64)).encode() + b"1 2\n\n3"
+    (tmp_path / "cloud.txt").write_bytes(text)
+    _run(["txt", tmp_path / "cloud.txt", tmp_path / "o.bin"], tmp_path)
+    got = np.fromfile(tmp_path / "o.bin", np.float32).reshape(-1, 4)
+    ref = oracle.txt2pc(text)
+    np.testing.assert_array_equal(got[0], np.array([-1, -2, -3, -4], np.float32))
+    np.testing.assert_array_equal(got[1:].view(np.uint32), ref.view(np.uint32))
