@@ -431,8 +431,8 @@ extern "C" __attribute__((visibility("default"))) int pcp_debug_tile_stats(unsig
 int pcp_knn_tile_launch(pcp_ctx* ctx, const SearchParams& sp, const KArgs& a, int radius_cap) {
   int rc;
   if ((rc = pcp_reserve(ctx, ctx->work_list, (size_t)ctx->n * sizeof(uint32_t)))) return rc;
-  if ((rc = pcp_reserve(ctx, ctx->work_count, sizeof(uint32_t)))) return rc;
-  PCP_CUDA(cudaMemsetAsync(ctx->work_count.p, 0, sizeof(uint32_t), ctx->stream));
+  if ((rc = pcp_reserve(ctx, ctx->work_count, 2 * sizeof(uint32_t)))) return rc;  // [0] list length, [1] ticket counter of the work-list kernel
+  PCP_CUDA(cudaMemsetAsync(ctx->work_count.p, 0, 2 * sizeof(uint32_t), ctx->stream));
   const int64_t tiles = (ctx->n + 31) / 32;
   const int blocks = (int)((tiles + TA_WARPS - 1) / TA_WARPS);
   // a tile's stencil is widened when (uncovered lanes) * grow exceeds the size of the wider union

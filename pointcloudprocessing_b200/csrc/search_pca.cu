@@ -595,19 +595,24 @@ __global__ void __launch_bounds__(WARPS * 32, 3) search_pca_kernel(KArgs a) {
   search_tile<MODE>(a, ws, lane, pos0 + lane, (int)min((int64_t)32, a.n - pos0));
 }
 
-// the queries a faster kernel deferred: work_list[0 .. *work_count) are sorted positions; warps take
-// tiles of 32 list entries grid-stride (the count is only known on the device)
+// the queries a faster kernel deferred: work_list[0 .. work_count[0]) are sorted positions.  Warps draw tiles of
+// `tile` list entries from a ticket counter (work_count[1]) until the list is empty — the count is only known on
+// the device, and drawing tickets keeps every resident warp busy to the end whatever the list length.
 template <int MODE>
-__global__ void __launch_bounds__(WARPS * 32, 3) search_pca_worklist_kernel(KArgs a, const uint32_t* __restrict__ work_count,
-                                                                         const uint32_t* __restrict__ work_list) {
+__global__ void __launch_bounds__(WARPS * 32, 3) search_pca_worklist_kernel(KArgs a, uint32_t* work_count, const uint32_t* __restrict__ work_list,
+                                                                         int tile) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   WarpSmem<MODE>* ws = reinterpret_cast<WarpSmem<MODE>*>(smem_raw) + (threadIdx.x >> 5);
   const int lane = threadIdx.x & 31;
-  const int64_t n_items = (int64_t)*work_count;
-  const int64_t stride = (int64_t)gridDim.x * WARPS * 32;
+  const int64_t n_items = (int64_t)__ldg(work_count);
 #pragma unroll 1
-  for (int64_t i0 = ((int64_t)blockIdx.x * WARPS + (threadIdx.x >> 5)) * 32; i0 < n_items; i0 += stride) {
-    const int nq = (int)min((int64_t)32, n_items - i0);
+  for (;;) {
+    uint32_t t = 0;
+    if (lane == 0) t = atomicAdd(work_count + 1, 1u);
+    t = __shfl_sync(PCP_FULL, t, 0);
+    const int64_t i0 = (int64_t)t * tile;
+    if (i0 >= n_items) break;
+    const int nq = (int)min((int64_t)tile, n_items - i0);
     const int64_t my_pos = lane < nq ? (int64_t)work_list[i0 + lane] : 0;
     search_tile<MODE>(a, ws, lane, my_pos, nq);
     __syncwarp();
@@ -668,17 +673,22 @@ int pcp_search_launch(pcp_ctx* ctx, const SearchParams& sp) {
   if ((sp.mode == 0 && !use_v3) || radius_tile) {
     int rc = pcp_knn_tile_launch(ctx, sp, a, radius_cap);
     if (rc) return rc;
-    const int wl_blocks = blocks < 148 * 4 ? blocks : 148 * 4;
+    // one wave of resident CTAs (3 per SM at 80 registers); tiles of 16 list entries drawn by ticket
+    // (tuning hooks: PCP_WL_BLOCKS, PCP_WL_TILE)
+    int wl_blocks = blocks < 148 * 3 ? blocks : 148 * 3;
+    int wl_tile = 16;
+    if (const char* e = getenv("PCP_WL_BLOCKS")) wl_blocks = atoi(e) > 0 ? atoi(e) : wl_blocks;
+    if (const char* e = getenv("PCP_WL_TILE")) wl_tile = atoi(e) >= 1 && atoi(e) <= 32 ? atoi(e) : wl_tile;
     if (sp.mode == 0) {
       size_t smem = sizeof(WarpSmem<0>) * WARPS;
       PCP_CUDA(cudaFuncSetAttribute(search_pca_worklist_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-      search_pca_worklist_kernel<0><<<wl_blocks, WARPS * 32, smem, ctx->stream>>>(a, (const uint32_t*)ctx->work_count.p,
-                                                                                  (const uint32_t*)ctx->work_list.p);
+      search_pca_worklist_kernel<0><<<wl_blocks, WARPS * 32, smem, ctx->stream>>>(a, (uint32_t*)ctx->work_count.p,
+                                                                                  (const uint32_t*)ctx->work_list.p, wl_tile);
     } else {
       size_t smem = sizeof(WarpSmem<1>) * WARPS;
       PCP_CUDA(cudaFuncSetAttribute(search_pca_worklist_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-      search_pca_worklist_kernel<1><<<wl_blocks, WARPS * 32, smem, ctx->stream>>>(a, (const uint32_t*)ctx->work_count.p,
-                                                                                  (const uint32_t*)ctx->work_list.p);
+      search_pca_worklist_kernel<1><<<wl_blocks, WARPS * 32, smem, ctx->stream>>>(a, (uint32_t*)ctx->work_count.p,
+                                                                                  (const uint32_t*)ctx->work_list.p, wl_tile);
     }
   } else if (sp.mode == 0) {
     size_t smem = sizeof(WarpSmem<0>) * WARPS;
