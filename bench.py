@@ -154,7 +154,16 @@ def reference_arm(args, rank, world):
                          "sample": f"spatial tile of ~{target} points of the same cloud per step, OpenMP over points"},
         "e2e": {"value": value, "unit": "points/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
-    print(json.dumps(line), flush=True)
+    emit_line(line)
+
+
+def emit_line(line):
+    """The bench contract's single stdout line (see the __main__ block: fd 1 itself points at stderr)."""
+    fd = globals().get("_JSON_FD")
+    if fd is None:
+        emit_line(line)
+    else:
+        os.write(fd, (json.dumps(line) + "\n").encode())
 
 
 def main():
@@ -384,7 +393,7 @@ def main():
         line["cpu_baseline"] = {"value": vall, "unit": "points/s", "cores": threads, "kind": "port", "value_1core": v1,
                                 "sample": f"spatial tile of {mall} points (all cores, {dt:.1f} s) / {m1} points (1 core) of the same cloud"}
     if rank == 0:
-        print(json.dumps(line), flush=True)
+        emit_line(line)
     # orderly teardown: tensors that lived on the library's stream go first, then the stream itself
     p.synchronize()
     keep.clear()
@@ -405,4 +414,8 @@ def main():
 
 
 if __name__ == "__main__":
+    # stdout carries the ONE JSON line and nothing else: libraries that write to file descriptor 1 (NCCL prints
+    # its version banner there when NCCL_DEBUG is set on the box) are sent to stderr for the whole run
+    _JSON_FD = os.dup(1)
+    os.dup2(2, 1)
     main()
