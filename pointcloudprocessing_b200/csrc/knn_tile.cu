@@ -173,6 +173,7 @@ __global__ void __launch_bounds__(TA_WARPS * 32, CAP == 24 ? 6 : (CAP == 64 ? 3 
   const int c0 = (int)(cid - my_row * (uint32_t)g.dim[0]);
   bool pending = finite;     // not yet served by a row group
   bool ok = false;           // the lane's k nearest are in its column
+  bool far = false;          // k-NN: the k-th neighbour lies beyond the block of half-width 1 (told to the work-list kernel)
 
   // ---- a tile usually lies in ONE stencil row; where it crosses row ends, each row is a group of its own
 #pragma unroll 1
@@ -296,6 +297,7 @@ __global__ void __launch_bounds__(TA_WARPS * 32, CAP == 24 ? 6 : (CAP == 64 ? 3 
     TSTAT(5, (in_grp && bstar < 0) ? 1 : 0);                          // deferred: k-th beyond the cover radius
     TSTAT(6, (in_grp && bstar >= 0 && cum_star > CAP) ? 1 : 0);    // deferred: threshold bin too full
     bool grp_ok = in_grp && bstar >= 0 && cum_star <= CAP;
+    if (MODE == 0 && in_grp && bstar < 0 && R >= 1) far = true;  // d_k > the lane's cover radius >= one cell
     // the collect test is d2 * Sb < thr_bin: the bin bound (k-NN) or, with Sb = 1, r2 itself (radius: strict
     // d2 < r2 as FLANN's RadiusResultSet); other lanes collect nothing
     const float thr_bin = grp_ok ? (MODE == 1 ? sp.r2 : (float)(bstar + 1)) : -3.0e38f;
@@ -383,7 +385,7 @@ __global__ void __launch_bounds__(TA_WARPS * 32, CAP == 24 ? 6 : (CAP == 64 ? 3 
       uint32_t base = 0;
       if (lane == 0) base = atomicAdd(work_count, (uint32_t)__popc(dm));
       base = __shfl_sync(PCP_FULL, base, 0);
-      if (defer) work_list[base + __popc(dm & ((1u << lane) - 1u))] = (uint32_t)p;
+      if (defer) work_list[base + __popc(dm & ((1u << lane) - 1u))] = (uint32_t)p | (far ? 0x80000000u : 0u);
     }
   }
   // The sorting network and the finish stage are ~50 KB of straight-line code walked once per tile: the

@@ -288,7 +288,10 @@ __device__ __noinline__ void heavy_moment(const KArgs& a, const float4 Q, int c0
 
 // nq queries one after the other and writes their outputs.
 template <int MODE>
-__device__ __forceinline__ void search_tile(const KArgs& a, WarpSmem<MODE>* ws, const int lane, const int64_t my_pos, const int nq) {
+// `my_r0`: first stencil half-width of this lane's query (k-NN; the tile kernel flags the entries whose k-th
+// neighbour it found beyond the half-width-1 block, so their scan of that block is not repeated for nothing)
+__device__ __forceinline__ void search_tile(const KArgs& a, WarpSmem<MODE>* ws, const int lane, const int64_t my_pos, const int nq,
+                                            const int my_r0) {
   const float4* __restrict__ sorted = a.sorted;
   const GridDesc& g = a.g;
   const SearchParams& sp = a.sp;
@@ -392,7 +395,7 @@ __device__ __forceinline__ void search_tile(const KArgs& a, WarpSmem<MODE>* ws, 
           }
         }
       } else {
-        int Rp = -1, R = sp.R0;
+        int Rp = -1, R = min(__shfl_sync(PCP_FULL, my_r0, q), max_dim);
         // seed: the tightest upper bound on this query's k-th distance from the solved queries of
         // the tile; with it the first pass already filters and prunes like a radius search
         float bound = 3.4e38f;
@@ -592,7 +595,7 @@ __global__ void __launch_bounds__(WARPS * 32, 3) search_pca_kernel(KArgs a) {
   const int lane = threadIdx.x & 31;
   const int64_t pos0 = ((int64_t)blockIdx.x * WARPS + (threadIdx.x >> 5)) * 32;
   if (pos0 >= a.n) return;
-  search_tile<MODE>(a, ws, lane, pos0 + lane, (int)min((int64_t)32, a.n - pos0));
+  search_tile<MODE>(a, ws, lane, pos0 + lane, (int)min((int64_t)32, a.n - pos0), a.sp.R0);
 }
 
 // the queries a faster kernel deferred: work_list[0 .. work_count[0]) are sorted positions.  Warps draw tiles of
@@ -613,8 +616,9 @@ __global__ void __launch_bounds__(WARPS * 32, 3) search_pca_worklist_kernel(KArg
     const int64_t i0 = (int64_t)t * tile;
     if (i0 >= n_items) break;
     const int nq = (int)min((int64_t)tile, n_items - i0);
-    const int64_t my_pos = lane < nq ? (int64_t)work_list[i0 + lane] : 0;
-    search_tile<MODE>(a, ws, lane, my_pos, nq);
+    const uint32_t entry = lane < nq ? work_list[i0 + lane] : 0u;  // bit 31: "not covered by the half-width-1 block"
+    const int64_t my_pos = (int64_t)(entry & 0x7FFFFFFFu);
+    search_tile<MODE>(a, ws, lane, my_pos, nq, (MODE == 0 && (entry >> 31)) ? max(2, a.sp.R0) : a.sp.R0);
     __syncwarp();
   }
 }
