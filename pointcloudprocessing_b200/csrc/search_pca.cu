@@ -22,6 +22,7 @@
 #include <cstdlib>
 
 #include "eigen3.cuh"
+#include "knn_finish.cuh"
 #include "pcp_internal.cuh"
 #include "search_common.cuh"
 
@@ -37,6 +38,7 @@ namespace {
 constexpr int WARPS = 8;            // warps per CTA
 constexpr int RADIUS_CAP = 512;     // radius mode: neighbours kept per query in shared memory
 constexpr int REC_WORDS = 17;       // 68-byte record
+constexpr int KNN_LW = 16;          // k-NN: queries per tile of the warp-per-query kernel (columns of the list planes)
 
 // shared memory of one warp; the record staging area reuses the search buffers (disjoint phases)
 template <int MODE>
@@ -49,10 +51,15 @@ struct WarpSmem {
     } s;
     float rec[32][REC_WORDS];
   } u;
-  float mom[32][6];    // query-centred moment (normalised)
-  float momM[32][6];   // mean-centred moment (normalised), only when needed
+  float mom[MODE == 0 ? 1 : 32][6];    // radius mode: query-centred moment (normalised)
+  float momM[MODE == 0 ? 1 : 32][6];   // radius mode: mean-centred moment (normalised), only when needed
   int cnt[32];
   int gidq[32];
+  // k-NN: the ordered neighbour lists of the tile's queries, query q in column q (KNN_LW columns, 32 rows of
+  // ord and of bits(d2)), so that the moment / eigen / record stage runs once per tile with one query per
+  // lane (knn_finish) instead of once per query with the warp idling behind six summing lanes
+  uint32_t list_lo[MODE == 0 ? 32 * KNN_LW : 1];
+  uint32_t list_hi[MODE == 0 ? 32 * KNN_LW : 1];
 };
 
 // Ordered second moment about (cx,cy,cz) of the m neighbours whose keys sit in list[0..m)
@@ -453,7 +460,16 @@ __device__ __forceinline__ void search_tile(const KArgs& a, WarpSmem<MODE>* ws, 
       }
     }
 
-    // ---- ordered neighbour list -> outputs
+    if (MODE == 0) {
+      // the ordered list (one key per lane) goes to column q; everything after the search runs per tile below
+      if (lane < sp.k) {
+        ws->list_lo[lane * KNN_LW + q] = (uint32_t)st.best;
+        ws->list_hi[lane * KNN_LW + q] = (uint32_t)(st.best >> 32);
+      }
+      if (lane == 0) ws->cnt[q] = n_nb;
+      continue;
+    }
+    // ---- ordered neighbour list -> outputs (radius mode)
     const int ord_q = __float_as_int(Q.w);
     const int gid_q = a.gid_of_ord ? __ldg(&a.gid_of_ord[ord_q]) : ord_q;
     const bool valid = !overflow && (MODE == 0 ? n_nb > 0 : n_nb >= sp.min_pts);
@@ -528,6 +544,11 @@ __device__ __forceinline__ void search_tile(const KArgs& a, WarpSmem<MODE>* ws, 
   }
   __syncwarp();
 
+  if (MODE == 0) {
+    const int n_mine = my_slot >= 0 ? ws->cnt[lane] : 0;
+    knn_finish(a, ws->list_lo + lane, ws->list_hi + lane, KNN_LW, n_mine, 1, myP, my_slot, ws->u.rec, lane);
+    return;
+  }
   // ---- lane-parallel eigen + features: lane l finishes query l of the tile
   if (my_slot >= 0) {
     const int c = ws->cnt[lane];
@@ -595,7 +616,15 @@ __global__ void __launch_bounds__(WARPS * 32, 3) search_pca_kernel(KArgs a) {
   const int lane = threadIdx.x & 31;
   const int64_t pos0 = ((int64_t)blockIdx.x * WARPS + (threadIdx.x >> 5)) * 32;
   if (pos0 >= a.n) return;
-  search_tile<MODE>(a, ws, lane, pos0 + lane, (int)min((int64_t)32, a.n - pos0), a.sp.R0);
+  if (MODE == 0) {  // k-NN tiles hold KNN_LW queries
+    for (int h = 0; h < 32; h += KNN_LW) {
+      if (pos0 + h >= a.n) break;
+      search_tile<MODE>(a, ws, lane, pos0 + h + lane, (int)min((int64_t)KNN_LW, a.n - pos0 - h), a.sp.R0);
+      __syncwarp();
+    }
+  } else {
+    search_tile<MODE>(a, ws, lane, pos0 + lane, (int)min((int64_t)32, a.n - pos0), a.sp.R0);
+  }
 }
 
 // the queries a faster kernel deferred: work_list[0 .. work_count[0]) are sorted positions.  Warps draw tiles of
@@ -683,6 +712,7 @@ int pcp_search_launch(pcp_ctx* ctx, const SearchParams& sp) {
     int wl_tile = 16;
     if (const char* e = getenv("PCP_WL_BLOCKS")) wl_blocks = atoi(e) > 0 ? atoi(e) : wl_blocks;
     if (const char* e = getenv("PCP_WL_TILE")) wl_tile = atoi(e) >= 1 && atoi(e) <= 32 ? atoi(e) : wl_tile;
+    if (sp.mode == 0 && wl_tile > KNN_LW) wl_tile = KNN_LW;
     if (sp.mode == 0) {
       size_t smem = sizeof(WarpSmem<0>) * WARPS;
       PCP_CUDA(cudaFuncSetAttribute(search_pca_worklist_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
