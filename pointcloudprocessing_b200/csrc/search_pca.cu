@@ -349,12 +349,15 @@ __device__ __forceinline__ void search_tile(const KArgs& a, WarpSmem<MODE>* ws, 
         // inside the radius and are ordered by index).
         int R = sp.R0;
         float lo2 = 0.f, hi2 = 0.f;
+        const float diag2 = g.cell * g.cell * 1.01f *
+                            ((float)g.dim[0] * (float)g.dim[0] + (float)g.dim[1] * (float)g.dim[1] + (float)g.dim[2] * (float)g.dim[2]) + 1e-30f;
         overflow = true;
 #pragma unroll 1
         for (int it = 0; it < 96; ++it) {
           const bool whole = (c0 - R <= 0) && (c0 + R >= g.dim[0] - 1) && (c1 - R <= 0) && (c1 + R >= g.dim[1] - 1) &&
                              (c2 - R <= 0) && (c2 + R >= g.dim[2] - 1);
-          const float cov = whole ? 3.0e38f : cover2_of(R, g.cell);
+          // the whole grid in reach: every point lies within the box diagonal (a finite radius the bisection can halve)
+          const float cov = whole ? diag2 : cover2_of(R, g.cell);
           const bool bisect = hi2 > 0.f && hi2 <= cov;
           const float r2q = bisect ? 0.5f * lo2 + 0.5f * hi2 : cov;
           if (bisect && !(r2q > lo2 && r2q < hi2)) break;  // more than RADIUS_CAP points at one distance: give up

@@ -135,3 +135,16 @@ def test_knn_wide_k_pca_records(pcp, oracle):
     if kth is not None:
         _, rd2 = oracle.KdTree(pts).knn_all(60)
         np.testing.assert_array_equal(kth.view(np.uint32), rd2[:, 59].view(np.uint32))
+
+
+@pytest.mark.parametrize("cell", [0.0, 10.0, 40.0])
+def test_knn_wide_k_whole_grid_in_reach(pcp, oracle, cell):
+    """A small dense cloud: the stencil soon spans the whole grid with far more than 512 points inside, so the
+    radius is bisected down from the box diagonal."""
+    pts = synth.urban(1, 6000, extent=20.0)
+    pcp.set_cloud(pts)
+    pcp.build_grid(cell, 50)
+    idx, d2 = pcp.knn_neighbors(50)
+    ridx, rd2 = oracle.KdTree(pts).knn_all(50)
+    np.testing.assert_array_equal(idx, ridx)
+    np.testing.assert_array_equal(d2.view(np.uint32), rd2.view(np.uint32))
