@@ -40,7 +40,10 @@ __device__ unsigned long long g_tile_stats[16];
 
 namespace {
 
-constexpr int TA_WARPS = 4;        // warps per CTA
+#ifndef PCP_TA_WARPS
+#define PCP_TA_WARPS 4
+#endif
+constexpr int TA_WARPS = PCP_TA_WARPS;  // warps per CTA (2 / 4 / 8 measured: see DESIGN §6)
 constexpr int TA_CH = 128;         // staged candidates per chunk
 // CAP (template parameter: 24 or 32 for k-NN, 32 or 64 for radius search) = candidates a lane can hold = width of the sorting network;
 // the histogram has BINS = 2*CAP - 1 linear d2 bins inside the cover radius + 1 overflow bin, so that it
@@ -149,7 +152,7 @@ __device__ __forceinline__ uint32_t tile_setup(const KArgs& a, TaSmem<CAP>& sm, 
 // MODE 0: k nearest (two passes: histogram select, then collect).  MODE 1: radius search — membership is
 // d2 < r2 itself, so there is no selection pass; a lane is served when its neighbourhood fits its column.
 template <int CAP, int MODE>
-__global__ void __launch_bounds__(TA_WARPS * 32, CAP == 24 ? 6 : (CAP == 64 ? 3 : 5)) knn_tile_kernel(KArgs a, int R0, float grow, int max_groups, uint32_t* __restrict__ work_count,
+__global__ void __launch_bounds__(TA_WARPS * 32, (CAP == 24 ? 24 : (CAP == 64 ? 12 : 20)) / TA_WARPS) knn_tile_kernel(KArgs a, int R0, float grow, int max_groups, uint32_t* __restrict__ work_count,
                                                                  uint32_t* __restrict__ work_list) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   constexpr int BINS = 2 * CAP - 1;
