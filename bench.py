@@ -37,7 +37,7 @@ def peaks():
 def ncu_traffic(n: int):
     """DRAM bytes per launch of the search stage (dram__bytes_read.sum + dram__bytes_write.sum of its two
     kernels) from the committed `ncu --set full` capture of this workload; null for any other size."""
-    path = os.path.join(ROOT, "profiles", "r01d_knn_tile_and_worklist_ncu_summary.txt")
+    path = os.path.join(ROOT, "profiles", "r01f_knn_tile_and_worklist_ncu_summary.txt")
     if n != 1_000_000 or not os.path.exists(path):
         return None
     total = 0.0
