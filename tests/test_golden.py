@@ -79,3 +79,74 @@ def test_decode_oracle_is_pinned_to_the_reference_binary(oracle, name):
         np.testing.assert_array_equal(got[key][:n].view(np.uint64), g[key].view(np.uint64), err_msg=key)
     for key in ("intensity", "laser_id", "azimuth", "ms"):
         np.testing.assert_array_equal(got[key][:n], g[key], err_msg=key)
+
+
+# ---- the rows added last (tests/golden/golden_consumers.npz, made by tests/golden/make_golden_consumers.py) ----
+GC = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "golden_consumers.npz"))
+
+
+def _bits(a):
+    return np.ascontiguousarray(a).view(np.uint32)
+
+
+def test_oracle_reproduces_consumer_golden(oracle):
+    fr = GC["odom_in"]
+    cnt = oracle.KdTree(fr).radius_counts(3.0)
+    np.testing.assert_array_equal(np.minimum(cnt, 6), GC["odom_counts_capped"])
+    rng, pid, pti, stats, mm = oracle.odom_range_image(fr, cnt)
+    np.testing.assert_array_equal(_bits(rng), _bits(GC["odom_range"]))
+    np.testing.assert_array_equal(pti, GC["odom_index"])
+    np.testing.assert_array_equal(stats, GC["odom_stats"])
+    np.testing.assert_array_equal(mm, GC["odom_minmax"])
+    sm, ty = oracle.odom_smoothness(rng)
+    np.testing.assert_array_equal(_bits(sm), _bits(GC["odom_smooth"]))
+    np.testing.assert_array_equal(ty, GC["odom_type"])
+    urban = GC["db_in"]
+    flat = urban.copy()
+    flat[:, 2] = 0.0
+    lab, nc = oracle.dbscan(flat, 0.3, 8)
+    assert nc == int(GC["db_n"])
+    np.testing.assert_array_equal(lab, GC["db_labels"])
+    nxt, _, mcnt = oracle.mean_shift_step(urban, urban, 2.0, 15)
+    np.testing.assert_array_equal(_bits(nxt), _bits(GC["ms_next"]))
+    np.testing.assert_array_equal(mcnt, GC["ms_counts"])
+    np.testing.assert_array_equal(_bits(oracle.txt2pc(GC["txt_in"].tobytes())), _bits(GC["txt_points"]))
+
+
+@pytest.mark.gpu
+def test_cuda_matches_consumer_golden(pcp):
+    fr = GC["odom_in"]
+    pcp.set_cloud(fr)
+    pcp.build_grid(3.0, 0)
+    np.testing.assert_array_equal(pcp.radius_count(3.0, 6), GC["odom_counts_capped"])
+    od = pcp.odom_range_image()
+    np.testing.assert_array_equal(_bits(od["range"][0]), _bits(GC["odom_range"]))
+    np.testing.assert_array_equal(_bits(od["ptid"][0]), _bits(GC["odom_ptid"]))
+    np.testing.assert_array_equal(od["pt_index"][0], GC["odom_index"])
+    np.testing.assert_array_equal(od["stats"][0], GC["odom_stats"])
+    np.testing.assert_array_equal(od["minmax"][0], GC["odom_minmax"])
+    sm, ty = pcp.odom_smoothness(n_frames=1)
+    np.testing.assert_array_equal(_bits(sm[0]), _bits(GC["odom_smooth"]))
+    np.testing.assert_array_equal(ty[0], GC["odom_type"])
+    urban = GC["db_in"]
+    flat = urban.copy()
+    flat[:, 2] = 0.0
+    pcp.set_cloud(flat)
+    pcp.build_grid(0.3, 0)
+    lab, nc = pcp.dbscan(0.3, 8)
+    assert nc == int(GC["db_n"])
+    np.testing.assert_array_equal(lab, GC["db_labels"])
+    pcp.set_cloud(urban)
+    cen, lo, hi, cc = pcp.cluster_boxes(lab, nc)
+    np.testing.assert_array_equal(cc, GC["db_count"])
+    np.testing.assert_array_equal(_bits(lo), _bits(GC["db_min"]))
+    np.testing.assert_array_equal(_bits(hi), _bits(GC["db_max"]))
+    assert np.abs(cen - GC["db_centroid"]).max() <= 2e-4
+    pcp.build_grid(2.0, 0)
+    got, cnt = pcp.mean_shift(2.0, 15, 1)
+    np.testing.assert_array_equal(cnt, GC["ms_counts"])
+    assert np.abs(got[:, :3] - GC["ms_next"][:, :3]).max() <= 2e-5
+    got2, cnt2 = pcp.mean_shift(2.0, 15, 1, start=GC["ms_next"])
+    np.testing.assert_array_equal(cnt2, GC["ms_counts2"])
+    assert np.abs(got2[:, :3] - GC["ms_next2"][:, :3]).max() <= 2e-5
+    np.testing.assert_array_equal(_bits(pcp.set_cloud_txt(GC["txt_in"].tobytes())), _bits(GC["txt_points"]))
