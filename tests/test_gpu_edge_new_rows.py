@@ -69,3 +69,37 @@ def test_txt_odd_inputs(pcp, oracle):
         got = pcp.set_cloud_txt(text)
         assert got.shape == ref.shape, text[:40]
         np.testing.assert_array_equal(got.view(np.uint32), ref.view(np.uint32), err_msg=repr(text[:60]))
+
+
+def test_error_behaviour_of_new_entry_points():
+    """Status codes instead of crashes: no cloud / no grid / bad arguments / sharded or batched clouds where undefined."""
+    import ctypes as C
+
+    from pointcloudprocessing_b200 import capi
+
+    with capi.Pcp(0) as p:
+        lib, h = p.lib, p.h
+        buf = np.zeros(64, np.int32)
+        nc = C.c_int32()
+        prm = capi.odom_params_default()
+        img = np.zeros((16, 900), np.float32)
+        assert lib.pcp_radius_count(h, 1.0, 0, buf.ctypes.data, 0) == -4          # PCP_ERR_NO_CLOUD
+        assert lib.pcp_dbscan(h, 1.0, 5, buf.ctypes.data, C.addressof(nc), 0) == -4
+        pts = synth.urban(2, 64, extent=5.0)
+        p.set_cloud(pts)
+        assert lib.pcp_radius_count(h, 1.0, 0, buf.ctypes.data, 0) == -5          # PCP_ERR_NO_GRID
+        assert lib.pcp_mean_shift(h, 1.0, 5, 1, None, 0, img.ctypes.data, None, 0) == -5
+        assert lib.pcp_odom_range_image(h, C.byref(prm), None, 1, img.ctypes.data, None, None, None, None, 0) == -5
+        p.build_grid(1.0, 0)
+        assert lib.pcp_radius_count(h, -1.0, 0, buf.ctypes.data, 0) == -1         # PCP_ERR_INVALID_ARG
+        assert lib.pcp_dbscan(h, 1.0, 0, buf.ctypes.data, C.addressof(nc), 0) == -1
+        assert lib.pcp_odom_range_image(h, C.byref(prm), None, 2, img.ctypes.data, None, None, None, None, 0) == -1  # offsets required
+        bad = capi.odom_params_default()
+        bad.n_blocks = 0
+        assert lib.pcp_odom_smoothness(h, C.byref(bad), img.ctypes.data, 0, 1, None, img.ctypes.data, 0) == -1
+        assert lib.pcp_odom_smoothness(h, C.byref(prm), None, 0, 3, None, img.ctypes.data, 0) == -1   # no images of 3 frames here
+        assert lib.pcp_knn_pca(h, 65, 0, buf.ctypes.data, None, 0) == -7          # PCP_ERR_K_UNSUPPORTED
+        n = C.c_int64(-1)
+        assert lib.pcp_set_cloud_txt(h, None, 0, 0, C.addressof(n), None, 0, 0) == 0 and n.value == 0
+        assert lib.pcp_set_cloud_txt(h, None, 5, 0, C.addressof(n), None, 0, 0) == -1
+        assert b"pcp_set_cloud_txt" in lib.pcp_last_error(h)
