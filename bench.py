@@ -100,11 +100,16 @@ class ClockSampler:
         return {"sm_mhz": med, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons)}
 
 
-def make_cloud(points: int, rank: int):
+def make_cloud(points: int, rank: int, per_rank_seed: bool = False):
     from pointcloudprocessing_b200 import synth
 
-    # configs[2] shape: 1 M-point urban scan over 200 m x 200 m, random point order (worst case)
-    return synth.urban(3 + 1000 * rank, points, extent=200.0 * (points / 1e6) ** 0.5, order="random")
+    # configs[2] shape: 1 M-point urban scan over 200 m x 200 m, random point order (worst case).
+    # Weak scaling (N > 1): every rank owns a translated copy of the SAME tile, so the work per GPU is identical by
+    # construction and the per-N values measure the sharding, not the luck of a seed (tiles of different seeds
+    # differ by up to 17 % in search time on one GPU: 1.43 vs 1.71 ms, tools/shard_step_breakdown.py);
+    # --rank-clouds seeded gives every rank its own tile as before.
+    seed = 3 + 1000 * rank if per_rank_seed else 3
+    return synth.urban(seed, points, extent=200.0 * (points / 1e6) ** 0.5, order="random")
 
 
 def cpu_tile(pts: np.ndarray, target: int) -> np.ndarray:
@@ -180,6 +185,8 @@ def main():
     ap.add_argument("--halo-impl", default="peer", choices=["peer", "nccl"],
                     help="N > 1: halo strips by peer stores + flags (pcp_halo_push / pcp_halo_wait) or by NCCL send/recv")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--rank-clouds", default="tile", choices=["tile", "seeded"],
+                    help="N > 1: every rank's slab is a translated copy of the same 1 M-point tile (identical work per GPU), or a tile of its own seed")
     ap.add_argument("--e2e-contexts", type=int, default=3, help="C-ABI contexts in flight for the end-to-end figure (N = 1)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
@@ -200,7 +207,7 @@ def main():
     from pointcloudprocessing_b200 import sharding
 
     n, k = args.points, args.k
-    pts = make_cloud(n, rank)
+    pts = make_cloud(n, rank, args.rank_clouds == "seeded")
     L = 200.0 * (n / 1e6) ** 0.5
     halo = args.halo
     if world > 1:
@@ -366,7 +373,9 @@ def main():
                    "order": "random", "l2": "flushed between steps (256 MiB fill, untimed)",
                    "step": "bbox+keys+radix sort+cell table+fused search/moment/eigen, 68 B records",
                    "sharding": "single cloud" if world == 1 else
-                   f"x-slabs of one {world}x{L:.0f} m x {L:.0f} m scan, halo {halo} m exchanged every step (" +
+                   f"x-slabs of one {world}x{L:.0f} m x {L:.0f} m scan (" +
+                   ("each slab a translated copy of the N = 1 tile: identical work per GPU" if args.rank_clouds == "tile" else "one tile per rank, seeds 3 + 1000 rank") +
+                   f"), halo {halo} m exchanged every step (" +
                    ("pcp_halo_push: the classification kernel stores the strips straight into the neighbours' halo regions over NVLink and raises their flags; pcp_halo_wait on the receiver; no NCCL, no host sync"
                     if args.halo_impl == "peer" else
                     "pcp_halo_pack kernel + grouped NCCL send/recv into fixed-capacity buffers, no host sync in the exchange") +
