@@ -12,6 +12,7 @@ split into contiguous blocks (`sharding.frame_shard`).  No torch here: numpy + c
 """
 from __future__ import annotations
 
+import ctypes as C
 import threading
 from typing import List, Optional, Sequence
 
@@ -120,9 +121,12 @@ class FrameBatcher:
     to `FramePipeline` (tests/test_gpu_frames.py)."""
 
     def __init__(self, device: int = 0, n_ctx: int = 2, batch: int = 64, max_points: int = 32768,
-                 calib: Optional[capi.RingCalib] = None, segment: bool = False):
+                 calib: Optional[capi.RingCalib] = None, segment: bool = False, odom: bool = False):
         self.calib = calib or capi.ring_calib_default()
         self.segment = segment  # also run groundRemoval + cloudSegmentation (RingProjector::fullSegmentation)
+        self.odom = odom        # also lidarOdometryClass::getRangeAndptIdImage + calculateSmoothness per frame
+        self.odom_prm = capi.odom_params_default()
+        self.odom_cells = self.odom_prm.n_rows * self.odom_prm.n_cols
         self.seg_prm = capi.ring_seg_params_default()
         self.cells = self.calib.n_scan * self.calib.horizon_scan
         self.batch, self.max_points = batch, max_points
@@ -138,6 +142,11 @@ class FrameBatcher:
                 "index": capi.PinnedArray((batch * self.cells,), np.int32),
                 "long": capi.PinnedArray((batch,), np.int32),
             })
+            if odom:
+                self.slots[-1].update({
+                    "odom_range": capi.PinnedArray((batch * self.odom_cells,), np.float32),
+                    "odom_type": capi.PinnedArray((batch * self.odom_cells,), np.float32),
+                })
             if segment:
                 self.slots[-1].update({
                     "ground": capi.PinnedArray((batch * self.cells,), np.int8),
@@ -181,6 +190,11 @@ class FrameBatcher:
             c.ring_project_host_ptr(self.calib, s["range"].ptr, s["index"].ptr, s["long"].ptr, frame_offsets=offs)
         c.build_grid(cell, k)
         c.knn_pca(k, capi.CENTER_QUERY, out_host_ptr=s["feat"].ptr)
+        if self.odom:
+            # on the k-NN grid of the batch: capped radius count (3 m, 6 hits), images, smoothness from the device images
+            c._ck(c.lib.pcp_odom_range_image(c.h, C.byref(self.odom_prm), offs.ctypes.data, nb, s["odom_range"].ptr, None, None, None,
+                                             None, 0))
+            c._ck(c.lib.pcp_odom_smoothness(c.h, C.byref(self.odom_prm), None, 1, nb, None, s["odom_type"].ptr, 0))
         c.synchronize()
         if not keep:
             return
@@ -194,6 +208,10 @@ class FrameBatcher:
                 "index": s["index"].array[j * self.cells:(j + 1) * self.cells].reshape(ns, hs).copy(),
                 "long_range": int(s["long"].array[j]),
             }
+            if self.odom:
+                oc, shp = self.odom_cells, (self.odom_prm.n_rows, self.odom_prm.n_cols)
+                out[f0 + j]["odom_range"] = s["odom_range"].array[j * oc:(j + 1) * oc].reshape(shp).copy()
+                out[f0 + j]["odom_type"] = s["odom_type"].array[j * oc:(j + 1) * oc].reshape(shp).copy()
             if ring and self.segment:
                 na = int(s["above_count"].array[j])
                 out[f0 + j].update({

@@ -119,3 +119,15 @@ def test_frame_batcher_full_segmentation(oracle):
         assert np.array_equal(got[f]["ground"], g) and np.array_equal(got[f]["label"], lab)
         assert np.array_equal(got[f]["above_idx"], above) and got[f]["n_labels"] == nl
     check_features(got[4]["features"], oracle.knn_pca_cloud(fr[4], 10, 0), None, "frame 4")
+
+
+def test_frame_batcher_odometry_images(oracle):
+    """FrameBatcher(odom=True): per frame the lidarOdometry range image and point types of a run on that frame alone."""
+    from pointcloudprocessing_b200 import frames as F
+    fr = [synth.vlp16_frame(400 + f, pose_jitter=0.5) for f in range(5)]
+    with F.FrameBatcher(0, n_ctx=2, batch=3, odom=True) as bat:
+        res = bat.run(fr, k=10)
+    for f, r in zip(fr, res):
+        rng = oracle.odom_range_image(f, oracle.KdTree(f).radius_counts(3.0))[0]
+        np.testing.assert_array_equal(r["odom_range"].view(np.uint32), rng.view(np.uint32))
+        np.testing.assert_array_equal(r["odom_type"], oracle.odom_smoothness(rng)[1])
