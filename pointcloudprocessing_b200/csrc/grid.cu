@@ -239,6 +239,10 @@ int pcp_grid_build_impl(pcp_ctx* ctx, float cell, int k_hint) {
     // uncovered queries beat the larger candidate set) so a 3×3×3 stencil usually covers the k-NN ball.
     double area = std::max(ext[order[0]], 1e-3) * std::max(ext[order[1]], 1e-3);
     cell0 = (float)std::sqrt(1.9 * kk * area / ((double)n / (double)n_seg));  // per frame: the frames share the box
+    // k close to the 32-entry lane capacity: the threshold bin overflows the lane's column more and more often as
+    // cells grow (measured cliff, 1 M-point urban cloud: k = 32 2.94 ms at this guess vs 2.30 ms at 0.85 x, k = 30
+    // 2.31 vs ~2.1 ms; k <= 25 is best at the plain guess), so the guess is taken 15 % smaller there
+    if (kk > 26) cell0 *= 0.85f;
     if (!(cell0 > 0.f)) cell0 = 1.f;
     learned = ctx->scale_n > 0 && ctx->scale_seg == n_seg && ctx->scale_k == kk && (double)n >= 0.8 * (double)ctx->scale_n &&
               (double)n <= 1.25 * (double)ctx->scale_n;
