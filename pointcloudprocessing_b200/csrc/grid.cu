@@ -282,12 +282,15 @@ int pcp_grid_build_impl(pcp_ctx* ctx, float cell, int k_hint) {
     PCP_LAUNCH_CHECK("invert_kernel");
   }
 
+  // diagnostic knob: lower the grid origin by a fraction of a cell on every axis
+  double origin_shift = 0.0;
+  if (const char* e = getenv("PCP_GRID_SHIFT")) origin_shift = std::min(std::max(atof(e), 0.0), 0.999);
   for (int attempt = 0;; ++attempt) {
   const double max_cells = 1.0e9;
   for (;;) {
     double total = 1.0;
     for (int a = 0; a < 3; ++a) {
-      double cnt = std::floor(ext[g.ax[a]] / (double)cell) + 1.0;
+      double cnt = std::floor(ext[g.ax[a]] / (double)cell + origin_shift) + 1.0;
       if (cnt > 2.0e9) cnt = 2.0e9;
       g.dim[a] = (int)cnt;
       total *= cnt;
@@ -303,7 +306,7 @@ int pcp_grid_build_impl(pcp_ctx* ctx, float cell, int k_hint) {
   }
   g.cell = cell;
   g.inv_cell = 1.0 / (double)cell;
-  for (int d = 0; d < 3; ++d) g.origin[d] = lo[d];
+  for (int d = 0; d < 3; ++d) g.origin[d] = lo[d] - origin_shift * (double)cell;
   ctx->grid = g;
 
   // ---- keys
