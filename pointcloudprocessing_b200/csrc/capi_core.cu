@@ -38,6 +38,7 @@ void pcp_tic(pcp_ctx* ctx, int stage) { cudaEventRecord(ctx->ev[2 * stage], ctx-
 void pcp_toc(pcp_ctx* ctx, int stage) {
   cudaEventRecord(ctx->ev[2 * stage + 1], ctx->stream);
   ctx->ev_used[stage] = true;
+  if (stage == PCP_T_SEARCH_PCA) ctx->searches++;
 }
 void pcp_collect_timings(pcp_ctx* ctx) {
   for (int s = 0; s < PCP_T_COUNT; ++s) {

@@ -69,6 +69,13 @@ struct pcp_ctx {
   cudaEvent_t occ_ev = nullptr;         // recorded behind an asynchronous copy into h_occ
   bool occ_pending = false;
   unsigned occ_tick = 0;
+  // learned alignment of the grid along its shortest axis (grid.cu): the first builds of a stream of similar clouds
+  // try four origin offsets, the search time of each (events of the previous cloud) decides which one stays
+  int tune_phase = 0;                   // trials handed out so far (5 = settled)
+  bool tune_done = false;               // the last trial's time has been read
+  int tune_idx = -1;                    // candidate the last build used (-1: none)
+  float tune_ms[4] = {0.f, 0.f, 0.f, 0.f};
+  int64_t searches = 0, tune_seen = -1; // search launches so far / at the last tuned build
   double cell_scale = 1.0;              // learned correction of the first-guess cell for clouds like the last one
   int64_t scale_n = 0;
   int scale_seg = 0, scale_k = 0;

@@ -9,8 +9,12 @@ pts = synth.urban(3, 1_000_000, extent=200.0)
 p = capi.Pcp(0)
 p.set_cloud(pts)
 ref = None
-for cell in cells:
-    row = []
+axes = [int(a) for a in sys.argv[3].split(",")] if len(sys.argv) > 3 else [-1]
+for cell in [c for c in cells for _ in axes]:
+    axis = axes[0]
+    axes = axes[1:] + axes[:1]
+    os.environ["PCP_GRID_SHIFT_AXIS"] = str(axis)
+    row = [f"axis {axis}"]
     for sh in (0.0, 0.2, 0.4, 0.6, 0.8):
         os.environ["PCP_GRID_SHIFT"] = str(sh)
         ts = []
