@@ -34,18 +34,59 @@ def peaks():
     return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
 
 
-def ncu_traffic(n: int):
-    """DRAM bytes per launch of the search stage (dram__bytes_read.sum + dram__bytes_write.sum of its two
-    kernels) from the committed `ncu --set full` capture of this workload; null for any other size."""
-    path = os.path.join(ROOT, "profiles", "r01f_knn_tile_and_worklist_ncu_summary.txt")
+def host_threads() -> int:
+    """Host cores this process may use.  torchrun exports OMP_NUM_THREADS=1; the CPU arm passes this count to the
+    oracle explicitly (num_threads clause), so the environment variable does not shrink it."""
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except AttributeError:
+        return max(1, os.cpu_count() or 1)
+
+
+def source_id() -> str:
+    """Hash of the CUDA sources libpcp.so is built from: names the ncu capture the traffic figure belongs to."""
+    import hashlib
+
+    h = hashlib.sha1()
+    csrc = os.path.join(ROOT, "pointcloudprocessing_b200", "csrc")
+    for name in sorted(os.listdir(csrc)):
+        if name.endswith((".cu", ".cuh")) or name == "Makefile":
+            with open(os.path.join(csrc, name), "rb") as f:
+                h.update(name.encode() + b"\0" + f.read())
+    return h.hexdigest()[:12]
+
+
+def workload_config(n: int, k: int, world: int, rank_clouds: str = "tile", halo: float = 6.0, halo_impl: str = "peer") -> dict:
+    """`config` of the JSON line; both arms (ours / --impl reference) emit the same keys and values."""
+    L = 200.0 * (n / 1e6) ** 0.5
+    return {"workload": f"urban_{n}pts_knn_k{k}_pca (configs[2] shape, metric's k)", "points_per_gpu": n, "k": k,
+            "order": "random", "l2": "flushed between steps (256 MiB fill, untimed)",
+            "step": "bbox+keys+radix sort+cell table+fused search/moment/eigen, 68 B records",
+            "sharding": "single cloud" if world == 1 else
+            f"x-slabs of one {world}x{L:.0f} m x {L:.0f} m scan (" +
+            ("each slab a translated copy of the N = 1 tile: identical work per GPU" if rank_clouds == "tile" else "one tile per rank, seeds 3 + 1000 rank") +
+            f"), halo {halo} m exchanged every step (" +
+            ("pcp_halo_push: the classification kernel stores the strips straight into the neighbours' halo regions over NVLink and raises their flags; pcp_halo_wait on the receiver; no NCCL, no host sync"
+             if halo_impl == "peer" else
+             "pcp_halo_pack kernel + grouped NCCL send/recv into fixed-capacity buffers, no host sync in the exchange") +
+            "), global-index tie-break"}
+
+
+def ncu_capture(n: int):
+    """(DRAM bytes, warp instructions) per launch of the search stage from the `ncu --set full` capture of THIS
+    build — profiles/r02_search_ncu_<source_id()>.txt, written by tools/ncu_summary.py from a capture of this very
+    command — or (None, None): a capture of other sources says nothing about these kernels."""
+    path = os.path.join(ROOT, "profiles", f"r02_search_ncu_{source_id()}.txt")
     if n != 1_000_000 or not os.path.exists(path):
-        return None
-    total = 0.0
+        return None, None
+    dram, inst = 0.0, 0.0
     with open(path) as f:
         for line in f:
             if line.startswith("dram__bytes_read.sum [Mbyte]") or line.startswith("dram__bytes_write.sum [Mbyte]"):
-                total += float(line.split("=")[1]) * 1e6
-    return total or None
+                dram += float(line.split("=")[1]) * 1e6
+            elif line.startswith("smsp__inst_executed.sum [inst]"):
+                inst += float(line.split("=")[1])
+    return (dram or None), (inst or None)
 
 
 class ClockSampler:
@@ -139,7 +180,7 @@ def reference_arm(args, rank, world):
     from oracle import oracle_py as O
 
     pts = make_cloud(args.points, 0)
-    threads = O.num_threads()
+    threads = host_threads()  # not O.num_threads(): torchrun sets OMP_NUM_THREADS=1
     target = args.cpu_sample
     for _ in range(min(args.warmup, 1)):
         run_cpu(pts, args.k, threads, target // 4)
@@ -154,7 +195,7 @@ def reference_arm(args, rank, world):
         "impl": "reference", "metric": "kNN+PCA feature points/sec (k=%d)" % args.k, "value": value, "unit": "points/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total / args.steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"urban_{args.points}pts_knn_k{args.k}_pca (configs[2] shape, metric's k)"},
+        "config": workload_config(args.points, args.k, world, args.rank_clouds, args.halo, args.halo_impl),
         "cpu_baseline": {"value": value, "unit": "points/s", "cores": threads, "kind": "port",
                          "sample": f"spatial tile of ~{target} points of the same cloud per step, OpenMP over points"},
         "e2e": {"value": value, "unit": "points/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -162,13 +203,71 @@ def reference_arm(args, rank, world):
     emit_line(line)
 
 
+def rank_cloud(n: int, rank: int, world: int, seeded: bool) -> np.ndarray:
+    """The slab rank `rank` owns: the N = 1 cloud, shifted to x in [rank L, (rank + 1) L) when world > 1."""
+    pts = make_cloud(n, rank, seeded)
+    if world > 1:
+        L = 200.0 * (n / 1e6) ** 0.5
+        pts[:, 0] = np.clip(pts[:, 0], 0.0, L - 1e-3) + np.float32(rank * L)
+    return pts
+
+
+def check_parity(args, p, stream, pts, d_out, n, k, rank, world, local, step_device):
+    """Compares the records of one more (untimed) step with the checker; raises SystemExit on any difference.
+    N = 1: neighbour indices and d2 of EVERY query bit-exact against the CPU oracle (pcp_knn_neighbors), the 68-byte
+    records against the oracle's within tests/parity.py's tolerances.  N > 1: this rank's records bitwise equal to the
+    records of the same points in an unsharded run of the union cloud on this GPU (global-index tie-break)."""
+    import torch
+
+    from pointcloudprocessing_b200 import capi
+
+    step_device()
+    p.synchronize()
+    got = d_out.cpu().numpy().view(capi.FEATURE_DTYPE)
+    if world > 1:
+        union = np.concatenate([rank_cloud(n, r, world, args.rank_clouds == "seeded") for r in range(world)])
+        d_union = torch.from_numpy(union).cuda(local)
+        d_uout = torch.empty(union.shape[0] * 68, dtype=torch.uint8, device=local)
+        with capi.Pcp(local) as q:
+            q.set_cloud_device(d_union.data_ptr(), union.shape[0])
+            q.build_grid(args.cell, k)
+            q.knn_pca(k, capi.CENTER_QUERY, out_device=d_uout.data_ptr())
+            q.synchronize()
+        mine = d_uout[rank * n * 68:(rank + 1) * n * 68]
+        if not torch.equal(mine, d_out):
+            diff = int((mine.view(-1, 68) != d_out.view(-1, 68)).any(1).sum().item())
+            raise SystemExit(f"rank {rank}: {diff} sharded records differ from the unsharded run of the union cloud")
+        return n, f"every rank's {n} records bitwise equal to an unsharded run of the {world * n}-point union cloud on its own GPU"
+    from oracle import oracle_py as O
+
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from parity import check_features
+
+    threads = host_threads()
+    idx, d2 = p.knn_neighbors(k)
+    ridx, rd2 = O.KdTree(pts).knn_all(k, threads)
+    if not np.array_equal(idx, ridx):
+        raise SystemExit(f"parity: neighbour indices differ from the oracle on {int((idx != ridx).any(1).sum())} of {n} queries")
+    if not np.array_equal(d2.view(np.uint32), rd2.view(np.uint32)):
+        raise SystemExit("parity: neighbour distances differ from the oracle (bit compare)")
+    ref = O.knn_pca_cloud(pts, k, 0, nthreads=threads)
+    try:
+        check_features(got, ref, None, "bench records")
+    except AssertionError as e:
+        raise SystemExit(f"parity: {e}")
+    return n, (f"all {n} queries: k-NN indices and d2 bit-exact vs the CPU oracle (pcp_knn_neighbors), the timed step's records within "
+               "tests/parity.py's tolerances (ptID/ptNum exact, eigenvalues 1e-4, eigenvectors up to sign 1e-4)")
+
+
 def emit_line(line):
     """The bench contract's single stdout line (see the __main__ block: fd 1 itself points at stderr)."""
     fd = globals().get("_JSON_FD")
-    if fd is None:
-        emit_line(line)
+    data = (json.dumps(line) + "\n").encode()
+    if fd is None:  # imported as a module: plain stdout
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
     else:
-        os.write(fd, (json.dumps(line) + "\n").encode())
+        os.write(fd, data)
 
 
 def main():
@@ -185,6 +284,7 @@ def main():
     ap.add_argument("--halo-impl", default="peer", choices=["peer", "nccl"],
                     help="N > 1: halo strips by peer stores + flags (pcp_halo_push / pcp_halo_wait) or by NCCL send/recv")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-parity", action="store_true", help="skip the oracle / unsharded-run comparison of the timed records")
     ap.add_argument("--rank-clouds", default="tile", choices=["tile", "seeded"],
                     help="N > 1: every rank's slab is a translated copy of the same 1 M-point tile (identical work per GPU), or a tile of its own seed")
     ap.add_argument("--e2e-contexts", type=int, default=3, help="C-ABI contexts in flight for the end-to-end figure (N = 1)")
@@ -207,13 +307,11 @@ def main():
     from pointcloudprocessing_b200 import sharding
 
     n, k = args.points, args.k
-    pts = make_cloud(n, rank, args.rank_clouds == "seeded")
+    # weak scaling: rank r owns the slab x in [r*L, (r+1)*L) of a world*L x L scan; neighbours
+    # exchange the strips within `halo` of the shared faces every step (peer stores, or NCCL send/recv)
+    pts = rank_cloud(n, rank, world, args.rank_clouds == "seeded")
     L = 200.0 * (n / 1e6) ** 0.5
     halo = args.halo
-    if world > 1:
-        # weak scaling: rank r owns the slab x in [r*L, (r+1)*L) of a world*L x L scan; neighbours
-        # exchange the strips within `halo` of the shared faces every step (peer stores, or NCCL send/recv)
-        pts[:, 0] = np.clip(pts[:, 0], 0.0, L - 1e-3) + np.float32(rank * L)
     lo, hi = rank * L, (rank + 1) * L
     p = capi.Pcp(local)  # raises if libpcp.so / the GPU is missing: no fallback
     stream = torch.cuda.ExternalStream(p.stream, device=local)
@@ -356,7 +454,19 @@ def main():
             c.close()
         barrier()
 
-    t = torch.tensor([dev_ms, e2e_s * 1e3, kern_ms], dtype=torch.float64, device=local)
+    # ---- parity of the records that were just timed (outside every timed region)
+    parity_checked, parity_note = 0, "skipped (--no-parity)"
+    if not args.no_parity:
+        parity_checked, parity_note = check_parity(args, p, stream, pts, d_out, n, k, rank, world, local, step_device)
+        barrier()
+
+    t = torch.tensor([dev_ms, e2e_s * 1e3, kern_ms, float(parity_checked)], dtype=torch.float64, device=local)
+    if world > 1:
+        # parity counts add up over the ranks; the timings take the slowest rank
+        cnt = t[3:].clone()
+        dist.all_reduce(cnt, op=dist.ReduceOp.SUM)
+        parity_checked = int(cnt.item())
+    t = t[:3]
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     dev_ms, e2e_ms, kern_ms = t.tolist()
@@ -365,34 +475,32 @@ def main():
     peak, peak_src = peaks()
     kern_avg_s = kern_ms * 1e-3 / args.steps
     achieved = ALGO_BYTES_PER_POINT * n / kern_avg_s / 1e9
+    traffic, warp_inst = ncu_capture(n)
+    sm_hz = (clocks.get("sm_mhz") or 1965.0) * 1e6
+    issue_frac = (warp_inst / (kern_avg_s * 148 * 4 * sm_hz)) if warp_inst else None
     line = {
         "metric": "kNN+PCA feature points/sec (k=%d)" % k, "value": value, "unit": "points/s", "n_gpus": world,
         "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": dev_ms / args.steps, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"urban_{n}pts_knn_k{k}_pca (configs[2] shape, metric's k)", "points_per_gpu": n, "k": k,
-                   "order": "random", "l2": "flushed between steps (256 MiB fill, untimed)",
-                   "step": "bbox+keys+radix sort+cell table+fused search/moment/eigen, 68 B records",
-                   "sharding": "single cloud" if world == 1 else
-                   f"x-slabs of one {world}x{L:.0f} m x {L:.0f} m scan (" +
-                   ("each slab a translated copy of the N = 1 tile: identical work per GPU" if args.rank_clouds == "tile" else "one tile per rank, seeds 3 + 1000 rank") +
-                   f"), halo {halo} m exchanged every step (" +
-                   ("pcp_halo_push: the classification kernel stores the strips straight into the neighbours' halo regions over NVLink and raises their flags; pcp_halo_wait on the receiver; no NCCL, no host sync"
-                    if args.halo_impl == "peer" else
-                    "pcp_halo_pack kernel + grouped NCCL send/recv into fixed-capacity buffers, no host sync in the exchange") +
-                   "), global-index tie-break"},
+        "config": workload_config(n, k, world, args.rank_clouds, halo, args.halo_impl),
         "clocks": clocks,
         "e2e": {"value": total_pts / (e2e_ms * 1e-3), "unit": "points/s", "h2d_bytes_per_step": 16 * n, "d2h_bytes_per_step": 68 * n,
                 "mode": e2e_mode, "sequential_value": total_pts / e2e_seq_s},
         "gpu_launches": int(launches),
-        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": ncu_traffic(n),
-                     "kernel": "knn_tile_kernel + search_pca_worklist_kernel<0> (one stage: the tile kernel serves ~90 % of the queries, the work-list kernel the rest)", "bytes_per_point": ALGO_BYTES_PER_POINT, "peak_source": peak_src,
-                     "kernel_ms": kern_avg_s * 1e3,
-                     "note": "k-NN selection is issue-bound (≈1.5-3 kFLOP + top-k per point), far below the HBM roof by construction"},
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
+                     "kernel": "knn_tile_kernel + search_pca_worklist_kernel<0> (one stage: the tile kernel serves ~90 % of the queries, the work-list kernel the rest)",
+                     "bytes_per_point": ALGO_BYTES_PER_POINT, "peak_source": peak_src, "kernel_ms": kern_avg_s * 1e3,
+                     "traffic_source": (f"profiles/r02_search_ncu_{source_id()}.txt (ncu --set full of this build)" if traffic else
+                                        f"none: no capture of source id {source_id()} committed"),
+                     "issue_slot_frac": issue_frac,
+                     "note": "k-NN selection is issue-bound, not HBM-bound: issue_slot_frac = warp instructions of the stage (ncu, same build) / "
+                             "(kernel_ms x 148 SMs x 4 schedulers x SM clock) is the roofline that moves with the work done here"},
+        "parity_checked": parity_checked, "parity": parity_note,
     }
     if rank == 0 and world == 1 and not args.no_cpu:
         from oracle import oracle_py as O
 
-        threads = O.num_threads()
+        threads = host_threads()
         v1, m1, _ = run_cpu(pts, k, 1, args.cpu_sample // 4)
         best = None
         for _ in range(3):
@@ -419,7 +527,6 @@ def main():
         dist.destroy_process_group()
     p.close()
     sys.stdout.flush()
-    os._exit(0)
 
 
 if __name__ == "__main__":
