@@ -1,5 +1,6 @@
 // capi_core.cu — lifetime, buffers, timing and cloud hand-over of the pcp_* C-ABI (include/pcp.h).
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 
@@ -31,6 +32,10 @@ int pcp_reserve(pcp_ctx* ctx, DevBuf& b, size_t bytes) {
     return pcp_fail(ctx, PCP_ERR_OOM, "cudaMalloc", e);
   }
   b.cap = want;
+  if (!b.listed) {
+    b.listed = true;
+    ctx->owned.push_back(&b);
+  }
   return PCP_OK;
 }
 
@@ -38,7 +43,6 @@ void pcp_tic(pcp_ctx* ctx, int stage) { cudaEventRecord(ctx->ev[2 * stage], ctx-
 void pcp_toc(pcp_ctx* ctx, int stage) {
   cudaEventRecord(ctx->ev[2 * stage + 1], ctx->stream);
   ctx->ev_used[stage] = true;
-  if (stage == PCP_T_SEARCH_PCA) ctx->searches++;
 }
 void pcp_collect_timings(pcp_ctx* ctx) {
   for (int s = 0; s < PCP_T_COUNT; ++s) {
@@ -52,6 +56,17 @@ static void free_buf(DevBuf& b) {
   if (b.p) cudaFree(b.p);
   b.p = nullptr;
   b.cap = 0;
+}
+
+// the environment is looked at here and nowhere else
+static void read_knobs(PcpKnobs& kn) {
+  if (const char* e = getenv("PCP_KNN_IMPL")) kn.knn_impl = !strcmp(e, "v3") ? 3 : (!strcmp(e, "tile4") ? 4 : 0);
+  if (const char* e = getenv("PCP_KNN_GROUPS")) kn.knn_groups = atoi(e);
+  if (const char* e = getenv("PCP_RADIUS_IMPL")) kn.radius_impl = !strcmp(e, "v3") ? 3 : (!strcmp(e, "tile64") ? 2 : (!strncmp(e, "tile", 4) ? 1 : 0));
+  if (const char* e = getenv("PCP_WL_BLOCKS")) kn.wl_blocks = atoi(e) > 0 ? atoi(e) : 0;
+  if (const char* e = getenv("PCP_WL_TILE")) kn.wl_tile = (atoi(e) >= 1 && atoi(e) <= 32) ? atoi(e) : 0;
+  if (const char* e = getenv("PCP_GRID_SHIFT")) kn.grid_shift = atof(e) < 0.0 ? 0.0 : (atof(e) > 0.999 ? 0.999 : atof(e));
+  if (const char* e = getenv("PCP_GRID_SHIFT_AXIS")) kn.grid_shift_axis = atoi(e);
 }
 
 extern "C" {
@@ -75,6 +90,7 @@ PCP_API int pcp_create(pcp_ctx** out, int device) {
     return PCP_ERR_CUDA;
   }
   for (int i = 0; i < 2 * PCP_T_COUNT; ++i) cudaEventCreate(&ctx->ev[i]);
+  read_knobs(ctx->knobs);
   *out = ctx;
   return PCP_OK;
 }
@@ -83,13 +99,7 @@ PCP_API int pcp_destroy(pcp_ctx* ctx) {
   if (!ctx) return PCP_OK;
   cudaSetDevice(ctx->device);
   cudaStreamSynchronize(ctx->stream);
-  DevBuf* bufs[] = {&ctx->work_list, &ctx->work_count, &ctx->own_cloud, &ctx->bbox, &ctx->keys_in, &ctx->keys_sorted, &ctx->vals_in, &ctx->vals_sorted,
-                    &ctx->sort_tmp, &ctx->sorted_pts, &ctx->inv_pos, &ctx->gid_sorted, &ctx->gid_tmp, &ctx->ord_of_li, &ctx->li_of_ord, &ctx->sorted_slot, &ctx->cell_end, &ctx->scan_tmp, &ctx->out_feat,
-                    &ctx->out_norm, &ctx->out_idx, &ctx->out_d2, &ctx->out_counts, &ctx->flags, &ctx->valid,
-                    &ctx->last_valid, &ctx->staging, &ctx->ring_range, &ctx->ring_idx, &ctx->ring_long,
-                    &ctx->ring_offsets, &ctx->ring_key, &ctx->frames, &ctx->occ_hist, &ctx->halo_done, &ctx->seg_ground, &ctx->seg_label,
-                    &ctx->seg_colmax, &ctx->seg_above, &ctx->seg_counts, &ctx->seg_nlabels, &ctx->dec_tables, &ctx->dec_packed, &ctx->dec_out};
-  for (DevBuf* b : bufs) free_buf(*b);
+  for (DevBuf* b : ctx->owned) free_buf(*b);  // everything pcp_reserve ever allocated, whichever call asked for it
   if (ctx->h_occ) cudaFreeHost(ctx->h_occ);
   if (ctx->occ_ev) cudaEventDestroy(ctx->occ_ev);
   for (int i = 0; i < 2 * PCP_T_COUNT; ++i)

@@ -284,62 +284,10 @@ int pcp_grid_build_impl(pcp_ctx* ctx, float cell, int k_hint) {
     PCP_LAUNCH_CHECK("invert_kernel");
   }
 
-  // diagnostic knob: lower the grid origin by a fraction of a cell on every axis
-  double origin_shift = 0.0;
-  int shift_axis = -1;  // PCP_GRID_SHIFT_AXIS = 0 / 1 / 2: x / y / z only
-  if (const char* e = getenv("PCP_GRID_SHIFT")) origin_shift = std::min(std::max(atof(e), 0.0), 0.999);
-  if (const char* e = getenv("PCP_GRID_SHIFT_AXIS")) shift_axis = atoi(e);
-  // Learned alignment (automatic cell, stream of similar clouds): where the cell faces of the SHORTEST axis fall
-  // relative to the cloud's layers (the ground plane of a scan) moves the search time by 10-20 % at the same cell
-  // size and with identical results (tools/grid_shift_sweep.py).  The first five builds of a stream try the offsets
-  // 0, 1/4, 1/2, 3/4 of a cell (and 0 once more, warm); each one's search time is read from the previous cloud's events (complete: this
-  // build has just waited for the bounding box on the same stream) and the fastest offset stays.  OPT-IN with
-  // PCP_GRID_TUNE=1 (single clouds only): with several contexts in flight the changing table sizes of the trial builds
-  // re-allocate (a device-wide synchronisation each) and cost frame batches far more than the alignment returns.
-  {
-    static const double cand[4] = {0.0, 0.25, 0.5, 0.75};
-    const char* te = getenv("PCP_GRID_TUNE");
-    const bool tune = auto_cell && te && te[0] == '1' && n_seg == 1 && !getenv("PCP_GRID_SHIFT");  // opt-in: see DESIGN §7
-    if (!tune || !learned) {
-      ctx->tune_phase = 0;
-      ctx->tune_idx = -1;
-    }
-    if (tune) {
-      // trial order: offset 0 first (its time is NOT used: the first search of a stream runs cold), then the other
-      // three, then offset 0 again
-      static const int trial[5] = {0, 1, 2, 3, 0};
-      if (ctx->tune_idx >= 0 && ctx->tune_phase >= 2 && ctx->tune_phase <= 5 && ctx->searches == ctx->tune_seen + 1 &&
-          ctx->ev_used[PCP_T_SEARCH_PCA]) {
-        float ms = 0.f;  // exactly one search ran on the previous build: its time belongs to that build's offset
-        if (cudaEventElapsedTime(&ms, ctx->ev[2 * PCP_T_SEARCH_PCA], ctx->ev[2 * PCP_T_SEARCH_PCA + 1]) == cudaSuccess && ms > 0.f &&
-            !ctx->tune_done)
-          ctx->tune_ms[ctx->tune_idx] = ms;
-        if (ctx->tune_phase == 5) ctx->tune_done = true;
-      }
-      int idx = 0;
-      if (ctx->tune_phase < 5) {
-        if (ctx->tune_phase == 0) {
-          for (int i = 0; i < 4; ++i) ctx->tune_ms[i] = 0.f;
-          ctx->tune_done = false;
-        }
-        idx = trial[ctx->tune_phase++];
-      } else {
-        float best = 3.0e38f;
-        for (int i = 0; i < 4; ++i)
-          if (ctx->tune_ms[i] > 0.f && ctx->tune_ms[i] < best) {
-            best = ctx->tune_ms[i];
-            idx = i;
-          }
-      }
-      if (getenv("PCP_GRID_TUNE_DEBUG"))
-        fprintf(stderr, "[pcp tune] phase %d idx %d ms %.3f %.3f %.3f %.3f searches %lld seen %lld\n", ctx->tune_phase, idx, ctx->tune_ms[0],
-                ctx->tune_ms[1], ctx->tune_ms[2], ctx->tune_ms[3], (long long)ctx->searches, (long long)ctx->tune_seen);
-      ctx->tune_idx = idx;
-      ctx->tune_seen = ctx->searches;
-      origin_shift = cand[idx];
-      shift_axis = g.ax[1];  // the shortest extent
-    }
-  }
+  // diagnostic knob: lower the grid origin by a fraction of a cell (all axes, or one); results are
+  // unchanged, only where the cell faces fall relative to the cloud's layers
+  const double origin_shift = ctx->knobs.grid_shift;
+  const int shift_axis = ctx->knobs.grid_shift_axis;
   for (int attempt = 0;; ++attempt) {
   const double max_cells = 1.0e9;
   for (;;) {

@@ -30,6 +30,7 @@
 #include "pcp_internal.cuh"
 #include "search_common.cuh"
 #include "knn_finish.cuh"
+#include "tile_common.cuh"
 
 #ifdef PCP_STATS
 __device__ unsigned long long g_tile_stats[16];
@@ -49,8 +50,6 @@ constexpr int TA_CH = 128;         // staged candidates per chunk
 // the histogram has BINS = 2*CAP - 1 linear d2 bins inside the cover radius + 1 overflow bin, so that it
 // occupies exactly the rows the candidate keys use afterwards.
 constexpr int TA_REC_WORDS = 17;   // 68-byte record
-constexpr int TA_MAXROWS = 64;     // stencil rows of a tile: (2R+1)^2 <= 49, R <= 3
-constexpr int TA_MAXR = 3;
 constexpr int TA_MAXGROUPS = 1;    // stencil rows (row groups) served per tile by default; lanes of further rows are
                                    // deferred (measured: a second pass for a few lanes costs more than deferring them)
 
@@ -68,14 +67,6 @@ struct __align__(16) TaSmem {
   uint32_t run_beg[TA_MAXROWS];          // first sorted position of each stencil row's run
   uint32_t run_off[TA_MAXROWS + 1];      // exclusive prefix of the run lengths
 };
-
-// fractional position of Q inside its cell c along the x/y/z axis `ax`, clamped to [0,1] (same double
-// arithmetic as the key kernel; selects instead of dynamic indexing keep the arguments in the constant bank)
-__device__ __forceinline__ float frac_of(const GridDesc& g, int ax, const float4 Q, int c) {
-  const double v = ax == 0 ? (double)Q.x : (ax == 1 ? (double)Q.y : (double)Q.z);
-  const double o = ax == 0 ? g.origin[0] : (ax == 1 ? g.origin[1] : g.origin[2]);
-  return fminf(fmaxf((float)((v - o) * g.inv_cell - (double)c), 0.f), 1.f);
-}
 
 // copies candidates [cb, cb + cnt) of the tile's virtual candidate sequence (the stencil rows' runs laid
 // end to end) into sm.cand: row by row, the 32 lanes reading consecutive float4 of the run
@@ -95,72 +86,18 @@ __device__ __forceinline__ void stage_chunk(const float4* __restrict__ sorted, T
   __syncwarp();
 }
 
-// One row group of a tile: the lanes whose query lies in stencil row `row0`.  Looks up the (2R+1)^2 runs
-// of the union of their stencils, writes them to sm.run_*, and returns the number of candidates;
-// cover_cells = radius (in cells) around THIS lane's query that the union is guaranteed to cover: its
-// distance to the nearest face of the union block that still has cells behind it (a face on the grid
-// boundary has no points beyond it), minus 2e-3 cells for the rounding of the fractional position.
-template <int CAP>
-__device__ __forceinline__ uint32_t tile_setup(const KArgs& a, TaSmem<CAP>& sm, const int lane, const int R, const int c0min,
-                                               const int c0max, const int c1, const int c2, const int zoff, const int c0, const float4 Q,
-                                               int& nrows, bool& whole, float& cover_cells) {
-  const GridDesc& g = a.g;
-  const int xlo = max(c0min - R, 0), xhi = min(c0max + R, g.dim[0] - 1);
-  const int lo1 = max(c1 - R, 0), n1 = min(c1 + R, g.dim[1] - 1) - lo1 + 1;
-  const int lo2 = max(c2 - R, 0), n2 = min(c2 + R, g.dim[2] - 1) - lo2 + 1;
-  nrows = n1 * n2;
-  uint32_t beg0 = 0, len0 = 0, beg1 = 0, len1 = 0;
-  if (lane < nrows) {
-    const int o2 = lane / n1, o1 = lane - o2 * n1;
-    const uint32_t base = ((uint32_t)(zoff + lo2 + o2) * (uint32_t)g.dim[1] + (uint32_t)(lo1 + o1)) * (uint32_t)g.dim[0];
-    beg0 = __ldg(&a.E[base + xlo]);
-    len0 = __ldg(&a.E[base + xhi + 1]) - beg0;
-  }
-  if (lane + 32 < nrows) {
-    const int o2 = (lane + 32) / n1, o1 = (lane + 32) - o2 * n1;
-    const uint32_t base = ((uint32_t)(zoff + lo2 + o2) * (uint32_t)g.dim[1] + (uint32_t)(lo1 + o1)) * (uint32_t)g.dim[0];
-    beg1 = __ldg(&a.E[base + xlo]);
-    len1 = __ldg(&a.E[base + xhi + 1]) - beg1;
-  }
-  uint32_t inc0 = len0, inc1 = len1;
-#pragma unroll
-  for (int o = 1; o < 32; o <<= 1) {
-    const uint32_t t0 = __shfl_up_sync(PCP_FULL, inc0, o), t1 = __shfl_up_sync(PCP_FULL, inc1, o);
-    if (lane >= o) {
-      inc0 += t0;
-      inc1 += t1;
-    }
-  }
-  const uint32_t tot0 = __shfl_sync(PCP_FULL, inc0, 31);
-  const uint32_t total = tot0 + __shfl_sync(PCP_FULL, inc1, 31);
-  __syncwarp();
-  sm.run_beg[lane] = beg0;
-  sm.run_off[lane] = inc0 - len0;
-  sm.run_beg[lane + 32] = beg1;
-  sm.run_off[lane + 32] = tot0 + inc1 - len1;
-  __syncwarp();
-  whole = xlo == 0 && xhi == g.dim[0] - 1 && n1 == g.dim[1] && n2 == g.dim[2];
-  const float f0 = frac_of(g, g.ax[0], Q, c0), f1 = frac_of(g, g.ax[1], Q, c1), f2 = frac_of(g, g.ax[2], Q, c2);
-  const float inf = 3.0e18f;
-  const float m0a = xlo > 0 ? (float)(c0 - xlo) + f0 : inf, m0b = xhi < g.dim[0] - 1 ? (float)(xhi + 1 - c0) - f0 : inf;
-  const float m1a = c1 - R > 0 ? (float)R + f1 : inf, m1b = c1 + R < g.dim[1] - 1 ? (float)(R + 1) - f1 : inf;
-  const float m2a = c2 - R > 0 ? (float)R + f2 : inf, m2b = c2 + R < g.dim[2] - 1 ? (float)(R + 1) - f2 : inf;
-  cover_cells = fminf(fminf(fminf(m0a, m0b), fminf(m1a, m1b)), fminf(m2a, m2b)) - 2e-3f;
-  return total;
-}
-
 // MODE 0: k nearest (two passes: histogram select, then collect).  MODE 1: radius search — membership is
 // d2 < r2 itself, so there is no selection pass; a lane is served when its neighbourhood fits its column.
 template <int CAP, int MODE>
-__global__ void __launch_bounds__(TA_WARPS * 32, (CAP == 24 ? 24 : (CAP == 64 ? 12 : 20)) / TA_WARPS) knn_tile_kernel(KArgs a, int R0, float grow, int max_groups, uint32_t* __restrict__ work_count,
+__global__ void __launch_bounds__(TA_WARPS * 32, (CAP == 64 ? 12 : 20) / TA_WARPS) knn_tile_kernel(KArgs a, int R0, float grow, int max_groups, uint32_t* __restrict__ work_count,
                                                                  uint32_t* __restrict__ work_list) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   constexpr int BINS = 2 * CAP - 1;
   TaSmem<CAP>& sm = reinterpret_cast<TaSmem<CAP>*>(smem_raw)[threadIdx.x >> 5];
   const int lane = threadIdx.x & 31;
   const int64_t pos0 = ((int64_t)blockIdx.x * TA_WARPS + (threadIdx.x >> 5)) * 32;
-  if (pos0 >= a.n) return;  // whole warp
-  const int64_t p = pos0 + lane;
+  const bool live_warp = pos0 < a.n;  // a tail warp stays (inactive) for the CTA barriers below
+  const int64_t p = live_warp ? pos0 + lane : a.n;
   const GridDesc& g = a.g;
   const SearchParams& sp = a.sp;
   const float4* __restrict__ sorted = a.sorted;
@@ -203,7 +140,7 @@ __global__ void __launch_bounds__(TA_WARPS * 32, (CAP == 24 ? 24 : (CAP == 64 ? 
       // radius: the stencil of half-width R0 covers the radius by construction (stencil_for_radius)
       bool whole;
       float cover_cells;
-      total = tile_setup(a, sm, lane, R, c0min, c0max, c1, c2, zoff, c0, Q, nrows, whole, cover_cells);
+      total = tile_setup(a, sm.run_beg, sm.run_off, lane, R, c0min, c0max, c1, c2, zoff, c0, Q, nrows, whole, cover_cells);
       Sb = 1.f;
       bstar = 0;
     } else {
@@ -217,7 +154,7 @@ __global__ void __launch_bounds__(TA_WARPS * 32, (CAP == 24 ? 24 : (CAP == 64 ? 
     for (;;) {
       if (fresh) {
         float cover_cells;
-        total = tile_setup(a, sm, lane, R, c0min, c0max, c1, c2, zoff, c0, Q, nrows, whole, cover_cells);
+        total = tile_setup(a, sm.run_beg, sm.run_off, lane, R, c0min, c0max, c1, c2, zoff, c0, Q, nrows, whole, cover_cells);
         Sb = (float)BINS / (cover_cells * cover_cells * g.cell * g.cell * (1.f - 1e-6f));
         noff = 0.f;
         hist_on = in_grp;
@@ -401,8 +338,7 @@ __global__ void __launch_bounds__(TA_WARPS * 32, (CAP == 24 ? 24 : (CAP == 64 ? 
   u64 keys[CAP];
 #pragma unroll
   for (int j = 0; j < CAP; ++j) keys[j] = j < cnt ? (((u64)hcol[(CAP + j) * 32] << 32) | (u64)hcol[j * 32]) : PCP_KEY_INF;
-  if (CAP == 24) sort24_regs(reinterpret_cast<u64(&)[24]>(keys));
-  else if (CAP == 32) sort32_regs(reinterpret_cast<u64(&)[32]>(keys));
+  if (CAP == 32) sort32_regs(reinterpret_cast<u64(&)[32]>(keys));
   else sort64_regs(reinterpret_cast<u64(&)[64]>(keys));
   // the ordered keys go back to the lane's column: everything after this point walks the list with rolled loops
 #pragma unroll
@@ -416,6 +352,7 @@ __global__ void __launch_bounds__(TA_WARPS * 32, (CAP == 24 ? 24 : (CAP == 64 ? 
 #if PCP_TILE_SYNC
   __syncthreads();
 #endif
+  if (!live_warp) return;
   knn_finish(a, hcol, hcol + CAP * 32, 32, n_nb, MODE == 1 ? sp.min_pts : 1, Q, emit ? my_slot : -1, sm.u.rec, lane);
 }
 
@@ -440,21 +377,13 @@ int pcp_knn_tile_launch(pcp_ctx* ctx, const SearchParams& sp, const KArgs& a, in
   PCP_CUDA(cudaMemsetAsync(ctx->work_count.p, 0, 2 * sizeof(uint32_t), ctx->stream));
   const int64_t tiles = (ctx->n + 31) / 32;
   const int blocks = (int)((tiles + TA_WARPS - 1) / TA_WARPS);
-  // a tile's stencil is widened when (uncovered lanes) * grow exceeds the size of the wider union
-  // (tuning hook: PCP_KNN_RGROW; 0 = never widen: measured slower on the urban cloud)
-  float grow = 0.f;
-  if (const char* e = getenv("PCP_KNN_RGROW")) grow = (float)atof(e);
+  const float grow = 0.f;  // never widen a tile's stencil (measured slower on the urban cloud)
   // Stencil rows served per tile.  One on big clouds (a second row group costs the urban cloud 5-10 %);
   // up to four when the rows are short — frame batches: 26 k points over a few hundred rows, where 8-30 %
   // of the lanes sit in another row than their tile's majority (measured 8.8 -> 7.1 ms per 128 frames).
-  // Tuning hook: PCP_KNN_GROUPS.
   const double pts_per_row = (double)ctx->n / ((double)ctx->grid.n_seg * (double)ctx->grid.dim[1] * (double)ctx->grid.dim[2]);
   int max_groups = pts_per_row < 256.0 ? 4 : TA_MAXGROUPS;
-  if (const char* e = getenv("PCP_KNN_GROUPS")) max_groups = atoi(e);
-  // 32-entry lanes by default; PCP_KNN_CAP=24 selects 24-entry lanes for k <= 20 (smaller network, 77
-  // registers, 6 CTAs/SM) — measured SLOWER on the urban cloud (1.82 vs 1.63 ms): its 47 bins leave more
-  // lanes with an over-full threshold bin than the extra occupancy pays for
-  const char* capenv = getenv("PCP_KNN_CAP");
+  if (ctx->knobs.knn_groups > 0) max_groups = ctx->knobs.knn_groups;
   uint32_t* wc = (uint32_t*)ctx->work_count.p;
   uint32_t* wl = (uint32_t*)ctx->work_list.p;
   if (sp.mode == 1 && radius_cap == 64) {
@@ -465,10 +394,6 @@ int pcp_knn_tile_launch(pcp_ctx* ctx, const SearchParams& sp, const KArgs& a, in
     const size_t smem = sizeof(TaSmem<32>) * TA_WARPS;
     PCP_CUDA(cudaFuncSetAttribute(knn_tile_kernel<32, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     knn_tile_kernel<32, 1><<<blocks, TA_WARPS * 32, smem, ctx->stream>>>(a, sp.R0, 0.f, max_groups, wc, wl);
-  } else if (sp.k <= 20 && capenv && capenv[0] == '2') {
-    const size_t smem = sizeof(TaSmem<24>) * TA_WARPS;
-    PCP_CUDA(cudaFuncSetAttribute(knn_tile_kernel<24, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    knn_tile_kernel<24, 0><<<blocks, TA_WARPS * 32, smem, ctx->stream>>>(a, sp.R0, grow, max_groups, wc, wl);
   } else {
     const size_t smem = sizeof(TaSmem<32>) * TA_WARPS;
     PCP_CUDA(cudaFuncSetAttribute(knn_tile_kernel<32, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

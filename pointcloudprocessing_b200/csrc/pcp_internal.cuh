@@ -39,6 +39,19 @@ __host__ __device__ __forceinline__ int pcp_unfold_z(const GridDesc& g, int& c2)
 struct DevBuf {
   void* p = nullptr;
   size_t cap = 0;
+  bool listed = false;  // registered in pcp_ctx::owned (pcp_destroy frees every buffer that was ever reserved)
+};
+
+// Environment knobs (A/B timing and tests), read ONCE in pcp_create — never on the launch path.
+struct PcpKnobs {
+  int knn_impl = 0;        // PCP_KNN_IMPL: 0 = tile kernel of knn_tile5.cu + work list (default), 4 = "tile4": the round-1
+                           // tile kernel (knn_tile.cu), 3 = "v3": the warp-per-query kernel for every point
+  int knn_groups = 0;      // PCP_KNN_GROUPS: stencil rows served per tile (0 = automatic)
+  int radius_impl = 0;     // PCP_RADIUS_IMPL: 0 = automatic, 1 = "tile" (32-entry lanes), 2 = "tile64", 3 = "v3"
+  int wl_blocks = 0;       // PCP_WL_BLOCKS / PCP_WL_TILE: work-list kernel grid and tile (0 = default)
+  int wl_tile = 0;
+  double grid_shift = 0.0; // PCP_GRID_SHIFT: lower the grid origin by this fraction of a cell (diagnostic; results unchanged)
+  int grid_shift_axis = -1;// PCP_GRID_SHIFT_AXIS: 0 / 1 / 2 = x / y / z only
 };
 
 struct pcp_ctx {
@@ -47,6 +60,8 @@ struct pcp_ctx {
   std::string err;
   bool host_async = false;  // pcp_set_host_async: host-pointer calls only enqueue
   int64_t launches = 0;
+  PcpKnobs knobs;
+  std::vector<DevBuf*> owned;  // every DevBuf pcp_reserve ever allocated for this context
   float t_ms[PCP_T_COUNT] = {0};
   cudaEvent_t ev[2 * PCP_T_COUNT] = {nullptr};
   bool ev_used[PCP_T_COUNT] = {false};
@@ -69,13 +84,6 @@ struct pcp_ctx {
   cudaEvent_t occ_ev = nullptr;         // recorded behind an asynchronous copy into h_occ
   bool occ_pending = false;
   unsigned occ_tick = 0;
-  // learned alignment of the grid along its shortest axis (grid.cu): the first builds of a stream of similar clouds
-  // try four origin offsets, the search time of each (events of the previous cloud) decides which one stays
-  int tune_phase = 0;                   // trials handed out so far (5 = settled)
-  bool tune_done = false;               // the last trial's time has been read
-  int tune_idx = -1;                    // candidate the last build used (-1: none)
-  float tune_ms[4] = {0.f, 0.f, 0.f, 0.f};
-  int64_t searches = 0, tune_seen = -1; // search launches so far / at the last tuned build
   double cell_scale = 1.0;              // learned correction of the first-guess cell for clouds like the last one
   int64_t scale_n = 0;
   int scale_seg = 0, scale_k = 0;
@@ -143,5 +151,5 @@ struct SearchParams {
 int pcp_search_launch(pcp_ctx* ctx, const SearchParams& sp);  // radius (and the v3 warp-per-query k-NN, A/B only)
 struct KArgs;
 int pcp_knn_tile_launch(pcp_ctx* ctx, const SearchParams& sp, const KArgs& a, int radius_cap);  // k-NN tile kernel (knn_tile.cu)
-int pcp_knn_launch(pcp_ctx* ctx, const SearchParams& sp);     // k-NN, one thread per query (knn_pca.cu)
+int pcp_knn_tile5_launch(pcp_ctx* ctx, const SearchParams& sp, const KArgs& a);  // k-NN tile kernel, round-2 form (knn_tile5.cu)
 int pcp_carry_forward_impl(pcp_ctx* ctx, pcp_feature68* d_out, const uint8_t* d_valid, int64_t n);

@@ -668,13 +668,11 @@ extern "C" __attribute__((visibility("default"))) int pcp_debug_stats(unsigned l
 #endif
 
 int pcp_search_launch(pcp_ctx* ctx, const SearchParams& sp) {
-  // PCP_KNN_IMPL selects the k-NN kernel for A/B timing: default = tile kernel (knn_tile.cu) + this
-  // file's warp-per-query kernel for the queries it defers; "v3" = warp-per-query for every point;
-  // "tq" = thread-per-query walk (knn_pca.cu).  All three give identical results.
-  const char* impl = getenv("PCP_KNN_IMPL");
-  const bool use_tq = sp.mode == 0 && impl && impl[0] == 't' && impl[1] == 'q' && ctx->grid.n_seg == 1;  // (no frame batches in the A/B kernel)
-  const bool use_v3 = sp.mode == 0 && impl && impl[0] == 'v' && impl[1] == '3';
-  if (use_tq) return pcp_knn_launch(ctx, sp);
+  // PCP_KNN_IMPL (read once in pcp_create) selects the k-NN kernel for A/B timing: default = tile kernel of
+  // knn_tile5.cu + this file's warp-per-query kernel for the queries it defers; "tile4" = the round-1 tile
+  // kernel (knn_tile.cu) instead; "v3" = warp-per-query for every point.  All give identical results.
+  const PcpKnobs& kn = ctx->knobs;
+  const bool use_v3 = sp.mode == 0 && kn.knn_impl == 3;
   KArgs a;
   a.sorted = (const float4*)ctx->sorted_pts.p;
   a.keys = (const uint32_t*)ctx->keys_sorted.p;
@@ -693,7 +691,6 @@ int pcp_search_launch(pcp_ctx* ctx, const SearchParams& sp) {
   // warp-per-query kernel.  Measured on B200: mean 8.7 neighbours -> 0.82 vs 0.99 ms per 1 M points, mean 32 ->
   // 3.2 vs 2.4 ms, so the switch is a surface-density guess n*pi*r^2 / (two largest extents) <= 40
   // (the urban clouds hold ~0.4 of that guess).  PCP_RADIUS_IMPL=tile|v3 forces either.
-  const char* rimpl = getenv("PCP_RADIUS_IMPL");
   bool radius_tile = false;
   int radius_cap = 32;
   if (sp.mode == 1 && sp.k == 0 && sp.out != nullptr && sp.counts == nullptr && sp.nn_idx == nullptr) {
@@ -703,18 +700,21 @@ int pcp_search_launch(pcp_ctx* ctx, const SearchParams& sp) {
     // the warp-per-query kernel alone beyond that
     radius_tile = guess <= 200.0;
     radius_cap = guess <= 40.0 ? 32 : 64;
-    if (rimpl && rimpl[0] == 't') { radius_tile = true; radius_cap = rimpl[4] == '6' ? 64 : 32; }  // tile32 / tile64
-    if (rimpl && rimpl[0] == 'v') radius_tile = false;
+    if (kn.radius_impl == 1 || kn.radius_impl == 2) { radius_tile = true; radius_cap = kn.radius_impl == 2 ? 64 : 32; }
+    if (kn.radius_impl == 3) radius_tile = false;
+    // the tile kernel's run tables hold (2R+1)^2 <= 49 stencil rows: a cell smaller than r/3 (R0 > 3: automatic
+    // k-NN cells, or a small cell chosen by the caller) goes to the warp-per-query kernel, which has no such bound
+    if (sp.R0 > 3) radius_tile = false;
   }
   if ((sp.mode == 0 && !use_v3) || radius_tile) {
-    int rc = pcp_knn_tile_launch(ctx, sp, a, radius_cap);
+    int rc = (sp.mode == 0 && kn.knn_impl != 4) ? pcp_knn_tile5_launch(ctx, sp, a) : pcp_knn_tile_launch(ctx, sp, a, radius_cap);
     if (rc) return rc;
     // one wave of resident CTAs (3 per SM at 80 registers); tiles of 16 list entries drawn by ticket
     // (tuning hooks: PCP_WL_BLOCKS, PCP_WL_TILE)
     int wl_blocks = blocks < 148 * 3 ? blocks : 148 * 3;
     int wl_tile = 16;
-    if (const char* e = getenv("PCP_WL_BLOCKS")) wl_blocks = atoi(e) > 0 ? atoi(e) : wl_blocks;
-    if (const char* e = getenv("PCP_WL_TILE")) wl_tile = atoi(e) >= 1 && atoi(e) <= 32 ? atoi(e) : wl_tile;
+    if (kn.wl_blocks > 0) wl_blocks = kn.wl_blocks;
+    if (kn.wl_tile > 0) wl_tile = kn.wl_tile;
     if (sp.mode == 0 && wl_tile > KNN_LW) wl_tile = KNN_LW;
     if (sp.mode == 0) {
       size_t smem = sizeof(WarpSmem<0>) * WARPS;

@@ -62,15 +62,18 @@ def test_segmented_grid_edge_cases(oracle):
             p.set_cloud(part)
             p.build_grid(0.0, k)
             want.append((p.knn_pca(k), p.knn_neighbors(k)))
-        for impl in ("", "v3"):
-            os.environ["PCP_KNN_IMPL"] = impl
-            try:
+    # PCP_KNN_IMPL is read when a context is created: "" = tile kernel (round-2 form), tile4 = round-1 tile kernel,
+    # v3 = warp per query for every point
+    for impl in ("", "tile4", "v3"):
+        os.environ["PCP_KNN_IMPL"] = impl
+        try:
+            with capi.Pcp(0) as q:
                 for cell in (0.0, 0.9, 40.0):
-                    p.set_cloud(cloud)
-                    p.set_frames(offs)
-                    p.build_grid(cell, k)
-                    feat = p.knn_pca(k)
-                    idx, d2 = p.knn_neighbors(k)
+                    q.set_cloud(cloud)
+                    q.set_frames(offs)
+                    q.build_grid(cell, k)
+                    feat = q.knn_pca(k)
+                    idx, d2 = q.knn_neighbors(k)
                     for f, part in enumerate(parts):
                         if want[f] is None:
                             continue
@@ -83,8 +86,9 @@ def test_segmented_grid_edge_cases(oracle):
                         gi[gi >= 0] -= a
                         assert np.array_equal(gi, wi), (impl, cell, f)
                         assert np.array_equal(d2[a:b].view(np.uint32), wd.view(np.uint32)), (impl, cell, f)
-            finally:
-                os.environ.pop("PCP_KNN_IMPL", None)
+        finally:
+            os.environ.pop("PCP_KNN_IMPL", None)
+    with capi.Pcp(0) as p:
         # radius mode: the stale-record carry restarts at every frame
         r = 0.6
         p.set_cloud(cloud)

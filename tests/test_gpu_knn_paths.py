@@ -1,5 +1,6 @@
-"""GPU: the k-NN kernels (tile kernel + work-list kernel = the product path; PCP_KNN_IMPL=v3 / tq = the
-earlier kernels kept for A/B timing) must give bit-identical neighbour lists, equal to the oracle's, on
+"""GPU: the k-NN kernels (tile kernel of knn_tile5.cu + work-list kernel = the product path; PCP_KNN_IMPL=tile4 / v3 =
+the round-1 tile kernel and the warp-per-query kernel kept for A/B timing; the variable is read when a context is
+created) must give bit-identical neighbour lists, equal to the oracle's, on
 the inputs that stress the hand-over between them: exact ties, duplicates, sparse and tiny clouds, k
 larger than the cloud, clouds thinner than one cell, non-finite points."""
 import os
@@ -13,7 +14,7 @@ pytestmark = pytest.mark.gpu
 
 
 def _knn(pts, k, impl=None, cell=0.0, env=None):
-    old = {v: os.environ.get(v) for v in ("PCP_KNN_IMPL", "PCP_KNN_RGROW", "PCP_KNN_GROUPS", "PCP_KNN_FORCE_EXACT")}
+    old = {v: os.environ.get(v) for v in ("PCP_KNN_IMPL", "PCP_KNN_GROUPS")}
     try:
         if impl:
             os.environ["PCP_KNN_IMPL"] = impl
@@ -62,8 +63,7 @@ def test_knn_matches_oracle_and_other_kernels(oracle, name):
     np.testing.assert_array_equal(idx[fin], ridx)
     np.testing.assert_array_equal(d2[fin].view(np.uint32), rd2.view(np.uint32))
     assert (idx[~fin] == -1).all()
-    for impl, env in (("v3", None), ("tq", None), ("tq", {"PCP_KNN_FORCE_EXACT": "1"}),
-                      (None, {"PCP_KNN_RGROW": "70", "PCP_KNN_GROUPS": "4"})):
+    for impl, env in (("v3", None), ("tile4", None), ("tile4", {"PCP_KNN_GROUPS": "4"}), (None, {"PCP_KNN_GROUPS": "4"})):
         i2, e2, f2 = _knn(pts, k, impl, env=env)
         np.testing.assert_array_equal(i2, idx)
         np.testing.assert_array_equal(e2.view(np.uint32), d2.view(np.uint32))
@@ -123,13 +123,14 @@ def test_radius_pca_both_kernels(oracle, impl):
     pts = synth.urban(17, 40000, extent=22.0)  # ~83 pts/m^2: many neighbourhoods above and below 32
     old = os.environ.get("PCP_RADIUS_IMPL")
     try:
-        os.environ["PCP_RADIUS_IMPL"] = impl
-        with capi.Pcp(0) as p:
-            p.set_cloud(pts)
-            p.build_grid(0.5005, 0)
-            got = p.radius_pca(0.5, 13, capi.CENTER_QUERY, True)
-            os.environ["PCP_RADIUS_IMPL"] = "v3"
-            ref_gpu = p.radius_pca(0.5, 13, capi.CENTER_QUERY, True)
+        res = {}
+        for which in (impl, "v3"):  # the variable is read when a context is created
+            os.environ["PCP_RADIUS_IMPL"] = which
+            with capi.Pcp(0) as p:
+                p.set_cloud(pts)
+                p.build_grid(0.5005, 0)
+                res[which] = p.radius_pca(0.5, 13, capi.CENTER_QUERY, True)
+        got, ref_gpu = res[impl], res["v3"]
     finally:
         if old is None:
             os.environ.pop("PCP_RADIUS_IMPL", None)

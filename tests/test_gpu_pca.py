@@ -157,3 +157,18 @@ def test_radius_pca_heavy_neighbourhoods(pcp, oracle):
     assert (got["ptNum"] > 512).any() and (got["ptNum"] < 200).any()
     assert np.array_equal(got["ptNum"], ref["ptNum"])
     check_features(got, ref, valid, "radius mixed")
+
+
+@pytest.mark.parametrize("div", [3.5, 5.0])
+def test_radius_pca_small_cell(pcp, oracle, div):
+    """A cell smaller than r / 3 (stencil half-width 4-6: more rows than the tile kernel's run tables hold) must
+    take the warp-per-query path and still match the oracle (such grids arise from
+    build_grid(0.0, k) followed by radius_pca, or from a small cell chosen by the caller on a sparse cloud)."""
+    pts = synth.urban(9, 20000, extent=60.0)  # sparse: ~5 points/m^2, so the density guess stays on the tile side
+    r = 1.0
+    pcp.set_cloud(pts)
+    pcp.build_grid(r / div, 0)
+    got = pcp.radius_pca(r, 13, CENTER_QUERY, True)
+    ref, valid = oracle.radius_pca_cloud(pts, r, 13, True, nthreads=0)
+    assert np.array_equal(got["ptNum"], ref["ptNum"])
+    check_features(got, ref, valid, f"radius cell=r/{div}")
