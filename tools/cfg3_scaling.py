@@ -1,0 +1,135 @@
+"""configs[3] for real: the synthetic 100 M-point cloud (100 points / m^2 over 1 km x 1 km), radiusSearch r = 0.5 m +
+PCA (src/pcaAnalysis.cpp:11-42), sharded into equal-count x-slabs over the GPUs of one box with a halo of width r
+exchanged EVERY step (NCCL send/recv between slab neighbours), strong scaling.  Every rank then runs the WHOLE cloud
+unsharded on its own GPU and compares its slab's records with that run bit for bit (global-index tie-break).
+
+  python tools/cfg3_scaling.py [--n N] [--steps K] [--out file.json]                      # 1 GPU
+  python -m torch.distributed.run --nnodes=1 --nproc-per-node G --master-addr 127.0.0.1 --master-port 29511 tools/cfg3_scaling.py ...
+
+One JSON object on rank 0: points/s per step (max over ranks, wall clock around barrier + step + synchronize, and the
+device time between CUDA events on the library's stream), halo bytes per rank, bitwise equality per rank."""
+import argparse, json, os, sys, time
+import numpy as np
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import torch
+import torch.distributed as dist
+from pointcloudprocessing_b200 import capi, sharding, synth
+
+ap = argparse.ArgumentParser()
+ap.add_argument("--n", type=int, default=100_000_000)
+ap.add_argument("--steps", type=int, default=5)
+ap.add_argument("--radius", type=float, default=0.5)
+ap.add_argument("--out", default="")
+ap.add_argument("--no-verify", action="store_true")
+args = ap.parse_args()
+rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1")); local = int(os.environ.get("LOCAL_RANK", "0"))
+torch.cuda.set_device(local)
+if world > 1:
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+n, r = args.n, args.radius
+ext = (n / 100.0) ** 0.5
+t0 = time.time()
+pts = synth.urban(4, n, extent=ext, order="asis")  # every rank generates the same bytes (numpy PCG64 keyed by the seed)
+gen_s = time.time() - t0
+# equal-count slabs along x (the splitters are quantiles of the whole cloud; every rank computes the same ones)
+edges = [float(-np.inf)] + [float(v) for v in np.quantile(pts[:, 0], [i / world for i in range(1, world)])] + [float(np.inf)]
+lo, hi = edges[rank], edges[rank + 1]
+own = np.nonzero((pts[:, 0] >= lo) & (pts[:, 0] < hi))[0].astype(np.int32)
+n_own = int(own.size)
+p = capi.Pcp(local)
+stream = torch.cuda.ExternalStream(p.stream, device=local)
+d_own = torch.from_numpy(np.ascontiguousarray(pts[own])).cuda(local)
+d_gid = torch.from_numpy(own).cuda(local)
+d_out = torch.empty(n_own * 68, dtype=torch.uint8, device=local)
+h = sharding.radius_halo_width(r)
+flo = lo if rank > 0 else -1e30
+fhi = hi if rank < world - 1 else 1e30
+torch.cuda.synchronize()
+
+def barrier():
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+
+keep = {}
+def step():
+    with torch.cuda.stream(stream):
+        if world > 1:
+            pa, ga, no = sharding.exchange_halo(d_own, d_gid, 0, flo, fhi, h, rank, world)
+        else:
+            pa, ga, no = d_own, d_gid, n_own
+        keep["bufs"] = (pa, ga)
+    p.set_cloud_device(pa.data_ptr(), pa.shape[0], ga.data_ptr() if world > 1 else None, no)
+    p.build_grid(r * 1.001, 0)
+    p.radius_pca(r, 13, capi.CENTER_QUERY, False, out_device=d_out.data_ptr())
+    return pa.shape[0]
+
+for _ in range(2):
+    n_all = step()
+p.synchronize()
+walls, devs = [], []
+for s in range(args.steps):
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0 = time.perf_counter()
+    e0.record(stream)
+    step()
+    e1.record(stream)
+    p.synchronize()
+    walls.append(time.perf_counter() - t0)
+    devs.append(e0.elapsed_time(e1) * 1e-3)
+tm = p.timings()
+barrier()
+t = torch.tensor([sum(walls) / len(walls), min(walls), sum(devs) / len(devs), tm["search_pca"], tm["bbox"] + tm["keys"] + tm["sort"] + tm["table"]],
+                 dtype=torch.float64, device=local)
+if world > 1:
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+wall_avg, wall_min, dev_avg, search_ms, grid_ms = t.tolist()
+# ---- bitwise check against the unsharded run of the whole cloud on this rank's own GPU
+equal, differing = None, None
+if not args.no_verify:
+    d_full = torch.from_numpy(pts).cuda(local)
+    d_fout = torch.empty(n * 68, dtype=torch.uint8, device=local)
+    with capi.Pcp(local) as q:
+        q.set_cloud_device(d_full.data_ptr(), n)
+        q.build_grid(r * 1.001, 0)
+        q.radius_pca(r, 13, capi.CENTER_QUERY, False, out_device=d_fout.data_ptr())
+        q.synchronize()
+    mine = d_fout.view(-1, 68)[d_gid.long()]
+    diff = (mine != d_out.view(-1, 68)).any(1)
+    differing = int(diff.sum().item())
+    equal = differing == 0
+    ptnum = d_out.view(-1, 68)[:, 52:56].contiguous().view(torch.int32).view(-1)
+    mean_nb = float(ptnum.float().mean().item())
+    del d_full, d_fout, mine
+info = torch.tensor([n_own, n_all - n_own, differing if differing is not None else -1], dtype=torch.int64, device=local)
+gathered = [torch.zeros_like(info) for _ in range(world)]
+if world > 1:
+    dist.all_gather(gathered, info)
+else:
+    gathered = [info]
+if rank == 0:
+    res = {"workload": f"configs[3]: urban(seed 4) {n} points over {ext:.0f} m x {ext:.0f} m, radiusSearch r = {r} m + PCA (13-neighbour gate, no stale-record carry), "
+                       f"equal-count x-slabs, halo {h:.4f} m exchanged every step (NCCL send/recv)",
+           "n_gpus": world, "points": n, "steps": args.steps, "scaling": "strong",
+           "points_per_s_wall": n / wall_avg, "ms_per_step_wall_avg": wall_avg * 1e3, "ms_per_step_wall_min": wall_min * 1e3,
+           "ms_per_step_device_events": dev_avg * 1e3, "search_pca_ms_max_rank": search_ms, "grid_ms_max_rank": grid_ms,
+           "per_rank": [{"own_points": int(g[0]), "halo_points": int(g[1]), "halo_bytes": int(g[1]) * 20,
+                         "records_differing_from_unsharded_run": (int(g[2]) if int(g[2]) >= 0 else None)} for g in gathered],
+           "bitwise_equal_to_unsharded_run": (all(int(g[2]) == 0 for g in gathered) if not args.no_verify else None),
+           "generate_s": round(gen_s, 1)}
+    if not args.no_verify:
+        res["mean_ptNum_rank0"] = mean_nb
+    s = json.dumps(res, indent=1)
+    print(s)
+    if args.out:
+        open(args.out, "w").write(s)
+p.synchronize()
+keep.clear()
+del d_own, d_gid, d_out
+torch.cuda.synchronize()
+if world > 1:
+    dist.barrier()
+    dist.destroy_process_group()
+p.close()
