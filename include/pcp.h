@@ -228,6 +228,24 @@ PCP_API int pcp_knn_neighbors(pcp_ctx* ctx, int k, int32_t* idx, float* d2, int 
 PCP_API int pcp_radius_neighbors(pcp_ctx* ctx, float radius, int32_t* counts, const int64_t* offsets,
                                  int32_t* idx, float* d2, int out_is_device);
 
+/* ---- whole-cloud PCA bounding box ---------------------------------------------------
+ * Replaces `pcaAnalysist::getMiniBoundingBox(cloud)` (src/pcaAnalysis.cpp:123-148): centroid
+ * (pcl::compute3DCentroid, :125-126), moment about it with divisor n (:128-129), eigenvectors
+ * ascending with the third axis replaced by col0 x col1 (:131-133), extents of the cloud after the
+ * rigid transform [R | -R c] (:135-146) and meanDiag (:147).  The reference discards all of it;
+ * here it is returned.  Device reductions over the current cloud (no grid needed); `out` is a host
+ * pointer; the call synchronises. */
+typedef struct pcp_obb {
+  float centroid[3];
+  float eigval[3];     /* ascending */
+  float axes[3][3];    /* rows: eigenvector 0, eigenvector 1, their cross product (rows of the rotation R) */
+  float min_pt[3];     /* extents of R (p - centroid) */
+  float max_pt[3];
+  float mean_diag[3];  /* 0.5 (max_pt + min_pt) */
+  int64_t n_points;    /* finite points that entered the sums */
+} pcp_obb;
+PCP_API int pcp_bbox_pca(pcp_ctx* ctx, pcp_obb* out);
+
 /* ---- segment PCA ------------------------------------------------------------------
  * Replaces `pcaAnalysist::calculatePCAofPoint(cloud, centro, idx, fea)`
  * (src/pcaAnalysis.cpp:89-121; caller src/buildingFacadeExtraction.cpp:212-219):

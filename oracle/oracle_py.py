@@ -54,6 +54,7 @@ def load() -> C.CDLL:
         "orc_radius_pca_cloud": (None, [vp, i64, f32, i32, i32, vp, vp, i32]),
         "orc_knn_pca_cloud": (None, [vp, i64, i32, i32, vp, vp, i32]),
         "orc_segment_pca": (None, [vp, vp, vp, vp, i64, vp]),
+        "orc_bbox_pca": (None, [vp, i64, vp]),
         "orc_ring_project": (i32, [vp, i64, i32, i32, f32, f32, f32, vp, vp, vp]),
         "orc_decode_packets": (i64, [vp, i64, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i64, vp]),
         "orc_ring_segment": (i32, [vp, i32, i32, f32, f32, i32, f32, f32, i32, i32, vp, vp, vp, vp, vp, vp, vp]),
@@ -171,6 +172,16 @@ def structure_features(la1, la2, la3):
     o = np.zeros(3, np.float32)
     load().orc_structure_features(la1, la2, la3, o.ctypes.data)
     return o
+
+
+def bbox_pca(pts):
+    """getMiniBoundingBox restated (src/pcaAnalysis.cpp:123-148): dict of centroid, eigval, axes (3x3 rows), min_pt,
+    max_pt, mean_diag."""
+    pts = _f4(pts)
+    out = np.zeros(24, np.float32)
+    load().orc_bbox_pca(pts.ctypes.data, pts.shape[0], out.ctypes.data)
+    return {"centroid": out[0:3], "eigval": out[3:6], "axes": out[6:15].reshape(3, 3), "min_pt": out[15:18], "max_pt": out[18:21],
+            "mean_diag": out[21:24]}
 
 
 def radius_pca_cloud(pts, radius: float, min_pts: int = 13, carry_forward: bool = True, nthreads: int = 1):

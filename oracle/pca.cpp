@@ -236,3 +236,54 @@ extern "C" void orc_segment_pca(const float* xyzi, const float* centres_xyz, con
     out[s] = f;
   }
 }
+
+// pcaAnalysist::getMiniBoundingBox (src/pcaAnalysis.cpp:123-148), statement by statement, with the result returned
+// instead of discarded (and a real cloud where the reference dereferences a null pointer).
+// out: centroid[3], eigval[3], axes[9] (rows: eigenvector 0, eigenvector 1, their cross product), min[3], max[3],
+// mean_diag[3] = 24 floats.
+extern "C" void orc_bbox_pca(const float* xyzi, int64_t n, float* out) {
+  // pcl::compute3DCentroid (:125-126): fp32 running sums in index order, divided by n
+  float sx = 0.f, sy = 0.f, sz = 0.f;
+  for (int64_t i = 0; i < n; ++i) {
+    sx += xyzi[4 * i];
+    sy += xyzi[4 * i + 1];
+    sz += xyzi[4 * i + 2];
+  }
+  const float centre[3] = {sx / (float)n, sy / (float)n, sz / (float)n};
+  // pcl::computeCovarianceMatrixNormalized(cloud, centroid, cov) (:128-129): the whole-cloud overload, same loop
+  std::vector<int32_t> all((size_t)n);
+  for (int64_t i = 0; i < n; ++i) all[(size_t)i] = (int32_t)i;
+  float C[9], ev[3], Q[9];
+  orc_covariance_about(xyzi, all.data(), n, centre, C);
+  orc_eigen_sym3_qr(C, ev, Q);  // :131-132, columns ascending
+  float a[3], b[3], c[3];
+  for (int r = 0; r < 3; ++r) {
+    a[r] = Q[3 * r + 0];
+    b[r] = Q[3 * r + 1];
+  }
+  c[0] = a[1] * b[2] - a[2] * b[1];  // pcaVecs.col(2) = col(0).cross(col(1)) (:133)
+  c[1] = a[2] * b[0] - a[0] * b[2];
+  c[2] = a[0] * b[1] - a[1] * b[0];
+  const float* R[3] = {a, b, c};  // transMatrix.block<3,3>(0,0) = pcaVecs.transpose() (:138)
+  float t[3];
+  for (int k = 0; k < 3; ++k) t[k] = -1.f * (R[k][0] * centre[0] + R[k][1] * centre[1] + R[k][2] * centre[2]);  // :139
+  float lo[3] = {3.4e38f, 3.4e38f, 3.4e38f}, hi[3] = {-3.4e38f, -3.4e38f, -3.4e38f};
+  for (int64_t i = 0; i < n; ++i) {  // pcl::transformPointCloud + pcl::getMinMax3D (:142-145)
+    const float* p = xyzi + 4 * i;
+    for (int k = 0; k < 3; ++k) {
+      const float v = R[k][0] * p[0] + R[k][1] * p[1] + R[k][2] * p[2] + t[k];
+      lo[k] = v < lo[k] ? v : lo[k];
+      hi[k] = v > hi[k] ? v : hi[k];
+    }
+  }
+  for (int k = 0; k < 3; ++k) {
+    out[k] = centre[k];
+    out[3 + k] = ev[k];
+    out[6 + k] = a[k];
+    out[9 + k] = b[k];
+    out[12 + k] = c[k];
+    out[15 + k] = lo[k];
+    out[18 + k] = hi[k];
+    out[21 + k] = 0.5f * (hi[k] + lo[k]);  // meanDiag (:146)
+  }
+}

@@ -82,6 +82,8 @@ void orc_radius_pca_cloud(const float* xyzi, int64_t n, float radius, int min_pt
 void orc_knn_pca_cloud(const float* xyzi, int64_t n, int k, int center_mode, orc_feature68* out,
                        float* normals4, int nthreads);
 /* pcaAnalysist::calculatePCAofPoint(cloud, centro, idx, fea) (src/pcaAnalysis.cpp:89-121) */
+/* pcaAnalysist::getMiniBoundingBox (src/pcaAnalysis.cpp:123-148): 24 floats out (see pca.cpp) */
+void orc_bbox_pca(const float* xyzi, int64_t n, float* out);
 void orc_segment_pca(const float* xyzi, const float* centres_xyz, const int64_t* seg_offsets,
                      const int32_t* seg_idx, int64_t n_seg, orc_feature68* out);
 

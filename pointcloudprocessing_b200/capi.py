@@ -46,6 +46,7 @@ EXPORTS = (
     "pcp_ring_seg_params_default", "pcp_ring_segment", "pcp_decode_packets",
     "pcp_dbscan", "pcp_cluster_boxes", "pcp_mean_shift", "pcp_set_cloud_txt",
     "pcp_radius_count", "pcp_odom_params_default", "pcp_odom_range_image", "pcp_odom_smoothness",
+    "pcp_bbox_pca",
 )
 
 
@@ -107,6 +108,12 @@ class Decoded(C.Structure):
                 ("laser_id", C.c_void_p), ("azimuth", C.c_void_p), ("ms", C.c_void_p)]
 
 
+class Obb(C.Structure):
+    """pcp_obb (include/pcp.h): getMiniBoundingBox's quantities (src/pcaAnalysis.cpp:123-148)."""
+    _fields_ = [("centroid", C.c_float * 3), ("eigval", C.c_float * 3), ("axes", (C.c_float * 3) * 3), ("min_pt", C.c_float * 3),
+                ("max_pt", C.c_float * 3), ("mean_diag", C.c_float * 3), ("n_points", C.c_int64)]
+
+
 class PcpError(RuntimeError):
     def __init__(self, status: int, msg: str):
         super().__init__(f"pcp status {status}: {msg}")
@@ -157,6 +164,7 @@ def load() -> C.CDLL:
         "pcp_knn_neighbors": (i32, [vp, i32, vp, vp, i32]),
         "pcp_radius_neighbors": (i32, [vp, f32, vp, vp, vp, vp, i32]),
         "pcp_segment_pca": (i32, [vp, vp, vp, vp, i64, vp]),
+        "pcp_bbox_pca": (i32, [vp, C.POINTER(Obb)]),
         "pcp_ring_calib_default": (i32, [C.POINTER(RingCalib)]),
         "pcp_ring_calib_from_xml": (i32, [C.c_char_p, C.POINTER(RingCalib)]),
         "pcp_ring_project": (i32, [vp, C.POINTER(RingCalib), vp, i64, vp, vp, vp, i32]),
@@ -396,6 +404,14 @@ class Pcp:
         out = np.zeros(nseg, FEATURE_DTYPE)
         self._ck(self.lib.pcp_segment_pca(self.h, centres.ctypes.data, offsets.ctypes.data, idx.ctypes.data, nseg, out.ctypes.data))
         return out
+
+    def bbox_pca(self) -> dict:
+        """getMiniBoundingBox (src/pcaAnalysis.cpp:123-148) of the current cloud: centroid, eigenvalues, rotation rows, extents."""
+        o = Obb()
+        self._ck(self.lib.pcp_bbox_pca(self.h, C.byref(o)))
+        return {"centroid": np.array(o.centroid, np.float32), "eigval": np.array(o.eigval, np.float32),
+                "axes": np.array([list(r) for r in o.axes], np.float32), "min_pt": np.array(o.min_pt, np.float32),
+                "max_pt": np.array(o.max_pt, np.float32), "mean_diag": np.array(o.mean_diag, np.float32), "n_points": int(o.n_points)}
 
     def ring_project_host_ptr(self, calib: RingCalib, range_ptr: int, index_ptr: int, long_ptr: int,
                               frame_offsets: Optional[np.ndarray] = None):

@@ -60,6 +60,12 @@ constexpr int T5_NB = 63;       // bins 0..62 inside the cover radius, bin 63 = 
 constexpr float T5_MAGIC = 8388608.f;        // 2^23: float_as_uint(x + 2^23) - 0x4B000000 = round-to-nearest-even(x), 0 <= x < 2^22
 constexpr uint32_t T5_MAGIC_BITS = 0x4B000000u;
 constexpr int T5_REC_WORDS = 17;
+#ifndef T5_PRED63
+#define T5_PRED63 0   // 1: candidates at or beyond the cover radius (bin 63, never read by the scan) skip the shared reduction
+#endif
+#ifndef T5_SYNC
+#define T5_SYNC 1     // CTA barriers around the straight-line sorting network (instruction-cache alignment of the four warps)
+#endif
 
 struct __align__(16) T5Smem {
   float4 cand[T5_CH];                    // staged candidates of the current chunk: local x, y, z and |p'|^2
@@ -100,6 +106,14 @@ __device__ __forceinline__ void sts_u32(const uint32_t addr, const uint32_t v) {
 }
 __device__ __forceinline__ void red_add_u32(const uint32_t addr, const uint32_t v) {
   asm volatile("red.shared.add.u32 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
+}
+// histogram update of one candidate: z = 2^23 + bin as a float
+__device__ __forceinline__ void hist_add(const float z, const uint32_t hbase, const uint32_t inc) {
+#if T5_PRED63
+  if (z < T5_MAGIC + (float)T5_NB) red_add_u32(__float_as_uint(z) * 128u + hbase, inc);
+#else
+  red_add_u32(__float_as_uint(z) * 128u + hbase, inc);
+#endif
 }
 __device__ __forceinline__ uint32_t smem_addr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
@@ -232,12 +246,12 @@ __global__ void __launch_bounds__(T5_WARPS * 32, 5) knn_tile5_kernel(KArgs a, in
           const float4 P0 = lds_f4<0>(ca), P1 = lds_f4<16>(ca), P2 = lds_f4<32>(ca), P3 = lds_f4<48>(ca);
           const float z0 = bin_z(P0, S, K, A0, A1, A2), z1 = bin_z(P1, S, K, A0, A1, A2);
           const float z2 = bin_z(P2, S, K, A0, A1, A2), z3 = bin_z(P3, S, K, A0, A1, A2);
-          red_add_u32(__float_as_uint(z0) * 128u + hbase, inc);
-          red_add_u32(__float_as_uint(z1) * 128u + hbase, inc);
-          red_add_u32(__float_as_uint(z2) * 128u + hbase, inc);
-          red_add_u32(__float_as_uint(z3) * 128u + hbase, inc);
+          hist_add(z0, hbase, inc);
+          hist_add(z1, hbase, inc);
+          hist_add(z2, hbase, inc);
+          hist_add(z3, hbase, inc);
         }
-        for (; j < n_ch; ++j, ca += 16) red_add_u32(__float_as_uint(bin_z(lds_f4<0>(ca), S, K, A0, A1, A2)) * 128u + hbase, inc);
+        for (; j < n_ch; ++j, ca += 16) hist_add(bin_z(lds_f4<0>(ca), S, K, A0, A1, A2), hbase, inc);
         __syncwarp();
       }
       // the bin holding the k-th smallest, and how many candidates lie at or below it
@@ -376,7 +390,9 @@ __global__ void __launch_bounds__(T5_WARPS * 32, 5) knn_tile5_kernel(KArgs a, in
   // The sorting network and the finish stage are ~50 KB of straight-line code walked once per tile: the warps of a
   // CTA re-align here so that they fetch it together (one miss serves four warps) instead of evicting each
   // other's lines.
+#if T5_SYNC
   __syncthreads();
+#endif
   // ---- order the collected keys by (d2, index)
   {
     u64 keys[CAP];
@@ -411,7 +427,9 @@ __global__ void __launch_bounds__(T5_WARPS * 32, 5) knn_tile5_kernel(KArgs a, in
   const int n_nb = ok ? k : 0;
   const bool emit = active && (ok || !finite);  // non-finite queries get their empty record here
   __syncwarp();
+#if T5_SYNC
   __syncthreads();
+#endif
   if (!live_warp) return;
   knn_finish(a, hcol, hcol + CAP * 32, 32, n_nb, 1, Q, emit ? my_slot : -1, sm.u.rec, lane);
 }

@@ -99,6 +99,7 @@ struct pcp_ctx {
   DevBuf work_list, work_count;  // k-NN queries deferred by the tile kernel (sorted positions)
   DevBuf out_feat, out_norm, out_idx, out_d2, out_counts, flags, valid, last_valid, staging;
   DevBuf ring_range, ring_idx, ring_long, ring_offsets, ring_key;
+  DevBuf obb;         // pcp_bbox_pca: sums, extents and the result
   DevBuf halo_done;   // block counter of halo_pad_signal_kernel
   DevBuf dec_tables, dec_packed, dec_out;  // pcp_decode_packets: azimuth cos/sin tables, per-block scan, staged outputs
   DevBuf odom_counts, odom_range, odom_ptid, odom_index, odom_stats, odom_minmax, odom_smooth, odom_type;  // lidarOdometry images

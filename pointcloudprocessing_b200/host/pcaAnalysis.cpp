@@ -148,36 +148,10 @@ bool pcaAnalysist::getMiniBoundingBox(pcXYZIptr inputCloud) {
   if (!ctx) return false;
   int rc = ensure_cloud(ctx, *inputCloud);
   if (rc) return fail(ctx, "getMiniBoundingBox", rc);
-  // pcl::compute3DCentroid: fp32 running sum / n (src/pcaAnalysis.cpp:125-126)
-  const size_t n = inputCloud->points.size();
-  float sx = 0.f, sy = 0.f, sz = 0.f;
-  for (const pcl::PointXYZI& p : inputCloud->points) {
-    sx += p.x;
-    sy += p.y;
-    sz += p.z;
-  }
-  const float centre[3] = {sx / (float)n, sy / (float)n, sz / (float)n};
-  std::vector<int> all(n);
-  for (size_t i = 0; i < n; ++i) all[i] = (int)i;
-  const int64_t offs[2] = {0, (int64_t)n};
-  pcp_feature68 r;
-  if ((rc = pcp_segment_pca(ctx, centre, offs, all.data(), 1, &r))) return fail(ctx, "getMiniBoundingBox", rc);
-  // right-handed frame col2 = col0 × col1 (:133), rigid transform, extents (:137-146); like the
-  // reference the result is not returned to the caller
-  const float* a = r.v1;
-  const float* b = r.v2;
-  const float c[3] = {a[1] * b[2] - a[2] * b[1], a[2] * b[0] - a[0] * b[2], a[0] * b[1] - a[1] * b[0]};
-  float lo[3] = {3.4e38f, 3.4e38f, 3.4e38f}, hi[3] = {-3.4e38f, -3.4e38f, -3.4e38f};
-  for (const pcl::PointXYZI& p : inputCloud->points) {
-    const float d[3] = {p.x - centre[0], p.y - centre[1], p.z - centre[2]};
-    const float t[3] = {a[0] * d[0] + a[1] * d[1] + a[2] * d[2], b[0] * d[0] + b[1] * d[1] + b[2] * d[2],
-                        c[0] * d[0] + c[1] * d[1] + c[2] * d[2]};
-    for (int k = 0; k < 3; ++k) {
-      lo[k] = t[k] < lo[k] ? t[k] : lo[k];
-      hi[k] = t[k] > hi[k] ? t[k] : hi[k];
-    }
-  }
-  (void)lo;
-  (void)hi;
+  // centroid, moment, eigen-solve, right-handed frame, rigid transform and extents (:125-147) as device reductions over the
+  // resident cloud; like the reference the result is not returned to the caller
+  pcp_obb box;
+  if ((rc = pcp_bbox_pca(ctx, &box))) return fail(ctx, "getMiniBoundingBox", rc);
+  (void)box;
   return true;
 }

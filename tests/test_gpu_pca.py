@@ -172,3 +172,31 @@ def test_radius_pca_small_cell(pcp, oracle, div):
     ref, valid = oracle.radius_pca_cloud(pts, r, 13, True, nthreads=0)
     assert np.array_equal(got["ptNum"], ref["ptNum"])
     check_features(got, ref, valid, f"radius cell=r/{div}")
+
+
+def test_bbox_pca(pcp, oracle):
+    """getMiniBoundingBox (src/pcaAnalysis.cpp:123-148) as device reductions: against the statement-by-statement restatement
+    (whose fp32 running sums carry ~1e-4 on a cloud of this size) and against an fp64 evaluation."""
+    pts = synth.urban(5, 200000, extent=60.0)
+    pts[::1000, 1] = np.nan  # non-finite points do not enter the sums
+    fin = np.isfinite(pts[:, :3]).all(1)
+    pcp.set_cloud(pts)
+    got = pcp.bbox_pca()
+    assert got["n_points"] == int(fin.sum())
+    ref = oracle.bbox_pca(pts[fin])
+    x = pts[fin, :3].astype(np.float64)
+    c = x.mean(0)
+    w, v = np.linalg.eigh(np.cov((x - c).T, bias=True))
+    assert np.abs(got["centroid"] - c).max() < 1e-5 * 60
+    assert np.abs(got["eigval"] - w).max() < 1e-5 * w.max()
+    assert np.abs(got["centroid"] - ref["centroid"]).max() < 2e-3 and np.abs(got["eigval"] - ref["eigval"]).max() < 2e-3 * w.max()
+    R = got["axes"].astype(np.float64)
+    assert np.allclose(R @ R.T, np.eye(3), atol=1e-5) and np.linalg.det(R) > 0.999  # right-handed: row 2 = row 0 x row 1
+    for kk in range(2):
+        assert 1 - abs(R[kk] @ v[:, kk]) < 1e-5
+    t = (x - c) @ R.T
+    assert np.abs(got["min_pt"] - t.min(0)).max() < 1e-3 and np.abs(got["max_pt"] - t.max(0)).max() < 1e-3
+    assert np.allclose(got["mean_diag"], 0.5 * (got["min_pt"] + got["max_pt"]), atol=1e-5)
+    # the restatement agrees up to eigenvector signs and its fp32 sums
+    s = np.sign((got["axes"] * ref["axes"]).sum(1))
+    assert np.abs(got["axes"] - s[:, None] * ref["axes"]).max() < 2e-3
