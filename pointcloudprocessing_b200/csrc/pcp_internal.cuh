@@ -44,7 +44,7 @@ struct DevBuf {
 
 // Environment knobs (A/B timing and tests), read ONCE in pcp_create — never on the launch path.
 struct PcpKnobs {
-  int knn_impl = 0;        // PCP_KNN_IMPL: 0 = tile kernel of knn_tile5.cu + work list (default), 4 = "tile4": the round-1
+  int knn_impl = 0;        // PCP_KNN_IMPL: 0 = tile kernel of knn_tile6.cu + work list (default), 4 = "tile4": the round-1
                            // tile kernel (knn_tile.cu), 3 = "v3": the warp-per-query kernel for every point
   int knn_groups = 0;      // PCP_KNN_GROUPS: stencil rows served per tile (0 = automatic)
   int radius_impl = 0;     // PCP_RADIUS_IMPL: 0 = automatic, 1 = "tile" (32-entry lanes), 2 = "tile64", 3 = "v3"
@@ -152,5 +152,7 @@ struct SearchParams {
 int pcp_search_launch(pcp_ctx* ctx, const SearchParams& sp);  // radius (and the v3 warp-per-query k-NN, A/B only)
 struct KArgs;
 int pcp_knn_tile_launch(pcp_ctx* ctx, const SearchParams& sp, const KArgs& a, int radius_cap);  // k-NN tile kernel (knn_tile.cu)
-int pcp_knn_tile5_launch(pcp_ctx* ctx, const SearchParams& sp, const KArgs& a);  // k-NN tile kernel, round-2 form (knn_tile5.cu)
+int pcp_knn_tile6_launch(pcp_ctx* ctx, const SearchParams& sp, const KArgs& a);  // k-NN tile kernel (knn_tile6.cu): k <= PCP_T6_KMAX
+#define PCP_T6_K32 24   // 32-member lanes up to this k, 64-member lanes above
+#define PCP_T6_KMAX 32   // (the work-list kernel that finishes the deferred lanes keeps one key per lane)
 int pcp_carry_forward_impl(pcp_ctx* ctx, pcp_feature68* d_out, const uint8_t* d_valid, int64_t n);

@@ -669,7 +669,7 @@ extern "C" __attribute__((visibility("default"))) int pcp_debug_stats(unsigned l
 
 int pcp_search_launch(pcp_ctx* ctx, const SearchParams& sp) {
   // PCP_KNN_IMPL (read once in pcp_create) selects the k-NN kernel for A/B timing: default = tile kernel of
-  // knn_tile5.cu + this file's warp-per-query kernel for the queries it defers; "tile4" = the round-1 tile
+  // knn_tile6.cu + this file's warp-per-query kernel for the queries it defers; "tile4" = the round-1 tile
   // kernel (knn_tile.cu) instead; "v3" = warp-per-query for every point.  All give identical results.
   const PcpKnobs& kn = ctx->knobs;
   const bool use_v3 = sp.mode == 0 && kn.knn_impl == 3;
@@ -707,7 +707,7 @@ int pcp_search_launch(pcp_ctx* ctx, const SearchParams& sp) {
     if (sp.R0 > 3) radius_tile = false;
   }
   if ((sp.mode == 0 && !use_v3) || radius_tile) {
-    int rc = (sp.mode == 0 && kn.knn_impl != 4) ? pcp_knn_tile5_launch(ctx, sp, a) : pcp_knn_tile_launch(ctx, sp, a, radius_cap);
+    int rc = (sp.mode == 0 && kn.knn_impl == 0) ? pcp_knn_tile6_launch(ctx, sp, a) : pcp_knn_tile_launch(ctx, sp, a, radius_cap);
     if (rc) return rc;
     // one wave of resident CTAs (3 per SM at 80 registers); tiles of 16 list entries drawn by ticket
     // (tuning hooks: PCP_WL_BLOCKS, PCP_WL_TILE)

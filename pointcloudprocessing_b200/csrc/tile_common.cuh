@@ -1,4 +1,4 @@
-// tile_common.cuh — what the tile kernels (knn_tile.cu: radius search, knn_tile5.cu: k-NN) share: the stencil rows of a
+// tile_common.cuh — what the tile kernels (knn_tile.cu: radius search, knn_tile6.cu: k-NN) share: the stencil rows of a
 // tile of 32 cell-sorted queries as contiguous runs of the sorted point array, and every lane's cover radius.
 #pragma once
 #include "pcp_internal.cuh"

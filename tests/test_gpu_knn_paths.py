@@ -1,4 +1,4 @@
-"""GPU: the k-NN kernels (tile kernel of knn_tile5.cu + work-list kernel = the product path; PCP_KNN_IMPL=tile4 / v3 =
+"""GPU: the k-NN kernels (tile kernel of knn_tile6.cu + work-list kernel = the product path; PCP_KNN_IMPL=tile4 / v3 =
 the round-1 tile kernel and the warp-per-query kernel kept for A/B timing; the variable is read when a context is
 created) must give bit-identical neighbour lists, equal to the oracle's, on
 the inputs that stress the hand-over between them: exact ties, duplicates, sparse and tiny clouds, k

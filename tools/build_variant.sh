@@ -8,7 +8,7 @@ NV="/usr/local/cuda/bin/nvcc $DEFS -O3 -std=c++17 -lineinfo -gencode arch=comput
 OBJS=""
 for f in *.cu; do
   o=${f%.cu}.o
-  if [ "$f" = knn_tile5.cu ] || [ "$f" = search_pca.cu ] || [ "$f" = knn_finish.cuh ]; then $NV -c $f -o $OUT/obj_$NAME/$o & OBJS="$OBJS $OUT/obj_$NAME/$o"; else OBJS="$OBJS $o"; fi
+  if [ "$f" = knn_tile6.cu ] || [ "$f" = search_pca.cu ]; then $NV -c $f -o $OUT/obj_$NAME/$o & OBJS="$OBJS $OUT/obj_$NAME/$o"; else OBJS="$OBJS $o"; fi
 done
 wait
 /usr/local/cuda/bin/nvcc -shared -gencode arch=compute_100a,code=sm_100a -ccbin /usr/bin/g++ -o $OUT/libpcp_$NAME.so $OBJS -lcudart_static -lpthread -ldl -lrt

@@ -15,9 +15,9 @@ p.set_cloud(cloud)
 for cell in (0.0, 0.3, 0.5, 1.5, 2.5):
     p.set_frames(offs)
     p.build_grid(cell, k)
-    lib.pcp_debug_tile_stats(st)
+    lib.pcp_debug_tile6_stats(st)
     p.knn_pca(k)
-    lib.pcp_debug_tile_stats(st)
+    lib.pcp_debug_tile6_stats(st)
     q = st[0]
     t = p.timings()
-    print(f"cell {p.grid_info()[1]:.3f} search {t['search_pca']:.2f} ms queries {q} deferred {st[1] / q:.4f} staged/tile {st[2] * 32 / q:.1f} sorted_in/ok {st[3] / max(q - st[1], 1):.2f} | other-row {st[4] / q:.4f} uncovered {st[5] / q:.4f} bin-full {st[6] / q:.4f} refined {st[9] / q:.4f}", flush=True)
+    print(f"cell {p.grid_info()[1]:.3f} search {t['search_pca']:.2f} ms queries {q} deferred {st[1] / q:.4f} staged/tile {st[2] * 32 / q:.1f} sorted_in/ok {st[3] / max(q - st[1], 1):.2f} | other-row {st[4] / q:.4f} uncovered {st[5] / q:.4f} bin-full {st[6] / q:.4f} refined {st[9] / q:.4f} unproven {st[10] / q:.5f} kept-in-pass2/tile {st[8] * 32 / q:.1f}", flush=True)

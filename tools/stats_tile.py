@@ -12,8 +12,8 @@ st = (ctypes.c_ulonglong * 16)()
 p.set_cloud(pts)
 for cell in [float(c) for c in (sys.argv[3].split(",") if len(sys.argv) > 3 else ["0"])]:
     p.build_grid(cell, k)
-    lib.pcp_debug_tile5_stats(st)
+    lib.pcp_debug_tile6_stats(st)
     p.knn_pca(k)
-    lib.pcp_debug_tile5_stats(st)
+    lib.pcp_debug_tile6_stats(st)
     q = st[0]
     print(f"cell {p.grid_info()[1]:.3f} queries {q} deferred {st[1] / q:.4f} staged/tile {st[2] * 32 / q:.1f} sorted_in/ok {st[3] / max(q - st[1], 1):.2f} | other-row {st[4] / q:.4f} uncovered {st[5] / q:.4f} bin-full {st[6] / q:.4f} refined {st[9] / q:.4f} unproven {st[10] / q:.5f} kept-in-pass2/tile {st[8] * 32 / q:.1f}", flush=True)
