@@ -346,7 +346,7 @@ def main():
         torch.cuda.synchronize()
         dist.barrier()
 
-    def shard_step(src_pts):
+    def shard_step(src_pts, out=None):
         # halo classification kernel + grouped NCCL send/recv + sharded hand-over, all enqueued on the
         # library's stream: the exchange needs no host synchronisation (sizes are fixed)
         with torch.cuda.stream(stream):
@@ -354,7 +354,7 @@ def main():
                 ex.own_pts.copy_(src_pts, non_blocking=True)
             ex.step()
         p.build_grid(args.cell, k)
-        p.knn_pca(k, capi.CENTER_QUERY, out_device=d_out.data_ptr(), kth_device=d_kth.data_ptr())
+        p.knn_pca(k, capi.CENTER_QUERY, out_device=(d_out if out is None else out).data_ptr(), kth_device=d_kth.data_ptr())
 
     def step_device():
         if world > 1:
@@ -460,6 +460,49 @@ def main():
         parity_checked, parity_note = check_parity(args, p, stream, pts, d_out, n, k, rank, world, local, step_device)
         barrier()
 
+    if world > 1:
+        # (b') N > 1, one context per rank: the copies run on two streams of their own, double-buffered, so that the
+        # upload of step s + 1 and the download of step s - 1 overlap the exchange / grid / search of step s; every step
+        # still moves its 16 n bytes up from pinned memory and its 68 n bytes down
+        cs_in, cs_out = torch.cuda.Stream(device=local), torch.cuda.Stream(device=local)
+        d_in2 = [torch.empty_like(d_pts) for _ in range(2)]
+        d_out2 = [torch.empty_like(d_out) for _ in range(2)]
+        h_out2 = [h_out, torch.empty(n * 68, dtype=torch.uint8).pin_memory()]
+        ev_in = [torch.cuda.Event() for _ in range(2)]
+        ev_cmp = [torch.cuda.Event() for _ in range(2)]
+        ev_out = [torch.cuda.Event() for _ in range(2)]
+
+        def step_pipe(s):
+            b = s & 1
+            with torch.cuda.stream(cs_in):
+                if s >= 2:
+                    cs_in.wait_event(ev_cmp[b])  # step s - 2 has consumed d_in2[b]
+                d_in2[b].copy_(h_in, non_blocking=True)
+                ev_in[b].record(cs_in)
+            stream.wait_event(ev_in[b])
+            if s >= 2:
+                stream.wait_event(ev_out[b])  # the records of step s - 2 have left d_out2[b]
+            shard_step(d_in2[b], d_out2[b])
+            ev_cmp[b].record(stream)
+            with torch.cuda.stream(cs_out):
+                cs_out.wait_event(ev_cmp[b])
+                h_out2[b].copy_(d_out2[b], non_blocking=True)
+                ev_out[b].record(cs_out)
+
+        for s in range(4):
+            step_pipe(s)
+        torch.cuda.synchronize()
+        barrier()
+        t0 = time.perf_counter()
+        for s in range(args.steps):
+            step_pipe(s + 4)
+        torch.cuda.synchronize()
+        e2e_s = time.perf_counter() - t0
+        e2e_mode = ("one context per rank; upload and download on their own streams, double-buffered (upload of step s + 1 and download of "
+                    "step s - 1 overlap the halo exchange + grid + search of step s); each step = H2D cloud + exchange + grid + search + D2H records")
+        barrier()
+        del d_in2, d_out2, h_out2, ev_in, ev_cmp, ev_out, cs_in, cs_out
+
     t = torch.tensor([dev_ms, e2e_s * 1e3, kern_ms, float(parity_checked)], dtype=torch.float64, device=local)
     if world > 1:
         # parity counts add up over the ranks; the timings take the slowest rank
@@ -511,7 +554,9 @@ def main():
                                 "sample": f"spatial tile of {mall} points (all cores, {dt:.1f} s) / {m1} points (1 core) of the same cloud"}
     if rank == 0:
         emit_line(line)
-    # orderly teardown: tensors that lived on the library's stream go first, then the stream itself
+    # Orderly teardown, so that the process can simply return (no os._exit): EVERY torch object that was used on the
+    # library's stream goes before the stream does — device tensors, the pinned host tensors (torch's host allocator
+    # records an event on each stream a block was used on when the block is freed), the events and the stream wrapper.
     p.synchronize()
     keep.clear()
     if world > 1:
@@ -519,12 +564,19 @@ def main():
         if hasattr(ex, "close"):
             ex.close()
     ex = None
-    del d_pts, d_out, d_kth, flush, d_gid
+    del d_pts, d_out, d_kth, flush, d_gid, h_in, h_out, ev, t
+    if world == 1:
+        del h_outs
+    import gc
+
+    gc.collect()
     torch.cuda.synchronize()
     torch.cuda.empty_cache()
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
+    del stream
+    gc.collect()
     p.close()
     sys.stdout.flush()
 
