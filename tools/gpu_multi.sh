@@ -4,8 +4,6 @@ N=$1; TAG=${2:-r02}
 mkdir -p gpurun_out
 RUN="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1"
 if [ "$N" = 1 ]; then RUNC="python"; else RUNC="$RUN --master-port 29511"; fi
-timeout 600 $RUNC tools/cfg3_scaling.py --n 4000000 --steps 3 > gpurun_out/${TAG}_cfg3_small_${N}gpu.json 2> gpurun_out/${TAG}_cfg3_small_${N}gpu.err; echo "cfg3 small rc=$?"
-grep -E "bitwise|points_per_s_wall" gpurun_out/${TAG}_cfg3_small_${N}gpu.json
 timeout 1500 $RUNC tools/cfg3_scaling.py --steps 5 --out gpurun_out/${TAG}_cfg3_${N}gpu.json > /dev/null 2> gpurun_out/${TAG}_cfg3_${N}gpu.err; echo "cfg3 rc=$?"
 grep -E "bitwise|points_per_s_wall|ms_per_step" gpurun_out/${TAG}_cfg3_${N}gpu.json; tail -3 gpurun_out/${TAG}_cfg3_${N}gpu.err
 if [ "$N" != 1 ]; then
