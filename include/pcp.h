@@ -228,6 +228,21 @@ PCP_API int pcp_knn_neighbors(pcp_ctx* ctx, int k, int32_t* idx, float* d2, int 
 PCP_API int pcp_radius_neighbors(pcp_ctx* ctx, float radius, int32_t* counts, const int64_t* offsets,
                                  int32_t* idx, float* d2, int out_is_device);
 
+/* ---- stale-record carry without any allocation ----------------------------------------
+ * NO COUNTERPART IN THE REFERENCE: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  It is the stale-record
+ * carry that pcp_radius_pca(carry_forward = 1) applies (a record below the min_pts gate repeats everything but
+ * ptID / ptNum of the last record at or above it; leading ones keep their own words), as a call of its own whose
+ * scratch lives in a static device array inside libpcp.so instead of cudaMalloc'ed buffers:
+ *   - d_in / d_out: DEVICE pointers to n records (they may be the same pointer); a record is valid when ptNum >= min_pts;
+ *   - n <= pcp_carry_forward_static_max() = 1 048 576 records, else PCP_ERR_INVALID_ARG (4 MiB + 4 KiB of device
+ *     memory are held by every GPU that loads the library, until exit);
+ *   - asynchronous on the context's stream; calls no cudaMalloc / cudaFree / allocating routine;
+ *   - every call on a GPU shares the scratch array: calls that overlap on one GPU (two contexts) race — serialise them;
+ *   - one cloud per call (frame batches: call once per frame). */
+PCP_API int pcp_carry_forward_static(pcp_ctx* ctx, const pcp_feature68* d_in, pcp_feature68* d_out, int64_t n, int min_pts);
+PCP_API int64_t pcp_carry_forward_static_max(void);
+
 /* ---- whole-cloud PCA bounding box ---------------------------------------------------
  * Replaces `pcaAnalysist::getMiniBoundingBox(cloud)` (src/pcaAnalysis.cpp:123-148): centroid
  * (pcl::compute3DCentroid, :125-126), moment about it with divisor n (:128-129), eigenvectors

@@ -46,7 +46,7 @@ EXPORTS = (
     "pcp_ring_seg_params_default", "pcp_ring_segment", "pcp_decode_packets",
     "pcp_dbscan", "pcp_cluster_boxes", "pcp_mean_shift", "pcp_set_cloud_txt",
     "pcp_radius_count", "pcp_odom_params_default", "pcp_odom_range_image", "pcp_odom_smoothness",
-    "pcp_bbox_pca",
+    "pcp_bbox_pca", "pcp_carry_forward_static", "pcp_carry_forward_static_max",
 )
 
 
@@ -165,6 +165,8 @@ def load() -> C.CDLL:
         "pcp_radius_neighbors": (i32, [vp, f32, vp, vp, vp, vp, i32]),
         "pcp_segment_pca": (i32, [vp, vp, vp, vp, i64, vp]),
         "pcp_bbox_pca": (i32, [vp, C.POINTER(Obb)]),
+        "pcp_carry_forward_static": (i32, [vp, vp, vp, i64, i32]),
+        "pcp_carry_forward_static_max": (i64, []),
         "pcp_ring_calib_default": (i32, [C.POINTER(RingCalib)]),
         "pcp_ring_calib_from_xml": (i32, [C.c_char_p, C.POINTER(RingCalib)]),
         "pcp_ring_project": (i32, [vp, C.POINTER(RingCalib), vp, i64, vp, vp, vp, i32]),
@@ -404,6 +406,10 @@ class Pcp:
         out = np.zeros(nseg, FEATURE_DTYPE)
         self._ck(self.lib.pcp_segment_pca(self.h, centres.ctypes.data, offsets.ctypes.data, idx.ctypes.data, nseg, out.ctypes.data))
         return out
+
+    def carry_forward_static(self, d_in: int, d_out: int, n: int, min_pts: int = 13):
+        """Stale-record carry on DEVICE records with the library's static scratch (no allocation): pcp_carry_forward_static."""
+        self._ck(self.lib.pcp_carry_forward_static(self.h, d_in, d_out, n, min_pts))
 
     def bbox_pca(self) -> dict:
         """getMiniBoundingBox (src/pcaAnalysis.cpp:123-148) of the current cloud: centroid, eigenvalues, rotation rows, extents."""
