@@ -431,8 +431,17 @@ PCP_API int pcp_mean_shift(pcp_ctx* ctx, float radius, int min_pts, int iteratio
  * not parse becomes 0 and ends the line, values are the correctly rounded floats strtof gives (exact for up to
  * 19 significant digits).  The points become the CURRENT CLOUD of the context; *n_points (HOST) receives their
  * number and out_xyzi (optional, n x 4 floats, host or device, capacity in points) a copy.  Synchronises.
- * preprocess::xyz2pc (:83-125) is not offered: it sscanf's a %s into a single char (undefined upstream). */
+ * preprocess::xyz2pc (:83-125) has its own entry point below. */
 PCP_API int pcp_set_cloud_txt(pcp_ctx* ctx, const void* text, int64_t n_bytes, int text_is_device, int64_t* n_points,
+                              float* out_xyzi, int64_t out_capacity, int out_is_device);
+/* Replaces preprocess::xyz2pc (src/smoothing.cpp:83-125): `while (!eof()) { getline(line, 256); sscanf(line, "%f %f %f %s",
+ * &x, &y, &z, &intens); intensity = intens; push_back }` — three floats and the FIRST BYTE of the fourth token as a
+ * signed char (the reference scans %s into one char: the overflow is the one undefined part and is not reproduced);
+ * a field that does not parse ends the line and keeps the previous line's value, as every field after it; a value
+ * beyond the float range becomes +-inf; the eof() loop pushes one more copy of the last point after a final newline
+ * (and one zero point for an empty file).  A line of 255 characters or more is PCP_ERR_INVALID_ARG (the reference
+ * never returns from it).  inf / nan / hexadecimal fields are not recognised.  Same arguments as pcp_set_cloud_txt. */
+PCP_API int pcp_set_cloud_xyz(pcp_ctx* ctx, const void* text, int64_t n_bytes, int text_is_device, int64_t* n_points,
                               float* out_xyzi, int64_t out_capacity, int out_is_device);
 
 #ifdef __cplusplus

@@ -65,6 +65,7 @@ def load() -> C.CDLL:
         "orc_cluster_boxes": (None, [vp, i64, vp, i32, vp, vp, vp, vp]),
         "orc_mean_shift_step": (None, [vp, vp, i64, f32, i32, vp, vp, vp]),
         "orc_txt2pc": (i64, [C.c_char_p, i64, vp, i64]),
+        "orc_xyz2pc": (i64, [C.c_char_p, i64, vp, i64]),
         "orc_num_threads": (i32, []),
     }
     for name, (res, args) in sig.items():
@@ -326,3 +327,12 @@ def txt2pc(text: bytes):
     out = np.zeros((cap, 4), np.float32)
     n = load().orc_txt2pc(text, len(text), out.ctypes.data, cap)
     return out[:n].copy()
+
+
+def xyz2pc(text: bytes):
+    """preprocess::xyz2pc (src/smoothing.cpp:83-125) on an in-memory file: (n_points, 4) float32; None when a line has 255
+    characters or more (the reference's loop never ends on such a file)."""
+    cap = text.count(b"\n") + 2
+    out = np.zeros((cap, 4), np.float32)
+    n = load().orc_xyz2pc(text, len(text), out.ctypes.data, cap)
+    return None if n < 0 else out[:n].copy()

@@ -28,3 +28,34 @@ extern "C" int64_t orc_txt2pc(const char* text, int64_t n_bytes, float* out_xyzi
   }
   return count;
 }
+
+// preprocess::xyz2pc (src/smoothing.cpp:83-125), the reference's own statements on this image's C library:
+//   while (!xyzfile.eof()) { xyzfile.getline(line, 256); sscanf(line, "%f %f %f %s", &pt.x, &pt.y, &pt.z, &intens);
+//                            pt.intensity = intens; origiCloud.push_back(pt); }
+// with ONE change that keeps the run defined: the reference scans "%s" into a single `char` (any token overflows it
+// by at least the terminating NUL); here the token lands in a line-sized buffer and its first byte is what the
+// reference's `intens` would hold.  `intens` and `pt` live across lines as upstream (fields a line does not
+// supply keep their previous values; the reference's are uninitialised at first, here 0).  Returns the number of
+// points, or -1 when a line has 255 characters or more (getline(line, 256) then sets failbit and the reference's
+// loop never ends).
+#include <cstdio>
+extern "C" int64_t orc_xyz2pc(const char* text, int64_t n_bytes, float* out_xyzi, int64_t capacity) {
+  std::istringstream xyzfile(std::string(text, (size_t)n_bytes));
+  float pt[4] = {0.f, 0.f, 0.f, 0.f};
+  char line[256];
+  char token[256];
+  char intens = 0;
+  int64_t count = 0;
+  while (!xyzfile.eof()) {
+    xyzfile.getline(line, 256);
+    if (xyzfile.fail() && !xyzfile.eof()) return -1;  // 255 characters without a newline
+    token[0] = intens;
+    const int got = std::sscanf(line, "%f %f %f %255s", &pt[0], &pt[1], &pt[2], token);
+    if (got == 4) intens = token[0];
+    pt[3] = intens;  // char -> float (signed on this platform, as on the reference's)
+    if (count < capacity)
+      for (int a = 0; a < 4; ++a) out_xyzi[4 * count + a] = pt[a];
+    ++count;
+  }
+  return count;
+}

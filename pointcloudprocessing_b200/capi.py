@@ -46,7 +46,7 @@ EXPORTS = (
     "pcp_ring_seg_params_default", "pcp_ring_segment", "pcp_decode_packets",
     "pcp_dbscan", "pcp_cluster_boxes", "pcp_mean_shift", "pcp_set_cloud_txt",
     "pcp_radius_count", "pcp_odom_params_default", "pcp_odom_range_image", "pcp_odom_smoothness",
-    "pcp_bbox_pca", "pcp_carry_forward_static", "pcp_carry_forward_static_max",
+    "pcp_bbox_pca", "pcp_carry_forward_static", "pcp_carry_forward_static_max", "pcp_set_cloud_xyz",
 )
 
 
@@ -175,6 +175,7 @@ def load() -> C.CDLL:
         "pcp_radius_count": (i32, [vp, f32, i32, vp, i32]),
         "pcp_dbscan": (i32, [vp, f32, i32, vp, vp, i32]),
         "pcp_set_cloud_txt": (i32, [vp, vp, i64, i32, vp, vp, i64, i32]),
+        "pcp_set_cloud_xyz": (i32, [vp, vp, i64, i32, vp, vp, i64, i32]),
         "pcp_cluster_boxes": (i32, [vp, vp, i32, i32, vp, vp, vp, vp]),
         "pcp_mean_shift": (i32, [vp, f32, i32, i32, vp, i32, vp, vp, i32]),
         "pcp_odom_params_default": (i32, [C.POINTER(OdomParams)]),
@@ -564,5 +565,15 @@ class Pcp:
         out = np.zeros((cap, 4), np.float32)
         n = C.c_int64()
         self._ck(self.lib.pcp_set_cloud_txt(self.h, buf.ctypes.data if len(text) else None, len(text), 0, C.addressof(n), out.ctypes.data, cap, 0))
+        self.n = self.n_query = int(n.value)
+        return out[: int(n.value)].copy()
+
+    def set_cloud_xyz(self, text: bytes) -> np.ndarray:
+        """preprocess::xyz2pc on the device (pcp_set_cloud_xyz): the parsed points become the current cloud; returns them (n, 4)."""
+        buf = np.frombuffer(text, np.uint8)
+        cap = text.count(b"\n") + 2
+        out = np.zeros((cap, 4), np.float32)
+        n = C.c_int64()
+        self._ck(self.lib.pcp_set_cloud_xyz(self.h, buf.ctypes.data if len(text) else None, len(text), 0, C.addressof(n), out.ctypes.data, cap, 0))
         self.n = self.n_query = int(n.value)
         return out[: int(n.value)].copy()

@@ -27,7 +27,7 @@ int pcp_cluster_boxes_impl(pcp_ctx* ctx, const int32_t* d_labels, int n_clusters
                            int32_t* d_counts);
 int pcp_mean_shift_impl(pcp_ctx* ctx, const float4* d_cur, float r2, int R, int min_pts, float4* d_next, int32_t* d_counts);
 
-int pcp_parse_txt_impl(pcp_ctx* ctx, const unsigned char* d_text, int64_t n_bytes, int64_t* n_lines_out);
+int pcp_parse_txt_impl(pcp_ctx* ctx, const unsigned char* d_text, int64_t n_bytes, int64_t* n_lines_out, int xyz, int* too_long_out);
 
 namespace {
 
@@ -631,24 +631,37 @@ PCP_API int pcp_mean_shift(pcp_ctx* ctx, float radius, int min_pts, int iteratio
   return PCP_OK;
 }
 
-PCP_API int pcp_set_cloud_txt(pcp_ctx* ctx, const void* text, int64_t n_bytes, int text_is_device, int64_t* n_points,
-                              float* out_xyzi, int64_t out_capacity, int out_is_device) {
+static int set_cloud_text(pcp_ctx* ctx, const void* text, int64_t n_bytes, int text_is_device, int64_t* n_points, float* out_xyzi,
+                          int64_t out_capacity, int out_is_device, int xyz, const char* who) {
   if (!ctx) return PCP_ERR_INVALID_ARG;
-  if (n_bytes < 0 || (n_bytes > 0 && !text) || !n_points || (out_xyzi && out_capacity < 0))
-    return pcp_fail(ctx, PCP_ERR_INVALID_ARG, "pcp_set_cloud_txt: bad argument");
+  if (n_bytes < 0 || (n_bytes > 0 && !text) || !n_points || (out_xyzi && out_capacity < 0)) return pcp_fail(ctx, PCP_ERR_INVALID_ARG, who);
   PCP_CUDA(cudaSetDevice(ctx->device));
   *n_points = 0;
-  if (n_bytes == 0) return PCP_OK;
   int rc;
-  const unsigned char* d_text = (const unsigned char*)text;
-  if (!text_is_device) {
-    if ((rc = pcp_reserve(ctx, ctx->txt_in, (size_t)n_bytes))) return rc;
-    PCP_CUDA(cudaMemcpyAsync(ctx->txt_in.p, text, (size_t)n_bytes, cudaMemcpyHostToDevice, ctx->stream));
-    d_text = (const unsigned char*)ctx->txt_in.p;
+  if (n_bytes == 0) {
+    if (!xyz) return PCP_OK;
+    // xyz2pc on an empty file: eof() is not set before the first getline, so ONE (zero) point is pushed
+    if ((rc = pcp_reserve(ctx, ctx->txt_out, sizeof(float4)))) return rc;
+    PCP_CUDA(cudaMemsetAsync(ctx->txt_out.p, 0, sizeof(float4), ctx->stream));
+    *n_points = 1;
+  } else {
+    const unsigned char* d_text = (const unsigned char*)text;
+    if (!text_is_device) {
+      if ((rc = pcp_reserve(ctx, ctx->txt_in, (size_t)n_bytes))) return rc;
+      PCP_CUDA(cudaMemcpyAsync(ctx->txt_in.p, text, (size_t)n_bytes, cudaMemcpyHostToDevice, ctx->stream));
+      d_text = (const unsigned char*)ctx->txt_in.p;
+    }
+    int64_t n = 0;
+    int too_long = 0;
+    if ((rc = pcp_parse_txt_impl(ctx, d_text, n_bytes, &n, xyz, &too_long))) return rc;
+    if (xyz) {
+      PCP_CUDA(cudaStreamSynchronize(ctx->stream));
+      if (too_long)
+        return pcp_fail(ctx, PCP_ERR_INVALID_ARG, "pcp_set_cloud_xyz: a line of 255 characters or more (the reference's getline(line, 256) loop never ends on it)");
+    }
+    *n_points = n;
   }
-  int64_t n = 0;
-  if ((rc = pcp_parse_txt_impl(ctx, d_text, n_bytes, &n))) return rc;
-  *n_points = n;
+  const int64_t n = *n_points;
   if (n > 0 && (rc = pcp_set_cloud_device(ctx, ctx->txt_out.p, n))) return rc;
   if (out_xyzi) {
     const size_t m = (size_t)(n < out_capacity ? n : out_capacity);
@@ -657,6 +670,16 @@ PCP_API int pcp_set_cloud_txt(pcp_ctx* ctx, const void* text, int64_t n_bytes, i
   }
   PCP_CUDA(cudaStreamSynchronize(ctx->stream));
   return PCP_OK;
+}
+
+PCP_API int pcp_set_cloud_txt(pcp_ctx* ctx, const void* text, int64_t n_bytes, int text_is_device, int64_t* n_points, float* out_xyzi,
+                              int64_t out_capacity, int out_is_device) {
+  return set_cloud_text(ctx, text, n_bytes, text_is_device, n_points, out_xyzi, out_capacity, out_is_device, 0, "pcp_set_cloud_txt: bad argument");
+}
+
+PCP_API int pcp_set_cloud_xyz(pcp_ctx* ctx, const void* text, int64_t n_bytes, int text_is_device, int64_t* n_points, float* out_xyzi,
+                              int64_t out_capacity, int out_is_device) {
+  return set_cloud_text(ctx, text, n_bytes, text_is_device, n_points, out_xyzi, out_capacity, out_is_device, 1, "pcp_set_cloud_xyz: bad argument");
 }
 
 }  // extern "C"

@@ -197,20 +197,33 @@ __device__ __forceinline__ bool is_space(unsigned char c) { return c == ' ' || (
 __device__ __forceinline__ bool is_digit(unsigned char c) { return c >= '0' && c <= '9'; }
 
 // line j = bytes [starts[j], end_j): one thread parses its four fields.  set_mask bit f: the field wrote a value.
+// XYZ = false: txt2pc (stream extraction, above).  XYZ = true: xyz2pc (src/smoothing.cpp:83-125) — getline(line, 256) +
+// sscanf(line, "%f %f %f %s", &x, &y, &z, &intens); pt.intensity = intens: three floats and the FIRST BYTE of the
+// fourth token as a signed char; a field that does not parse ends the line WITHOUT being written (it keeps the
+// previous line's value, like every field after it), a value beyond the float range is stored as +-inf and the scan
+// goes on; a line of 255 characters or more raises *too_long (the reference's loop never ends on it).  Fields in
+// inf / nan / hexadecimal notation, which sscanf would accept, are outside the subset offered here (they end the line).
+template <bool XYZ>
 __global__ void __launch_bounds__(128) txt_parse_kernel(const unsigned char* __restrict__ text, int64_t n_bytes,
                                                         const int64_t* __restrict__ starts, int64_t n_lines, float4* __restrict__ vals,
-                                                        int* __restrict__ last_set /* 4 arrays of n_lines */) {
+                                                        int* __restrict__ last_set /* 4 arrays of n_lines */, int* __restrict__ too_long) {
   const int64_t j = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (j >= n_lines) return;
   int64_t p = starts[j];
   int64_t end = j + 1 < n_lines ? starts[j + 1] - 1 : n_bytes;  // drop the '\n'
   if (j + 1 == n_lines && end > p && text[end - 1] == '\n') --end;
+  if (XYZ && end - p >= 255) atomicExch(too_long, 1);
   float v[4] = {0.f, 0.f, 0.f, 0.f};
   int set_mask = 0;
   bool good = true;  // the stringstream's good(): no failbit, no eofbit
   for (int f = 0; f < 4 && good; ++f) {
     while (p < end && is_space(text[p])) ++p;  // sentry: skip whitespace
     if (p >= end) break;                       // eof before any character: failbit, the value is NOT written
+    if (XYZ && f == 3) {                       // %s: the token's first byte, as the signed char the reference declares
+      v[3] = (float)(signed char)text[p];
+      set_mask |= 8;
+      break;
+    }
     // ---- _M_extract_float: collect the characters of the field
     bool neg = false, found_mantissa = false, found_dec = false, found_sci = false, any_digit = false;
     bool exp_neg = false, exp_digits = false, sticky = false, bad = false;
@@ -256,11 +269,12 @@ __global__ void __launch_bounds__(128) txt_parse_kernel(const unsigned char* __r
         break;
       }
     }
-    if (p >= end) good = false;  // the extraction ran into the end of the line: eofbit
+    if (!XYZ && p >= end) good = false;  // the extraction ran into the end of the line: eofbit
     // ---- strtof on the collected string: it must be a complete number
     if (!any_digit || (found_sci && !exp_digits)) bad = true;
     uint32_t bits = 0;
     if (bad) {
+      if (XYZ) break;  // matching failure: sscanf stops, nothing is stored
       v[f] = 0.f;  // num_get stores 0 and sets failbit
       set_mask |= 1 << f;
       good = false;
@@ -271,9 +285,9 @@ __global__ void __launch_bounds__(128) txt_parse_kernel(const unsigned char* __r
       E = E > 100000 ? 100000 : (E < -100000 ? -100000 : E);
       bool ovf;
       bits = decimal_to_float(M, sticky, (int)E, &ovf);
-      if (ovf) {  // strtof returns HUGE_VALF: the library stores +-FLT_MAX and sets failbit
-        bits = 0x7F7FFFFFu;
-        good = false;
+      if (ovf) {  // strtof returns HUGE_VALF: the stream stores +-FLT_MAX and sets failbit; sscanf stores the infinity and goes on
+        bits = XYZ ? 0x7F800000u : 0x7F7FFFFFu;
+        good = XYZ;
       }
     }
     v[f] = __uint_as_float(bits | (neg ? 0x80000000u : 0u));
@@ -284,12 +298,13 @@ __global__ void __launch_bounds__(128) txt_parse_kernel(const unsigned char* __r
   for (int f = 0; f < 4; ++f) last_set[(int64_t)f * n_lines + j] = (set_mask >> f) & 1 ? (int)j : -1;
 }
 
+// last_too: the (empty) line after a final '\n' is a line of its own (xyz2pc's eof() loop)
 __global__ void __launch_bounds__(256) txt_starts_kernel(const unsigned char* __restrict__ text, const int* __restrict__ rank, int64_t n_bytes,
-                                                         int64_t* __restrict__ starts) {
+                                                         int64_t* __restrict__ starts, int last_too) {
   const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (i >= n_bytes) return;
   if (i == 0) starts[0] = 0;
-  if (text[i] == '\n' && i + 1 < n_bytes) starts[rank[i] + 1] = i + 1;
+  if (text[i] == '\n' && (i + 1 < n_bytes || last_too)) starts[rank[i] + 1] = i + 1;
 }
 
 // field f of line j = the value of the last line <= j that set it (0 when none: pcl::PointXYZI() starts at 0)
@@ -312,8 +327,10 @@ __global__ void __launch_bounds__(256) txt_fill_kernel(const float4* __restrict_
 
 // d_text: n_bytes on the device.  Returns the number of lines through *n_lines_out (host) and leaves the points in
 // ctx->txt_out (float4 per line).  Synchronises once (the line count sizes everything that follows).
-int pcp_parse_txt_impl(pcp_ctx* ctx, const unsigned char* d_text, int64_t n_bytes, int64_t* n_lines_out) {
+// xyz != 0: the xyz2pc form (one more point after a final newline; *too_long_out set when a line has 255+ characters).
+int pcp_parse_txt_impl(pcp_ctx* ctx, const unsigned char* d_text, int64_t n_bytes, int64_t* n_lines_out, int xyz, int* too_long_out) {
   *n_lines_out = 0;
+  if (too_long_out) *too_long_out = 0;
   if (n_bytes <= 0) return PCP_OK;
   if (n_bytes > 0x7FFFFFF0ll) return pcp_fail(ctx, PCP_ERR_INVALID_ARG, "pcp_set_cloud_txt: more than 2 GiB of text per call");
   int rc;
@@ -331,18 +348,27 @@ int pcp_parse_txt_impl(pcp_ctx* ctx, const unsigned char* d_text, int64_t n_byte
   PCP_CUDA(cudaMemcpyAsync(&last_byte, d_text + n_bytes - 1, 1, cudaMemcpyDeviceToHost, ctx->stream));
   PCP_CUDA(cudaStreamSynchronize(ctx->stream));
   // getline: every '\n' ends a line; bytes after the last '\n' are one more line
-  const int64_t n_lines = (int64_t)last_rank + 1;  // rank of the last byte = newlines before it; the last byte closes or is in a line
+  // rank of the last byte = newlines before it; the last byte closes or is in a line.  xyz2pc's `while (!eof())` loop
+  // reads one more (empty) line after a final newline and pushes the previous point again
+  const int64_t n_lines = (int64_t)last_rank + 1 + ((xyz && last_byte == '\n') ? 1 : 0);
   if ((rc = pcp_reserve(ctx, ctx->txt_starts, (size_t)(n_lines + 1) * sizeof(int64_t)))) return rc;
   if ((rc = pcp_reserve(ctx, ctx->txt_vals, (size_t)n_lines * sizeof(float4)))) return rc;
   if ((rc = pcp_reserve(ctx, ctx->txt_last, (size_t)n_lines * 4 * sizeof(int)))) return rc;
   if ((rc = pcp_reserve(ctx, ctx->txt_out, (size_t)n_lines * sizeof(float4)))) return rc;
-  (void)last_byte;
+  if ((rc = pcp_reserve(ctx, ctx->flags, sizeof(int)))) return rc;
+  PCP_CUDA(cudaMemsetAsync(ctx->flags.p, 0, sizeof(int), ctx->stream));
   int64_t* starts = (int64_t*)ctx->txt_starts.p;
-  txt_starts_kernel<<<(unsigned)((n_bytes + 255) / 256), 256, 0, ctx->stream>>>(d_text, rank, n_bytes, starts);
+  txt_starts_kernel<<<(unsigned)((n_bytes + 255) / 256), 256, 0, ctx->stream>>>(d_text, rank, n_bytes, starts, xyz ? 1 : 0);
   PCP_LAUNCH_CHECK("txt_starts_kernel");
   int* last = (int*)ctx->txt_last.p;
-  txt_parse_kernel<<<(unsigned)((n_lines + 127) / 128), 128, 0, ctx->stream>>>(d_text, n_bytes, starts, n_lines, (float4*)ctx->txt_vals.p, last);
+  if (xyz)
+    txt_parse_kernel<true><<<(unsigned)((n_lines + 127) / 128), 128, 0, ctx->stream>>>(d_text, n_bytes, starts, n_lines, (float4*)ctx->txt_vals.p, last,
+                                                                                         (int*)ctx->flags.p);
+  else
+    txt_parse_kernel<false><<<(unsigned)((n_lines + 127) / 128), 128, 0, ctx->stream>>>(d_text, n_bytes, starts, n_lines, (float4*)ctx->txt_vals.p, last,
+                                                                                          (int*)ctx->flags.p);
   PCP_LAUNCH_CHECK("txt_parse_kernel");
+  if (xyz && too_long_out) PCP_CUDA(cudaMemcpyAsync(too_long_out, ctx->flags.p, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
   PCP_CUDA(cub::DeviceScan::InclusiveScan(nullptr, tmp, last, last, MaxInt(), (int)n_lines, ctx->stream));
   if ((rc = pcp_reserve(ctx, ctx->scan_tmp, tmp))) return rc;
   for (int f = 0; f < 4; ++f) {

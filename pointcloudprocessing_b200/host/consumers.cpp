@@ -154,10 +154,10 @@ bool buildingFacadeExtractor::meanShiftClustering(pcXYZIptr inputcloud, int iter
   return true;
 }
 
-bool preprocess::txt2pc(std::string txtpath, pcXYZI& origiCloud) {
+static bool text_cloud(const std::string& txtpath, pcXYZI& origiCloud, bool xyz) {
   FILE* f = std::fopen(txtpath.c_str(), "rb");
   if (!f) {
-    std::fprintf(stderr, "Wrong txt file! \n");  // (:47-49); the reference still returns true
+    std::fprintf(stderr, xyz ? "Wrong *.xyz file! \n" : "Wrong txt file! \n");  // (:47-49, :91-94); the reference still returns true
     return true;
   }
   std::vector<char> text;
@@ -167,12 +167,17 @@ bool preprocess::txt2pc(std::string txtpath, pcXYZI& origiCloud) {
   std::fclose(f);
   pcp_ctx* ctx = context();
   if (!ctx) return false;
-  size_t lines = 1;
+  size_t lines = 2;
   for (char c : text) lines += c == '\n';
   std::vector<float> pts(4 * lines);
   int64_t n = 0;
-  const int rc = pcp_set_cloud_txt(ctx, text.data(), (int64_t)text.size(), 0, &n, pts.data(), (int64_t)lines, 0);
-  if (rc) return fail(ctx, "txt2pc", rc);
+  const int rc = xyz ? pcp_set_cloud_xyz(ctx, text.data(), (int64_t)text.size(), 0, &n, pts.data(), (int64_t)lines, 0)
+                     : pcp_set_cloud_txt(ctx, text.data(), (int64_t)text.size(), 0, &n, pts.data(), (int64_t)lines, 0);
+  if (rc) return fail(ctx, xyz ? "xyz2pc" : "txt2pc", rc);
   for (int64_t i = 0; i < n; ++i) origiCloud.push_back(pcl::PointXYZI(pts[4 * i], pts[4 * i + 1], pts[4 * i + 2], pts[4 * i + 3]));
   return true;
 }
+
+bool preprocess::txt2pc(std::string txtpath, pcXYZI& origiCloud) { return text_cloud(txtpath, origiCloud, false); }
+// getline(line, 256) + sscanf("%f %f %f %s") per line (src/smoothing.cpp:83-125); intensity = first byte of the 4th token
+bool preprocess::xyz2pc(std::string txtpath, pcXYZI& origiCloud) { return text_cloud(txtpath, origiCloud, true); }

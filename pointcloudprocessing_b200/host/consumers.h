@@ -3,7 +3,7 @@
 //   lidarOdometry::lidarOdometryClass::getRangeAndptIdImage / calculateSmoothness  (include/lidarOdometry.h:31-33)
 //   DynaTools::clusterDBSCAN                                                       (include/dbscanCLuster.h:256-260)
 //   buildingFacadeExtractor::meanShiftClustering                                   (include/buildingFacadeExtraction.h)
-//   preprocess::txt2pc                                                             (src/smoothing.cpp:39-81)
+//   preprocess::txt2pc / xyz2pc                                                    (src/smoothing.cpp:39-125)
 // Bodies (consumers.cpp) forward to the CUDA path behind include/pcp.h; there is no CPU path.  Differences a
 // caller can observe: the bool methods really return true/false (the reference falls off their ends), nothing
 // is printed to std::cout, and where the reference indexes outside its 16 x 900 matrices the point is skipped.
@@ -31,6 +31,7 @@ int clusterDBSCAN(pcXYZIptr inCloud, double r, int minptNum, pcXYZIptr pcCluster
 class preprocess {
  public:
   bool txt2pc(std::string txtpath, pcXYZI& origiCloud);
+  bool xyz2pc(std::string txtpath, pcXYZI& origiCloud);  // src/smoothing.cpp:83-125
 };
 
 class buildingFacadeExtractor {

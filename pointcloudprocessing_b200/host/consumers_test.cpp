@@ -60,11 +60,11 @@ int main(int argc, char** argv) {
     std::fclose(o);
     return 0;
   }
-  if (!std::strcmp(argv[1], "txt") && argc >= 4) {  // consumers_test txt file.txt out.bin  (n x 4 floats)
+  if ((!std::strcmp(argv[1], "txt") || !std::strcmp(argv[1], "xyz")) && argc >= 4) {  // consumers_test txt|xyz file out.bin  (n x 4 floats)
     preprocess pre;
     pcXYZI cl;
-    cl.push_back(pcl::PointXYZI(-1.f, -2.f, -3.f, -4.f));  // txt2pc appends
-    if (!pre.txt2pc(argv[2], cl)) return 1;
+    cl.push_back(pcl::PointXYZI(-1.f, -2.f, -3.f, -4.f));  // txt2pc / xyz2pc append
+    if (!(argv[1][0] == 'x' ? pre.xyz2pc(argv[2], cl) : pre.txt2pc(argv[2], cl))) return 1;
     FILE* o = std::fopen(argv[3], "wb");
     for (size_t i = 0; i < cl.points.size(); ++i) {
       const float v[4] = {cl.points[i].x, cl.points[i].y, cl.points[i].z, cl.points[i].intensity};

@@ -114,3 +114,15 @@ def test_consumers_dropin_txt2pc(tmp_path, oracle):
     ref = oracle.txt2pc(text)
     np.testing.assert_array_equal(got[0], np.array([-1, -2, -3, -4], np.float32))
     np.testing.assert_array_equal(got[1:].view(np.uint32), ref.view(np.uint32))
+
+
+def test_consumers_dropin_xyz2pc(tmp_path, oracle):
+    """preprocess::xyz2pc(path, cloud) through the C++ signature (src/smoothing.cpp:83-125): appends to the caller's cloud."""
+    pts = synth.urban(31, 5000, extent=20.0)
+    text = "".join("%.4f %.4f %.4f %s\n" % (p[0], p[1], p[2], "abcxyz"[i % 6]) for i, p in enumerate(pts.astype(np.float64))).encode() + b"1 2\n\n3\n"
+    (tmp_path / "cloud.xyz").write_bytes(text)
+    _run(["xyz", tmp_path / "cloud.xyz", tmp_path / "o.bin"], tmp_path)
+    got = np.fromfile(tmp_path / "o.bin", np.float32).reshape(-1, 4)
+    ref = oracle.xyz2pc(text)
+    np.testing.assert_array_equal(got[0], np.array([-1, -2, -3, -4], np.float32))
+    np.testing.assert_array_equal(got[1:].view(np.uint32), ref.view(np.uint32))

@@ -84,3 +84,57 @@ def test_txt_cloud_file_then_pca(pcp, oracle):
     pcp.build_grid(0.0, 20)
     rec = pcp.knn_pca(20)
     check_features(rec, oracle.knn_pca_cloud(got, 20, 0), None, "txt cloud k=20")
+
+
+XYZ_CASES = [
+    b"1 2 3 a\n4.5 5 6 zz\n7 8\n\n9 x 1 2\n",            # token's first byte; short lines keep old fields; matching failure ends a line
+    b"1 2 3 7",                                            # no final newline: no repeated last point
+    b"",                                                   # an empty file pushes one zero point
+    b"\n",                                                 # ... and a lone newline two
+    b"1e40 -1e40 1e-50 \xff\n",                            # +-inf, underflow to 0, a byte above 127 is a negative char
+    b"  -0.5\t+.25 5. 0x\r\n1e 2 3 4\n1e+ 2 3 4\n. 1 2 3\n- 1 2 3\n+ 1 2 3\n1.5e3 2E-2 3e+1 q rest of line\n",
+    b"1 2 3\n4 5 6 \n7 8 9 k\n1,2 3 4 5\n1 2 3abc 4\n00012.50 -0 1e0 9\n",
+]
+
+
+@pytest.mark.parametrize("text", XYZ_CASES)
+def test_xyz_cases(pcp, oracle, text):
+    """preprocess::xyz2pc (src/smoothing.cpp:83-125): the device parser against the reference's own getline + sscanf
+    statements run on this image's C library (oracle/textio.cpp), bit for bit."""
+    ref = oracle.xyz2pc(text)
+    got = pcp.set_cloud_xyz(text)
+    assert got.shape == ref.shape
+    np.testing.assert_array_equal(got.view(np.uint32), ref.view(np.uint32))
+
+
+def test_xyz_random_and_limits(pcp, oracle):
+    rs = np.random.default_rng(11)
+    pts = synth.urban(29, 30000, extent=40.0).astype(np.float64)
+    lines = []
+    for i, p in enumerate(pts):
+        kind = rs.integers(0, 12)
+        if kind == 0:
+            lines.append("%.4f %.4f" % (p[0], p[1]))                      # short line
+        elif kind == 1:
+            lines.append("")                                              # empty line
+        elif kind == 2:
+            lines.append("%.9e %.3f %.17g %s" % (p[0], p[1], p[2], "ab"[i & 1]))
+        elif kind == 3:
+            lines.append("nope %.3f %.3f 1" % (p[1], p[2]))               # first field does not parse
+        else:
+            lines.append("%.3f %.3f %.3f %d" % (p[0], p[1], p[2], int(p[3])))
+    text = ("\n".join(lines) + "\n").encode()
+    ref = oracle.xyz2pc(text)
+    got = pcp.set_cloud_xyz(text)
+    np.testing.assert_array_equal(got.view(np.uint32), ref.view(np.uint32))
+    assert got.shape[0] == len(lines) + 1  # the eof() loop's extra point
+    # the parsed points are the current cloud
+    pcp.build_grid(0.5, 0)
+    assert pcp.radius_count(0.5, 4).shape[0] == got.shape[0]
+    # a line the reference never returns from is an error here, as in the oracle
+    bad = b"1 2 3 4\n" + b"7" * 255 + b"\n"
+    assert oracle.xyz2pc(bad) is None
+    with pytest.raises(Exception):
+        pcp.set_cloud_xyz(bad)
+    ok = b"1 2 3 4\n" + b" " * 250 + b"7 8\n"   # 254 characters: fine
+    np.testing.assert_array_equal(pcp.set_cloud_xyz(ok).view(np.uint32), oracle.xyz2pc(ok).view(np.uint32))

@@ -284,3 +284,13 @@ def test_odom_smoothness_known_answers(oracle):
     img2[0, 29] = 5.0      # ten values, all 0: `0 >= sorted[size-3] = 0` marks the whole block, empty pixels too
     sm, ty = oracle.odom_smoothness(img2)
     assert (ty[0, 9:180] == 1).all() and (ty[0, :9] == 0).all() and (ty[1:] == 0).all() and (ty[0, 180:] == 0).all()
+
+
+def test_xyz2pc_known_answers(oracle):
+    """preprocess::xyz2pc (src/smoothing.cpp:83-125) by hand: intensity = first byte of the 4th token, fields a line does
+    not supply keep the previous line's values, the eof() loop repeats the last point after a final newline."""
+    got = oracle.xyz2pc(b"1 2 3 a\n4.5 5 6 zz\n7 8\n")
+    assert got.tolist() == [[1, 2, 3, 97], [4.5, 5, 6, 122], [7, 8, 6, 122], [7, 8, 6, 122]]
+    assert oracle.xyz2pc(b"1 2 3 7").tolist() == [[1, 2, 3, 55]]  # '7' is the character, not the number
+    assert oracle.xyz2pc(b"").tolist() == [[0, 0, 0, 0]]
+    assert oracle.xyz2pc(b"x" * 300) is None  # getline(line, 256) sets failbit: the reference loops forever
