@@ -332,6 +332,7 @@ def main():
     keep = {}
     ex = None
     if world > 1:
+        sharding.check_halo_reach([r_ * L for r_ in range(world + 1)], halo)  # halos come from the adjacent slabs only
         # fixed-capacity halo buffers: own points first, then the two received strips (sharding.SlabExchange)
         cap = max(4096, int(n * min(0.5, 1.6 * halo / L)))
         if args.halo_impl == "peer":

@@ -3,6 +3,7 @@
 // src/buildingFacadeExtraction.cpp:59-132.  Host work is packing and hand-over only.
 #include "consumers.h"
 
+#include <algorithm>
 #include <cstdint>
 #include <cstdio>
 #include <cstdlib>
@@ -136,6 +137,36 @@ int clusterDBSCAN(pcXYZIptr inCloud, double r, int minptNum, pcXYZIptr pcCluster
 }
 
 }  // namespace DynaTools
+
+bool buildingFacadeExtractor::makeSuperVoxels(voxel* voxelArrptr, int voxelNums, pcXYZIptr inputCloud, std::vector<voxel>& superVoxels,
+                                              std::vector<pcaAnalysist::pcaFeature>* features) {
+  if (features) features->clear();
+  if (voxelNums <= 0) return true;
+  if (!voxelArrptr || !inputCloud || inputCloud->points.empty()) return false;
+  pcp_ctx* ctx = context();
+  if (!ctx) return false;
+  int rc = pcp_set_cloud_host(ctx, inputCloud->points.data(), (int64_t)inputCloud->points.size(), (int)sizeof(pcl::PointXYZI));
+  if (rc) return fail(ctx, "makeSuperVoxels", rc);
+  // CSR batch: every voxel is one segment about ITS centre (the voxel centre, not the data mean: :216-218)
+  std::vector<float> centres(3 * (size_t)voxelNums);
+  std::vector<int64_t> offs((size_t)voxelNums + 1, 0);
+  for (int v = 0; v < voxelNums; ++v) offs[(size_t)v + 1] = offs[(size_t)v] + (int64_t)voxelArrptr[v].ptIndices.size();
+  std::vector<int32_t> idx((size_t)offs[(size_t)voxelNums]);
+  for (int v = 0; v < voxelNums; ++v) {
+    centres[3 * (size_t)v] = voxelArrptr[v].centroid.x;
+    centres[3 * (size_t)v + 1] = voxelArrptr[v].centroid.y;
+    centres[3 * (size_t)v + 2] = voxelArrptr[v].centroid.z;
+    std::copy(voxelArrptr[v].ptIndices.begin(), voxelArrptr[v].ptIndices.end(), idx.begin() + offs[(size_t)v]);
+  }
+  static_assert(sizeof(pcp_feature68) == sizeof(pcaAnalysist::pcaFeature), "layout");
+  std::vector<pcaAnalysist::pcaFeature> rec((size_t)voxelNums);
+  rc = pcp_segment_pca(ctx, centres.data(), offs.data(), idx.data(), voxelNums, reinterpret_cast<pcp_feature68*>(rec.data()));
+  if (rc) return fail(ctx, "makeSuperVoxels", rc);
+  for (int v = 0; v < voxelNums; ++v)
+    if (rec[(size_t)v].planeStruc > 0.6) superVoxels.push_back(voxelArrptr[v]);  // (:219-220; never true upstream, SURVEY Q3: kept)
+  if (features) features->swap(rec);
+  return true;
+}
 
 bool buildingFacadeExtractor::meanShiftClustering(pcXYZIptr inputcloud, int iterTimes) {
   if (!inputcloud || inputcloud->points.empty()) return true;

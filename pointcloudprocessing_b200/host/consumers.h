@@ -2,7 +2,7 @@
 // range image next to the PCA stage, with the reference's names and signatures:
 //   lidarOdometry::lidarOdometryClass::getRangeAndptIdImage / calculateSmoothness  (include/lidarOdometry.h:31-33)
 //   DynaTools::clusterDBSCAN                                                       (include/dbscanCLuster.h:256-260)
-//   buildingFacadeExtractor::meanShiftClustering                                   (include/buildingFacadeExtraction.h)
+//   buildingFacadeExtractor::meanShiftClustering / makeSuperVoxels                 (include/buildingFacadeExtraction.h)
 //   preprocess::txt2pc / xyz2pc                                                    (src/smoothing.cpp:39-125)
 // Bodies (consumers.cpp) forward to the CUDA path behind include/pcp.h; there is no CPU path.  Differences a
 // caller can observe: the bool methods really return true/false (the reference falls off their ends), nothing
@@ -11,6 +11,7 @@
 #define PCP_HOST_CONSUMERS_H_
 
 #include <string>
+#include <vector>
 
 #include "pcaAnalysis.h"  // pcXYZIptr / pcXYZI and the PCL / Eigen types (real or compat)
 
@@ -36,7 +37,18 @@ class preprocess {
 
 class buildingFacadeExtractor {
  public:
+  struct voxel {  // include/buildingFacadeExtraction.h:24-30
+    int id;
+    int ptNums;
+    std::vector<int> ptIndices;
+    pcl::PointXYZI centroid;
+  };
   bool meanShiftClustering(pcXYZIptr inputcloud, int iterTimes);
+  // src/buildingFacadeExtraction.cpp:207-223: the PCA of every voxel about its centre, voxels with planeStruc > 0.6 are
+  // appended to superVoxels.  ONE batched pcp_segment_pca call for all voxels (the reference: one calculatePCAofPoint
+  // per voxel).  `features` (optional, not in the reference's signature) receives the record of every voxel.
+  bool makeSuperVoxels(voxel* voxelArrptr, int voxelNums, pcXYZIptr inputCloud, std::vector<voxel>& superVoxels,
+                       std::vector<pcaAnalysist::pcaFeature>* features = nullptr);
 };
 
 #endif

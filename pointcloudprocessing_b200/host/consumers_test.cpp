@@ -2,10 +2,14 @@
 //   consumers_test odom  cloud.bin out_range.bin out_ptid.bin out_type.bin     (16 x 900 floats each, row-major)
 //   consumers_test dbscan cloud.bin r minpts out.bin      (int32 clusterID, int32 n_kept, then n_kept x 9 floats)
 //   consumers_test meanshift cloud.bin iters out.bin      (n x 3 floats)
-//   consumers_test txt file.txt out.bin                   (1 + n points x 4 floats; the first is the caller's own)
+//   consumers_test txt|xyz file out.bin                   (1 + n points x 4 floats; the first is the caller's own)
+//   consumers_test supervoxels cloud.bin cell out.bin     (makeSuperVoxels over voxels of `cell` metres: see the test)
 // cloud.bin: n x 4 float32 (x, y, z, intensity).
 #include <cstdint>
 #include <cstdio>
+#include <utility>
+#include <cmath>
+#include <algorithm>
 #include <cstdlib>
 #include <cstring>
 #include <vector>
@@ -69,6 +73,55 @@ int main(int argc, char** argv) {
     for (size_t i = 0; i < cl.points.size(); ++i) {
       const float v[4] = {cl.points[i].x, cl.points[i].y, cl.points[i].z, cl.points[i].intensity};
       std::fwrite(v, 4, 4, o);
+    }
+    std::fclose(o);
+    return 0;
+  }
+  if (!std::strcmp(argv[1], "supervoxels") && argc >= 5) {  // consumers_test supervoxels cloud.bin cell out.bin: voxels of `cell` metres, >= 20 points
+    const float cell = (float)std::atof(argv[3]);
+    std::vector<buildingFacadeExtractor::voxel> vox;
+    {
+      std::vector<std::pair<long long, int> > key(cloud->points.size());
+      for (size_t i = 0; i < cloud->points.size(); ++i) {
+        const pcl::PointXYZI& p = cloud->points[i];
+        const long long a = (long long)std::floor(p.x / cell), b = (long long)std::floor(p.y / cell), c = (long long)std::floor(p.z / cell);
+        key[i] = std::make_pair((a * 100003LL + b) * 100003LL + c, (int)i);
+      }
+      std::sort(key.begin(), key.end());
+      for (size_t i = 0; i < key.size();) {
+        size_t j = i;
+        buildingFacadeExtractor::voxel v;
+        while (j < key.size() && key[j].first == key[i].first) v.ptIndices.push_back(key[j++].second);
+        if (v.ptIndices.size() >= 20) {  // src/buildingFacadeExtraction.cpp:172
+          const pcl::PointXYZI& p = cloud->points[(size_t)v.ptIndices[0]];
+          v.id = (int)vox.size();
+          v.ptNums = (int)v.ptIndices.size();
+          v.centroid = pcl::PointXYZI((std::floor(p.x / cell) + 0.5f) * cell, (std::floor(p.y / cell) + 0.5f) * cell, (std::floor(p.z / cell) + 0.5f) * cell, 0.f);
+          vox.push_back(v);
+        }
+        i = j;
+      }
+    }
+    buildingFacadeExtractor bfe;
+    std::vector<buildingFacadeExtractor::voxel> super;
+    std::vector<pcaAnalysist::pcaFeature> fea;
+    if (!bfe.makeSuperVoxels(vox.data(), (int)vox.size(), cloud, super, &fea)) return 1;
+    // the same voxels one by one through the class method the reference calls (:212-219)
+    pcaAnalysist pca;
+    FILE* o = std::fopen(argv[4], "wb");
+    const int32_t nv = (int32_t)vox.size(), ns = (int32_t)super.size();
+    std::fwrite(&nv, 4, 1, o);
+    std::fwrite(&ns, 4, 1, o);
+    for (size_t v = 0; v < vox.size(); ++v) {
+      pcaAnalysist::pcaFeature one;
+      std::memset(&one, 0, sizeof(one));
+      if (v < 64 && !pca.calculatePCAofPoint(cloud, vox[v].centroid, vox[v].ptIndices, one)) return 1;
+      std::fwrite(&fea[v], sizeof(one), 1, o);
+      std::fwrite(&one, sizeof(one), 1, o);
+      std::fwrite(&vox[v].centroid.x, 4, 3, o);
+      const int32_t m = (int32_t)vox[v].ptIndices.size();
+      std::fwrite(&m, 4, 1, o);
+      std::fwrite(vox[v].ptIndices.data(), 4, (size_t)m, o);
     }
     std::fclose(o);
     return 0;

@@ -104,6 +104,19 @@ def knn_halo_violations(own_pts: torch.Tensor, kth_d2: torch.Tensor, axis: int, 
     return int((kth_d2 > reach * reach).sum())
 
 
+def check_halo_reach(edges: List[float], h: float) -> None:
+    """Halos come from the two ADJACENT slabs only: a halo of width h is complete only if no slab is narrower than h
+    (else points two slabs away fall inside [lo - h, hi + h) and are never received, while knn_halo_violations and
+    radius_halo_width still count that range as covered).  Raises ValueError; call it once after the splitters are
+    known (edges = the world + 1 slab boundaries; infinite outer faces are fine)."""
+    widths = [b - a for a, b in zip(edges[:-1], edges[1:])]
+    inner = widths[1:-1] if len(widths) > 2 else []
+    # the end slabs only have to supply their inner neighbour; an inner slab lies between two halos
+    narrow = [w for w in (inner + widths[:1] + widths[-1:]) if w < h]
+    if len(widths) > 1 and narrow:
+        raise ValueError(f"halo width {h} exceeds the width of a slab ({min(narrow):.6g}): fewer ranks, or an exchange with further neighbours, is needed")
+
+
 def radius_halo_width(radius: float) -> float:
     """Radius search: a halo of r (plus rounding slack) is exact."""
     return float(radius) * (1.0 + 1e-5) + 1e-6

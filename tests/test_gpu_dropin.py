@@ -126,3 +126,35 @@ def test_consumers_dropin_xyz2pc(tmp_path, oracle):
     ref = oracle.xyz2pc(text)
     np.testing.assert_array_equal(got[0], np.array([-1, -2, -3, -4], np.float32))
     np.testing.assert_array_equal(got[1:].view(np.uint32), ref.view(np.uint32))
+
+
+def test_consumers_dropin_make_super_voxels(tmp_path, oracle):
+    """buildingFacadeExtractor::makeSuperVoxels (src/buildingFacadeExtraction.cpp:207-223) as ONE batched segment-PCA call:
+    every voxel's record equals the oracle's calculatePCAofPoint(cloud, centro, idx) (:89-121) and, bitwise, the record
+    the per-voxel class method gives; planeStruc > 0.6 selects nothing, like upstream."""
+    from parity import check_features
+    from pointcloudprocessing_b200 import capi
+
+    pts = synth.urban(37, 60000, extent=40.0)
+    pts.tofile(tmp_path / "cloud.bin")
+    _run(["supervoxels", tmp_path / "cloud.bin", 3.0, tmp_path / "o.bin"], tmp_path)
+    raw = (tmp_path / "o.bin").read_bytes()
+    nv, ns = np.frombuffer(raw[:8], np.int32)
+    assert nv > 150 and ns == 0
+    pos, batched, single, centres, offs, idx = 8, [], [], [], [0], []
+    for v in range(nv):
+        batched.append(np.frombuffer(raw[pos:pos + 68], capi.FEATURE_DTYPE)[0]); pos += 68
+        single.append(np.frombuffer(raw[pos:pos + 68], capi.FEATURE_DTYPE)[0]); pos += 68
+        centres.append(np.frombuffer(raw[pos:pos + 12], np.float32)); pos += 12
+        m = int(np.frombuffer(raw[pos:pos + 4], np.int32)[0]); pos += 4
+        idx.append(np.frombuffer(raw[pos:pos + 4 * m], np.int32)); pos += 4 * m
+        offs.append(offs[-1] + m)
+    assert pos == len(raw)
+    batched = np.array(batched, capi.FEATURE_DTYPE)
+    single = np.array(single, capi.FEATURE_DTYPE)
+    ref = oracle.segment_pca(pts, np.array(centres), np.array(offs, np.int64), np.concatenate(idx))
+    ref["ptID"] = batched["ptID"]  # not set by this overload (src/pcaAnalysis.cpp:92)
+    check_features(batched, ref, None, "makeSuperVoxels")
+    for name in ("la", "v1", "v2", "v3", "ptNum", "lineStruc", "planeStruc", "scatterStruc"):
+        assert batched[name][:64].tobytes() == single[name][:64].tobytes(), name
+    assert (batched["planeStruc"] <= 0.6).all()

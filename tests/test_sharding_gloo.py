@@ -1,3 +1,4 @@
+import pytest
 """CPU, world_size 2 over gloo: slab sharding + halo exchange (the N>1 host logic of bench.py)."""
 import os
 import socket
@@ -89,3 +90,14 @@ def test_frame_shard_partition():
         assert all(a[1] == b[0] for a, b in zip(spans, spans[1:]))
         sizes = [e - b for b, e in spans]
         assert max(sizes) - min(sizes) <= 1
+
+
+def test_halo_reach_check():
+    """A halo wider than a slab cannot be served by the two adjacent slabs alone: refused up front."""
+    from pointcloudprocessing_b200 import sharding
+
+    sharding.check_halo_reach([0.0, 10.0, 20.0, 30.0], 6.0)
+    sharding.check_halo_reach([float("-inf"), 10.0, 20.0, float("inf")], 6.0)
+    sharding.check_halo_reach([0.0, 5.0], 100.0)  # one rank: nothing to exchange
+    with pytest.raises(ValueError):
+        sharding.check_halo_reach([0.0, 10.0, 14.0, 30.0], 6.0)

@@ -43,6 +43,7 @@ d_own = torch.from_numpy(np.ascontiguousarray(pts[own])).cuda(local)
 d_gid = torch.from_numpy(own).cuda(local)
 d_out = torch.empty(n_own * 68, dtype=torch.uint8, device=local)
 h = sharding.radius_halo_width(r)
+sharding.check_halo_reach(edges, h)  # halos come from the adjacent slabs only
 flo = lo if rank > 0 else -1e30
 fhi = hi if rank < world - 1 else 1e30
 torch.cuda.synchronize()
