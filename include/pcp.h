@@ -46,8 +46,10 @@ typedef enum pcp_status {
   PCP_ERR_K_UNSUPPORTED = -7,  /* k outside [1, PCP_MAX_K] */
   PCP_ERR_OOM = -8,
   PCP_ERR_IO = -9,             /* calibration file could not be read / parsed */
-  PCP_ERR_NEIGHBOR_OVERFLOW = -10 /* pcp_radius_neighbors: a neighbour LIST exceeded the 512-entry on-chip buffer (records and normals of such
-                                     neighbourhoods are still computed: unordered double-precision accumulation) */
+  PCP_ERR_NEIGHBOR_OVERFLOW = -10 /* k-NN with 32 < k <= 64: more than 512 points at one distance (exact duplicates) inside the cover radius.
+                                     (pcp_radius_neighbors no longer returns it: lists beyond the 512-entry on-chip buffer are filled
+                                     through global memory; records and normals of such neighbourhoods come from an unordered
+                                     double-precision accumulation) */
 } pcp_status;
 
 #define PCP_MAX_K 64 /* k <= 32: the tile / warp-per-query k-NN kernels; 33..64 (SOR k = 60, region growing k = 50 upstream): cover-radius form, same results */

@@ -7,6 +7,7 @@
 #include <vector>
 
 #include "pcp_internal.cuh"
+#include "search_common.cuh"
 
 int pcp_segment_pca_impl(pcp_ctx* ctx, const float* d_centres, const int64_t* d_offs, const int32_t* d_idx, int64_t n_seg,
                          pcp_feature68* d_out);
@@ -218,13 +219,22 @@ PCP_API int pcp_radius_neighbors(pcp_ctx* ctx, float radius, int32_t* counts, co
   if ((rc = pick_out(ctx, ctx->out_idx, idx, out_is_device, total, &sp.nn_idx))) return rc;
   if ((rc = pick_out(ctx, ctx->out_d2, d2, out_is_device, total, &sp.nn_d2))) return rc;
   if ((rc = pcp_search_launch(ctx, sp))) return rc;
+  if (idx) {
+    // neighbourhoods beyond the on-chip buffer (r = 2-3 m on a dense scan: src/lidarOdometry.cpp:76,
+    // src/buildingFacadeExtraction.cpp:83) raised the flag and left their list slots empty: filled through global memory
+    int h_flag = 0;
+    PCP_CUDA(cudaMemcpyAsync(&h_flag, ctx->flags.p, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+    PCP_CUDA(cudaStreamSynchronize(ctx->stream));
+    if (h_flag) {
+      KArgs a;
+      pcp_make_kargs(ctx, sp, a);
+      if ((rc = pcp_radius_heavy_lists_impl(ctx, a, sp.r2, sp.R0, d_offsets, (int64_t)total, sp.nn_idx, sp.nn_d2))) return rc;
+    }
+  }
   if ((rc = copy_back(ctx, counts, sp.counts, out_is_device, (size_t)nq))) return rc;
   if ((rc = copy_back(ctx, idx, sp.nn_idx, out_is_device, total))) return rc;
   if ((rc = copy_back(ctx, d2, sp.nn_d2, out_is_device, total))) return rc;
-  int h_flag = 0;
-  PCP_CUDA(cudaMemcpyAsync(&h_flag, ctx->flags.p, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
   PCP_CUDA(cudaStreamSynchronize(ctx->stream));
-  if (h_flag && idx) return pcp_fail(ctx, PCP_ERR_NEIGHBOR_OVERFLOW, "pcp_radius_neighbors: a neighbourhood exceeded the per-query buffer");
   return PCP_OK;
 }
 

@@ -60,7 +60,7 @@ static void free_buf(DevBuf& b) {
 
 // the environment is looked at here and nowhere else
 static void read_knobs(PcpKnobs& kn) {
-  if (const char* e = getenv("PCP_KNN_IMPL")) kn.knn_impl = !strcmp(e, "v3") ? 3 : (!strcmp(e, "tile4") ? 4 : 0);
+  if (const char* e = getenv("PCP_KNN_IMPL")) kn.knn_impl = !strcmp(e, "v3") ? 3 : (!strcmp(e, "tile4") ? 4 : (!strcmp(e, "tile6") ? 6 : 0));
   if (const char* e = getenv("PCP_KNN_GROUPS")) kn.knn_groups = atoi(e);
   if (const char* e = getenv("PCP_RADIUS_IMPL")) kn.radius_impl = !strcmp(e, "v3") ? 3 : (!strcmp(e, "tile64") ? 2 : (!strncmp(e, "tile", 4) ? 1 : 0));
   if (const char* e = getenv("PCP_WL_BLOCKS")) kn.wl_blocks = atoi(e) > 0 ? atoi(e) : 0;

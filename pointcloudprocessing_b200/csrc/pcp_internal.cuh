@@ -44,7 +44,7 @@ struct DevBuf {
 
 // Environment knobs (A/B timing and tests), read ONCE in pcp_create — never on the launch path.
 struct PcpKnobs {
-  int knn_impl = 0;        // PCP_KNN_IMPL: 0 = tile kernel of knn_tile6.cu + work list (default), 4 = "tile4": the round-1
+  int knn_impl = 0;        // PCP_KNN_IMPL: 0 = automatic (knn_tile6.cu for single clouds, knn_tile.cu for frame batches) + work list, 6 = "tile6" / 4 = "tile4" force one: the round-1
                            // tile kernel (knn_tile.cu), 3 = "v3": the warp-per-query kernel for every point
   int knn_groups = 0;      // PCP_KNN_GROUPS: stencil rows served per tile (0 = automatic)
   int radius_impl = 0;     // PCP_RADIUS_IMPL: 0 = automatic, 1 = "tile" (32-entry lanes), 2 = "tile64", 3 = "v3"
@@ -100,6 +100,7 @@ struct pcp_ctx {
   DevBuf out_feat, out_norm, out_idx, out_d2, out_counts, flags, valid, last_valid, staging;
   DevBuf ring_range, ring_idx, ring_long, ring_offsets, ring_key;
   DevBuf obb;         // pcp_bbox_pca: sums, extents and the result
+  DevBuf heavy_keys, heavy_keys2, heavy_seg;  // radius_heavy.cu: keys of the heavy lists (in / sorted), segment bounds
   DevBuf halo_done;   // block counter of halo_pad_signal_kernel
   DevBuf dec_tables, dec_packed, dec_out;  // pcp_decode_packets: azimuth cos/sin tables, per-block scan, staged outputs
   DevBuf odom_counts, odom_range, odom_ptid, odom_index, odom_stats, odom_minmax, odom_smooth, odom_type;  // lidarOdometry images
@@ -151,6 +152,10 @@ struct SearchParams {
 };
 int pcp_search_launch(pcp_ctx* ctx, const SearchParams& sp);  // radius (and the v3 warp-per-query k-NN, A/B only)
 struct KArgs;
+void pcp_make_kargs(pcp_ctx* ctx, const SearchParams& sp, KArgs& a);  // search_pca.cu
+// radius_heavy.cu: lists of neighbourhoods beyond the 512-entry on-chip buffer (count-then-fill through global memory)
+int pcp_radius_heavy_lists_impl(pcp_ctx* ctx, const KArgs& a, float r2, int R, const int64_t* d_offsets, int64_t total, int32_t* d_idx,
+                                float* d_d2);
 int pcp_knn_tile_launch(pcp_ctx* ctx, const SearchParams& sp, const KArgs& a, int radius_cap);  // k-NN tile kernel (knn_tile.cu)
 int pcp_knn_tile6_launch(pcp_ctx* ctx, const SearchParams& sp, const KArgs& a);  // k-NN tile kernel (knn_tile6.cu): k <= PCP_T6_KMAX
 #define PCP_T6_K32 24   // 32-member lanes up to this k, 64-member lanes above

@@ -667,13 +667,8 @@ extern "C" __attribute__((visibility("default"))) int pcp_debug_stats(unsigned l
 }
 #endif
 
-int pcp_search_launch(pcp_ctx* ctx, const SearchParams& sp) {
-  // PCP_KNN_IMPL (read once in pcp_create) selects the k-NN kernel for A/B timing: default = tile kernel of
-  // knn_tile6.cu + this file's warp-per-query kernel for the queries it defers; "tile4" = the round-1 tile
-  // kernel (knn_tile.cu) instead; "v3" = warp-per-query for every point.  All give identical results.
-  const PcpKnobs& kn = ctx->knobs;
-  const bool use_v3 = sp.mode == 0 && kn.knn_impl == 3;
-  KArgs a;
+// the kernel arguments every search kernel takes: the grid of the context's current cloud + the call's parameters
+void pcp_make_kargs(pcp_ctx* ctx, const SearchParams& sp, KArgs& a) {
   a.sorted = (const float4*)ctx->sorted_pts.p;
   a.keys = (const uint32_t*)ctx->keys_sorted.p;
   a.slot = (const int32_t*)ctx->sorted_slot.p;
@@ -683,6 +678,16 @@ int pcp_search_launch(pcp_ctx* ctx, const SearchParams& sp) {
   a.g = ctx->grid;
   a.n = ctx->n;
   a.sp = sp;
+}
+
+int pcp_search_launch(pcp_ctx* ctx, const SearchParams& sp) {
+  // PCP_KNN_IMPL (read once in pcp_create) selects the k-NN kernel for A/B timing: default = tile kernel of
+  // knn_tile6.cu + this file's warp-per-query kernel for the queries it defers; "tile4" = the round-1 tile
+  // kernel (knn_tile.cu) instead; "v3" = warp-per-query for every point.  All give identical results.
+  const PcpKnobs& kn = ctx->knobs;
+  const bool use_v3 = sp.mode == 0 && kn.knn_impl == 3;
+  KArgs a;
+  pcp_make_kargs(ctx, sp, a);
   const int64_t tiles = (ctx->n + 31) / 32;
   const int blocks = (int)((tiles + WARPS - 1) / WARPS);
   pcp_tic(ctx, PCP_T_SEARCH_PCA);
@@ -707,7 +712,10 @@ int pcp_search_launch(pcp_ctx* ctx, const SearchParams& sp) {
     if (sp.R0 > 3) radius_tile = false;
   }
   if ((sp.mode == 0 && !use_v3) || radius_tile) {
-    int rc = (sp.mode == 0 && kn.knn_impl == 0) ? pcp_knn_tile6_launch(ctx, sp, a) : pcp_knn_tile_launch(ctx, sp, a, radius_cap);
+    // k-NN: knn_tile6.cu for single clouds; frame batches (segmented grid: short rows, up to four row groups per tile,
+    // k = 10) stay on the round-1 tile kernel, which re-stages less per row group (measured, 128 VLP-16 frames: 3.7 vs 4.1 ms)
+    const bool use_t6 = sp.mode == 0 && (kn.knn_impl == 6 || (kn.knn_impl == 0 && ctx->grid.n_seg == 1));  // PCP_KNN_IMPL=tile6 forces it
+    int rc = use_t6 ? pcp_knn_tile6_launch(ctx, sp, a) : pcp_knn_tile_launch(ctx, sp, a, radius_cap);
     if (rc) return rc;
     // one wave of resident CTAs (3 per SM at 80 registers); tiles of 16 list entries drawn by ticket
     // (tuning hooks: PCP_WL_BLOCKS, PCP_WL_TILE)

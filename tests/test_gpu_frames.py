@@ -62,9 +62,9 @@ def test_segmented_grid_edge_cases(oracle):
             p.set_cloud(part)
             p.build_grid(0.0, k)
             want.append((p.knn_pca(k), p.knn_neighbors(k)))
-    # PCP_KNN_IMPL is read when a context is created: "" = tile kernel (round-2 form), tile4 = round-1 tile kernel,
+    # PCP_KNN_IMPL is read when a context is created: "" = automatic (round-1 tile kernel for frame batches), tile6 = round-2 tile kernel, tile4 = round-1 tile kernel,
     # v3 = warp per query for every point
-    for impl in ("", "tile4", "v3"):
+    for impl in ("", "tile6", "tile4", "v3"):
         os.environ["PCP_KNN_IMPL"] = impl
         try:
             with capi.Pcp(0) as q:

@@ -137,7 +137,7 @@ def test_eigen_closer_to_fp64_truth(pcp, oracle):
 def test_radius_pca_heavy_neighbourhoods(pcp, oracle):
     """r = 3 m on a dense scan (the radius src/lidarOdometry.cpp:76 uses): thousands of hits per query, far
     beyond the 512-entry warp buffer — records come from the unordered double-precision accumulation, counts
-    stay exact, eigen outputs within the parity bar; neighbour LISTS of that size still fail loudly."""
+    stay exact, eigen outputs within the parity bar (lists of that size: test_radius_neighbors_heavy_lists)."""
     pts = synth.urban(8, 40000, extent=30.0)
     r = 3.0
     pcp.set_cloud(pts)
@@ -147,8 +147,6 @@ def test_radius_pca_heavy_neighbourhoods(pcp, oracle):
     assert got["ptNum"].max() > 2000 and (got["ptNum"] > 512).mean() > 0.5
     assert np.array_equal(got["ptNum"], ref["ptNum"])
     check_features(got, ref, valid, "radius heavy")
-    with pytest.raises(capi.PcpError):
-        pcp.radius_neighbors(r)
     # a mix: sparse clutter (short lists, bitwise path) next to dense ground (heavy path) in one launch
     r = 1.2
     pcp.build_grid(r * 1.001, 0)
@@ -200,3 +198,30 @@ def test_bbox_pca(pcp, oracle):
     # the restatement agrees up to eigenvector signs and its fp32 sums
     s = np.sign((got["axes"] * ref["axes"]).sum(1))
     assert np.abs(got["axes"] - s[:, None] * ref["axes"]).max() < 2e-3
+
+
+
+def test_radius_neighbors_heavy_lists(pcp, oracle):
+    """Neighbour LISTS beyond the 512-entry on-chip buffer (radiusSearch(i, 3.0): src/lidarOdometry.cpp:76, main.cpp:117;
+    r = 2.0: src/buildingFacadeExtraction.cpp:83): count-then-fill through global memory + segmented sort — indices and
+    distances bit-exact in (d2, index) order, heavy and light queries mixed in one call."""
+    pts = synth.urban(8, 14000, extent=18.0)
+    for r in (3.0, 1.2):
+        pcp.set_cloud(pts)
+        pcp.build_grid(r * 1.001, 0)
+        off, idx, d2 = pcp.radius_neighbors(r)
+        roff, ridx, rd2 = oracle.KdTree(pts).radius_all(r)
+        cnt = np.diff(roff)
+        assert (cnt > 512).any() and (r > 2 or (cnt <= 512).any())
+        assert np.array_equal(off, roff)
+        assert np.array_equal(idx, ridx)
+        assert np.array_equal(d2.view(np.uint32), rd2.view(np.uint32))
+    # duplicates: more than 512 points at distance 0 of each other (ties ordered by index)
+    dup = synth.urban(9, 3000, extent=10.0)
+    dup[500:1300] = dup[7]
+    pcp.set_cloud(dup)
+    pcp.build_grid(0.3, 0)
+    off, idx, d2 = pcp.radius_neighbors(0.25)
+    roff, ridx, rd2 = oracle.KdTree(dup).radius_all(0.25)
+    assert np.diff(roff).max() > 800
+    assert np.array_equal(off, roff) and np.array_equal(idx, ridx) and np.array_equal(d2.view(np.uint32), rd2.view(np.uint32))
