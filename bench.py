@@ -203,6 +203,35 @@ def reference_arm(args, rank, world):
     emit_line(line)
 
 
+def bind_to_gpu_numa_node(index: int):
+    """N > 1: run this rank (and first-touch its pinned buffers) on the NUMA node its GPU hangs off, so that eight ranks'
+    host<->device copies do not all cross the socket interconnect.  Returns a note for the JSON line; never raises."""
+    try:
+        import pynvml
+
+        pynvml.nvmlInit()
+        bus = pynvml.nvmlDeviceGetPciInfo(pynvml.nvmlDeviceGetHandleByIndex(index)).busId
+        bus = (bus.decode() if isinstance(bus, bytes) else bus).lower()
+        if len(bus.split(":")[0]) == 8:  # NVML prints an 8-digit domain, sysfs a 4-digit one
+            bus = bus[4:]
+        with open(f"/sys/bus/pci/devices/{bus}/numa_node") as f:
+            node = int(f.read().strip())
+        if node < 0:
+            return "no NUMA information for the GPU"
+        with open(f"/sys/devices/system/node/node{node}/cpulist") as f:
+            cpus = set()
+            for part in f.read().strip().split(","):
+                a, _, b = part.partition("-")
+                cpus.update(range(int(a), int(b or a) + 1))
+        cpus &= os.sched_getaffinity(0)
+        if not cpus:
+            return f"NUMA node {node} has no allowed CPUs"
+        os.sched_setaffinity(0, cpus)
+        return f"bound to NUMA node {node} ({len(cpus)} CPUs) of GPU {bus}"
+    except Exception as e:  # noqa: BLE001 — binding is an optimisation, never a reason to fail
+        return f"not bound ({type(e).__name__})"
+
+
 def rank_cloud(n: int, rank: int, world: int, seeded: bool) -> np.ndarray:
     """The slab rank `rank` owns: the N = 1 cloud, shifted to x in [rank L, (rank + 1) L) when world > 1."""
     pts = make_cloud(n, rank, seeded)
@@ -302,6 +331,7 @@ def main():
     from pointcloudprocessing_b200 import capi
 
     torch.cuda.set_device(local)
+    numa_note = bind_to_gpu_numa_node(local) if world > 1 else "N = 1: not bound (the CPU baseline uses every core)"
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     from pointcloudprocessing_b200 import sharding
@@ -529,7 +559,7 @@ def main():
         "config": workload_config(n, k, world, args.rank_clouds, halo, args.halo_impl),
         "clocks": clocks,
         "e2e": {"value": total_pts / (e2e_ms * 1e-3), "unit": "points/s", "h2d_bytes_per_step": 16 * n, "d2h_bytes_per_step": 68 * n,
-                "mode": e2e_mode, "sequential_value": total_pts / e2e_seq_s},
+                "mode": e2e_mode, "sequential_value": total_pts / e2e_seq_s, "host_binding_rank0": numa_note},
         "gpu_launches": int(launches),
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
                      "kernel": "knn_tile_kernel + search_pca_worklist_kernel<0> (one stage: the tile kernel serves ~90 % of the queries, the work-list kernel the rest)",

@@ -10,6 +10,9 @@
 // Second half of every finish stage: eigen-solve of the moment(s), structure features, PCL-twin normal, record staging
 // and the coalesced 68-byte record write.  mq / mm = query- / mean-centred moment {c00, c01, c02, c11, c12, c22}
 // (already divided by n); `valid` = the PCA is to be computed.  Must be called by all 32 lanes of the warp.
+// LEAN = the caller guarantees: records wanted, query-centred, no normals, no validity bytes, no lists (the k-NN hot
+// path): the code of the optional outputs is not generated (the tile kernel's straight-line part is bound by instruction fetch).
+template <bool LEAN = false>
 __device__ __forceinline__ void knn_emit(const KArgs& a, const float (&mq)[6], const float (&mm)[6], const bool valid, const int n_nb,
                                          const float4 Q, const int my_slot, const int gid_q, float (*rec_all)[17], const int lane) {
   const SearchParams& sp = a.sp;
@@ -23,9 +26,9 @@ __device__ __forceinline__ void knn_emit(const KArgs& a, const float (&mq)[6], c
     rec[13] = __int_as_float(n_nb);
     // one call site of the (noinline) solver on the hot path: the matrix the records need, which is also
     // the normals' matrix unless query-centred records AND normals were requested
-    const bool want_out = valid && sp.out != nullptr;
-    const bool want_nrm = sp.normals != nullptr && valid && n_nb >= 3;
-    const bool first_is_mean = !want_out || sp.center_mode == PCP_CENTER_MEAN;
+    const bool want_out = valid && (LEAN || sp.out != nullptr);
+    const bool want_nrm = !LEAN && sp.normals != nullptr && valid && n_nb >= 3;
+    const bool first_is_mean = !LEAN && (!want_out || sp.center_mode == PCP_CENTER_MEAN);
     Sym3Eig e1;
     if (want_out || want_nrm) sym3_eigen_call(first_is_mean ? mm : mq, e1);
     if (want_out) {
@@ -40,7 +43,7 @@ __device__ __forceinline__ void knn_emit(const KArgs& a, const float (&mq)[6], c
       rec[15] = __fdiv_rn(__fsub_rn(s2, s3), s1);
       rec[16] = __fdiv_rn(s3, s1);
     }
-    if (sp.normals != nullptr) {
+    if (!LEAN && sp.normals != nullptr) {
       pcp_normal16 nrm;
       if (!want_nrm) {
         nrm.nx = nrm.ny = nrm.nz = nrm.curvature = __int_as_float(0x7FC00000);
@@ -56,11 +59,11 @@ __device__ __forceinline__ void knn_emit(const KArgs& a, const float (&mq)[6], c
       }
       sp.normals[my_slot] = nrm;
     }
-    if (sp.valid) sp.valid[my_slot] = valid ? 1 : 0;
+    if (!LEAN && sp.valid) sp.valid[my_slot] = valid ? 1 : 0;
   }
   __syncwarp();
   // ---- lanes 0..16 write one contiguous 68-byte record per step
-  if (sp.out != nullptr) {
+  if (LEAN || sp.out != nullptr) {
     float* outw = reinterpret_cast<float*>(sp.out);
 #pragma unroll 1
     for (int r = 0; r < 32; ++r) {
@@ -184,6 +187,7 @@ static __device__ __noinline__ void knn_fix_order(const float4* __restrict__ sor
   col[(i + 1) * 32] = pos;
 }
 
+template <bool LEAN = false>
 __device__ __forceinline__ void knn_finish_pos(const KArgs& a, uint32_t* col, const int cnt, const int n_nb, const uint32_t prefix_mask,
                                                const float4 Q, const int my_slot, float (*rec_all)[17], const int lane) {
   const SearchParams& sp = a.sp;
@@ -192,8 +196,8 @@ __device__ __forceinline__ void knn_finish_pos(const KArgs& a, uint32_t* col, co
   const int ord_q = __float_as_int(Q.w);
   const int gid_q = (my_slot >= 0 && a.gid_of_ord) ? __ldg(&a.gid_of_ord[ord_q]) : ord_q;
   const bool valid = my_slot >= 0 && n_nb >= 1;
-  const bool need_q = sp.out != nullptr && sp.center_mode == PCP_CENTER_QUERY;
-  const bool need_m = sp.normals != nullptr || (sp.out != nullptr && sp.center_mode == PCP_CENTER_MEAN);
+  const bool need_q = LEAN || (sp.out != nullptr && sp.center_mode == PCP_CENTER_QUERY);
+  const bool need_m = !LEAN && (sp.normals != nullptr || (sp.out != nullptr && sp.center_mode == PCP_CENTER_MEAN));
   float mq[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f}, mm[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
   float sx = 0.f, sy = 0.f, sz = 0.f;
   if (valid) {
@@ -226,7 +230,7 @@ __device__ __forceinline__ void knn_finish_pos(const KArgs& a, uint32_t* col, co
               redo = true;
             } else {
               prev = key;
-              if (sp.nn_idx != nullptr) {
+              if (!LEAN && sp.nn_idx != nullptr) {
                 const int ord = (int)(uint32_t)key;
                 sp.nn_idx[o + j] = a.gid_of_ord ? __ldg(&a.gid_of_ord[ord]) : ord;
                 if (sp.nn_d2) sp.nn_d2[o + j] = __uint_as_float((uint32_t)(key >> 32));
@@ -240,9 +244,11 @@ __device__ __forceinline__ void knn_finish_pos(const KArgs& a, uint32_t* col, co
               mq[3] = __fadd_rn(mq[3], __fmul_rn(py, py));
               mq[4] = __fadd_rn(mq[4], __fmul_rn(py, pz));
               mq[5] = __fadd_rn(mq[5], __fmul_rn(pz, pz));
-              sx = __fadd_rn(sx, P[u].x);
-              sy = __fadd_rn(sy, P[u].y);
-              sz = __fadd_rn(sz, P[u].z);
+              if (!LEAN) {
+                sx = __fadd_rn(sx, P[u].x);
+                sy = __fadd_rn(sy, P[u].y);
+                sz = __fadd_rn(sz, P[u].z);
+              }
             }
           }
         }
@@ -283,7 +289,7 @@ __device__ __forceinline__ void knn_finish_pos(const KArgs& a, uint32_t* col, co
   } else if (my_slot >= 0) {
     // no result here (non-finite query, or handed to the work list which rewrites these): empty lists
     if (sp.kth_d2) sp.kth_d2[my_slot] = INFINITY;
-    if (sp.nn_idx != nullptr) {
+    if (!LEAN && sp.nn_idx != nullptr) {
       const int64_t o = (int64_t)my_slot * k;
       for (int j = 0; j < k; ++j) {
         sp.nn_idx[o + j] = -1;
@@ -291,5 +297,5 @@ __device__ __forceinline__ void knn_finish_pos(const KArgs& a, uint32_t* col, co
       }
     }
   }
-  knn_emit(a, mq, mm, valid, n_nb, Q, my_slot, gid_q, rec_all, lane);
+  knn_emit<LEAN>(a, mq, mm, valid, n_nb, Q, my_slot, gid_q, rec_all, lane);
 }

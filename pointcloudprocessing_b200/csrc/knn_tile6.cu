@@ -58,7 +58,11 @@ namespace {
 #define T6_NWARPS 4
 #endif
 constexpr int T6_WARPS = T6_NWARPS;     // warps per CTA
-constexpr int T6_CH = 128;      // staged candidates per chunk
+#ifndef T6_CHUNK
+#define T6_CHUNK 128
+#endif
+constexpr int T6_CH = T6_CHUNK;  // staged candidates per chunk (a multiple of 32)
+constexpr int T6_NL = T6_CH / 32;  // loads a lane has in flight while a chunk is staged
 // CAP (template parameter, 32 or 64) = members a lane can hold = rows of its column = width of the sorting network; the
 // histogram uses the same rows: NB = CAP - 1 bins inside the cover radius, bin NB = at or beyond it.
 constexpr float T6_MAGIC = 8388608.f;        // 2^23: float_as_uint(x + 2^23) - 0x4B000000 = round-to-nearest-even(x), 0 <= x < 2^22
@@ -136,32 +140,35 @@ __device__ __forceinline__ float bin_z(const float4 P, const float S, const floa
 }
 
 // Copies candidates [cb, cb + cnt) of the tile's virtual candidate sequence (the stencil rows' runs laid end to end)
-// into sm.cand / sm.cpos, coordinates relative to (cx, cy, cz).  Lane l takes the candidates cb + l + 32 i, i < 4
+// into sm.cand / sm.cpos, coordinates relative to (cx, cy, cz).  Lane l takes the candidates cb + l + 32 i, i < T6_NL = 4
 // (consecutive lanes read consecutive float4 of a run): it first finds the four stencil rows (counting the row ends
-// at or below each index: the rows are few), then issues the FOUR loads back to back — one round trip to L2 per
+// at or below each index: the rows are few), then issues the T6_NL loads back to back — one round trip to L2 per
 // chunk instead of one per row piece — and converts and stores when they land.
 template <int CAP>
 __device__ __forceinline__ void stage6(const float4* __restrict__ sorted, T6Smem<CAP>& sm, const int nrows, const uint32_t cb, const int cnt,
                                        const int lane, const float cx, const float cy, const float cz) {
-  uint32_t v[4];
-  int row[4] = {0, 0, 0, 0};
+  uint32_t v[T6_NL];
+  int row[T6_NL];
 #pragma unroll
-  for (int i = 0; i < 4; ++i) v[i] = cb + (uint32_t)(lane + 32 * i);
+  for (int i = 0; i < T6_NL; ++i) {
+    v[i] = cb + (uint32_t)(lane + 32 * i);
+    row[i] = 0;
+  }
 #pragma unroll 4
   for (int r = 1; r < nrows; ++r) {
     const uint32_t off = sm.run_off[r];  // broadcast
 #pragma unroll
-    for (int i = 0; i < 4; ++i) row[i] += (off <= v[i]) ? 1 : 0;
+    for (int i = 0; i < T6_NL; ++i) row[i] += (off <= v[i]) ? 1 : 0;
   }
-  uint32_t pos[4];
-  float4 P[4];
+  uint32_t pos[T6_NL];
+  float4 P[T6_NL];
 #pragma unroll
-  for (int i = 0; i < 4; ++i) pos[i] = sm.run_beg[row[i]] + (v[i] - sm.run_off[row[i]]);
+  for (int i = 0; i < T6_NL; ++i) pos[i] = sm.run_beg[row[i]] + (v[i] - sm.run_off[row[i]]);
 #pragma unroll
-  for (int i = 0; i < 4; ++i)
+  for (int i = 0; i < T6_NL; ++i)
     if (lane + 32 * i < cnt) P[i] = __ldg(&sorted[pos[i]]);
 #pragma unroll
-  for (int i = 0; i < 4; ++i) {
+  for (int i = 0; i < T6_NL; ++i) {
     if (lane + 32 * i < cnt) {
       const float x = __fsub_rn(P[i].x, cx), y = __fsub_rn(P[i].y, cy), z = __fsub_rn(P[i].z, cz);
       sm.cand[lane + 32 * i] = make_float4(x, y, z, __fmaf_rn(z, z, __fmaf_rn(y, y, __fmul_rn(x, x))));
@@ -171,7 +178,8 @@ __device__ __forceinline__ void stage6(const float4* __restrict__ sorted, T6Smem
   __syncwarp();
 }
 
-template <int CAP>
+// LEAN: records only (query-centred; the k-th distance may be asked for): see knn_finish.cuh
+template <int CAP, bool LEAN>
 __global__ void __launch_bounds__(T6_WARPS * 32, CAP == 32 ? (T6_MINB * 4) / T6_WARPS : 16 / T6_WARPS)
     knn_tile6_kernel(KArgs a, int R0, int max_groups, uint32_t* __restrict__ work_count, uint32_t* __restrict__ work_list) {
   constexpr int NB = CAP - 1;
@@ -473,7 +481,7 @@ __global__ void __launch_bounds__(T6_WARPS * 32, CAP == 32 ? (T6_MINB * 4) / T6_
   __syncthreads();
 #endif
   if (!live_warp) return;
-  knn_finish_pos(a, hcol, cnt, n_nb, ~(uint32_t)(CAP - 1), Q, emit ? my_slot : -1, sm.u.rec, lane);
+  knn_finish_pos<LEAN>(a, hcol, cnt, n_nb, ~(uint32_t)(CAP - 1), Q, emit ? my_slot : -1, sm.u.rec, lane);
 }
 
 }  // namespace
@@ -505,15 +513,19 @@ int pcp_knn_tile6_launch(pcp_ctx* ctx, const SearchParams& sp, const KArgs& a) {
   if (ctx->knobs.knn_groups > 0) max_groups = ctx->knobs.knn_groups;
   uint32_t* wc = (uint32_t*)ctx->work_count.p;
   uint32_t* wl = (uint32_t*)ctx->work_list.p;
+  const bool lean = sp.out != nullptr && sp.center_mode == PCP_CENTER_QUERY && sp.normals == nullptr && sp.nn_idx == nullptr && sp.valid == nullptr;
+#define T6_LAUNCH(CAPV, LEANV)                                                                                                  \
+  do {                                                                                                                         \
+    const size_t smem = sizeof(T6Smem<CAPV>) * T6_WARPS;                                                                       \
+    PCP_CUDA(cudaFuncSetAttribute(knn_tile6_kernel<CAPV, LEANV>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));    \
+    knn_tile6_kernel<CAPV, LEANV><<<blocks, T6_WARPS * 32, smem, ctx->stream>>>(a, sp.R0, max_groups, wc, wl);                 \
+  } while (0)
   if (sp.k <= PCP_T6_K32) {
-    const size_t smem = sizeof(T6Smem<32>) * T6_WARPS;
-    PCP_CUDA(cudaFuncSetAttribute(knn_tile6_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    knn_tile6_kernel<32><<<blocks, T6_WARPS * 32, smem, ctx->stream>>>(a, sp.R0, max_groups, wc, wl);
+    if (lean) T6_LAUNCH(32, true); else T6_LAUNCH(32, false);
   } else {
-    const size_t smem = sizeof(T6Smem<64>) * T6_WARPS;
-    PCP_CUDA(cudaFuncSetAttribute(knn_tile6_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    knn_tile6_kernel<64><<<blocks, T6_WARPS * 32, smem, ctx->stream>>>(a, sp.R0, max_groups, wc, wl);
+    if (lean) T6_LAUNCH(64, true); else T6_LAUNCH(64, false);
   }
+#undef T6_LAUNCH
   PCP_LAUNCH_CHECK("knn_tile6_kernel");
   return PCP_OK;
 }

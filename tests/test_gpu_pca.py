@@ -206,7 +206,7 @@ def test_radius_neighbors_heavy_lists(pcp, oracle):
     r = 2.0: src/buildingFacadeExtraction.cpp:83): count-then-fill through global memory + segmented sort — indices and
     distances bit-exact in (d2, index) order, heavy and light queries mixed in one call."""
     pts = synth.urban(8, 14000, extent=18.0)
-    for r in (3.0, 1.2):
+    for r in (3.0, 2.2):
         pcp.set_cloud(pts)
         pcp.build_grid(r * 1.001, 0)
         off, idx, d2 = pcp.radius_neighbors(r)
