@@ -271,7 +271,8 @@ __global__ void __launch_bounds__(128) txt_parse_kernel(const unsigned char* __r
     }
     if (!XYZ && p >= end) good = false;  // the extraction ran into the end of the line: eofbit
     // ---- strtof on the collected string: it must be a complete number
-    if (!any_digit || (found_sci && !exp_digits)) bad = true;
+    // (glibc's sscanf converts "1e" / "1e+" as 1 and consumes the exponent marker: only txt2pc's strtof-complete rule rejects them)
+    if (!any_digit || (!XYZ && found_sci && !exp_digits)) bad = true;
     uint32_t bits = 0;
     if (bad) {
       if (XYZ) break;  // matching failure: sscanf stops, nothing is stored
