@@ -44,13 +44,16 @@ def host_threads() -> int:
 
 
 def source_id() -> str:
-    """Hash of the CUDA sources libpcp.so is built from: names the ncu capture the traffic figure belongs to."""
+    """Hash of the CUDA sources the search stage (grid build + the two k-NN kernels) is compiled from: names the ncu
+    capture the traffic figure belongs to.  Sources of other entry points (text parsing, clustering, ...) do not enter."""
     import hashlib
 
     h = hashlib.sha1()
     csrc = os.path.join(ROOT, "pointcloudprocessing_b200", "csrc")
+    stage = ("Makefile", "eigen3.cuh", "grid.cu", "knn_finish.cuh", "knn_tile.cu", "knn_tile6.cu", "pcp_internal.cuh",
+             "search_common.cuh", "search_pca.cu", "sortnet32.cuh", "tile_common.cuh")
     for name in sorted(os.listdir(csrc)):
-        if name.endswith((".cu", ".cuh")) or name == "Makefile":
+        if name in stage:
             with open(os.path.join(csrc, name), "rb") as f:
                 h.update(name.encode() + b"\0" + f.read())
     return h.hexdigest()[:12]

@@ -441,7 +441,7 @@ PCP_API int pcp_set_cloud_txt(pcp_ctx* ctx, const void* text, int64_t n_bytes, i
  * signed char (the reference scans %s into one char: the overflow is the one undefined part and is not reproduced);
  * a field that does not parse ends the line and keeps the previous line's value, as every field after it; a value
  * beyond the float range becomes +-inf; the eof() loop pushes one more copy of the last point after a final newline
- * (and one zero point for an empty file).  A line of 255 characters or more is PCP_ERR_INVALID_ARG (the reference
+ * (and one zero point for an empty file).  A line of 256 characters or more is PCP_ERR_INVALID_ARG (the reference
  * never returns from it).  inf / nan / hexadecimal fields are not recognised.  Same arguments as pcp_set_cloud_txt. */
 PCP_API int pcp_set_cloud_xyz(pcp_ctx* ctx, const void* text, int64_t n_bytes, int text_is_device, int64_t* n_points,
                               float* out_xyzi, int64_t out_capacity, int out_is_device);

@@ -135,7 +135,7 @@ void orc_mean_shift_step(const float* orig_xyzi, const float* cur_xyzi, int64_t 
 /* preprocess::txt2pc (src/smoothing.cpp:39-81): text -> points (x y z intensity per line), the reference's own
  * stream statements.  Returns the number of lines = points; writes at most `capacity` of them. */
 int64_t orc_txt2pc(const char* text, int64_t n_bytes, float* out_xyzi, int64_t capacity);
-/* preprocess::xyz2pc (src/smoothing.cpp:83-125): getline(line, 256) + sscanf("%f %f %f %s"); -1 for a line of 255+ characters */
+/* preprocess::xyz2pc (src/smoothing.cpp:83-125): getline(line, 256) + sscanf("%f %f %f %s"); -1 for a line of 256+ characters (255 still fit: the delimiter is tested before the count, [istream.unformatted]) */
 int64_t orc_xyz2pc(const char* text, int64_t n_bytes, float* out_xyzi, int64_t capacity);
 
 int orc_num_threads(void);

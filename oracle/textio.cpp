@@ -36,7 +36,7 @@ extern "C" int64_t orc_txt2pc(const char* text, int64_t n_bytes, float* out_xyzi
 // by at least the terminating NUL); here the token lands in a line-sized buffer and its first byte is what the
 // reference's `intens` would hold.  `intens` and `pt` live across lines as upstream (fields a line does not
 // supply keep their previous values; the reference's are uninitialised at first, here 0).  Returns the number of
-// points, or -1 when a line has 255 characters or more (getline(line, 256) then sets failbit and the reference's
+// points, or -1 when a line has 256 characters or more (getline(line, 256) then sets failbit and the reference's
 // loop never ends).
 #include <cstdio>
 extern "C" int64_t orc_xyz2pc(const char* text, int64_t n_bytes, float* out_xyzi, int64_t capacity) {
@@ -48,7 +48,7 @@ extern "C" int64_t orc_xyz2pc(const char* text, int64_t n_bytes, float* out_xyzi
   int64_t count = 0;
   while (!xyzfile.eof()) {
     xyzfile.getline(line, 256);
-    if (xyzfile.fail() && !xyzfile.eof()) return -1;  // 255 characters without a newline
+    if (xyzfile.fail() && !xyzfile.eof()) return -1;  // more than 255 characters before the newline
     token[0] = intens;
     const int got = std::sscanf(line, "%f %f %f %255s", &pt[0], &pt[1], &pt[2], token);
     if (got == 4) intens = token[0];

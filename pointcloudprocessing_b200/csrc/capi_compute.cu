@@ -667,7 +667,7 @@ static int set_cloud_text(pcp_ctx* ctx, const void* text, int64_t n_bytes, int t
     if (xyz) {
       PCP_CUDA(cudaStreamSynchronize(ctx->stream));
       if (too_long)
-        return pcp_fail(ctx, PCP_ERR_INVALID_ARG, "pcp_set_cloud_xyz: a line of 255 characters or more (the reference's getline(line, 256) loop never ends on it)");
+        return pcp_fail(ctx, PCP_ERR_INVALID_ARG, "pcp_set_cloud_xyz: a line of 256 characters or more (the reference's getline(line, 256) loop never ends on it)");
     }
     *n_points = n;
   }

@@ -201,7 +201,7 @@ __device__ __forceinline__ bool is_digit(unsigned char c) { return c >= '0' && c
 // sscanf(line, "%f %f %f %s", &x, &y, &z, &intens); pt.intensity = intens: three floats and the FIRST BYTE of the
 // fourth token as a signed char; a field that does not parse ends the line WITHOUT being written (it keeps the
 // previous line's value, like every field after it), a value beyond the float range is stored as +-inf and the scan
-// goes on; a line of 255 characters or more raises *too_long (the reference's loop never ends on it).  Fields in
+// goes on; a line of 256 characters or more raises *too_long (the reference's loop never ends on it).  Fields in
 // inf / nan / hexadecimal notation, which sscanf would accept, are outside the subset offered here (they end the line).
 template <bool XYZ>
 __global__ void __launch_bounds__(128) txt_parse_kernel(const unsigned char* __restrict__ text, int64_t n_bytes,
@@ -212,7 +212,7 @@ __global__ void __launch_bounds__(128) txt_parse_kernel(const unsigned char* __r
   int64_t p = starts[j];
   int64_t end = j + 1 < n_lines ? starts[j + 1] - 1 : n_bytes;  // drop the '\n'
   if (j + 1 == n_lines && end > p && text[end - 1] == '\n') --end;
-  if (XYZ && end - p >= 255) atomicExch(too_long, 1);
+  if (XYZ && end - p >= 256) atomicExch(too_long, 1);
   float v[4] = {0.f, 0.f, 0.f, 0.f};
   int set_mask = 0;
   bool good = true;  // the stringstream's good(): no failbit, no eofbit

@@ -132,9 +132,13 @@ def test_xyz_random_and_limits(pcp, oracle):
     pcp.build_grid(0.5, 0)
     assert pcp.radius_count(0.5, 4).shape[0] == got.shape[0]
     # a line the reference never returns from is an error here, as in the oracle
-    bad = b"1 2 3 4\n" + b"7" * 255 + b"\n"
-    assert oracle.xyz2pc(bad) is None
-    with pytest.raises(Exception):
-        pcp.set_cloud_xyz(bad)
-    ok = b"1 2 3 4\n" + b" " * 250 + b"7 8\n"   # 254 characters: fine
-    np.testing.assert_array_equal(pcp.set_cloud_xyz(ok).view(np.uint32), oracle.xyz2pc(ok).view(np.uint32))
+    # (getline(line, 256) stores up to 255 characters and tests the delimiter before the count: 255 fit, 256 set failbit)
+    for tail in (b"\n", b""):
+        bad = b"1 2 3 4\n" + b"7" * 256 + tail
+        assert oracle.xyz2pc(bad) is None
+        with pytest.raises(Exception):
+            pcp.set_cloud_xyz(bad)
+        for ok in (b"1 2 3 4\n" + b" " * 250 + b"7 8\n" + tail,          # 254 characters
+                   b"1 2 3 4\n" + b"7" * 255 + tail,                      # 255 characters: the longest line the reference reads
+                   b"1 2 3 4\n" + b" " * 249 + b"7.5 8 9" + tail):
+            np.testing.assert_array_equal(pcp.set_cloud_xyz(ok).view(np.uint32), oracle.xyz2pc(ok).view(np.uint32))

@@ -294,3 +294,7 @@ def test_xyz2pc_known_answers(oracle):
     assert oracle.xyz2pc(b"1 2 3 7").tolist() == [[1, 2, 3, 55]]  # '7' is the character, not the number
     assert oracle.xyz2pc(b"").tolist() == [[0, 0, 0, 0]]
     assert oracle.xyz2pc(b"x" * 300) is None  # getline(line, 256) sets failbit: the reference loops forever
+    # the boundary: 255 characters are stored and the delimiter (or the end of the file) is tested before the count
+    # ([istream.unformatted]: eof, delimiter, then n - 1 characters stored), so a 255-character line reads and 256 fail
+    assert oracle.xyz2pc(b"5" * 255 + b"\n").shape == (2, 4) and oracle.xyz2pc(b"5" * 255).shape == (1, 4)
+    assert oracle.xyz2pc(b"5" * 256 + b"\n") is None and oracle.xyz2pc(b"5" * 256) is None
