@@ -6,8 +6,12 @@
 // The kernel is bound by latency and by what a warp keeps resident (shared memory, registers), not by arithmetic
 // (ncu, profiles/r02a_*: 9 % of a warp's cycles issue), so every stage is built to hold little and wait little:
 //   staging   the union of the tile's stencils (contiguous runs of the cell-sorted array) is copied to shared memory
-//             128 candidates at a time, FOUR loads in flight per lane, in a LOCAL frame (p' = p - centre) together
-//             with |p'|^2 and the candidate's sorted position;
+//             128 candidates at a time by the TMA unit: one 1-D bulk copy (cp.async.bulk.shared.global, SASS UBLKCP) per
+//             piece of a run, completion counted in bytes by an mbarrier, two buffers — the copy of chunk c + 1 is in
+//             flight while the warp works on chunk c and costs it neither registers nor issue slots; the chunk is then
+//             rewritten in place in a LOCAL frame (p' = p - centre) together with |p'|^2 (and, in pass 2 only, the
+//             candidates' sorted positions).  -DT6_TMA=0 keeps the earlier register staging (four LDG.128 in flight
+//             per lane) for A/B runs;
 //   pass 1    bin coordinate Y = S |p' - q'|^2 + off = S |p'|^2 + (S |q'|^2 + off) - 2 S q'.p': one broadcast LDS.128 +
 //             four FFMA with per-lane constants (the last one saturating to [0, 1]: FFMA.SAT), one more FFMA adds 2^23
 //             so that the float's low bits ARE the bin, one IMAD forms the address and one shared reduction counts
@@ -71,14 +75,17 @@ constexpr int T6_REC_WORDS = 17;
 #ifndef T6_SYNC
 #define T6_SYNC 1     // CTA barriers around the straight-line sorting network (instruction-cache alignment of the four warps)
 #endif
+#ifndef T6_TMA
+#define T6_TMA 1      // stage the candidate chunks with 1-D TMA bulk copies + mbarrier, double-buffered (0: LDG.128 -> STS.128 through registers)
+#endif
 #ifndef T6_MINB
 #define T6_MINB 5     // CTAs per SM the 32-member kernel is compiled for (register budget 65536 / (128 * T6_MINB)); measured: 5 beats 6 and 7 (spills)
 #endif
 
 template <int CAP>
 struct __align__(16) T6Smem {
-  float4 cand[T6_CH];                    // staged candidates of the current chunk: local x, y, z and |p'|^2
-  uint32_t cpos[T6_CH];                  // their sorted positions
+  float4 cand[T6_TMA ? 2 : 1][T6_CH];    // staged candidates of the current chunk (and, with TMA staging, the next one in flight): local x, y, z and |p'|^2
+  uint32_t cpos[T6_CH];                  // their sorted positions (pass 2)
   // One 32-bit column per lane, three uses: pass 1 counts into plane[bin][lane]; pass 2 stores the sorted position of
   // member j in plane[j][lane]; after the sort the same rows hold the positions in neighbour order.  The record
   // staging (32 x 17 floats) reuses the space at the end.
@@ -88,6 +95,9 @@ struct __align__(16) T6Smem {
   } u;
   uint32_t run_beg[TA_MAXROWS];
   uint32_t run_off[TA_MAXROWS + 1];
+#if T6_TMA
+  unsigned long long bar[2];             // one mbarrier per chunk buffer (transaction bytes of the bulk copies)
+#endif
 };
 
 __device__ __forceinline__ float fma_sat(float a, float b, float c) {
@@ -120,6 +130,40 @@ __device__ __forceinline__ void red_add_u32(const uint32_t addr, const uint32_t 
 }
 __device__ __forceinline__ uint32_t smem_addr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
+#if T6_TMA
+// ---- 1-D TMA bulk copies global -> shared, completion on an mbarrier (PTX ISA: cp.async.bulk, mbarrier) ----
+__device__ __forceinline__ void mbar_init(const uint32_t bar, const uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+// one arrival (the barrier's only one) + the bytes the phase waits for
+__device__ __forceinline__ void mbar_arrive_expect_tx(const uint32_t bar, const uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+// src and dst 16-byte aligned, bytes a multiple of 16; the copy's bytes are counted on `bar`
+__device__ __forceinline__ void bulk_g2s(const uint32_t dst, const void* src, const uint32_t bytes, const uint32_t bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst), "l"(src), "r"(bytes), "r"(bar)
+               : "memory");
+}
+// waits for the phase of the given parity; a wait that does not end (a lost copy) traps instead of hanging the GPU
+__device__ __forceinline__ void mbar_wait(const uint32_t bar, const uint32_t parity) {
+  uint32_t done = 0;
+#pragma unroll 1
+  for (uint32_t spins = 0; !done; ++spins) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+        "selp.u32 %0, 1, 0, p;\n"
+        "}"
+        : "=r"(done)
+        : "r"(bar), "r"(parity)
+        : "memory");
+    if (spins > (1u << 22)) __trap();
+  }
+}
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+#endif
+
 __device__ __forceinline__ float sqrt_approx(float x) {
   float r;
   asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));  // one MUFU.SQRT; relative error below 2^-22 (PTX ISA), denormals -> 0
@@ -139,14 +183,11 @@ __device__ __forceinline__ float bin_z(const float4 P, const float S, const floa
   return __fmaf_rn(sqrt_approx(y), (float)NB, T6_MAGIC);
 }
 
-// Copies candidates [cb, cb + cnt) of the tile's virtual candidate sequence (the stencil rows' runs laid end to end)
-// into sm.cand / sm.cpos, coordinates relative to (cx, cy, cz).  Lane l takes the candidates cb + l + 32 i, i < T6_NL = 4
-// (consecutive lanes read consecutive float4 of a run): it first finds the four stencil rows (counting the row ends
-// at or below each index: the rows are few), then issues the T6_NL loads back to back — one round trip to L2 per
-// chunk instead of one per row piece — and converts and stores when they land.
+// The sorted positions of the candidates [cb, cb + cnt) of the tile's virtual candidate sequence (the stencil rows' runs
+// laid end to end): lane l takes the candidates cb + l + 32 i, i < T6_NL, and finds their stencil rows by counting the
+// row ends at or below each index (the rows are few).
 template <int CAP>
-__device__ __forceinline__ void stage6(const float4* __restrict__ sorted, T6Smem<CAP>& sm, const int nrows, const uint32_t cb, const int cnt,
-                                       const int lane, const float cx, const float cy, const float cz) {
+__device__ __forceinline__ void chunk_positions(const T6Smem<CAP>& sm, const int nrows, const uint32_t cb, const int lane, uint32_t (&pos)[T6_NL]) {
   uint32_t v[T6_NL];
   int row[T6_NL];
 #pragma unroll
@@ -160,10 +201,67 @@ __device__ __forceinline__ void stage6(const float4* __restrict__ sorted, T6Smem
 #pragma unroll
     for (int i = 0; i < T6_NL; ++i) row[i] += (off <= v[i]) ? 1 : 0;
   }
-  uint32_t pos[T6_NL];
-  float4 P[T6_NL];
 #pragma unroll
   for (int i = 0; i < T6_NL; ++i) pos[i] = sm.run_beg[row[i]] + (v[i] - sm.run_off[row[i]]);
+}
+
+#if T6_TMA
+// Starts the copy of candidates [cb, cb + cnt) into chunk buffer `buf`: the chunk is a few contiguous pieces of the
+// cell-sorted array (one per stencil row that overlaps it); lane r issues the piece of row r as ONE bulk copy.  The
+// buffer's mbarrier completes when all cnt * 16 bytes have landed.  The proxy fence orders the warp's earlier
+// (generic) reads and writes of the buffer before the copy unit's writes.
+template <int CAP>
+__device__ __forceinline__ void chunk_issue(const float4* __restrict__ sorted, T6Smem<CAP>& sm, const int nrows, const uint32_t cb, const int cnt,
+                                            const int lane, const int buf) {
+  const uint32_t bar = smem_addr(&sm.bar[buf]);
+  fence_proxy_async();
+  if (lane == 0) mbar_arrive_expect_tx(bar, (uint32_t)cnt * 16u);
+  __syncwarp();
+#pragma unroll 1
+  for (int r = lane; r < nrows; r += 32) {
+    const uint32_t o0 = sm.run_off[r], o1 = sm.run_off[r + 1];
+    const uint32_t s = max(o0, cb), e = min(o1, cb + (uint32_t)cnt);
+    if (s < e) bulk_g2s(smem_addr(&sm.cand[buf][s - cb]), sorted + sm.run_beg[r] + (s - o0), (e - s) * 16u, bar);
+  }
+}
+// Waits for chunk buffer `buf` and rewrites it in place in the local frame: x - cx, y - cy, z - cz and |p'|^2.
+// WITH_POS (pass 2): the candidates' sorted positions go to sm.cpos.  CONV = false: the chunk was converted before
+// (a tile whose candidates fit one chunk keeps it from pass 1), only the positions are wanted.
+template <int CAP, bool CONV, bool WITH_POS>
+__device__ __forceinline__ void chunk_land(T6Smem<CAP>& sm, const int nrows, const uint32_t cb, const int cnt, const int lane, const int buf,
+                                           uint32_t& parity, const float cx, const float cy, const float cz) {
+  if (CONV) {
+    mbar_wait(smem_addr(&sm.bar[buf]), (parity >> buf) & 1u);
+    parity ^= 1u << buf;
+    float4* c = sm.cand[buf];
+#pragma unroll
+    for (int i = 0; i < T6_NL; ++i) {
+      if (lane + 32 * i < cnt) {
+        const float4 P = c[lane + 32 * i];
+        const float x = __fsub_rn(P.x, cx), y = __fsub_rn(P.y, cy), z = __fsub_rn(P.z, cz);
+        c[lane + 32 * i] = make_float4(x, y, z, __fmaf_rn(z, z, __fmaf_rn(y, y, __fmul_rn(x, x))));
+      }
+    }
+  }
+  if (WITH_POS) {
+    uint32_t pos[T6_NL];
+    chunk_positions(sm, nrows, cb, lane, pos);
+#pragma unroll
+    for (int i = 0; i < T6_NL; ++i)
+      if (lane + 32 * i < cnt) sm.cpos[lane + 32 * i] = pos[i];
+  }
+  __syncwarp();
+}
+#else
+// Register staging: copies candidates [cb, cb + cnt) into sm.cand[0] / sm.cpos, coordinates relative to (cx, cy, cz):
+// every lane issues its T6_NL loads back to back — one round trip to L2 per chunk instead of one per row piece —
+// and converts and stores when they land.
+template <int CAP>
+__device__ __forceinline__ void stage6(const float4* __restrict__ sorted, T6Smem<CAP>& sm, const int nrows, const uint32_t cb, const int cnt,
+                                       const int lane, const float cx, const float cy, const float cz) {
+  uint32_t pos[T6_NL];
+  float4 P[T6_NL];
+  chunk_positions(sm, nrows, cb, lane, pos);
 #pragma unroll
   for (int i = 0; i < T6_NL; ++i)
     if (lane + 32 * i < cnt) P[i] = __ldg(&sorted[pos[i]]);
@@ -171,12 +269,13 @@ __device__ __forceinline__ void stage6(const float4* __restrict__ sorted, T6Smem
   for (int i = 0; i < T6_NL; ++i) {
     if (lane + 32 * i < cnt) {
       const float x = __fsub_rn(P[i].x, cx), y = __fsub_rn(P[i].y, cy), z = __fsub_rn(P[i].z, cz);
-      sm.cand[lane + 32 * i] = make_float4(x, y, z, __fmaf_rn(z, z, __fmaf_rn(y, y, __fmul_rn(x, x))));
+      sm.cand[0][lane + 32 * i] = make_float4(x, y, z, __fmaf_rn(z, z, __fmaf_rn(y, y, __fmul_rn(x, x))));
       sm.cpos[lane + 32 * i] = pos[i];
     }
   }
   __syncwarp();
 }
+#endif
 
 // LEAN: records only (query-centred; the k-th distance may be asked for): see knn_finish.cuh
 template <int CAP, bool LEAN>
@@ -201,6 +300,15 @@ __global__ void __launch_bounds__(T6_WARPS * 32, CAP == 32 ? (T6_MINB * 4) / T6_
   const bool finite = active && cid < g.n_cells;
   uint32_t* const hcol = &sm.u.plane[0][lane];
   const uint32_t hcol_a = smem_addr(hcol), cand_a = smem_addr(sm.cand), cpos_a = smem_addr(sm.cpos);
+#if T6_TMA
+  uint32_t parity = 0;  // bit b: the phase of chunk buffer b's mbarrier the next wait is for
+  if (lane == 0) {
+    mbar_init(smem_addr(&sm.bar[0]), 1);
+    mbar_init(smem_addr(&sm.bar[1]), 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncwarp();
+#endif
   const uint32_t hbase = hcol_a - T6_MAGIC_BITS * 128u;  // (bits of 2^23 + bin) * 128 + hbase = address of plane[bin][lane], modulo 2^32
   uint32_t wp = hcol_a;      // next free entry of this lane's member column
   const uint32_t my_row = cid / (uint32_t)g.dim[0];
@@ -268,13 +376,23 @@ __global__ void __launch_bounds__(T6_WARPS * 32, CAP == 32 ? (T6_MINB * 4) / T6_
       }
       const uint32_t inc = hist_on ? 1u : 0u;
       __syncwarp();
+#if T6_TMA
+      if (total > 0) chunk_issue(sorted, sm, nrows, 0u, (int)min((uint32_t)T6_CH, total), lane, 0);
+#endif
 #pragma unroll 1
       for (uint32_t cb = 0; cb < total; cb += T6_CH) {
         const int n_ch = (int)min((uint32_t)T6_CH, total - cb);
+#if T6_TMA
+        const int buf = (int)((cb / T6_CH) & 1u);
+        if (cb + T6_CH < total) chunk_issue(sorted, sm, nrows, cb + T6_CH, (int)min((uint32_t)T6_CH, total - cb - T6_CH), lane, buf ^ 1);
+        chunk_land<CAP, true, false>(sm, nrows, cb, n_ch, lane, buf, parity, cx, cy, cz);
+        uint32_t ca = cand_a + (uint32_t)buf * (uint32_t)(T6_CH * 16);
+#else
         stage6(sorted, sm, nrows, cb, n_ch, lane, cx, cy, cz);
+        uint32_t ca = cand_a;
+#endif
         // four candidates per step: broadcast loads, five FFMA each, and the histogram update as one IMAD (the
         // float's bits times the row stride, the constant part folded into hbase) + one shared reduction
-        uint32_t ca = cand_a;
         int j = 0;
 #pragma unroll 2
         for (; j + 4 <= n_ch; j += 4, ca += 64) {
@@ -361,10 +479,22 @@ __global__ void __launch_bounds__(T6_WARPS * 32, CAP == 32 ? (T6_MINB * 4) / T6_
         tmax = fmaxf(tmax, __shfl_xor_sync(PCP_FULL, tmax, o));
       }
       tmax = tmax * 1.001f + 1e-5f * g.cell * g.cell;  // slack for the rounding of the local coordinates and of the box distance
+#if T6_TMA
+      if (!resident) chunk_issue(sorted, sm, nrows, 0u, (int)min((uint32_t)T6_CH, total), lane, 0);
+#endif
 #pragma unroll 1
       for (uint32_t cb = 0; cb < total; cb += T6_CH) {
         int n_ch = (int)min((uint32_t)T6_CH, total - cb);
+#if T6_TMA
+        const int buf = (int)((cb / T6_CH) & 1u);
+        if (cb + T6_CH < total) chunk_issue(sorted, sm, nrows, cb + T6_CH, (int)min((uint32_t)T6_CH, total - cb - T6_CH), lane, buf ^ 1);
+        if (resident) chunk_land<CAP, false, true>(sm, nrows, cb, n_ch, lane, buf, parity, cx, cy, cz);
+        else chunk_land<CAP, true, true>(sm, nrows, cb, n_ch, lane, buf, parity, cx, cy, cz);
+        float4* const cand = sm.cand[buf];
+#else
         if (!resident) stage6(sorted, sm, nrows, cb, n_ch, lane, cx, cy, cz);
+        float4* const cand = sm.cand[0];
+#endif
         {
           int kept = 0;
 #pragma unroll 1
@@ -374,7 +504,7 @@ __global__ void __launch_bounds__(T6_WARPS * 32, CAP == 32 ? (T6_MINB * 4) / T6_
             uint32_t ps = 0;
             bool keep = false;
             if (i < n_ch) {
-              P = sm.cand[i];
+              P = cand[i];
               ps = sm.cpos[i];
               const float dx = fmaxf(fmaxf(bx0 - P.x, P.x - bx1), 0.f), dy = fmaxf(fmaxf(by0 - P.y, P.y - by1), 0.f);
               const float dz = fmaxf(fmaxf(bz0 - P.z, P.z - bz1), 0.f);
@@ -384,7 +514,7 @@ __global__ void __launch_bounds__(T6_WARPS * 32, CAP == 32 ? (T6_MINB * 4) / T6_
             __syncwarp();  // every lane has read its candidate before any slot is overwritten
             if (keep) {
               const int d = kept + __popc(km & ((1u << lane) - 1u));
-              sm.cand[d] = P;
+              cand[d] = P;
               sm.cpos[d] = ps;
             }
             kept += __popc(km);
@@ -393,7 +523,11 @@ __global__ void __launch_bounds__(T6_WARPS * 32, CAP == 32 ? (T6_MINB * 4) / T6_
           T6STAT(8, lane == 0 ? kept : 0);
           n_ch = kept;
         }
+#if T6_TMA
+        uint32_t ca = cand_a + (uint32_t)buf * (uint32_t)(T6_CH * 16), pa = cpos_a;
+#else
         uint32_t ca = cand_a, pa = cpos_a;
+#endif
         int j = 0;
 #pragma unroll 2
         for (; j + 4 <= n_ch; j += 4, ca += 64, pa += 16) {

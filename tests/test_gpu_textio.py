@@ -140,5 +140,5 @@ def test_xyz_random_and_limits(pcp, oracle):
             pcp.set_cloud_xyz(bad)
         for ok in (b"1 2 3 4\n" + b" " * 250 + b"7 8\n" + tail,          # 254 characters
                    b"1 2 3 4\n" + b"7" * 255 + tail,                      # 255 characters: the longest line the reference reads
-                   b"1 2 3 4\n" + b" " * 249 + b"7.5 8 9" + tail):
+                   b"1 2 3 4\n" + b" " * 248 + b"7.5 8 9" + tail):
             np.testing.assert_array_equal(pcp.set_cloud_xyz(ok).view(np.uint32), oracle.xyz2pc(ok).view(np.uint32))
