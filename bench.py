@@ -320,6 +320,7 @@ def main():
     ap.add_argument("--rank-clouds", default="tile", choices=["tile", "seeded"],
                     help="N > 1: every rank's slab is a translated copy of the same 1 M-point tile (identical work per GPU), or a tile of its own seed")
     ap.add_argument("--e2e-contexts", type=int, default=3, help="C-ABI contexts in flight for the end-to-end figure (N = 1)")
+    ap.add_argument("--e2e-threads", type=int, default=1, help="1: one host thread per context (default); 0: one thread issues every context's calls")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -465,23 +466,44 @@ def main():
 
         def step_async(s):
             c = ctxs[s % nctx]
-            c.synchronize()  # its previous cloud (step s-2) is complete; buffers may be reused
+            c.synchronize()  # its previous cloud (step s - nctx) is complete; buffers may be reused
             c.set_cloud_host_ptr(h_in.data_ptr(), n, 16)
             c.build_grid(args.cell, k)
             c.knn_pca(k, capi.CENTER_QUERY, out_host_ptr=h_outs[s % nctx].data_ptr())
 
-        for s in range(2 * nctx):
-            step_async(s)
-        for c in ctxs:
-            c.synchronize()
+        # One host thread per context (ctypes releases the GIL inside the library): a context's grid build waits on the
+        # host for its bounding box, and with a single thread that wait also held back the launches of the other contexts.
+        # Thread t runs the steps s = t, t + nctx, ... of the args.steps timed steps; the clock stops when all are done.
+        def run_steps(first, count):
+            if args.e2e_threads:
+                go = threading.Barrier(nctx + 1)
+
+                def worker(t):
+                    go.wait()
+                    for s in range(first + t, first + count, nctx):
+                        step_async(s)
+                    ctxs[t].synchronize()
+
+                ths = [threading.Thread(target=worker, args=(t,)) for t in range(nctx)]
+                for th in ths:
+                    th.start()
+                go.wait()
+                t_start = time.perf_counter()
+                for th in ths:
+                    th.join()
+                return time.perf_counter() - t_start
+            t_start = time.perf_counter()
+            for s in range(first, first + count):
+                step_async(s)
+            for c in ctxs:
+                c.synchronize()
+            return time.perf_counter() - t_start
+
+        run_steps(0, 2 * nctx)
         barrier()
-        t0 = time.perf_counter()
-        for s in range(args.steps):
-            step_async(s)
-        for c in ctxs:
-            c.synchronize()
-        e2e_s = time.perf_counter() - t0
-        e2e_mode = f"{nctx} contexts in flight (pcp_set_host_async), each step = H2D cloud + grid + search + D2H records"
+        e2e_s = run_steps(2 * nctx, args.steps)
+        e2e_mode = (f"{nctx} contexts in flight (pcp_set_host_async), " + ("one host thread each, " if args.e2e_threads else "one host thread, ") +
+                    "each step = H2D cloud + grid + search + D2H records")
         for c in ctxs:
             c.set_host_async(False)
         for c in extra:

@@ -76,7 +76,19 @@ __global__ void __launch_bounds__(256) bbox_kernel(const float4* __restrict__ pt
 
 __global__ void bbox_init_kernel(uint32_t* bbox) {
   if (threadIdx.x < 3) bbox[threadIdx.x] = 0xFFFFFFFFu;
-  else if (threadIdx.x < 6) bbox[threadIdx.x] = 0u;
+  else if (threadIdx.x < 8) bbox[threadIdx.x] = 0u;  // [6]: "the shard's own global ids are not strictly ascending"
+}
+
+// Shards: are the own points' global ids strictly ascending (a slab cut out of a cloud in index order)?  Then only the
+// halo entries need sorting to rank every id (below).  Sets *flag otherwise.
+__global__ void __launch_bounds__(256) gid_ascending_kernel(const int32_t* __restrict__ gid, int64_t n_own, uint32_t* __restrict__ flag) {
+  const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  bool bad = false;
+  if (i < n_own) {
+    const int32_t g = __ldg(gid + i);
+    bad = g < 0 || g == 0x7fffffff || (i + 1 < n_own && __ldg(gid + i + 1) <= g);
+  }
+  if (__any_sync(0xffffffffu, bad) && (threadIdx.x & 31) == 0) atomicOr(flag, 1u);
 }
 
 // Cell coordinates in double: (p − origin) is exact for fp32 inputs, so a neighbour within
@@ -142,6 +154,38 @@ __global__ void __launch_bounds__(256) iota_kernel(int32_t* __restrict__ v, int6
   int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (i < n) v[i] = (int32_t)i;
 }
+// Rank of every global id when the own ids ascend and the halo ids hs[0..m) are sorted: an own point's rank is its
+// index plus the halo ids below it, a halo entry's rank its sorted position plus the own ids at or below it — what
+// a stable sort of all n ids gives (own entries come first in local order), from a sort of the m halo entries only.
+__global__ void __launch_bounds__(256) rank_own_kernel(const int32_t* __restrict__ gid, int64_t n_own, const uint32_t* __restrict__ hs, int m,
+                                                       int32_t* __restrict__ ord_of_li, int32_t* __restrict__ gid_of_ord) {
+  const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i >= n_own) return;
+  const uint32_t g = (uint32_t)__ldg(gid + i);
+  int lo = 0, hi = m;  // first halo id >= g
+  while (lo < hi) {
+    const int mid = (lo + hi) >> 1;
+    if (__ldg(hs + mid) < g) lo = mid + 1; else hi = mid;
+  }
+  const int32_t ord = (int32_t)(i + lo);
+  ord_of_li[i] = ord;
+  gid_of_ord[ord] = (int32_t)g;
+}
+__global__ void __launch_bounds__(256) rank_halo_kernel(const int32_t* __restrict__ gid, int64_t n_own, const uint32_t* __restrict__ hs,
+                                                        const int32_t* __restrict__ hv, int m, int32_t* __restrict__ ord_of_li,
+                                                        int32_t* __restrict__ gid_of_ord) {
+  const int r = blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= m) return;
+  const uint32_t g = __ldg(hs + r);
+  int64_t lo = 0, hi = n_own;  // first own id > g
+  while (lo < hi) {
+    const int64_t mid = (lo + hi) >> 1;
+    if ((uint32_t)__ldg(gid + mid) <= g) lo = mid + 1; else hi = mid;
+  }
+  const int32_t ord = (int32_t)(r + lo);
+  ord_of_li[n_own + __ldg(hv + r)] = ord;
+  gid_of_ord[ord] = (int32_t)g;
+}
 __global__ void __launch_bounds__(256) invert_kernel(const int32_t* __restrict__ li_of_ord, int32_t* __restrict__ ord_of_li, int64_t n) {
   int64_t o = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (o < n) ord_of_li[li_of_ord[o]] = (int32_t)o;
@@ -187,7 +231,7 @@ int pcp_grid_build_impl(pcp_ctx* ctx, float cell, int k_hint) {
   int rc;
 
   // ---- bbox
-  if ((rc = pcp_reserve(ctx, ctx->bbox, 6 * sizeof(uint32_t)))) return rc;
+  if ((rc = pcp_reserve(ctx, ctx->bbox, 8 * sizeof(uint32_t)))) return rc;
   pcp_tic(ctx, PCP_T_BBOX);
   bbox_init_kernel<<<1, 32, 0, st>>>((uint32_t*)ctx->bbox.p);
   PCP_LAUNCH_CHECK("bbox_init_kernel");
@@ -197,7 +241,11 @@ int pcp_grid_build_impl(pcp_ctx* ctx, float cell, int k_hint) {
     PCP_LAUNCH_CHECK("bbox_kernel");
   }
   pcp_toc(ctx, PCP_T_BBOX);
-  uint32_t hb[6];
+  if (ctx->d_gid && ctx->n_query > 0) {  // rides on the bounding box's read-back: no host wait of its own
+    gid_ascending_kernel<<<(int)((ctx->n_query + 255) / 256), 256, 0, st>>>(ctx->d_gid, ctx->n_query, (uint32_t*)ctx->bbox.p + 6);
+    PCP_LAUNCH_CHECK("gid_ascending_kernel");
+  }
+  uint32_t hb[8];
   PCP_CUDA(cudaMemcpyAsync(hb, ctx->bbox.p, sizeof(hb), cudaMemcpyDeviceToHost, st));
   PCP_CUDA(cudaStreamSynchronize(st));
   double lo[3], hi[3], ext[3];
@@ -269,19 +317,45 @@ int pcp_grid_build_impl(pcp_ctx* ctx, float cell, int k_hint) {
     if ((rc = pcp_reserve(ctx, ctx->gid_sorted, n * sizeof(int32_t)))) return rc;
     if ((rc = pcp_reserve(ctx, ctx->gid_tmp, n * sizeof(int32_t)))) return rc;
     if ((rc = pcp_reserve(ctx, ctx->ord_of_li, n * sizeof(int32_t)))) return rc;
-    if ((rc = pcp_reserve(ctx, ctx->li_of_ord, n * sizeof(int32_t)))) return rc;
     const int nbi = (int)((n + 255) / 256);
-    iota_kernel<<<nbi, 256, 0, st>>>((int32_t*)ctx->gid_tmp.p, n);
-    PCP_LAUNCH_CHECK("iota_kernel");
-    size_t tb = 0;
-    PCP_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tb, (const uint32_t*)ctx->d_gid, (uint32_t*)ctx->gid_sorted.p,
-                                             (const int32_t*)ctx->gid_tmp.p, (int32_t*)ctx->li_of_ord.p, (int)n, 0, 32, st));
-    if ((rc = pcp_reserve(ctx, ctx->sort_tmp, tb))) return rc;
-    PCP_CUDA(cub::DeviceRadixSort::SortPairs(ctx->sort_tmp.p, tb, (const uint32_t*)ctx->d_gid, (uint32_t*)ctx->gid_sorted.p,
-                                             (const int32_t*)ctx->gid_tmp.p, (int32_t*)ctx->li_of_ord.p, (int)n, 0, 32, st));
-    ctx->launches += 5;
-    invert_kernel<<<nbi, 256, 0, st>>>((const int32_t*)ctx->li_of_ord.p, (int32_t*)ctx->ord_of_li.p, n);
-    PCP_LAUNCH_CHECK("invert_kernel");
+    const int64_t n_own = ctx->n_query;
+    const int64_t m = n - n_own;  // halo entries (padding included: ids 0x7fffffff, ranked last in arrival order)
+    if (n_own > 0 && hb[6] == 0u && !ctx->knobs.shard_full_sort) {
+      // the own ids ascend (a slab cut from a cloud in index order): sort the halo entries only and rank by two
+      // binary searches — the full-width sort of all n ids was the largest fixed cost of a sharded build
+      int32_t* hv_in = (int32_t*)ctx->gid_tmp.p;    // 0 .. m-1
+      if ((rc = pcp_reserve(ctx, ctx->li_of_ord, (size_t)std::max<int64_t>(n, 2 * m) * sizeof(int32_t)))) return rc;
+      uint32_t* hs = (uint32_t*)ctx->li_of_ord.p;   // the halo ids, sorted
+      int32_t* hv = (int32_t*)ctx->li_of_ord.p + m; // their halo-local indices
+      if (m > 0) {
+        iota_kernel<<<(int)((m + 255) / 256), 256, 0, st>>>(hv_in, m);
+        PCP_LAUNCH_CHECK("iota_kernel");
+        size_t tb = 0;
+        PCP_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tb, (const uint32_t*)(ctx->d_gid + n_own), hs, (const int32_t*)hv_in, hv, (int)m, 0, 32, st));
+        if ((rc = pcp_reserve(ctx, ctx->sort_tmp, tb))) return rc;
+        PCP_CUDA(cub::DeviceRadixSort::SortPairs(ctx->sort_tmp.p, tb, (const uint32_t*)(ctx->d_gid + n_own), hs, (const int32_t*)hv_in, hv, (int)m, 0, 32, st));
+        ctx->launches += 5;
+      }
+      rank_own_kernel<<<(int)((n_own + 255) / 256), 256, 0, st>>>(ctx->d_gid, n_own, hs, (int)m, (int32_t*)ctx->ord_of_li.p, (int32_t*)ctx->gid_sorted.p);
+      PCP_LAUNCH_CHECK("rank_own_kernel");
+      if (m > 0) {
+        rank_halo_kernel<<<(int)((m + 255) / 256), 256, 0, st>>>(ctx->d_gid, n_own, hs, hv, (int)m, (int32_t*)ctx->ord_of_li.p, (int32_t*)ctx->gid_sorted.p);
+        PCP_LAUNCH_CHECK("rank_halo_kernel");
+      }
+    } else {
+      if ((rc = pcp_reserve(ctx, ctx->li_of_ord, n * sizeof(int32_t)))) return rc;
+      iota_kernel<<<nbi, 256, 0, st>>>((int32_t*)ctx->gid_tmp.p, n);
+      PCP_LAUNCH_CHECK("iota_kernel");
+      size_t tb = 0;
+      PCP_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tb, (const uint32_t*)ctx->d_gid, (uint32_t*)ctx->gid_sorted.p,
+                                               (const int32_t*)ctx->gid_tmp.p, (int32_t*)ctx->li_of_ord.p, (int)n, 0, 32, st));
+      if ((rc = pcp_reserve(ctx, ctx->sort_tmp, tb))) return rc;
+      PCP_CUDA(cub::DeviceRadixSort::SortPairs(ctx->sort_tmp.p, tb, (const uint32_t*)ctx->d_gid, (uint32_t*)ctx->gid_sorted.p,
+                                               (const int32_t*)ctx->gid_tmp.p, (int32_t*)ctx->li_of_ord.p, (int)n, 0, 32, st));
+      ctx->launches += 5;
+      invert_kernel<<<nbi, 256, 0, st>>>((const int32_t*)ctx->li_of_ord.p, (int32_t*)ctx->ord_of_li.p, n);
+      PCP_LAUNCH_CHECK("invert_kernel");
+    }
   }
 
   // diagnostic knob: lower the grid origin by a fraction of a cell (all axes, or one); results are

@@ -79,7 +79,7 @@ constexpr int T6_REC_WORDS = 17;
 #define T6_TMA 1      // stage the candidate chunks with 1-D TMA bulk copies + mbarrier, double-buffered (0: LDG.128 -> STS.128 through registers)
 #endif
 #ifndef T6_MINB
-#define T6_MINB 5     // CTAs per SM the 32-member kernel is compiled for (register budget 65536 / (128 * T6_MINB)); measured: 5 beats 6 and 7 (spills)
+#define T6_MINB 6     // CTAs per SM the 32-member kernel is compiled for (register budget 65536 / (128 * T6_MINB) = 80, no spills; shared memory allows 6).  With TMA staging 6 beats 5 (1.26 vs 1.28 ms); with register staging 5 was best
 #endif
 
 template <int CAP>

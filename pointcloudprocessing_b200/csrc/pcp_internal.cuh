@@ -52,6 +52,7 @@ struct PcpKnobs {
   int wl_tile = 0;
   double grid_shift = 0.0; // PCP_GRID_SHIFT: lower the grid origin by this fraction of a cell (diagnostic; results unchanged)
   int grid_shift_axis = -1;// PCP_GRID_SHIFT_AXIS: 0 / 1 / 2 = x / y / z only
+  int shard_full_sort = 0; // PCP_SHARD_SORT=full: rank a shard's global ids by sorting all of them even when the own ids ascend (A/B, tests)
 };
 
 struct pcp_ctx {

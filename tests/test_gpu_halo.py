@@ -119,3 +119,45 @@ def test_halo_wait_times_out_instead_of_hanging():
             ex.check()
         ex.close()
         other.close()
+
+
+def test_shard_id_ranking_paths_agree(monkeypatch):
+    """A shard's tie order is the rank of the global ids.  Own ids that ascend (a slab cut from a cloud in index
+    order) are ranked from a sort of the halo entries alone; PCP_SHARD_SORT=full and own points in any other order take
+    the full sort of all ids.  All three must give the same records, halo padding (ids INT_MAX, non-finite points)
+    included, and the neighbour lists must name the same global ids."""
+    pts = synth.urban(35, 40000, extent=40.0)
+    k, split, h = 12, 20.0, 4.0
+    own = pts[:, 0] < split
+    halo = (~own) & (pts[:, 0] < split + h)
+    gid = np.arange(pts.shape[0], dtype=np.int32) * 3 + 7  # not contiguous
+    rs = np.random.default_rng(5)
+    hsel = rs.permutation(np.flatnonzero(halo))             # halo entries arrive in any order
+    pad = 700
+    cloud = np.concatenate([pts[own], pts[hsel], np.full((pad, 4), np.nan, np.float32)])
+    ids = np.concatenate([gid[own], gid[hsel], np.full(pad, 0x7FFFFFFF, np.int32)])
+    n_own = int(own.sum())
+
+    def run(cloud_, ids_):
+        with capi.Pcp(0) as p:
+            d_c, d_i = torch.from_numpy(cloud_).cuda(), torch.from_numpy(ids_).cuda()
+            torch.cuda.synchronize()  # torch's stream and the library's stream are not ordered
+            p.set_cloud_device(d_c.data_ptr(), cloud_.shape[0], d_i.data_ptr(), n_own)
+            p.build_grid(0.0, k)
+            idx, d2 = p.knn_neighbors(k)
+            return p.knn_pca(k), idx, d2
+
+    fast = run(cloud, ids)
+    monkeypatch.setenv("PCP_SHARD_SORT", "full")
+    full = run(cloud, ids)
+    monkeypatch.delenv("PCP_SHARD_SORT")
+    perm = rs.permutation(n_own)                            # own ids no longer ascend: the full sort is taken
+    cloud_p, ids_p = cloud.copy(), ids.copy()
+    cloud_p[:n_own], ids_p[:n_own] = cloud[:n_own][perm], ids[:n_own][perm]
+    shuf = run(cloud_p, ids_p)
+    assert fast[0].tobytes() == full[0].tobytes()
+    assert np.array_equal(fast[1], full[1]) and np.array_equal(fast[2].view(np.uint32), full[2].view(np.uint32))
+    assert fast[0][perm].tobytes() == shuf[0].tobytes()
+    assert np.array_equal(fast[1][perm], shuf[1]) and np.array_equal(fast[2][perm].view(np.uint32), shuf[2].view(np.uint32))
+    # the lists name global ids of real points (never the padding)
+    assert np.isin(fast[1], gid).all()
