@@ -320,7 +320,9 @@ def main():
     ap.add_argument("--rank-clouds", default="tile", choices=["tile", "seeded"],
                     help="N > 1: every rank's slab is a translated copy of the same 1 M-point tile (identical work per GPU), or a tile of its own seed")
     ap.add_argument("--e2e-contexts", type=int, default=3, help="C-ABI contexts in flight for the end-to-end figure (N = 1)")
-    ap.add_argument("--e2e-threads", type=int, default=1, help="1: one host thread per context (default); 0: one thread issues every context's calls")
+    ap.add_argument("--e2e-prefetch", type=int, default=0, help="1: enqueue the next step's upload before building the current step's grid (N = 1 pipelined leg; measured slower: 412 vs 583 M points/s with 3 contexts)")
+    ap.add_argument("--e2e-threads", type=int, default=0,
+                    help="0: one host thread issues every context's calls (default: measured faster, 506 vs 454 M points/s); 1: one host thread per context")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -464,10 +466,20 @@ def main():
         for c in ctxs:
             c.set_host_async(True)
 
-        def step_async(s):
+        def upload(s):
             c = ctxs[s % nctx]
             c.synchronize()  # its previous cloud (step s - nctx) is complete; buffers may be reused
-            c.set_cloud_host_ptr(h_in.data_ptr(), n, 16)
+            c.set_cloud_host_ptr(h_in.data_ptr(), n, 16)  # asynchronous mode: the bounding-box kernels follow the copy
+
+        def step_async(s, last=True):
+            # --e2e-prefetch 1 (measured and rejected, kept for A/B): step s + 1's upload is enqueued (on its own context) BEFORE step s's grid is built, so
+            # that the one host wait of a build (the bounding box) finds its cloud long uploaded instead of holding the
+            # host — and with it the launches of the other contexts — for the duration of the copy
+            c = ctxs[s % nctx]
+            if not args.e2e_prefetch:
+                upload(s)
+            elif not last:
+                upload(s + 1)
             c.build_grid(args.cell, k)
             c.knn_pca(k, capi.CENTER_QUERY, out_host_ptr=h_outs[s % nctx].data_ptr())
 
@@ -481,7 +493,9 @@ def main():
                 def worker(t):
                     go.wait()
                     for s in range(first + t, first + count, nctx):
-                        step_async(s)
+                        if args.e2e_prefetch:
+                            upload(s)
+                        step_async(s, last=True)
                     ctxs[t].synchronize()
 
                 ths = [threading.Thread(target=worker, args=(t,)) for t in range(nctx)]
@@ -493,8 +507,10 @@ def main():
                     th.join()
                 return time.perf_counter() - t_start
             t_start = time.perf_counter()
+            if args.e2e_prefetch:
+                upload(first)
             for s in range(first, first + count):
-                step_async(s)
+                step_async(s, last=(s == first + count - 1))
             for c in ctxs:
                 c.synchronize()
             return time.perf_counter() - t_start
@@ -503,6 +519,7 @@ def main():
         barrier()
         e2e_s = run_steps(2 * nctx, args.steps)
         e2e_mode = (f"{nctx} contexts in flight (pcp_set_host_async), " + ("one host thread each, " if args.e2e_threads else "one host thread, ") +
+                    ("step s + 1's upload enqueued before step s's grid build, " if args.e2e_prefetch and not args.e2e_threads else "") +
                     "each step = H2D cloud + grid + search + D2H records")
         for c in ctxs:
             c.set_host_async(False)

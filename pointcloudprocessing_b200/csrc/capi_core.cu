@@ -67,6 +67,7 @@ static void read_knobs(PcpKnobs& kn) {
   if (const char* e = getenv("PCP_WL_TILE")) kn.wl_tile = (atoi(e) >= 1 && atoi(e) <= 32) ? atoi(e) : 0;
   if (const char* e = getenv("PCP_GRID_SHIFT")) kn.grid_shift = atof(e) < 0.0 ? 0.0 : (atof(e) > 0.999 ? 0.999 : atof(e));
   if (const char* e = getenv("PCP_GRID_SHIFT_AXIS")) kn.grid_shift_axis = atoi(e);
+  if (const char* e = getenv("PCP_PRIO")) kn.flat_priority = !strcmp(e, "flat") ? 1 : (!strcmp(e, "two") ? 3 : 0);
   if (const char* e = getenv("PCP_SHARD_SORT")) kn.shard_full_sort = strcmp(e, "full") == 0 ? 1 : 0;
 }
 
@@ -86,12 +87,17 @@ PCP_API int pcp_create(pcp_ctx** out, int device) {
   pcp_ctx* ctx = new (std::nothrow) pcp_ctx();
   if (!ctx) return PCP_ERR_OOM;
   ctx->device = device;
-  if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) {
+  read_knobs(ctx->knobs);
+  int prio_least = 0, prio_greatest = 0;
+  cudaDeviceGetStreamPriorityRange(&prio_least, &prio_greatest);
+  const int prio_stream = (ctx->knobs.flat_priority == 1 || ctx->knobs.flat_priority == 3) ? prio_greatest : 0;
+  if (cudaStreamCreateWithPriority(&ctx->stream, cudaStreamNonBlocking, prio_stream) != cudaSuccess) {
     delete ctx;
     return PCP_ERR_CUDA;
   }
+  ctx->prio_search = ctx->knobs.flat_priority == 3 ? prio_least : prio_stream;
+  ctx->prio_high = prio_greatest;
   for (int i = 0; i < 2 * PCP_T_COUNT; ++i) cudaEventCreate(&ctx->ev[i]);
-  read_knobs(ctx->knobs);
   *out = ctx;
   return PCP_OK;
 }
@@ -161,6 +167,7 @@ PCP_API int pcp_set_cloud_host(pcp_ctx* ctx, const void* pts, int64_t n, int str
   if (!ctx || (!pts && n > 0) || n < 0 || stride_bytes < 12) return pcp_fail(ctx, PCP_ERR_INVALID_ARG, "pcp_set_cloud_host");
   PCP_CUDA(cudaSetDevice(ctx->device));
   ctx->grid_ok = false;
+  ctx->bbox_enqueued = false;
   ctx->n = ctx->n_query = n;
   ctx->d_gid = nullptr;
   ctx->n_frames = 1;
@@ -189,6 +196,7 @@ PCP_API int pcp_set_cloud_host(pcp_ctx* ctx, const void* pts, int64_t n, int str
   }
   pcp_toc(ctx, PCP_T_H2D);
   if (!ctx->host_async) PCP_CUDA(cudaStreamSynchronize(ctx->stream));
+  else if ((rc = pcp_bbox_enqueue(ctx))) return rc;  // the box travels with the upload: pcp_build_grid will not have to wait for it
   return PCP_OK;
 }
 
@@ -196,6 +204,7 @@ PCP_API int pcp_set_cloud_device_sharded(pcp_ctx* ctx, const void* d_xyzi, const
   if (!ctx || (!d_xyzi && n > 0) || n < 0 || n_query < 0 || n_query > n) return pcp_fail(ctx, PCP_ERR_INVALID_ARG, "pcp_set_cloud_device");
   PCP_CUDA(cudaSetDevice(ctx->device));
   ctx->grid_ok = false;
+  ctx->bbox_enqueued = false;
   ctx->d_cloud = (const float4*)d_xyzi;
   ctx->d_gid = d_global_id;
   ctx->n = n;

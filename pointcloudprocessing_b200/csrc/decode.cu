@@ -199,6 +199,7 @@ extern "C" PCP_API int pcp_decode_packets(pcp_ctx* ctx, const pcp_ring_calib* ca
   *n_frames_complete = complete;
   // the decoded points become the current cloud, its frames the segments of the next grid
   ctx->grid_ok = false;
+  ctx->bbox_enqueued = false;
   ctx->d_cloud = (const float4*)ctx->own_cloud.p;
   ctx->d_gid = nullptr;
   ctx->n = ctx->n_query = n;

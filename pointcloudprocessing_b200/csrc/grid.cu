@@ -221,6 +221,40 @@ int bits_for(uint32_t v) {
 
 }  // namespace
 
+// Bounding box of the current cloud (+ the "own ids ascend" flag of a shard) into ctx->bbox, at the device's highest
+// launch priority: the two kernels are tiny and a host thread will wait for their result.
+int pcp_bbox_enqueue(pcp_ctx* ctx) {
+  const int64_t n = ctx->n;
+  cudaStream_t st = ctx->stream;
+  int rc;
+  if (n <= 0) return PCP_OK;
+  if ((rc = pcp_reserve(ctx, ctx->bbox, 8 * sizeof(uint32_t)))) return rc;
+  pcp_tic(ctx, PCP_T_BBOX);
+  bbox_init_kernel<<<1, 32, 0, st>>>((uint32_t*)ctx->bbox.p);
+  PCP_LAUNCH_CHECK("bbox_init_kernel");
+  {
+    const int blocks = (int)std::min<int64_t>((n + 255) / 256, 148 * 4);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(blocks);
+    cfg.blockDim = dim3(256);
+    cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributePriority;
+    at[0].val.priority = ctx->prio_high;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+    PCP_CUDA(cudaLaunchKernelEx(&cfg, bbox_kernel, ctx->d_cloud, n, (uint32_t*)ctx->bbox.p));
+    PCP_LAUNCH_CHECK("bbox_kernel");
+  }
+  pcp_toc(ctx, PCP_T_BBOX);
+  if (ctx->d_gid && ctx->n_query > 0) {  // rides on the bounding box's read-back: no host wait of its own
+    gid_ascending_kernel<<<(int)((ctx->n_query + 255) / 256), 256, 0, st>>>(ctx->d_gid, ctx->n_query, (uint32_t*)ctx->bbox.p + 6);
+    PCP_LAUNCH_CHECK("gid_ascending_kernel");
+  }
+  ctx->bbox_enqueued = true;
+  return PCP_OK;
+}
+
 int pcp_grid_build_impl(pcp_ctx* ctx, float cell, int k_hint) {
   const int64_t n = ctx->n;
   const int n_seg = (int)ctx->n_frames;
@@ -230,21 +264,9 @@ int pcp_grid_build_impl(pcp_ctx* ctx, float cell, int k_hint) {
   cudaStream_t st = ctx->stream;
   int rc;
 
-  // ---- bbox
-  if ((rc = pcp_reserve(ctx, ctx->bbox, 8 * sizeof(uint32_t)))) return rc;
-  pcp_tic(ctx, PCP_T_BBOX);
-  bbox_init_kernel<<<1, 32, 0, st>>>((uint32_t*)ctx->bbox.p);
-  PCP_LAUNCH_CHECK("bbox_init_kernel");
-  {
-    int blocks = (int)std::min<int64_t>((n + 255) / 256, 148 * 4);
-    bbox_kernel<<<blocks, 256, 0, st>>>(ctx->d_cloud, n, (uint32_t*)ctx->bbox.p);
-    PCP_LAUNCH_CHECK("bbox_kernel");
-  }
-  pcp_toc(ctx, PCP_T_BBOX);
-  if (ctx->d_gid && ctx->n_query > 0) {  // rides on the bounding box's read-back: no host wait of its own
-    gid_ascending_kernel<<<(int)((ctx->n_query + 255) / 256), 256, 0, st>>>(ctx->d_gid, ctx->n_query, (uint32_t*)ctx->bbox.p + 6);
-    PCP_LAUNCH_CHECK("gid_ascending_kernel");
-  }
+  // ---- bbox (already in the stream when the upload enqueued it)
+  if (!ctx->bbox_enqueued && (rc = pcp_bbox_enqueue(ctx))) return rc;
+  ctx->bbox_enqueued = false;  // consumed: a second build of the same cloud (automatic cell) reads the same values, a new cloud resets it
   uint32_t hb[8];
   PCP_CUDA(cudaMemcpyAsync(hb, ctx->bbox.p, sizeof(hb), cudaMemcpyDeviceToHost, st));
   PCP_CUDA(cudaStreamSynchronize(st));

@@ -389,15 +389,15 @@ int pcp_knn_tile_launch(pcp_ctx* ctx, const SearchParams& sp, const KArgs& a, in
   if (sp.mode == 1 && radius_cap == 64) {
     const size_t smem = sizeof(TaSmem<64>) * TA_WARPS;
     PCP_CUDA(cudaFuncSetAttribute(knn_tile_kernel<64, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    knn_tile_kernel<64, 1><<<blocks, TA_WARPS * 32, smem, ctx->stream>>>(a, sp.R0, 0.f, max_groups, wc, wl);
+    PCP_CUDA(pcp_launch_search(ctx, knn_tile_kernel<64, 1>, dim3(blocks), dim3(TA_WARPS * 32), smem, a, sp.R0, 0.f, max_groups, wc, wl));
   } else if (sp.mode == 1) {
     const size_t smem = sizeof(TaSmem<32>) * TA_WARPS;
     PCP_CUDA(cudaFuncSetAttribute(knn_tile_kernel<32, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    knn_tile_kernel<32, 1><<<blocks, TA_WARPS * 32, smem, ctx->stream>>>(a, sp.R0, 0.f, max_groups, wc, wl);
+    PCP_CUDA(pcp_launch_search(ctx, knn_tile_kernel<32, 1>, dim3(blocks), dim3(TA_WARPS * 32), smem, a, sp.R0, 0.f, max_groups, wc, wl));
   } else {
     const size_t smem = sizeof(TaSmem<32>) * TA_WARPS;
     PCP_CUDA(cudaFuncSetAttribute(knn_tile_kernel<32, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    knn_tile_kernel<32, 0><<<blocks, TA_WARPS * 32, smem, ctx->stream>>>(a, sp.R0, grow, max_groups, wc, wl);
+    PCP_CUDA(pcp_launch_search(ctx, knn_tile_kernel<32, 0>, dim3(blocks), dim3(TA_WARPS * 32), smem, a, sp.R0, grow, max_groups, wc, wl));
   }
   PCP_LAUNCH_CHECK("knn_tile_kernel");
   return PCP_OK;

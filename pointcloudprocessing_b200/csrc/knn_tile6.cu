@@ -652,7 +652,7 @@ int pcp_knn_tile6_launch(pcp_ctx* ctx, const SearchParams& sp, const KArgs& a) {
   do {                                                                                                                         \
     const size_t smem = sizeof(T6Smem<CAPV>) * T6_WARPS;                                                                       \
     PCP_CUDA(cudaFuncSetAttribute(knn_tile6_kernel<CAPV, LEANV>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));    \
-    knn_tile6_kernel<CAPV, LEANV><<<blocks, T6_WARPS * 32, smem, ctx->stream>>>(a, sp.R0, max_groups, wc, wl);                 \
+    PCP_CUDA(pcp_launch_search(ctx, knn_tile6_kernel<CAPV, LEANV>, dim3(blocks), dim3(T6_WARPS * 32), smem, a, sp.R0, max_groups, wc, wl)); \
   } while (0)
   if (sp.k <= PCP_T6_K32) {
     if (lean) T6_LAUNCH(32, true); else T6_LAUNCH(32, false);

@@ -52,6 +52,7 @@ struct PcpKnobs {
   int wl_tile = 0;
   double grid_shift = 0.0; // PCP_GRID_SHIFT: lower the grid origin by this fraction of a cell (diagnostic; results unchanged)
   int grid_shift_axis = -1;// PCP_GRID_SHIFT_AXIS: 0 / 1 / 2 = x / y / z only
+  int flat_priority = 0;   // PCP_PRIO=flat: the search kernels run at the stream's priority (A/B of the two-level scheme below)
   int shard_full_sort = 0; // PCP_SHARD_SORT=full: rank a shard's global ids by sorting all of them even when the own ids ascend (A/B, tests)
 };
 
@@ -59,6 +60,13 @@ struct pcp_ctx {
   int device = 0;
   cudaStream_t stream = nullptr;
   std::string err;
+  // Launch priority of the long search kernels (a per-launch attribute; = the stream's own priority by default).
+  // Measured with three contexts in flight (PCP_PRIO=two: stream at the device's highest priority, search kernels at
+  // the lowest, so that one context's short grid kernels overtake another's search): 434 M points/s end to end against
+  // 587 M with everything at one priority — contexts that share the SMs evenly finish together and their result copies
+  // no longer overlap the next context's compute.  Kept as a knob; only the tiny bounding-box kernels run at high priority.
+  int prio_search = 0;
+  int prio_high = 0;
   bool host_async = false;  // pcp_set_host_async: host-pointer calls only enqueue
   int64_t launches = 0;
   PcpKnobs knobs;
@@ -79,7 +87,10 @@ struct pcp_ctx {
   // grid
   bool grid_ok = false;
   GridDesc grid;
-  DevBuf bbox;        // 6 ordered-uint encodings
+  DevBuf bbox;        // 6 ordered-uint encodings (+ the shard id flag)
+  bool bbox_enqueued = false;  // the bounding-box kernels of the CURRENT cloud are already in the stream (pcp_set_cloud_host in
+                               // pcp_set_host_async mode enqueues them behind the upload, so that a caller who uploads the next
+                               // cloud early finds the box ready when it builds that cloud's grid); reset by every pcp_set_cloud_*
   DevBuf occ_hist;    // automatic cell: point-weighted histogram of the cell occupancy
   unsigned long long* h_occ = nullptr;  // its page-locked host copy
   cudaEvent_t occ_ev = nullptr;         // recorded behind an asynchronous copy into h_occ
@@ -131,8 +142,25 @@ void pcp_collect_timings(pcp_ctx* ctx);
     if (e__ != cudaSuccess) return pcp_fail(ctx, PCP_ERR_CUDA, name, e__); \
   } while (0)
 
+// launch of a long-running search kernel on the context's stream at the low priority (see pcp_ctx::prio_search)
+template <typename... Params, typename... Args>
+inline cudaError_t pcp_launch_search(pcp_ctx* ctx, void (*kernel)(Params...), dim3 grid, dim3 block, size_t smem, Args... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = ctx->stream;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributePriority;
+  at[0].val.priority = ctx->prio_search;
+  cfg.attrs = at;
+  cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<Params>(args)...);
+}
+
 // implemented in grid.cu / search_pca.cu / ring.cu
 int pcp_grid_build_impl(pcp_ctx* ctx, float cell, int k_hint);
+int pcp_bbox_enqueue(pcp_ctx* ctx);  // grid.cu: bounding-box reduction of the current cloud into ctx->bbox (no host wait)
 
 struct SearchParams {
   int mode;           // 0 = k-NN, 1 = radius

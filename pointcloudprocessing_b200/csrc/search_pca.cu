@@ -35,7 +35,13 @@ __device__ unsigned long long g_stats[8];
 
 namespace {
 
-constexpr int WARPS = 8;            // warps per CTA
+#ifndef SP_WARPS
+#define SP_WARPS 8
+#endif
+#ifndef SP_MINB
+#define SP_MINB 3     // CTAs per SM the kernels are compiled for
+#endif
+constexpr int WARPS = SP_WARPS;     // warps per CTA
 constexpr int RADIUS_CAP = 512;     // radius mode: neighbours kept per query in shared memory
 constexpr int REC_WORDS = 17;       // 68-byte record
 constexpr int KNN_LW = 16;          // k-NN: queries per tile of the warp-per-query kernel (columns of the list planes)
@@ -613,7 +619,7 @@ __device__ __forceinline__ void search_tile(const KArgs& a, WarpSmem<MODE>* ws, 
 
 // every point of the cloud: tile t = sorted positions [32 t, 32 t + 32)
 template <int MODE>
-__global__ void __launch_bounds__(WARPS * 32, 3) search_pca_kernel(KArgs a) {
+__global__ void __launch_bounds__(WARPS * 32, SP_MINB) search_pca_kernel(KArgs a) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   WarpSmem<MODE>* ws = reinterpret_cast<WarpSmem<MODE>*>(smem_raw) + (threadIdx.x >> 5);
   const int lane = threadIdx.x & 31;
@@ -634,7 +640,7 @@ __global__ void __launch_bounds__(WARPS * 32, 3) search_pca_kernel(KArgs a) {
 // `tile` list entries from a ticket counter (work_count[1]) until the list is empty — the count is only known on
 // the device, and drawing tickets keeps every resident warp busy to the end whatever the list length.
 template <int MODE>
-__global__ void __launch_bounds__(WARPS * 32, 3) search_pca_worklist_kernel(KArgs a, uint32_t* work_count, const uint32_t* __restrict__ work_list,
+__global__ void __launch_bounds__(WARPS * 32, SP_MINB) search_pca_worklist_kernel(KArgs a, uint32_t* work_count, const uint32_t* __restrict__ work_list,
                                                                          int tile) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   WarpSmem<MODE>* ws = reinterpret_cast<WarpSmem<MODE>*>(smem_raw) + (threadIdx.x >> 5);
@@ -719,7 +725,7 @@ int pcp_search_launch(pcp_ctx* ctx, const SearchParams& sp) {
     if (rc) return rc;
     // one wave of resident CTAs (3 per SM at 80 registers); tiles of 16 list entries drawn by ticket
     // (tuning hooks: PCP_WL_BLOCKS, PCP_WL_TILE)
-    int wl_blocks = blocks < 148 * 3 ? blocks : 148 * 3;
+    int wl_blocks = blocks < 148 * SP_MINB ? blocks : 148 * SP_MINB;
     int wl_tile = 16;
     if (kn.wl_blocks > 0) wl_blocks = kn.wl_blocks;
     if (kn.wl_tile > 0) wl_tile = kn.wl_tile;
@@ -727,22 +733,22 @@ int pcp_search_launch(pcp_ctx* ctx, const SearchParams& sp) {
     if (sp.mode == 0) {
       size_t smem = sizeof(WarpSmem<0>) * WARPS;
       PCP_CUDA(cudaFuncSetAttribute(search_pca_worklist_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-      search_pca_worklist_kernel<0><<<wl_blocks, WARPS * 32, smem, ctx->stream>>>(a, (uint32_t*)ctx->work_count.p,
-                                                                                  (const uint32_t*)ctx->work_list.p, wl_tile);
+      PCP_CUDA(pcp_launch_search(ctx, search_pca_worklist_kernel<0>, dim3(wl_blocks), dim3(WARPS * 32), smem, a, (uint32_t*)ctx->work_count.p,
+                                 (const uint32_t*)ctx->work_list.p, wl_tile));
     } else {
       size_t smem = sizeof(WarpSmem<1>) * WARPS;
       PCP_CUDA(cudaFuncSetAttribute(search_pca_worklist_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-      search_pca_worklist_kernel<1><<<wl_blocks, WARPS * 32, smem, ctx->stream>>>(a, (uint32_t*)ctx->work_count.p,
-                                                                                  (const uint32_t*)ctx->work_list.p, wl_tile);
+      PCP_CUDA(pcp_launch_search(ctx, search_pca_worklist_kernel<1>, dim3(wl_blocks), dim3(WARPS * 32), smem, a, (uint32_t*)ctx->work_count.p,
+                                 (const uint32_t*)ctx->work_list.p, wl_tile));
     }
   } else if (sp.mode == 0) {
     size_t smem = sizeof(WarpSmem<0>) * WARPS;
     PCP_CUDA(cudaFuncSetAttribute(search_pca_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    search_pca_kernel<0><<<blocks, WARPS * 32, smem, ctx->stream>>>(a);
+    PCP_CUDA(pcp_launch_search(ctx, search_pca_kernel<0>, dim3(blocks), dim3(WARPS * 32), smem, a));
   } else {
     size_t smem = sizeof(WarpSmem<1>) * WARPS;
     PCP_CUDA(cudaFuncSetAttribute(search_pca_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    search_pca_kernel<1><<<blocks, WARPS * 32, smem, ctx->stream>>>(a);
+    PCP_CUDA(pcp_launch_search(ctx, search_pca_kernel<1>, dim3(blocks), dim3(WARPS * 32), smem, a));
   }
   PCP_LAUNCH_CHECK("search_pca_kernel");
   pcp_toc(ctx, PCP_T_SEARCH_PCA);
