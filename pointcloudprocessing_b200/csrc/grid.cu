@@ -79,16 +79,24 @@ __global__ void bbox_init_kernel(uint32_t* bbox) {
   else if (threadIdx.x < 8) bbox[threadIdx.x] = 0u;  // [6]: "the shard's own global ids are not strictly ascending"
 }
 
-// Shards: are the own points' global ids strictly ascending (a slab cut out of a cloud in index order)?  Then only the
-// halo entries need sorting to rank every id (below).  Sets *flag otherwise.
-__global__ void __launch_bounds__(256) gid_ascending_kernel(const int32_t* __restrict__ gid, int64_t n_own, uint32_t* __restrict__ flag) {
+// Shards, one pass over all n ids (own, halo, padding = INT_MAX): flag[0] |= 1 unless the own ids are strictly
+// ascending (a slab cut out of a cloud in index order: then only the halo entries need sorting to rank every id);
+// flag[0] |= 2 for a negative id; flag[1] = the largest real id (small ids serve as `ord` directly, no ranking at all).
+__global__ void __launch_bounds__(256) gid_scan_kernel(const int32_t* __restrict__ gid, int64_t n, int64_t n_own, uint32_t* __restrict__ flag) {
   const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
-  bool bad = false;
-  if (i < n_own) {
+  uint32_t bad = 0, top = 0;
+  if (i < n) {
     const int32_t g = __ldg(gid + i);
-    bad = g < 0 || g == 0x7fffffff || (i + 1 < n_own && __ldg(gid + i + 1) <= g);
+    if (g < 0) bad |= 2u;
+    if (i < n_own && (g == 0x7fffffff || (i + 1 < n_own && __ldg(gid + i + 1) <= g))) bad |= 1u;
+    if (g >= 0 && g != 0x7fffffff) top = (uint32_t)g;
   }
-  if (__any_sync(0xffffffffu, bad) && (threadIdx.x & 31) == 0) atomicOr(flag, 1u);
+  bad = __reduce_or_sync(0xffffffffu, bad);
+  top = __reduce_max_sync(0xffffffffu, top);
+  if ((threadIdx.x & 31) == 0) {
+    if (bad) atomicOr(flag, bad);
+    if (top) atomicMax(flag + 1, top);
+  }
 }
 
 // Cell coordinates in double: (p − origin) is exact for fp32 inputs, so a neighbour within
@@ -136,7 +144,7 @@ __global__ void __launch_bounds__(256) keys_kernel(const float4* __restrict__ pt
 __global__ void __launch_bounds__(256)
     gather_kernel(const float4* __restrict__ pts, const int32_t* __restrict__ ord_of_li, const uint32_t* __restrict__ keys_sorted,
                   const int32_t* __restrict__ vals_sorted, int64_t n, int64_t n_query, float4* __restrict__ sorted,
-                  int32_t* __restrict__ slot, uint32_t* __restrict__ inv, uint32_t* __restrict__ cell_end) {
+                  int32_t* __restrict__ slot, uint32_t* __restrict__ inv, uint32_t inv_size, uint32_t* __restrict__ cell_end) {
   int64_t pos = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (pos >= n) return;
   int32_t li = vals_sorted[pos];
@@ -144,7 +152,7 @@ __global__ void __launch_bounds__(256)
   int32_t ord = ord_of_li ? __ldg(ord_of_li + li) : li;
   p.w = __int_as_float(ord);
   sorted[pos] = p;
-  inv[ord] = (uint32_t)pos;
+  if ((uint32_t)ord < inv_size) inv[ord] = (uint32_t)pos;  // (a shard's padding entries carry id INT_MAX when the ids serve as ord)
   slot[pos] = li < n_query ? li : -1;
   uint32_t k = keys_sorted[pos];
   if (pos == n - 1 || keys_sorted[pos + 1] != k) cell_end[k + 1] = (uint32_t)(pos + 1);
@@ -247,9 +255,9 @@ int pcp_bbox_enqueue(pcp_ctx* ctx) {
     PCP_LAUNCH_CHECK("bbox_kernel");
   }
   pcp_toc(ctx, PCP_T_BBOX);
-  if (ctx->d_gid && ctx->n_query > 0) {  // rides on the bounding box's read-back: no host wait of its own
-    gid_ascending_kernel<<<(int)((ctx->n_query + 255) / 256), 256, 0, st>>>(ctx->d_gid, ctx->n_query, (uint32_t*)ctx->bbox.p + 6);
-    PCP_LAUNCH_CHECK("gid_ascending_kernel");
+  if (ctx->d_gid) {  // rides on the bounding box's read-back: no host wait of its own
+    gid_scan_kernel<<<(int)((n + 255) / 256), 256, 0, st>>>(ctx->d_gid, n, ctx->n_query, (uint32_t*)ctx->bbox.p + 6);
+    PCP_LAUNCH_CHECK("gid_scan_kernel");
   }
   ctx->bbox_enqueued = true;
   return PCP_OK;
@@ -334,15 +342,22 @@ int pcp_grid_build_impl(pcp_ctx* ctx, float cell, int k_hint) {
       PCP_CUDA(cudaEventCreateWithFlags(&ctx->occ_ev, cudaEventDisableTiming));
     }
   }
-  // ---- sharded clouds: ord = rank of the global id (ties are broken by global index)
-  if (ctx->d_gid) {
+  // ---- sharded clouds: ord = rank of the global id (ties are broken by global index) — or the id itself when the ids
+  // are small enough for a dense ord -> position table that stays in L2 (64 MB): nothing to rank, nothing to sort
+  ctx->gid_direct = false;
+  ctx->inv_size = (size_t)n;
+  if (ctx->d_gid && (hb[6] & 2u)) return pcp_fail(ctx, PCP_ERR_INVALID_ARG, "pcp_build_grid: negative global id");
+  if (ctx->d_gid && ctx->knobs.shard_full_sort == 0 && ((size_t)hb[7] + 1) * sizeof(uint32_t) <= ((size_t)64 << 20)) {
+    ctx->gid_direct = true;
+    ctx->inv_size = (size_t)hb[7] + 1;
+  } else if (ctx->d_gid) {
     if ((rc = pcp_reserve(ctx, ctx->gid_sorted, n * sizeof(int32_t)))) return rc;
     if ((rc = pcp_reserve(ctx, ctx->gid_tmp, n * sizeof(int32_t)))) return rc;
     if ((rc = pcp_reserve(ctx, ctx->ord_of_li, n * sizeof(int32_t)))) return rc;
     const int nbi = (int)((n + 255) / 256);
     const int64_t n_own = ctx->n_query;
     const int64_t m = n - n_own;  // halo entries (padding included: ids 0x7fffffff, ranked last in arrival order)
-    if (n_own > 0 && hb[6] == 0u && !ctx->knobs.shard_full_sort) {
+    if (n_own > 0 && (hb[6] & 1u) == 0u && ctx->knobs.shard_full_sort != 1) {
       // the own ids ascend (a slab cut from a cloud in index order): sort the halo entries only and rank by two
       // binary searches — the full-width sort of all n ids was the largest fixed cost of a sharded build
       int32_t* hv_in = (int32_t*)ctx->gid_tmp.p;    // 0 .. m-1
@@ -415,7 +430,7 @@ int pcp_grid_build_impl(pcp_ctx* ctx, float cell, int k_hint) {
   if ((rc = pcp_reserve(ctx, ctx->vals_sorted, n * sizeof(int32_t)))) return rc;
   if ((rc = pcp_reserve(ctx, ctx->sorted_pts, n * sizeof(float4)))) return rc;
   if ((rc = pcp_reserve(ctx, ctx->sorted_slot, n * sizeof(int32_t)))) return rc;
-  if ((rc = pcp_reserve(ctx, ctx->inv_pos, n * sizeof(uint32_t)))) return rc;
+  if ((rc = pcp_reserve(ctx, ctx->inv_pos, ctx->inv_size * sizeof(uint32_t)))) return rc;
   const size_t table_entries = (size_t)g.n_cells + 2;
   if ((rc = pcp_reserve(ctx, ctx->cell_end, table_entries * sizeof(uint32_t)))) return rc;
   const int nb = (int)((n + 255) / 256);
@@ -440,10 +455,10 @@ int pcp_grid_build_impl(pcp_ctx* ctx, float cell, int k_hint) {
   // ---- gather + cell table
   pcp_tic(ctx, PCP_T_TABLE);
   PCP_CUDA(cudaMemsetAsync(ctx->cell_end.p, 0, table_entries * sizeof(uint32_t), st));
-  gather_kernel<<<nb, 256, 0, st>>>(ctx->d_cloud, ctx->d_gid ? (const int32_t*)ctx->ord_of_li.p : nullptr,
+  gather_kernel<<<nb, 256, 0, st>>>(ctx->d_cloud, ctx->d_gid ? (ctx->gid_direct ? ctx->d_gid : (const int32_t*)ctx->ord_of_li.p) : nullptr,
                                     (const uint32_t*)ctx->keys_sorted.p, (const int32_t*)ctx->vals_sorted.p, n, ctx->n_query,
                                     (float4*)ctx->sorted_pts.p, (int32_t*)ctx->sorted_slot.p, (uint32_t*)ctx->inv_pos.p,
-                                    (uint32_t*)ctx->cell_end.p);
+                                    (uint32_t)std::min<size_t>(ctx->inv_size, 0xFFFFFFFFu), (uint32_t*)ctx->cell_end.p);
   PCP_LAUNCH_CHECK("gather_kernel");
   size_t scan_bytes = 0;
   uint32_t* E = (uint32_t*)ctx->cell_end.p;

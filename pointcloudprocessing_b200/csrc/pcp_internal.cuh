@@ -53,7 +53,8 @@ struct PcpKnobs {
   double grid_shift = 0.0; // PCP_GRID_SHIFT: lower the grid origin by this fraction of a cell (diagnostic; results unchanged)
   int grid_shift_axis = -1;// PCP_GRID_SHIFT_AXIS: 0 / 1 / 2 = x / y / z only
   int flat_priority = 0;   // PCP_PRIO=flat: the search kernels run at the stream's priority (A/B of the two-level scheme below)
-  int shard_full_sort = 0; // PCP_SHARD_SORT=full: rank a shard's global ids by sorting all of them even when the own ids ascend (A/B, tests)
+  int shard_full_sort = 0; // PCP_SHARD_SORT (A/B, tests): "rank" = rank a shard's global ids even when they are small enough to serve as ord (2),
+                           // "full" = rank them by sorting all of them even when the own ids ascend (1)
 };
 
 struct pcp_ctx {
@@ -101,7 +102,9 @@ struct pcp_ctx {
   int scale_seg = 0, scale_k = 0;
   DevBuf keys_in, keys_sorted, vals_in, vals_sorted, sort_tmp;
   DevBuf sorted_pts;  // float4 {x,y,z, ord bits} in cell order (ord = rank in index order)
-  DevBuf inv_pos;     // uint32 ord -> sorted position
+  DevBuf inv_pos;     // uint32 ord -> sorted position (inv_size entries: n, or the largest id + 1 of a shard whose ids serve as ord)
+  size_t inv_size = 0;
+  bool gid_direct = false;  // shard: ord IS the global id (no ranking; ord -> id is the identity)
   DevBuf gid_sorted, gid_tmp, ord_of_li, li_of_ord;  // sharded clouds: ord <-> local index <-> global id
   DevBuf sorted_slot; // int32 output slot (−1 for halo points) per sorted position
   DevBuf cell_end;    // uint32 E[c] = #points with cell id < c, n_cells + 2 entries

@@ -680,7 +680,7 @@ void pcp_make_kargs(pcp_ctx* ctx, const SearchParams& sp, KArgs& a) {
   a.slot = (const int32_t*)ctx->sorted_slot.p;
   a.E = (const uint32_t*)ctx->cell_end.p;
   a.inv = (const uint32_t*)ctx->inv_pos.p;
-  a.gid_of_ord = ctx->d_gid ? (const int32_t*)ctx->gid_sorted.p : nullptr;
+  a.gid_of_ord = (ctx->d_gid && !ctx->gid_direct) ? (const int32_t*)ctx->gid_sorted.p : nullptr;
   a.g = ctx->grid;
   a.n = ctx->n;
   a.sp = sp;

@@ -122,10 +122,10 @@ def test_halo_wait_times_out_instead_of_hanging():
 
 
 def test_shard_id_ranking_paths_agree(monkeypatch):
-    """A shard's tie order is the rank of the global ids.  Own ids that ascend (a slab cut from a cloud in index
-    order) are ranked from a sort of the halo entries alone; PCP_SHARD_SORT=full and own points in any other order take
-    the full sort of all ids.  All three must give the same records, halo padding (ids INT_MAX, non-finite points)
-    included, and the neighbour lists must name the same global ids."""
+    """A shard's tie order is the order of the global ids.  Small ids serve as the order key directly (no ranking);
+    PCP_SHARD_SORT=rank ranks them: from a sort of the halo entries alone when the own ids ascend (a slab cut from a
+    cloud in index order), by the full sort of all ids otherwise or with PCP_SHARD_SORT=full.  Every path must give the
+    same records, halo padding (ids INT_MAX, non-finite points) included, and neighbour lists naming the same ids."""
     pts = synth.urban(35, 40000, extent=40.0)
     k, split, h = 12, 20.0, 4.0
     own = pts[:, 0] < split
@@ -138,26 +138,42 @@ def test_shard_id_ranking_paths_agree(monkeypatch):
     ids = np.concatenate([gid[own], gid[hsel], np.full(pad, 0x7FFFFFFF, np.int32)])
     n_own = int(own.sum())
 
-    def run(cloud_, ids_):
-        with capi.Pcp(0) as p:
+    def run(cloud_, ids_, mode):
+        if mode:
+            monkeypatch.setenv("PCP_SHARD_SORT", mode)
+        else:
+            monkeypatch.delenv("PCP_SHARD_SORT", raising=False)
+        with capi.Pcp(0) as p:  # the knob is read when the context is created
             d_c, d_i = torch.from_numpy(cloud_).cuda(), torch.from_numpy(ids_).cuda()
             torch.cuda.synchronize()  # torch's stream and the library's stream are not ordered
             p.set_cloud_device(d_c.data_ptr(), cloud_.shape[0], d_i.data_ptr(), n_own)
             p.build_grid(0.0, k)
             idx, d2 = p.knn_neighbors(k)
-            return p.knn_pca(k), idx, d2
+            rec = p.knn_pca(k)
+            p.build_grid(0.45, 0)
+            return rec, idx, d2, p.radius_pca(0.45, 13, capi.CENTER_QUERY, False)
 
-    fast = run(cloud, ids)
-    monkeypatch.setenv("PCP_SHARD_SORT", "full")
-    full = run(cloud, ids)
-    monkeypatch.delenv("PCP_SHARD_SORT")
-    perm = rs.permutation(n_own)                            # own ids no longer ascend: the full sort is taken
+    def same(a, b, perm=None):
+        a = a if perm is None else tuple(x[perm] for x in a)
+        assert a[0].tobytes() == b[0].tobytes() and a[3].tobytes() == b[3].tobytes()
+        assert np.array_equal(a[1], b[1]) and np.array_equal(a[2].view(np.uint32), b[2].view(np.uint32))
+
+    direct = run(cloud, ids, None)
+    same(direct, run(cloud, ids, "rank"))                   # own ids ascend: halo-only sort
+    same(direct, run(cloud, ids, "full"))
+    perm = rs.permutation(n_own)                            # own ids no longer ascend
     cloud_p, ids_p = cloud.copy(), ids.copy()
     cloud_p[:n_own], ids_p[:n_own] = cloud[:n_own][perm], ids[:n_own][perm]
-    shuf = run(cloud_p, ids_p)
-    assert fast[0].tobytes() == full[0].tobytes()
-    assert np.array_equal(fast[1], full[1]) and np.array_equal(fast[2].view(np.uint32), full[2].view(np.uint32))
-    assert fast[0][perm].tobytes() == shuf[0].tobytes()
-    assert np.array_equal(fast[1][perm], shuf[1]) and np.array_equal(fast[2][perm].view(np.uint32), shuf[2].view(np.uint32))
+    same(direct, run(cloud_p, ids_p, None), perm)
+    same(direct, run(cloud_p, ids_p, "rank"), perm)         # falls back to the full sort
+    # ids too large for the dense table are ranked (fast path here): same geometry, so the same records up to the id fields
+    big = ids.copy()
+    big[big != 0x7FFFFFFF] += 1_500_000_000
+    far = run(cloud, big, None)
+    assert np.array_equal(far[1], direct[1] + 1_500_000_000) and np.array_equal(far[2].view(np.uint32), direct[2].view(np.uint32))
+    for name in capi.FEATURE_DTYPE.names:
+        if name != "ptID":
+            assert far[0][name].tobytes() == direct[0][name].tobytes(), name
+    assert np.array_equal(far[0]["ptID"], direct[0]["ptID"] + 1_500_000_000)
     # the lists name global ids of real points (never the padding)
-    assert np.isin(fast[1], gid).all()
+    assert np.isin(direct[1], gid).all()
