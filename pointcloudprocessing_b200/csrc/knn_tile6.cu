@@ -39,6 +39,8 @@
 // A candidate with |p'| > |q'| + 2 c (c = the lane's cover radius) is farther than 2 c from the query and cannot
 // matter (the k-th distance is checked to be < c); for the others |p'| + |q'| <= 2 |q'| + 2 c.  The kernel uses
 // eps_Y = 1.01 u (12 S (2 |q'| + 2 c)^2 + 12 |off| + 4), which also covers the float evaluation of t_safe itself.
+#include <cub/block/block_radix_sort.cuh>
+
 #include <cfloat>
 #include <cmath>
 #include <cstdlib>
@@ -77,6 +79,9 @@ constexpr int T6_REC_WORDS = 17;
 #endif
 #ifndef T6_TMA
 #define T6_TMA 1      // stage the candidate chunks with 1-D TMA bulk copies + mbarrier, double-buffered (0: LDG.128 -> STS.128 through registers)
+#endif
+#ifndef T6_ORDER
+#define T6_ORDER 1    // warps of a CTA take tiles of similar candidate counts (tile_order_kernel): they reach the CTA barriers together
 #endif
 #ifndef T6_MINB
 #define T6_MINB 6     // CTAs per SM the 32-member kernel is compiled for (register budget 65536 / (128 * T6_MINB) = 80, no spills; shared memory allows 6).  With TMA staging 6 beats 5 (1.26 vs 1.28 ms); with register staging 5 was best
@@ -277,16 +282,68 @@ __device__ __forceinline__ void stage6(const float4* __restrict__ sorted, T6Smem
 }
 #endif
 
+// The four warps of a CTA meet at two barriers (below), so a CTA is as slow as its slowest tile: 17 % of the kernel's
+// warp time was spent waiting there (ncu, profiles/r02_search_ncu_48f2d008099b.txt) because tiles next to each other in
+// cell order differ by +-30 % in candidates.  This kernel estimates every tile's candidate count (first and last
+// query's cells, two table reads per stencil row) and sorts each window of 256 consecutive tiles by it: warp w of CTA b
+// then serves tile perm[4 b + w], four tiles of nearly equal work, still from one neighbourhood of the cloud.
+#ifndef T6_WIN_ITEMS
+#define T6_WIN_ITEMS 1
+#endif
+constexpr int T6_WIN_THREADS = 256;
+constexpr int T6_WIN = T6_WIN_THREADS * T6_WIN_ITEMS;  // tiles per window
+__global__ void __launch_bounds__(T6_WIN_THREADS) tile_order_kernel(KArgs a, int R, int64_t n_tiles, uint32_t* __restrict__ perm) {
+  using Sort = cub::BlockRadixSort<uint32_t, T6_WIN_THREADS, T6_WIN_ITEMS, uint32_t>;
+  __shared__ typename Sort::TempStorage tmp;
+  const GridDesc& g = a.g;
+  uint32_t w[T6_WIN_ITEMS], id[T6_WIN_ITEMS];
+#pragma unroll
+  for (int it = 0; it < T6_WIN_ITEMS; ++it) {
+    const int64_t t = (int64_t)blockIdx.x * T6_WIN + threadIdx.x * T6_WIN_ITEMS + it;
+    w[it] = 0xFFFFFFFFu;
+    id[it] = (uint32_t)t;
+    if (t < n_tiles) {
+      const int64_t p0 = t * 32, p1 = min(p0 + 31, a.n - 1);
+      const uint32_t cid0 = __ldg(&a.keys[p0]), cid1 = __ldg(&a.keys[p1]);
+      w[it] = 0u;
+      if (cid0 < g.n_cells) {
+        const uint32_t row0 = cid0 / (uint32_t)g.dim[0];
+        const int c0a = (int)(cid0 - row0 * (uint32_t)g.dim[0]);
+        const int c0b = (cid1 < g.n_cells && cid1 / (uint32_t)g.dim[0] == row0) ? (int)(cid1 - row0 * (uint32_t)g.dim[0]) : g.dim[0] - 1;
+        const int c1 = (int)(row0 % (uint32_t)g.dim[1]);
+        int c2 = (int)(row0 / (uint32_t)g.dim[1]);
+        const int zoff = pcp_unfold_z(g, c2);
+        const int xlo = max(c0a - R, 0), xhi = min(c0b + R, g.dim[0] - 1);
+        uint32_t total = 0;
+        for (int e2 = max(c2 - R, 0); e2 <= min(c2 + R, g.dim[2] - 1); ++e2)
+          for (int e1 = max(c1 - R, 0); e1 <= min(c1 + R, g.dim[1] - 1); ++e1) {
+            const uint32_t base = ((uint32_t)(zoff + e2) * (uint32_t)g.dim[1] + (uint32_t)e1) * (uint32_t)g.dim[0];
+            total += __ldg(&a.E[base + xhi + 1]) - __ldg(&a.E[base + xlo]);
+          }
+        w[it] = total;
+      }
+    }
+  }
+  Sort(tmp).Sort(w, id);  // tiles past the end sort last: the first (n_tiles - window start) ranks are real tiles
+#pragma unroll
+  for (int it = 0; it < T6_WIN_ITEMS; ++it) {
+    const int64_t t = (int64_t)blockIdx.x * T6_WIN + threadIdx.x * T6_WIN_ITEMS + it;
+    if (t < n_tiles) perm[t] = id[it];
+  }
+}
+
 // LEAN: records only (query-centred; the k-th distance may be asked for): see knn_finish.cuh
 template <int CAP, bool LEAN>
 __global__ void __launch_bounds__(T6_WARPS * 32, CAP == 32 ? (T6_MINB * 4) / T6_WARPS : 16 / T6_WARPS)
-    knn_tile6_kernel(KArgs a, int R0, int max_groups, uint32_t* __restrict__ work_count, uint32_t* __restrict__ work_list) {
+    knn_tile6_kernel(KArgs a, int R0, int max_groups, uint32_t* __restrict__ work_count, uint32_t* __restrict__ work_list,
+                     const uint32_t* __restrict__ perm, int64_t n_tiles) {
   constexpr int NB = CAP - 1;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   T6Smem<CAP>& sm = reinterpret_cast<T6Smem<CAP>*>(smem_raw)[threadIdx.x >> 5];
   const int lane = threadIdx.x & 31;
-  const int64_t pos0 = ((int64_t)blockIdx.x * T6_WARPS + (threadIdx.x >> 5)) * 32;
-  const bool live_warp = pos0 < a.n;  // a tail warp stays (inactive) for the CTA barriers below
+  const int64_t wid = (int64_t)blockIdx.x * T6_WARPS + (threadIdx.x >> 5);
+  const bool live_warp = wid < n_tiles;  // a tail warp stays (inactive) for the CTA barriers below
+  const int64_t pos0 = (live_warp ? (perm ? (int64_t)__ldg(&perm[wid]) : wid) : n_tiles) * 32;
   const int64_t p = pos0 + lane;
   const GridDesc& g = a.g;
   const SearchParams& sp = a.sp;
@@ -647,12 +704,21 @@ int pcp_knn_tile6_launch(pcp_ctx* ctx, const SearchParams& sp, const KArgs& a) {
   if (ctx->knobs.knn_groups > 0) max_groups = ctx->knobs.knn_groups;
   uint32_t* wc = (uint32_t*)ctx->work_count.p;
   uint32_t* wl = (uint32_t*)ctx->work_list.p;
+  const uint32_t* perm = nullptr;
+#if T6_ORDER
+  if (tiles > 2 * T6_WARPS && !ctx->knobs.t6_no_order) {
+    if ((rc = pcp_reserve(ctx, ctx->tile_perm, (size_t)tiles * sizeof(uint32_t)))) return rc;
+    tile_order_kernel<<<(unsigned)((tiles + T6_WIN - 1) / T6_WIN), T6_WIN_THREADS, 0, ctx->stream>>>(a, sp.R0, tiles, (uint32_t*)ctx->tile_perm.p);
+    PCP_LAUNCH_CHECK("tile_order_kernel");
+    perm = (const uint32_t*)ctx->tile_perm.p;
+  }
+#endif
   const bool lean = sp.out != nullptr && sp.center_mode == PCP_CENTER_QUERY && sp.normals == nullptr && sp.nn_idx == nullptr && sp.valid == nullptr;
 #define T6_LAUNCH(CAPV, LEANV)                                                                                                  \
   do {                                                                                                                         \
     const size_t smem = sizeof(T6Smem<CAPV>) * T6_WARPS;                                                                       \
     PCP_CUDA(cudaFuncSetAttribute(knn_tile6_kernel<CAPV, LEANV>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));    \
-    PCP_CUDA(pcp_launch_search(ctx, knn_tile6_kernel<CAPV, LEANV>, dim3(blocks), dim3(T6_WARPS * 32), smem, a, sp.R0, max_groups, wc, wl)); \
+    PCP_CUDA(pcp_launch_search(ctx, knn_tile6_kernel<CAPV, LEANV>, dim3(blocks), dim3(T6_WARPS * 32), smem, a, sp.R0, max_groups, wc, wl, perm, tiles)); \
   } while (0)
   if (sp.k <= PCP_T6_K32) {
     if (lean) T6_LAUNCH(32, true); else T6_LAUNCH(32, false);

@@ -52,6 +52,7 @@ struct PcpKnobs {
   int wl_tile = 0;
   double grid_shift = 0.0; // PCP_GRID_SHIFT: lower the grid origin by this fraction of a cell (diagnostic; results unchanged)
   int grid_shift_axis = -1;// PCP_GRID_SHIFT_AXIS: 0 / 1 / 2 = x / y / z only
+  int t6_no_order = 0;     // PCP_T6_ORDER=0: warps take tiles in cell order (A/B of tile_order_kernel)
   int flat_priority = 0;   // PCP_PRIO=flat: the search kernels run at the stream's priority (A/B of the two-level scheme below)
   int shard_full_sort = 0; // PCP_SHARD_SORT (A/B, tests): "rank" = rank a shard's global ids even when they are small enough to serve as ord (2),
                            // "full" = rank them by sorting all of them even when the own ids ascend (1)
@@ -111,6 +112,7 @@ struct pcp_ctx {
   DevBuf scan_tmp;
 
   // outputs / scratch
+  DevBuf tile_perm;   // knn_tile6.cu: tile served by every warp (tiles of similar work share a CTA)
   DevBuf work_list, work_count;  // k-NN queries deferred by the tile kernel (sorted positions)
   DevBuf out_feat, out_norm, out_idx, out_d2, out_counts, flags, valid, last_valid, staging;
   DevBuf ring_range, ring_idx, ring_long, ring_offsets, ring_key;
