@@ -13,17 +13,20 @@
 //             candidates' sorted positions).  -DT6_TMA=0 keeps the earlier register staging (four LDG.128 in flight
 //             per lane) for A/B runs;
 //   pass 1    bin coordinate Y = S |p' - q'|^2 + off = S |p'|^2 + (S |q'|^2 + off) - 2 S q'.p': one broadcast LDS.128 +
-//             four FFMA with per-lane constants (the last one saturating to [0, 1]: FFMA.SAT), one more FFMA adds 2^23
-//             so that the float's low bits ARE the bin, one IMAD forms the address and one shared reduction counts
-//             into the lane's own histogram column (CAP rows: CAP - 1 bins inside the cover radius + 1 beyond);
-//   scan      the bin holding the k-th smallest (one refinement pass for an over-full bin);
-//   pass 2    the same five FFMA + one compare; members append their SORTED POSITION to the lane's column (the
-//             histogram rows are dead by then: the column is the kernel's only per-lane storage);
+//             four FFMA with per-lane constants (the last one saturating to [0, 1]: FFMA.SAT); the bin is
+//             round(NB sqrt~(Y)) — one MUFU.SQRT and one more FFMA that adds 2^23 so that the float's low bits ARE the
+//             bin (bins uniform in distance) — or, in the geometric mode, the top bits of the float Y itself (shift +
+//             clamp, no MUFU); one IMAD forms the address and one shared reduction counts into the lane's own
+//             histogram column (CAP rows: CAP - 1 bins inside the cover radius + 1 beyond);
+//   scan      the bin b* holding the k-th smallest (one refinement pass for an over-full bin);
+//   pass 2    the same four FFMA + ONE float compare Y < edge(b*) (geometric bins: exact, the bins are read off Y's own
+//             bits; sqrt bins re-evaluate the bin: MUFU + FFMA + compare); members append their SORTED POSITION to the
+//             lane's column (the histogram rows are dead by then: the column is the kernel's only per-lane storage);
 //   resolve   every lane reads its <= CAP members from the sorted array, computes the reference distance (FLANN
 //             L2_Simple arithmetic) and forms 32-BIT keys prefix(d2) | slot; a register sorting network orders them
 //             (one min/max pair per compare-exchange, CAP registers) and the column is permuted into that order;
 //   check     the inexact bin coordinate is within eps_Y of the exact one (bound below), so a point that was NOT
-//             collected has d2 >= t_safe := ((b* + 1/2)/NB - eps_Y - off) / S; the lane's result stands only if
+//             collected (Y_computed >= y*) has d2 >= t_safe := (y* - eps_Y - off) / S; the lane's result stands only if
 //             its k-th distance lies below t_safe, otherwise it goes to the work list like any lane the tile cannot
 //             serve;
 //   finish    knn_finish_pos (knn_finish.cuh) walks the column, recomputes the full keys bits(d2) << 32 | ord, repairs
@@ -80,6 +83,14 @@ constexpr int T6_REC_WORDS = 17;
 #ifndef T6_TMA
 #define T6_TMA 1      // stage the candidate chunks with 1-D TMA bulk copies + mbarrier, double-buffered (0: LDG.128 -> STS.128 through registers)
 #endif
+// Bin modes of the selection passes (template parameter BIN; chosen per k in the launcher, PCP_T6_BIN forces one):
+//   T6_BIN_SQRT   both passes evaluate round(NB sqrt~(Y)) (MUFU.SQRT): bins uniform in distance (the round-2 form, kept for A/B)
+//   T6_BIN_LOG    bins = top bits of the float Y itself (geometric): integer ops, no MUFU; pass 2 is the compare Y < edge
+// (measured and dropped: sqrt bins in pass 1 with the compare Y < y* in pass 2, y* found by bisection with the pass-1
+// instructions — needs a guard against a non-monotone MUFU and was the fastest form for no k)
+constexpr int T6_BIN_SQRT = 0, T6_BIN_LOG = 1;
+// (measured and dropped: no shared reduction for candidates beyond the cover radius — `if (Y < 1) red...` — 1.16 -> 1.28 ms:
+// the reductions are cheap, the divergence around them is not)
 #ifndef T6_ORDER
 #define T6_ORDER 1    // warps of a CTA take tiles of similar candidate counts (tile_order_kernel): they reach the CTA barriers together
 #endif
@@ -175,17 +186,35 @@ __device__ __forceinline__ float sqrt_approx(float x) {
   return r;
 }
 
-// the bin of one staged candidate for this lane, as the float 2^23 + round(NB sqrt(Y)), Y = S d2 + off clamped to [0, 1].
-// Bins are uniform in DISTANCE, not in squared distance: on a surface the members per bin grow with the bin
-// index instead of being constant, so a k-th neighbour far inside the cover radius (dense scan lines of a VLP-16
-// ring: d_k ~ cover / 20) still meets a bin narrow enough for the lane's column.
-template <int NB>
-__device__ __forceinline__ float bin_z(const float4 P, const float S, const float K, const float A0, const float A1, const float A2) {
+// the bin coordinate of one staged candidate for this lane: Y = S d2 + off clamped to [0, 1] (four chained FFMA, the last
+// one saturating)
+__device__ __forceinline__ float bin_y(const float4 P, const float S, const float K, const float A0, const float A1, const float A2) {
   float y = __fmaf_rn(P.w, S, K);
   y = __fmaf_rn(P.x, A0, y);
   y = __fmaf_rn(P.y, A1, y);
-  y = fma_sat(P.z, A2, y);
-  return __fmaf_rn(sqrt_approx(y), (float)NB, T6_MAGIC);
+  return fma_sat(P.z, A2, y);
+}
+// Geometric bins read off the float itself: code(Y) = bits(Y) >> SH keeps the exponent and the top 23 - SH mantissa bits
+// (SH = 21: four bins per octave of Y, a ratio of 2^(1/8) = 9 % in DISTANCE, for 32-row columns; SH = 20: eight per octave
+// for 64-row columns); Y <= 1 has code <= C1 = code(1.0), the bin is code - C0 clamped at 0, C0 = C1 - NB: bin NB <=> Y = 1
+// (at or beyond the cover radius), bin 0 = everything below 2^(-NB / bins per octave).  Monotone in Y, exact integer
+// arithmetic: "bin(Y) <= b" is the float compare Y < y_edge(b), which is all pass 2 needs (no MUFU in either pass).
+template <int CAP>
+struct LogBin {
+  static constexpr int SH = CAP == 32 ? 21 : 20;
+  static constexpr uint32_t C1 = 127u << (23 - SH);
+  static constexpr uint32_t C0 = C1 - (uint32_t)(CAP - 1);
+  // upper edge (exclusive) of bin b, 0 <= b < NB
+  static __device__ __forceinline__ float edge(const int b) { return __uint_as_float((C0 + (uint32_t)b + 1u) << SH); }
+  // byte offset of plane[bin][0] relative to plane[-C0][0] (the caller folds the constant into its base address)
+  static __device__ __forceinline__ uint32_t row(const float y) { return max(__float_as_uint(y) >> SH, C0) * 128u; }
+};
+// the bin as the float 2^23 + round(NB sqrt(Y)).  Bins are uniform in DISTANCE, not in squared distance: on a surface the
+// members per bin grow with the bin index instead of being constant, so a k-th neighbour far inside the cover radius
+// (dense scan lines of a VLP-16 ring: d_k ~ cover / 20) still meets a bin narrow enough for the lane's column.
+template <int NB>
+__device__ __forceinline__ float bin_z(const float4 P, const float S, const float K, const float A0, const float A1, const float A2) {
+  return __fmaf_rn(sqrt_approx(bin_y(P, S, K, A0, A1, A2)), (float)NB, T6_MAGIC);
 }
 
 // The sorted positions of the candidates [cb, cb + cnt) of the tile's virtual candidate sequence (the stencil rows' runs
@@ -333,11 +362,12 @@ __global__ void __launch_bounds__(T6_WIN_THREADS) tile_order_kernel(KArgs a, int
 }
 
 // LEAN: records only (query-centred; the k-th distance may be asked for): see knn_finish.cuh
-template <int CAP, bool LEAN>
+template <int CAP, bool LEAN, int BIN>
 __global__ void __launch_bounds__(T6_WARPS * 32, CAP == 32 ? (T6_MINB * 4) / T6_WARPS : 16 / T6_WARPS)
     knn_tile6_kernel(KArgs a, int R0, int max_groups, uint32_t* __restrict__ work_count, uint32_t* __restrict__ work_list,
-                     const uint32_t* __restrict__ perm, int64_t n_tiles) {
+                     const uint32_t* __restrict__ perm, int64_t n_tiles, int refine_min) {
   constexpr int NB = CAP - 1;
+  constexpr int CAPM = CAP;  // members a served lane may have
   extern __shared__ __align__(16) unsigned char smem_raw[];
   T6Smem<CAP>& sm = reinterpret_cast<T6Smem<CAP>*>(smem_raw)[threadIdx.x >> 5];
   const int lane = threadIdx.x & 31;
@@ -366,7 +396,8 @@ __global__ void __launch_bounds__(T6_WARPS * 32, CAP == 32 ? (T6_MINB * 4) / T6_
   }
   __syncwarp();
 #endif
-  const uint32_t hbase = hcol_a - T6_MAGIC_BITS * 128u;  // (bits of 2^23 + bin) * 128 + hbase = address of plane[bin][lane], modulo 2^32
+  // LogBin::row(Y) + hbase, or (bits of 2^23 + bin) * 128 + hbase (modulo 2^32) = address of plane[bin][lane]
+  const uint32_t hbase = BIN == T6_BIN_LOG ? hcol_a - LogBin<CAP>::C0 * 128u : hcol_a - T6_MAGIC_BITS * 128u;
   uint32_t wp = hcol_a;      // next free entry of this lane's member column
   const uint32_t my_row = cid / (uint32_t)g.dim[0];
   const int c0 = (int)(cid - my_row * (uint32_t)g.dim[0]);
@@ -454,14 +485,27 @@ __global__ void __launch_bounds__(T6_WARPS * 32, CAP == 32 ? (T6_MINB * 4) / T6_
 #pragma unroll 2
         for (; j + 4 <= n_ch; j += 4, ca += 64) {
           const float4 P0 = lds_f4<0>(ca), P1 = lds_f4<16>(ca), P2 = lds_f4<32>(ca), P3 = lds_f4<48>(ca);
-          const float z0 = bin_z<NB>(P0, S, K, A0, A1, A2), z1 = bin_z<NB>(P1, S, K, A0, A1, A2);
-          const float z2 = bin_z<NB>(P2, S, K, A0, A1, A2), z3 = bin_z<NB>(P3, S, K, A0, A1, A2);
-          red_add_u32(__float_as_uint(z0) * 128u + hbase, inc);
-          red_add_u32(__float_as_uint(z1) * 128u + hbase, inc);
-          red_add_u32(__float_as_uint(z2) * 128u + hbase, inc);
-          red_add_u32(__float_as_uint(z3) * 128u + hbase, inc);
+          if constexpr (BIN == T6_BIN_LOG) {
+            const float y0 = bin_y(P0, S, K, A0, A1, A2), y1 = bin_y(P1, S, K, A0, A1, A2);
+            const float y2 = bin_y(P2, S, K, A0, A1, A2), y3 = bin_y(P3, S, K, A0, A1, A2);
+            red_add_u32(LogBin<CAP>::row(y0) + hbase, inc);
+            red_add_u32(LogBin<CAP>::row(y1) + hbase, inc);
+            red_add_u32(LogBin<CAP>::row(y2) + hbase, inc);
+            red_add_u32(LogBin<CAP>::row(y3) + hbase, inc);
+          } else {
+            const float z0 = bin_z<NB>(P0, S, K, A0, A1, A2), z1 = bin_z<NB>(P1, S, K, A0, A1, A2);
+            const float z2 = bin_z<NB>(P2, S, K, A0, A1, A2), z3 = bin_z<NB>(P3, S, K, A0, A1, A2);
+            red_add_u32(__float_as_uint(z0) * 128u + hbase, inc);
+            red_add_u32(__float_as_uint(z1) * 128u + hbase, inc);
+            red_add_u32(__float_as_uint(z2) * 128u + hbase, inc);
+            red_add_u32(__float_as_uint(z3) * 128u + hbase, inc);
+          }
         }
-        for (; j < n_ch; ++j, ca += 16) red_add_u32(__float_as_uint(bin_z<NB>(lds_f4<0>(ca), S, K, A0, A1, A2)) * 128u + hbase, inc);
+        for (; j < n_ch; ++j, ca += 16) {
+          const float4 P = lds_f4<0>(ca);
+          if constexpr (BIN == T6_BIN_LOG) red_add_u32(LogBin<CAP>::row(bin_y(P, S, K, A0, A1, A2)) + hbase, inc);
+          else red_add_u32(__float_as_uint(bin_z<NB>(P, S, K, A0, A1, A2)) * 128u + hbase, inc);
+        }
         __syncwarp();
       }
       // the bin holding the k-th smallest, and how many candidates lie at or below it
@@ -478,18 +522,29 @@ __global__ void __launch_bounds__(T6_WARPS * 32, CAP == 32 ? (T6_MINB * 4) / T6_
         }
       }
       if (refined) break;
-      const bool refine = hist_on && bstar >= 0 && cum_star > CAP;
-      if (!__any_sync(PCP_FULL, refine)) break;
+      const bool refine = hist_on && bstar >= 0 && cum_star > CAPM;
+      // a refinement pass walks every candidate again for the whole tile: worth it only when several lanes want it;
+      // one or two go to the work list instead (their threshold bin stays too full: not served)
+      if (__popc(__ballot_sync(PCP_FULL, refine)) < refine_min) break;
       T6STAT(9, refine ? 1 : 0);
       refined = true;
       hist_on = refine;
       if (refine) {
-        // old bin b*: NB sqrt(Y) in [b* - 1/2, b* + 1/2).  New Y' = (Y - w0) / (w1 - w0) with the window [w0, w1) a little
-        // wider than the bin (b* - 0.52 .. b* + 0.60): the k-th stays inside (0, 0.92), i.e. below the new overflow bin;
-        // everything below the window saturates to bin 0 (fewer than k candidates: all collected), everything above it
-        // to bin NB
-        const float r0 = ((float)bstar - 0.52f) / (float)NB, r1 = ((float)bstar + 0.60f) / (float)NB;
-        const float w0 = bstar > 0 ? r0 * r0 : -r1 * r1 * 0.04f, w1 = r1 * r1;
+        // New Y' = (Y - w0) / (w1 - w0) with the window [w0, w1) a little wider than the old bin b*: the k-th stays below
+        // the new overflow bin; everything below the window saturates to bin 0 (fewer than k candidates: all collected),
+        // everything above it to bin NB.
+        float w0, w1;
+        if constexpr (BIN == T6_BIN_LOG) {
+          // old bin: Y in [edge(b* - 1), edge(b*)); the members (Y < edge(b*)) stay below Y' = 1.  The new bins are geometric
+          // in Y' (the top one takes the upper 16 % or 8 % of the window): coarse at the low end, fine where the k-th usually lies
+          w1 = LogBin<CAP>::edge(bstar) * 1.001f;
+          w0 = bstar > 0 ? LogBin<CAP>::edge(bstar - 1) * 0.999f : -0.04f * w1;
+        } else {
+          // old bin: NB sqrt(Y) in [b* - 1/2, b* + 1/2); window b* - 0.52 .. b* + 0.60: the k-th stays inside (0, 0.92)
+          const float r0 = ((float)bstar - 0.52f) / (float)NB, r1 = ((float)bstar + 0.60f) / (float)NB;
+          w0 = bstar > 0 ? r0 * r0 : -r1 * r1 * 0.04f;
+          w1 = r1 * r1;
+        }
         const float gain = 1.f / (w1 - w0);
         off = -w0 * gain;  // (the first pass has off = 0)
         S *= gain;
@@ -498,21 +553,31 @@ __global__ void __launch_bounds__(T6_WARPS * 32, CAP == 32 ? (T6_MINB * 4) / T6_
     }
     T6STAT(2, lane == 0 ? total : 0);
     T6STAT(5, (in_grp && bstar < 0) ? 1 : 0);                     // deferred: k-th beyond the cover radius
-    T6STAT(6, (in_grp && bstar >= 0 && cum_star > CAP) ? 1 : 0);  // deferred: threshold bin too full
-    const bool grp_ok = in_grp && bstar >= 0 && cum_star <= CAP;
+    T6STAT(6, (in_grp && bstar >= 0 && cum_star > CAPM) ? 1 : 0);  // deferred: threshold bin too full
+    const bool grp_ok = in_grp && bstar >= 0 && cum_star <= CAPM;
     if (in_grp && bstar < 0 && R >= 1) far = true;  // d_k > the lane's cover radius >= one cell
-    // collect test: round(NB Y) <= b*, i.e. the float 2^23 + round(NB Y) < 2^23 + b* + 1; other lanes collect nothing
-    const float thr_z = grp_ok ? T6_MAGIC + (float)(bstar + 1) : 0.f;
     float t_reach = 0.f;  // largest exact d2 a member of this lane can have
+    // Collect test of pass 2, one float compare against thr (other lanes collect nothing):
+    //   SQRT    the pass-1 value itself: 2^23 + round(NB sqrt~(Y)) < 2^23 + b* + 1;
+    //   LOG     bin(Y) <= b*  <=>  Y < edge(b*), exact: the bins are read off Y's own bits.
+    float thr = BIN == T6_BIN_SQRT ? 0.f : -1.f;
     if (grp_ok) {
       const float reach = 2.f * sqrtf(qq) + 2.f * cover_m;
       const float eps_y = 6.03e-8f * (12.f * S * reach * reach + 12.f * fabsf(off) + 4.f);
-      // a candidate that was NOT collected has NB sqrt~(Y) >= b* + 1/2, so Y >= edge^2 (1 - 2^-20) with the MUFU's error;
-      // a member has Y <= edge^2 (1 + 2^-20)
-      const float edge = ((float)bstar + 0.5f) / (float)NB;
-      const float e2 = edge * edge;
-      t_safe = ((e2 * (1.f - 2e-6f) - eps_y - off) / S) * (1.f - 4e-6f);
-      t_reach = ((e2 * (1.f + 2e-6f) + eps_y - off) / S) * (1.f + 4e-6f);
+      if constexpr (BIN == T6_BIN_SQRT) {
+        thr = T6_MAGIC + (float)(bstar + 1);
+        // a candidate that was NOT collected has NB sqrt~(Y) >= b* + 1/2, so Y >= edge^2 (1 - 2^-20) with the MUFU's error;
+        // a member has Y <= edge^2 (1 + 2^-20)
+        const float edge = ((float)bstar + 0.5f) / (float)NB;
+        const float e2 = edge * edge;
+        t_safe = ((e2 * (1.f - 2e-6f) - eps_y - off) / S) * (1.f - 4e-6f);
+        t_reach = ((e2 * (1.f + 2e-6f) + eps_y - off) / S) * (1.f + 4e-6f);
+      } else {
+        thr = LogBin<CAP>::edge(bstar);
+        // a candidate that was NOT collected has Y_computed >= thr, a member Y_computed < thr; Y_exact is within eps_y
+        t_safe = ((thr - eps_y - off) / S) * (1.f - 4e-6f);
+        t_reach = ((thr + eps_y - off) / S) * (1.f + 4e-6f);
+      }
     }
     __syncwarp();
     // ---- pass 2: collect the sorted positions of the candidates at or below the threshold bin
@@ -589,15 +654,23 @@ __global__ void __launch_bounds__(T6_WARPS * 32, CAP == 32 ? (T6_MINB * 4) / T6_
 #pragma unroll 2
         for (; j + 4 <= n_ch; j += 4, ca += 64, pa += 16) {
           const float4 P0 = lds_f4<0>(ca), P1 = lds_f4<16>(ca), P2 = lds_f4<32>(ca), P3 = lds_f4<48>(ca);
-          const float z0 = bin_z<NB>(P0, S, K, A0, A1, A2), z1 = bin_z<NB>(P1, S, K, A0, A1, A2);
-          const float z2 = bin_z<NB>(P2, S, K, A0, A1, A2), z3 = bin_z<NB>(P3, S, K, A0, A1, A2);
-          if (z0 < thr_z) { sts_u32(wp, lds_u32<0>(pa)); wp += 128; }
-          if (z1 < thr_z) { sts_u32(wp, lds_u32<4>(pa)); wp += 128; }
-          if (z2 < thr_z) { sts_u32(wp, lds_u32<8>(pa)); wp += 128; }
-          if (z3 < thr_z) { sts_u32(wp, lds_u32<12>(pa)); wp += 128; }
+          float z0, z1, z2, z3;
+          if constexpr (BIN == T6_BIN_SQRT) {
+            z0 = bin_z<NB>(P0, S, K, A0, A1, A2), z1 = bin_z<NB>(P1, S, K, A0, A1, A2);
+            z2 = bin_z<NB>(P2, S, K, A0, A1, A2), z3 = bin_z<NB>(P3, S, K, A0, A1, A2);
+          } else {
+            z0 = bin_y(P0, S, K, A0, A1, A2), z1 = bin_y(P1, S, K, A0, A1, A2);
+            z2 = bin_y(P2, S, K, A0, A1, A2), z3 = bin_y(P3, S, K, A0, A1, A2);
+          }
+          if (z0 < thr) { sts_u32(wp, lds_u32<0>(pa)); wp += 128u; }
+          if (z1 < thr) { sts_u32(wp, lds_u32<4>(pa)); wp += 128u; }
+          if (z2 < thr) { sts_u32(wp, lds_u32<8>(pa)); wp += 128u; }
+          if (z3 < thr) { sts_u32(wp, lds_u32<12>(pa)); wp += 128u; }
         }
         for (; j < n_ch; ++j, ca += 16, pa += 4) {
-          if (bin_z<NB>(lds_f4<0>(ca), S, K, A0, A1, A2) < thr_z) { sts_u32(wp, lds_u32<0>(pa)); wp += 128; }
+          const float4 P = lds_f4<0>(ca);
+          const float z = BIN == T6_BIN_SQRT ? bin_z<NB>(P, S, K, A0, A1, A2) : bin_y(P, S, K, A0, A1, A2);
+          if (z < thr) { sts_u32(wp, lds_u32<0>(pa)); wp += 128u; }
         }
         __syncwarp();
       }
@@ -714,17 +787,31 @@ int pcp_knn_tile6_launch(pcp_ctx* ctx, const SearchParams& sp, const KArgs& a) {
   }
 #endif
   const bool lean = sp.out != nullptr && sp.center_mode == PCP_CENTER_QUERY && sp.normals == nullptr && sp.nn_idx == nullptr && sp.valid == nullptr;
-#define T6_LAUNCH(CAPV, LEANV)                                                                                                  \
+#define T6_LAUNCH(CAPV, LEANV, BINV)                                                                                            \
   do {                                                                                                                         \
     const size_t smem = sizeof(T6Smem<CAPV>) * T6_WARPS;                                                                       \
-    PCP_CUDA(cudaFuncSetAttribute(knn_tile6_kernel<CAPV, LEANV>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));    \
-    PCP_CUDA(pcp_launch_search(ctx, knn_tile6_kernel<CAPV, LEANV>, dim3(blocks), dim3(T6_WARPS * 32), smem, a, sp.R0, max_groups, wc, wl, perm, tiles)); \
+    PCP_CUDA(cudaFuncSetAttribute(knn_tile6_kernel<CAPV, LEANV, BINV>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+    PCP_CUDA(pcp_launch_search(ctx, knn_tile6_kernel<CAPV, LEANV, BINV>, dim3(blocks), dim3(T6_WARPS * 32), smem, a, sp.R0, max_groups, wc, wl, perm, tiles, refine_min)); \
   } while (0)
+#define T6_LAUNCH_BIN(CAPV, LEANV)                                         \
+  do {                                                                     \
+    if (bin == T6_BIN_LOG) T6_LAUNCH(CAPV, LEANV, T6_BIN_LOG);             \
+    else T6_LAUNCH(CAPV, LEANV, T6_BIN_SQRT);                              \
+  } while (0)
+  // bin mode (see T6_BIN_*): PCP_T6_BIN=sqrt|log forces one
+  // Measured on one B200 (1 M-point urban cloud, search stage, sqrt / geometric bins): k = 10 1.11 / 1.05 ms, k = 15 1.145 /
+  // 1.094, k = 20 1.231 / 1.187, k = 24 1.38 / 1.45 (four bins per octave are too coarse once 1.2-1.3 k members approach
+  // the 32-row column), k = 30 (64-row columns, eight per octave) 1.68 / 1.61; 500 k-point playground, k = 20: 0.764 / 0.725.
+  // A refinement pass runs when at least 6 lanes of a tile want one (always: k = 20 1.26 instead of 1.19 ms).
+  const int refine_min = ctx->knobs.t6_refine_min > 0 ? ctx->knobs.t6_refine_min : 6;
+  int bin = (sp.k >= 22 && sp.k <= PCP_T6_K32) ? T6_BIN_SQRT : T6_BIN_LOG;
+  if (ctx->knobs.t6_bin >= 0) bin = ctx->knobs.t6_bin;
   if (sp.k <= PCP_T6_K32) {
-    if (lean) T6_LAUNCH(32, true); else T6_LAUNCH(32, false);
+    if (lean) T6_LAUNCH_BIN(32, true); else T6_LAUNCH_BIN(32, false);
   } else {
-    if (lean) T6_LAUNCH(64, true); else T6_LAUNCH(64, false);
+    if (lean) T6_LAUNCH_BIN(64, true); else T6_LAUNCH_BIN(64, false);
   }
+#undef T6_LAUNCH_BIN
 #undef T6_LAUNCH
   PCP_LAUNCH_CHECK("knn_tile6_kernel");
   return PCP_OK;

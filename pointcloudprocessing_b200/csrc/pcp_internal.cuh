@@ -52,6 +52,8 @@ struct PcpKnobs {
   int wl_tile = 0;
   double grid_shift = 0.0; // PCP_GRID_SHIFT: lower the grid origin by this fraction of a cell (diagnostic; results unchanged)
   int grid_shift_axis = -1;// PCP_GRID_SHIFT_AXIS: 0 / 1 / 2 = x / y / z only
+  int t6_bin = -1;         // PCP_T6_BIN=sqrt|log: bin mode of the k-NN tile kernel's selection passes (-1 = the launcher's choice)
+  int t6_refine_min = 0;   // PCP_T6_REFINE_MIN: lanes of a tile that must want a refinement pass for it to run (0 = default)
   int t6_no_order = 0;     // PCP_T6_ORDER=0: warps take tiles in cell order (A/B of tile_order_kernel)
   int flat_priority = 0;   // PCP_PRIO=flat: the search kernels run at the stream's priority (A/B of the two-level scheme below)
   int shard_full_sort = 0; // PCP_SHARD_SORT (A/B, tests): "rank" = rank a shard's global ids even when they are small enough to serve as ord (2),
