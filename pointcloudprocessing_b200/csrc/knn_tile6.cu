@@ -312,7 +312,7 @@ __device__ __forceinline__ void stage6(const float4* __restrict__ sorted, T6Smem
 #endif
 
 // The four warps of a CTA meet at two barriers (below), so a CTA is as slow as its slowest tile: 17 % of the kernel's
-// warp time was spent waiting there (ncu, profiles/r02_search_ncu_48f2d008099b.txt) because tiles next to each other in
+// warp time was spent waiting there (ncu, profiles/r02f_search_ncu_tma_sqrt_bins.txt) because tiles next to each other in
 // cell order differ by +-30 % in candidates.  This kernel estimates every tile's candidate count (first and last
 // query's cells, two table reads per stencil row) and sorts each window of 256 consecutive tiles by it: warp w of CTA b
 // then serves tile perm[4 b + w], four tiles of nearly equal work, still from one neighbourhood of the cloud.
