@@ -52,10 +52,17 @@ def source_id() -> str:
     csrc = os.path.join(ROOT, "pointcloudprocessing_b200", "csrc")
     stage = ("Makefile", "eigen3.cuh", "grid.cu", "knn_finish.cuh", "knn_tile.cu", "knn_tile6.cu", "pcp_internal.cuh",
              "search_common.cuh", "search_pca.cu", "sortnet32.cuh", "tile_common.cuh")
+    import re
+
     for name in sorted(os.listdir(csrc)):
         if name in stage:
-            with open(os.path.join(csrc, name), "rb") as f:
-                h.update(name.encode() + b"\0" + f.read())
+            with open(os.path.join(csrc, name), "r", encoding="utf-8", errors="replace") as f:
+                text = f.read()
+            # comments and layout do not change the kernels: hash the code alone
+            text = re.sub(r"/\*.*?\*/", " ", text, flags=re.S)
+            text = re.sub(r"//[^\n]*", " ", text)
+            text = " ".join(text.split())
+            h.update(name.encode() + b"\0" + text.encode())
     return h.hexdigest()[:12]
 
 

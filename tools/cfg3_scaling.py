@@ -22,6 +22,9 @@ ap.add_argument("--steps", type=int, default=5)
 ap.add_argument("--radius", type=float, default=0.5)
 ap.add_argument("--out", default="")
 ap.add_argument("--no-verify", action="store_true")
+ap.add_argument("--exchange", default="peer", choices=["peer", "nccl"],
+                help="halo strips by peer stores + flags into fixed-capacity regions (pcp_halo_push / pcp_halo_wait: no host sync, no NCCL on the data path) "
+                     "or by torch masks + NCCL send/recv (sizes travel first)")
 args = ap.parse_args()
 rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1")); local = int(os.environ.get("LOCAL_RANK", "0"))
 torch.cuda.set_device(local)
@@ -54,17 +57,33 @@ def barrier():
     torch.cuda.synchronize()
 
 keep = {}
+ex = None
+if world > 1 and args.exchange == "peer":
+    # fixed-capacity halo regions: 1.5 x the strip a uniform slab would send (the true counts are checked after the run)
+    width = (pts[:, 0].max() - pts[:, 0].min()) / world
+    cap = max(4096, int(1.5 * h / width * (n / world)) + 4096)
+    ex = sharding.SlabExchangePeer(p, n_own, cap, local, rank, world, 0, flo, fhi, h)
+    ex.connect_group()
+    ex.set_own(d_own, d_gid)
+    torch.cuda.synchronize()
+
 def step():
-    with torch.cuda.stream(stream):
-        if world > 1:
-            pa, ga, no = sharding.exchange_halo(d_own, d_gid, 0, flo, fhi, h, rank, world)
-        else:
-            pa, ga, no = d_own, d_gid, n_own
-        keep["bufs"] = (pa, ga)
-    p.set_cloud_device(pa.data_ptr(), pa.shape[0], ga.data_ptr() if world > 1 else None, no)
+    if ex is not None:
+        with torch.cuda.stream(stream):
+            ex.step()  # push + wait + hand-over (pcp_set_cloud_device_sharded) on the library's stream
+        n_tot = ex.n_all
+    else:
+        with torch.cuda.stream(stream):
+            if world > 1:
+                pa, ga, no = sharding.exchange_halo(d_own, d_gid, 0, flo, fhi, h, rank, world)
+            else:
+                pa, ga, no = d_own, d_gid, n_own
+            keep["bufs"] = (pa, ga)
+        p.set_cloud_device(pa.data_ptr(), pa.shape[0], ga.data_ptr() if world > 1 else None, no)
+        n_tot = pa.shape[0]
     p.build_grid(r * 1.001, 0)
     p.radius_pca(r, 13, capi.CENTER_QUERY, False, out_device=d_out.data_ptr())
-    return pa.shape[0]
+    return n_tot
 
 for _ in range(2):
     n_all = step()
@@ -82,6 +101,10 @@ for s in range(args.steps):
     devs.append(e0.elapsed_time(e1) * 1e-3)
 tm = p.timings()
 barrier()
+halo_real = None
+if ex is not None:
+    halo_real = sum(ex.check())  # both strips fitted their regions, no wait timed out
+
 t = torch.tensor([sum(walls) / len(walls), min(walls), sum(devs) / len(devs), tm["search_pca"], tm["bbox"] + tm["keys"] + tm["sort"] + tm["table"]],
                  dtype=torch.float64, device=local)
 if world > 1:
@@ -104,7 +127,7 @@ if not args.no_verify:
     ptnum = d_out.view(-1, 68)[:, 52:56].contiguous().view(torch.int32).view(-1)
     mean_nb = float(ptnum.float().mean().item())
     del d_full, d_fout, mine
-info = torch.tensor([n_own, n_all - n_own, differing if differing is not None else -1], dtype=torch.int64, device=local)
+info = torch.tensor([n_own, halo_real if halo_real is not None else n_all - n_own, differing if differing is not None else -1], dtype=torch.int64, device=local)
 gathered = [torch.zeros_like(info) for _ in range(world)]
 if world > 1:
     dist.all_gather(gathered, info)
@@ -112,7 +135,8 @@ else:
     gathered = [info]
 if rank == 0:
     res = {"workload": f"configs[3]: urban(seed 4) {n} points over {ext:.0f} m x {ext:.0f} m, radiusSearch r = {r} m + PCA (13-neighbour gate, no stale-record carry), "
-                       f"equal-count x-slabs, halo {h:.4f} m exchanged every step (NCCL send/recv)",
+                       f"equal-count x-slabs, halo {h:.4f} m exchanged every step (" +
+                       ("peer stores into the neighbours' halo regions + flags: pcp_halo_push / pcp_halo_wait, no host sync)" if ex is not None else "NCCL send/recv)"),
            "n_gpus": world, "points": n, "steps": args.steps, "scaling": "strong",
            "points_per_s_wall": n / wall_avg, "ms_per_step_wall_avg": wall_avg * 1e3, "ms_per_step_wall_min": wall_min * 1e3,
            "ms_per_step_device_events": dev_avg * 1e3, "search_pca_ms_max_rank": search_ms, "grid_ms_max_rank": grid_ms,
@@ -128,6 +152,8 @@ if rank == 0:
         open(args.out, "w").write(s)
 p.synchronize()
 keep.clear()
+if ex is not None:
+    ex.close()
 del d_own, d_gid, d_out
 torch.cuda.synchronize()
 if world > 1:
