@@ -17,7 +17,7 @@ import torch.distributed as dist
 from pointcloudprocessing_b200 import capi, sharding, synth
 
 ap = argparse.ArgumentParser()
-ap.add_argument("--n", type=int, default=100_000_000)
+ap.add_argument("--n", "--npts", dest="n", type=int, default=100_000_000)  # (--npts under torchrun, which reads --n as its own option)
 ap.add_argument("--steps", type=int, default=5)
 ap.add_argument("--radius", type=float, default=0.5)
 ap.add_argument("--out", default="")
@@ -59,9 +59,13 @@ def barrier():
 keep = {}
 ex = None
 if world > 1 and args.exchange == "peer":
-    # fixed-capacity halo regions: 1.5 x the strip a uniform slab would send (the true counts are checked after the run)
-    width = (pts[:, 0].max() - pts[:, 0].min()) / world
-    cap = max(4096, int(1.5 * h / width * (n / world)) + 4096)
+    # fixed-capacity halo regions, the same on every rank: the largest strip any face receives (every rank holds the whole
+    # cloud on the host here, so the counts are exact; a deployment sizes them from the previous cloud), + 2 % + 1024
+    xs = pts[:, 0]
+    strip = 0
+    for e in edges[1:-1]:
+        strip = max(strip, int(np.count_nonzero((xs >= e - h) & (xs < e))), int(np.count_nonzero((xs >= e) & (xs < e + h))))
+    cap = int(strip * 1.02) + 1024
     ex = sharding.SlabExchangePeer(p, n_own, cap, local, rank, world, 0, flo, fhi, h)
     ex.connect_group()
     ex.set_own(d_own, d_gid)
