@@ -67,6 +67,7 @@ static void read_knobs(PcpKnobs& kn) {
   if (const char* e = getenv("PCP_WL_TILE")) kn.wl_tile = (atoi(e) >= 1 && atoi(e) <= 32) ? atoi(e) : 0;
   if (const char* e = getenv("PCP_GRID_SHIFT")) kn.grid_shift = atof(e) < 0.0 ? 0.0 : (atof(e) > 0.999 ? 0.999 : atof(e));
   if (const char* e = getenv("PCP_GRID_SHIFT_AXIS")) kn.grid_shift_axis = atoi(e);
+  if (const char* e = getenv("PCP_RADIUS_T6")) kn.radius_t6 = atoi(e) != 0 ? 1 : 0;
   if (const char* e = getenv("PCP_T6_BIN")) kn.t6_bin = !strcmp(e, "sqrt") ? 0 : (!strcmp(e, "log") ? 1 : -1);
   if (const char* e = getenv("PCP_T6_REFINE_MIN")) kn.t6_refine_min = atoi(e) > 0 ? atoi(e) : 0;
   if (const char* e = getenv("PCP_T6_ORDER")) kn.t6_no_order = atoi(e) == 0 ? 1 : 0;

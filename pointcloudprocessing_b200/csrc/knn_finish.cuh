@@ -189,13 +189,14 @@ static __device__ __noinline__ void knn_fix_order(const float4* __restrict__ sor
 
 template <bool LEAN = false>
 __device__ __forceinline__ void knn_finish_pos(const KArgs& a, uint32_t* col, const int cnt, const int n_nb, const uint32_t prefix_mask,
-                                               const float4 Q, const int my_slot, float (*rec_all)[17], const int lane) {
+                                               const float4 Q, const int my_slot, float (*rec_all)[17], const int lane,
+                                               const int min_valid = 1) {
   const SearchParams& sp = a.sp;
   const int k = sp.k;
   const float4* __restrict__ sorted = a.sorted;
   const int ord_q = __float_as_int(Q.w);
   const int gid_q = (my_slot >= 0 && a.gid_of_ord) ? __ldg(&a.gid_of_ord[ord_q]) : ord_q;
-  const bool valid = my_slot >= 0 && n_nb >= 1;
+  const bool valid = my_slot >= 0 && n_nb >= max(min_valid, 1);  // radius search: the 13-neighbour gate (src/pcaAnalysis.cpp:50)
   const bool need_q = LEAN || (sp.out != nullptr && sp.center_mode == PCP_CENTER_QUERY);
   const bool need_m = !LEAN && (sp.normals != nullptr || (sp.out != nullptr && sp.center_mode == PCP_CENTER_MEAN));
   float mq[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f}, mm[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};

@@ -88,7 +88,11 @@ constexpr int T6_REC_WORDS = 17;
 //   T6_BIN_LOG    bins = top bits of the float Y itself (geometric): integer ops, no MUFU; pass 2 is the compare Y < edge
 // (measured and dropped: sqrt bins in pass 1 with the compare Y < y* in pass 2, y* found by bisection with the pass-1
 // instructions — needs a guard against a non-monotone MUFU and was the fastest form for no k)
-constexpr int T6_BIN_SQRT = 0, T6_BIN_LOG = 1;
+//   T6_BIN_RADIUS fixed-radius search (radiusSearch, src/pcaAnalysis.cpp:25): the threshold is known, so pass 1 and the scan
+//                 disappear; pass 2 collects the superset Y < 1 + eps (Y = d2 / r2 in the tile-local frame), the resolve step
+//                 keeps the members whose REFERENCE distance satisfies d2 < r2 (strict, FLANN's arithmetic) — exact by
+//                 construction, no proof needed; lanes with more hits than the column holds go to the work list
+constexpr int T6_BIN_SQRT = 0, T6_BIN_LOG = 1, T6_BIN_RADIUS = 2;
 // (measured and dropped: no shared reduction for candidates beyond the cover radius — `if (Y < 1) red...` — 1.16 -> 1.28 ms:
 // the reductions are cheap, the divergence around them is not)
 #ifndef T6_ORDER
@@ -188,11 +192,12 @@ __device__ __forceinline__ float sqrt_approx(float x) {
 
 // the bin coordinate of one staged candidate for this lane: Y = S d2 + off clamped to [0, 1] (four chained FFMA, the last
 // one saturating)
+template <bool SAT = true>
 __device__ __forceinline__ float bin_y(const float4 P, const float S, const float K, const float A0, const float A1, const float A2) {
   float y = __fmaf_rn(P.w, S, K);
   y = __fmaf_rn(P.x, A0, y);
   y = __fmaf_rn(P.y, A1, y);
-  return fma_sat(P.z, A2, y);
+  return SAT ? fma_sat(P.z, A2, y) : __fmaf_rn(P.z, A2, y);
 }
 // Geometric bins read off the float itself: code(Y) = bits(Y) >> SH keeps the exponent and the top 23 - SH mantissa bits
 // (SH = 21: four bins per octave of Y, a ratio of 2^(1/8) = 9 % in DISTANCE, for 32-row columns; SH = 20: eight per octave
@@ -368,6 +373,7 @@ __global__ void __launch_bounds__(T6_WARPS * 32, CAP == 32 ? (T6_MINB * 4) / T6_
                      const uint32_t* __restrict__ perm, int64_t n_tiles, int refine_min) {
   constexpr int NB = CAP - 1;
   constexpr int CAPM = CAP;  // members a served lane may have
+  constexpr bool RAD = BIN == T6_BIN_RADIUS;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   T6Smem<CAP>& sm = reinterpret_cast<T6Smem<CAP>*>(smem_raw)[threadIdx.x >> 5];
   const int lane = threadIdx.x & 31;
@@ -399,6 +405,7 @@ __global__ void __launch_bounds__(T6_WARPS * 32, CAP == 32 ? (T6_MINB * 4) / T6_
   // LogBin::row(Y) + hbase, or (bits of 2^23 + bin) * 128 + hbase (modulo 2^32) = address of plane[bin][lane]
   const uint32_t hbase = BIN == T6_BIN_LOG ? hcol_a - LogBin<CAP>::C0 * 128u : hcol_a - T6_MAGIC_BITS * 128u;
   uint32_t wp = hcol_a;      // next free entry of this lane's member column
+  const uint32_t wend = hcol_a + (uint32_t)CAP * 128u;
   const uint32_t my_row = cid / (uint32_t)g.dim[0];
   const int c0 = (int)(cid - my_row * (uint32_t)g.dim[0]);
   bool pending = finite;     // not yet served by a row group
@@ -448,13 +455,15 @@ __global__ void __launch_bounds__(T6_WARPS * 32, CAP == 32 ? (T6_MINB * 4) / T6_
       const float diag_cells = sqrtf(ex * ex + ey * ey + ez * ez) * 1.0001f;
       cover_m = fminf(cover_cells, diag_cells) * g.cell;
     }
-    float S = 1.f / (cover_m * cover_m * (1.f - 1e-6f));  // Y = S d2 + off reaches 1 just inside the cover radius
+    if (RAD) cover_m = sqrtf(sp.r2);  // the stencil covers the radius by construction (stencil_for_radius); Y = d2 / r2
+    float S = RAD ? 1.f / sp.r2 : 1.f / (cover_m * cover_m * (1.f - 1e-6f));  // Y = S d2 + off reaches 1 just inside the cover radius
     float off = 0.f;
     float A0 = -2.f * S * qx, A1 = -2.f * S * qy, A2 = -2.f * S * qz, K = __fmaf_rn(S, qq, off);
     // ---- pass 1: histogram of the bin coordinate over the staged candidates; a lane whose threshold bin holds
     // too many candidates for its column (d_k << cover: dense scan lines next to a sparse surrounding, e.g. the
     // near field of a VLP-16 frame) gets ONE refinement pass with the window narrowed to that bin (candidates
     // below the window saturate to bin 0 and are all collected, those above it to bin NB)
+    if constexpr (!RAD) {
     bool hist_on = in_grp, refined = false;
 #pragma unroll 1
     for (;;) {
@@ -551,11 +560,12 @@ __global__ void __launch_bounds__(T6_WARPS * 32, CAP == 32 ? (T6_MINB * 4) / T6_
         A0 = -2.f * S * qx, A1 = -2.f * S * qy, A2 = -2.f * S * qz, K = __fmaf_rn(S, qq, off);
       }
     }
+    }  // !RAD
     T6STAT(2, lane == 0 ? total : 0);
     T6STAT(5, (in_grp && bstar < 0) ? 1 : 0);                     // deferred: k-th beyond the cover radius
     T6STAT(6, (in_grp && bstar >= 0 && cum_star > CAPM) ? 1 : 0);  // deferred: threshold bin too full
-    const bool grp_ok = in_grp && bstar >= 0 && cum_star <= CAPM;
-    if (in_grp && bstar < 0 && R >= 1) far = true;  // d_k > the lane's cover radius >= one cell
+    const bool grp_ok = RAD ? in_grp : (in_grp && bstar >= 0 && cum_star <= CAPM);
+    if (!RAD && in_grp && bstar < 0 && R >= 1) far = true;  // d_k > the lane's cover radius >= one cell
     float t_reach = 0.f;  // largest exact d2 a member of this lane can have
     // Collect test of pass 2, one float compare against thr (other lanes collect nothing):
     //   SQRT    the pass-1 value itself: 2^23 + round(NB sqrt~(Y)) < 2^23 + b* + 1;
@@ -564,7 +574,13 @@ __global__ void __launch_bounds__(T6_WARPS * 32, CAP == 32 ? (T6_MINB * 4) / T6_
     if (grp_ok) {
       const float reach = 2.f * sqrtf(qq) + 2.f * cover_m;
       const float eps_y = 6.03e-8f * (12.f * S * reach * reach + 12.f * fabsf(off) + 4.f);
-      if constexpr (BIN == T6_BIN_SQRT) {
+      if constexpr (RAD) {
+        // superset of the neighbours: Y_exact < 1 <=> d2 < r2 in real arithmetic; the reference compares ITS rounded d2
+        // (relative error below 2^-21), the computed Y is within eps_y of the exact one
+        thr = 1.f + eps_y + 1e-6f;
+        t_safe = 0.f;
+        t_reach = ((thr + eps_y) / S) * (1.f + 4e-6f);
+      } else if constexpr (BIN == T6_BIN_SQRT) {
         thr = T6_MAGIC + (float)(bstar + 1);
         // a candidate that was NOT collected has NB sqrt~(Y) >= b* + 1/2, so Y >= edge^2 (1 - 2^-20) with the MUFU's error;
         // a member has Y <= edge^2 (1 + 2^-20)
@@ -582,7 +598,7 @@ __global__ void __launch_bounds__(T6_WARPS * 32, CAP == 32 ? (T6_MINB * 4) / T6_
     __syncwarp();
     // ---- pass 2: collect the sorted positions of the candidates at or below the threshold bin
     if (__any_sync(PCP_FULL, grp_ok)) {
-      const bool resident = total <= (uint32_t)T6_CH;  // one chunk: still staged from pass 1
+      const bool resident = !RAD && total <= (uint32_t)T6_CH;  // one chunk: still staged from pass 1 (the radius mode has no pass 1)
       // A candidate farther from the bounding box of the served queries than the largest member distance is
       // nobody's member: each chunk is compacted in place (one candidate per lane, ballot + rank) before the
       // per-lane loop, which then runs over about half of it.  Local coordinates throughout.
@@ -659,25 +675,31 @@ __global__ void __launch_bounds__(T6_WARPS * 32, CAP == 32 ? (T6_MINB * 4) / T6_
             z0 = bin_z<NB>(P0, S, K, A0, A1, A2), z1 = bin_z<NB>(P1, S, K, A0, A1, A2);
             z2 = bin_z<NB>(P2, S, K, A0, A1, A2), z3 = bin_z<NB>(P3, S, K, A0, A1, A2);
           } else {
-            z0 = bin_y(P0, S, K, A0, A1, A2), z1 = bin_y(P1, S, K, A0, A1, A2);
-            z2 = bin_y(P2, S, K, A0, A1, A2), z3 = bin_y(P3, S, K, A0, A1, A2);
+            z0 = bin_y<!RAD>(P0, S, K, A0, A1, A2), z1 = bin_y<!RAD>(P1, S, K, A0, A1, A2);
+            z2 = bin_y<!RAD>(P2, S, K, A0, A1, A2), z3 = bin_y<!RAD>(P3, S, K, A0, A1, A2);
           }
-          if (z0 < thr) { sts_u32(wp, lds_u32<0>(pa)); wp += 128u; }
-          if (z1 < thr) { sts_u32(wp, lds_u32<4>(pa)); wp += 128u; }
-          if (z2 < thr) { sts_u32(wp, lds_u32<8>(pa)); wp += 128u; }
-          if (z3 < thr) { sts_u32(wp, lds_u32<12>(pa)); wp += 128u; }
+          // (radius: a neighbourhood may hold more hits than the column has rows; the pointer keeps counting, the
+          // stores stop at the column's end and the lane is handed to the work list)
+          if (z0 < thr) { if (!RAD || wp < wend) sts_u32(wp, lds_u32<0>(pa)); wp += 128u; }
+          if (z1 < thr) { if (!RAD || wp < wend) sts_u32(wp, lds_u32<4>(pa)); wp += 128u; }
+          if (z2 < thr) { if (!RAD || wp < wend) sts_u32(wp, lds_u32<8>(pa)); wp += 128u; }
+          if (z3 < thr) { if (!RAD || wp < wend) sts_u32(wp, lds_u32<12>(pa)); wp += 128u; }
         }
         for (; j < n_ch; ++j, ca += 16, pa += 4) {
           const float4 P = lds_f4<0>(ca);
-          const float z = BIN == T6_BIN_SQRT ? bin_z<NB>(P, S, K, A0, A1, A2) : bin_y(P, S, K, A0, A1, A2);
-          if (z < thr) { sts_u32(wp, lds_u32<0>(pa)); wp += 128u; }
+          const float z = BIN == T6_BIN_SQRT ? bin_z<NB>(P, S, K, A0, A1, A2) : bin_y<!RAD>(P, S, K, A0, A1, A2);
+          if (z < thr) { if (!RAD || wp < wend) sts_u32(wp, lds_u32<0>(pa)); wp += 128u; }
         }
         __syncwarp();
       }
     }
     ok = ok || grp_ok;
   }
-  const int cnt = ok ? (int)((wp - hcol_a) >> 7) : 0;  // members collected into this lane's column
+  int cnt = ok ? (int)((wp - hcol_a) >> 7) : 0;  // members collected into this lane's column
+  if (RAD && cnt > CAP) {  // more candidates inside the radius than the column holds: the work list's 512-entry buffer takes it
+    ok = false;
+    cnt = 0;
+  }
   T6STAT(0, finite ? 1 : 0);
   T6STAT(3, cnt);
   T6STAT(4, pending ? 1 : 0);  // deferred: more row groups in the tile than the kernel serves
@@ -691,6 +713,7 @@ __global__ void __launch_bounds__(T6_WARPS * 32, CAP == 32 ? (T6_MINB * 4) / T6_
   // 32-bit key prefix(d2) | slot on registers; a d2 >= 0 orders like its bit pattern, the slot bits only make the
   // keys distinct.  After the network, slot j of the column is rewritten with the position of the j-th key's member.
   uint32_t kth_key = 0xFFFFFFFFu;
+  int n_in = 0;  // radius: members that pass the exact test (they sort in front of the dropped ones)
   {
     uint32_t keys[CAP];
     const int maxc = __reduce_max_sync(PCP_FULL, cnt);  // blocks of eight slots nobody uses are skipped (k = 10: half of them)
@@ -703,7 +726,11 @@ __global__ void __launch_bounds__(T6_WARPS * 32, CAP == 32 ? (T6_MINB * 4) / T6_
         for (int j = j0; j < j0 + 8; ++j) {
           if (j < cnt) {
             const float4 P = __ldg(&sorted[hcol[j * 32]]);
-            keys[j] = (__float_as_uint(dist2_nofma(Q.x, Q.y, Q.z, P)) & ~(uint32_t)(CAP - 1)) | (uint32_t)j;
+            const float d2 = dist2_nofma(Q.x, Q.y, Q.z, P);
+            if (!RAD || d2 < sp.r2) {  // radius: strict d2 < r2 with the reference's own arithmetic decides membership
+              keys[j] = (__float_as_uint(d2) & ~(uint32_t)(CAP - 1)) | (uint32_t)j;
+              ++n_in;
+            }
           }
         }
       }
@@ -713,15 +740,16 @@ __global__ void __launch_bounds__(T6_WARPS * 32, CAP == 32 ? (T6_MINB * 4) / T6_
 #pragma unroll
     for (int j = 0; j < CAP; ++j) {
       if (j == k - 1) kth_key = keys[j];
-      keys[j] = j < cnt ? hcol[(keys[j] & (uint32_t)(CAP - 1)) * 32] : 0u;
+      keys[j] = j < (RAD ? n_in : cnt) ? hcol[(keys[j] & (uint32_t)(CAP - 1)) * 32] : 0u;
     }
 #pragma unroll
     for (int j = 0; j < CAP; ++j)
-      if (j < cnt) hcol[j * 32] = keys[j];
+      if (j < (RAD ? n_in : cnt)) hcol[j * 32] = keys[j];
   }
+  if (RAD) cnt = n_in;
   // ---- proof of the selection: every point that was not collected is at least t_safe away; the k-th member's
   // distance is at most its key with the slot bits set
-  if (ok && !(__uint_as_float(kth_key | (uint32_t)(CAP - 1)) < t_safe)) {
+  if (!RAD && ok && !(__uint_as_float(kth_key | (uint32_t)(CAP - 1)) < t_safe)) {
     ok = false;
     far = false;
     T6STAT(10, 1);
@@ -738,14 +766,14 @@ __global__ void __launch_bounds__(T6_WARPS * 32, CAP == 32 ? (T6_MINB * 4) / T6_
       if (defer) work_list[base + __popc(dm & ((1u << lane) - 1u))] = (uint32_t)p | (far ? 0x80000000u : 0u);
     }
   }
-  const int n_nb = ok ? k : 0;
+  const int n_nb = ok ? (RAD ? cnt : k) : 0;
   const bool emit = active && (ok || !finite);  // non-finite queries get their empty record here
   __syncwarp();
 #if T6_SYNC
   __syncthreads();
 #endif
   if (!live_warp) return;
-  knn_finish_pos<LEAN>(a, hcol, cnt, n_nb, ~(uint32_t)(CAP - 1), Q, emit ? my_slot : -1, sm.u.rec, lane);
+  knn_finish_pos<LEAN>(a, hcol, cnt, n_nb, ~(uint32_t)(CAP - 1), Q, emit ? my_slot : -1, sm.u.rec, lane, RAD ? sp.min_pts : 1);
 }
 
 }  // namespace
@@ -762,7 +790,8 @@ extern "C" __attribute__((visibility("default"))) int pcp_debug_tile6_stats(unsi
 
 // Launches the k-NN tile kernel over the whole cloud; deferred queries are left in ctx->work_list /
 // ctx->work_count (device) for the work-list kernel.  32-member lanes for k <= 24, 64-member lanes for 24 < k <= 32.
-int pcp_knn_tile6_launch(pcp_ctx* ctx, const SearchParams& sp, const KArgs& a) {
+// sp.mode == 1: fixed-radius search through the same kernel (T6_BIN_RADIUS), lanes of `radius_cap` (32 or 64) hits.
+int pcp_knn_tile6_launch(pcp_ctx* ctx, const SearchParams& sp, const KArgs& a, int radius_cap) {
   int rc;
   if ((rc = pcp_reserve(ctx, ctx->work_list, (size_t)ctx->n * sizeof(uint32_t)))) return rc;
   if ((rc = pcp_reserve(ctx, ctx->work_count, 2 * sizeof(uint32_t)))) return rc;  // [0] list length, [1] ticket counter of the work-list kernel
@@ -806,7 +835,13 @@ int pcp_knn_tile6_launch(pcp_ctx* ctx, const SearchParams& sp, const KArgs& a) {
   const int refine_min = ctx->knobs.t6_refine_min > 0 ? ctx->knobs.t6_refine_min : 6;
   int bin = (sp.k >= 22 && sp.k <= PCP_T6_K32) ? T6_BIN_SQRT : T6_BIN_LOG;
   if (ctx->knobs.t6_bin >= 0) bin = ctx->knobs.t6_bin;
-  if (sp.k <= PCP_T6_K32) {
+  if (sp.mode == 1) {
+    if (radius_cap <= 32) {
+      if (lean) T6_LAUNCH(32, true, T6_BIN_RADIUS); else T6_LAUNCH(32, false, T6_BIN_RADIUS);
+    } else {
+      if (lean) T6_LAUNCH(64, true, T6_BIN_RADIUS); else T6_LAUNCH(64, false, T6_BIN_RADIUS);
+    }
+  } else if (sp.k <= PCP_T6_K32) {
     if (lean) T6_LAUNCH_BIN(32, true); else T6_LAUNCH_BIN(32, false);
   } else {
     if (lean) T6_LAUNCH_BIN(64, true); else T6_LAUNCH_BIN(64, false);

@@ -48,6 +48,7 @@ struct PcpKnobs {
                            // tile kernel (knn_tile.cu), 3 = "v3": the warp-per-query kernel for every point
   int knn_groups = 0;      // PCP_KNN_GROUPS: stencil rows served per tile (0 = automatic)
   int radius_impl = 0;     // PCP_RADIUS_IMPL: 0 = automatic, 1 = "tile" (32-entry lanes), 2 = "tile64", 3 = "v3"
+  int radius_t6 = -1;      // PCP_RADIUS_T6=1/0: fixed-radius tiles through knn_tile6.cu (T6_BIN_RADIUS) / through the round-1 kernel (-1 = automatic)
   int wl_blocks = 0;       // PCP_WL_BLOCKS / PCP_WL_TILE: work-list kernel grid and tile (0 = default)
   int wl_tile = 0;
   double grid_shift = 0.0; // PCP_GRID_SHIFT: lower the grid origin by this fraction of a cell (diagnostic; results unchanged)
@@ -193,7 +194,7 @@ void pcp_make_kargs(pcp_ctx* ctx, const SearchParams& sp, KArgs& a);  // search_
 int pcp_radius_heavy_lists_impl(pcp_ctx* ctx, const KArgs& a, float r2, int R, const int64_t* d_offsets, int64_t total, int32_t* d_idx,
                                 float* d_d2);
 int pcp_knn_tile_launch(pcp_ctx* ctx, const SearchParams& sp, const KArgs& a, int radius_cap);  // k-NN tile kernel (knn_tile.cu)
-int pcp_knn_tile6_launch(pcp_ctx* ctx, const SearchParams& sp, const KArgs& a);  // k-NN tile kernel (knn_tile6.cu): k <= PCP_T6_KMAX
+int pcp_knn_tile6_launch(pcp_ctx* ctx, const SearchParams& sp, const KArgs& a, int radius_cap = 32);  // k-NN tile kernel (knn_tile6.cu): k <= PCP_T6_KMAX
 #define PCP_T6_K32 24   // 32-member lanes up to this k, 64-member lanes above
 #define PCP_T6_KMAX 32   // (the work-list kernel that finishes the deferred lanes keeps one key per lane)
 int pcp_carry_forward_impl(pcp_ctx* ctx, pcp_feature68* d_out, const uint8_t* d_valid, int64_t n);

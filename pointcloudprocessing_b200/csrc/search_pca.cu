@@ -35,6 +35,9 @@ __device__ unsigned long long g_stats[8];
 
 namespace {
 
+#ifndef PCP_RADIUS_T6_DEFAULT
+#define PCP_RADIUS_T6_DEFAULT 1   // measured: 4 M points at configs[3] density (mean 31.6 hits) 5.12 -> 4.52 ms, urban 1 M (mean 8.7) 0.735 -> 0.706 ms
+#endif
 #ifndef SP_WARPS
 #define SP_WARPS 8
 #endif
@@ -299,6 +302,30 @@ __device__ __noinline__ void heavy_moment(const KArgs& a, const float4 Q, int c0
   for (int t = 0; t < 6; ++t) mom[t] = m[t];
 }
 
+// cell coordinates of the query at P with cell id `cid` (c2 frame-local, zoff = its frame's first z row) and its fractional
+// position inside the cell, clamped to [0, 1] (same double arithmetic as the key kernel; selects, not indexed arrays)
+struct QueryCell {
+  int c0, c1, c2, zoff;
+  float f0, f1, f2;
+};
+__device__ __forceinline__ QueryCell query_cell(const GridDesc& g, const float4 P, const uint32_t cid) {
+  QueryCell qc;
+  qc.c0 = (int)(cid % (uint32_t)g.dim[0]);
+  const uint32_t tq = cid / (uint32_t)g.dim[0];
+  qc.c1 = (int)(tq % (uint32_t)g.dim[1]);
+  qc.c2 = (int)(tq / (uint32_t)g.dim[1]);
+  qc.zoff = pcp_unfold_z(g, qc.c2);
+  const double qx = g.ax[0] == 0 ? P.x : (g.ax[0] == 1 ? P.y : P.z), qy = g.ax[1] == 0 ? P.x : (g.ax[1] == 1 ? P.y : P.z);
+  const double qz = g.ax[2] == 0 ? P.x : (g.ax[2] == 1 ? P.y : P.z);
+  const double ox = g.ax[0] == 0 ? g.origin[0] : (g.ax[0] == 1 ? g.origin[1] : g.origin[2]);
+  const double oy = g.ax[1] == 0 ? g.origin[0] : (g.ax[1] == 1 ? g.origin[1] : g.origin[2]);
+  const double oz = g.ax[2] == 0 ? g.origin[0] : (g.ax[2] == 1 ? g.origin[1] : g.origin[2]);
+  qc.f0 = fminf(fmaxf((float)((qx - ox) * g.inv_cell - (double)qc.c0), 0.f), 1.f);
+  qc.f1 = fminf(fmaxf((float)((qy - oy) * g.inv_cell - (double)qc.c1), 0.f), 1.f);
+  qc.f2 = fminf(fmaxf((float)((qz - oz) * g.inv_cell - (double)qc.c2), 0.f), 1.f);
+  return qc;
+}
+
 // nq queries one after the other and writes their outputs.
 template <int MODE>
 // `my_r0`: first stencil half-width of this lane's query (k-NN; the tile kernel flags the entries whose k-th
@@ -316,17 +343,36 @@ __device__ __forceinline__ void search_tile(const KArgs& a, WarpSmem<MODE>* ws, 
   // lane j remembers query j of the tile and, once solved, its k-th distance: later queries seed
   // their threshold from them (triangle inequality: d_k(q) <= d_k(q_j) + |q − q_j|)
   const float4 myP = lane < nq ? __ldg(&sorted[my_pos]) : make_float4(0.f, 0.f, 0.f, 0.f);
-  const uint32_t my_seg = (g.n_seg > 1 && lane < nq) ? __ldg(&a.keys[my_pos]) / g.seg_cells : 0u;  // a seed must come from the same frame
+  const uint32_t my_cid = lane < nq ? __ldg(&a.keys[my_pos]) : g.n_cells;
+  const uint32_t my_seg = (g.n_seg > 1 && lane < nq) ? my_cid / g.seg_cells : 0u;  // a seed must come from the same frame
   float my_dk = 3.4e38f;
+  // k-NN: lane j works out the cell of ITS query once and parks it in warp-private shared memory (the product rows and
+  // the id row, which only the radius mode uses during the search): the query loop then costs neither the two integer
+  // divisions and the double arithmetic per query nor registers across the loop
+  if (MODE == 0) {
+    QueryCell mine = {0, 0, 0, 0, 0.f, 0.f, 0.f};
+    if (my_cid < g.n_cells) mine = query_cell(g, myP, my_cid);
+    __syncwarp();
+    ws->u.s.prod[0][lane] = __int_as_float(mine.c0);
+    ws->u.s.prod[1][lane] = __int_as_float(mine.c1);
+    ws->u.s.prod[2][lane] = __int_as_float(mine.c2);
+    ws->u.s.prod[3][lane] = mine.f0;
+    ws->u.s.prod[4][lane] = mine.f1;
+    ws->u.s.prod[5][lane] = mine.f2;
+    ws->gidq[lane] = mine.zoff;
+    __syncwarp();
+  }
 
 #pragma unroll 1
   for (int q = 0; q < nq; ++q) {
     const int slot_q = __shfl_sync(PCP_FULL, my_slot, q);
     if (slot_q < 0) continue;  // halo point: neighbour only
-    const int64_t pq = __shfl_sync(PCP_FULL, my_pos, q);
     STAT(0, 1);
-    const float4 Q = __ldg(&sorted[pq]);
-    const uint32_t cid = __ldg(&a.keys[pq]);
+    // the query's point and cell were loaded by lane q with the tile's other queries (one round trip to L2 per tile,
+    // not two dependent ones per query)
+    const float4 Q = make_float4(__shfl_sync(PCP_FULL, myP.x, q), __shfl_sync(PCP_FULL, myP.y, q), __shfl_sync(PCP_FULL, myP.z, q),
+                                 __shfl_sync(PCP_FULL, myP.w, q));
+    const uint32_t cid = __shfl_sync(PCP_FULL, my_cid, q);
     int n_nb = 0;
     bool overflow = false, heavy = false;
     Search st;
@@ -334,19 +380,22 @@ __device__ __forceinline__ void search_tile(const KArgs& a, WarpSmem<MODE>* ws, 
     st.thr = PCP_KEY_INF;
     st.cnt = 0;
     if (cid < g.n_cells) {
-      const int c0 = (int)(cid % (uint32_t)g.dim[0]);
-      const uint32_t tq = cid / (uint32_t)g.dim[0];
-      const int c1 = (int)(tq % (uint32_t)g.dim[1]);
-      int c2 = (int)(tq / (uint32_t)g.dim[1]);
-      const int zoff = pcp_unfold_z(g, c2);  // frame batches: first z row of the query's frame; c2 is frame-local
-      // fractional position inside the own cell (same double arithmetic as the key kernel)
-      const float qc[3] = {Q.x, Q.y, Q.z};
-      float f0 = (float)(((double)qc[g.ax[0]] - g.origin[g.ax[0]]) * g.inv_cell - (double)c0);
-      float f1 = (float)(((double)qc[g.ax[1]] - g.origin[g.ax[1]]) * g.inv_cell - (double)c1);
-      float f2 = (float)(((double)qc[g.ax[2]] - g.origin[g.ax[2]]) * g.inv_cell - (double)c2);
-      f0 = fminf(fmaxf(f0, 0.f), 1.f);
-      f1 = fminf(fmaxf(f1, 0.f), 1.f);
-      f2 = fminf(fmaxf(f2, 0.f), 1.f);
+      // cell coordinates, frame row offset and fractional position inside the own cell: lane q worked them out for
+      // its query before the loop
+      QueryCell qc;
+      if (MODE == 0) {
+        qc.c0 = __float_as_int(ws->u.s.prod[0][q]);
+        qc.c1 = __float_as_int(ws->u.s.prod[1][q]);
+        qc.c2 = __float_as_int(ws->u.s.prod[2][q]);
+        qc.zoff = ws->gidq[q];
+        qc.f0 = ws->u.s.prod[3][q];
+        qc.f1 = ws->u.s.prod[4][q];
+        qc.f2 = ws->u.s.prod[5][q];
+      } else {
+        qc = query_cell(g, Q, cid);
+      }
+      const int c0 = qc.c0, c1 = qc.c1, c2 = qc.c2, zoff = qc.zoff;
+      const float f0 = qc.f0, f1 = qc.f1, f2 = qc.f2;
       if (MODE == 1 && sp.k > 0) {
         // k nearest for 32 < k <= 64 (the best list above holds one key per lane): collect EVERY point inside
         // a radius the stencil is known to cover, and keep the first k of the sorted hits.  Fewer than k hits:
@@ -721,7 +770,9 @@ int pcp_search_launch(pcp_ctx* ctx, const SearchParams& sp) {
     // k-NN: knn_tile6.cu for single clouds; frame batches (segmented grid: short rows, up to four row groups per tile,
     // k = 10) stay on the round-1 tile kernel, which re-stages less per row group (measured, 128 VLP-16 frames: 3.7 vs 4.1 ms)
     const bool use_t6 = sp.mode == 0 && (kn.knn_impl == 6 || (kn.knn_impl == 0 && ctx->grid.n_seg == 1));  // PCP_KNN_IMPL=tile6 forces it
-    int rc = use_t6 ? pcp_knn_tile6_launch(ctx, sp, a) : pcp_knn_tile_launch(ctx, sp, a, radius_cap);
+    // fixed-radius tiles: knn_tile6.cu's radius mode for single clouds (PCP_RADIUS_T6=0 keeps the round-1 kernel)
+    const bool rad_t6 = sp.mode == 1 && (kn.radius_t6 == 1 || (kn.radius_t6 < 0 && PCP_RADIUS_T6_DEFAULT && ctx->grid.n_seg == 1));
+    int rc = (use_t6 || rad_t6) ? pcp_knn_tile6_launch(ctx, sp, a, radius_cap) : pcp_knn_tile_launch(ctx, sp, a, radius_cap);
     if (rc) return rc;
     // one wave of resident CTAs (3 per SM at 80 registers); tiles of 16 list entries drawn by ticket
     // (tuning hooks: PCP_WL_BLOCKS, PCP_WL_TILE)
