@@ -342,12 +342,14 @@ int pcp_grid_build_impl(pcp_ctx* ctx, float cell, int k_hint) {
       PCP_CUDA(cudaEventCreateWithFlags(&ctx->occ_ev, cudaEventDisableTiming));
     }
   }
-  // ---- sharded clouds: ord = rank of the global id (ties are broken by global index) — or the id itself when the ids
-  // are small enough for a dense ord -> position table that stays in L2 (64 MB): nothing to rank, nothing to sort
+  // ---- sharded clouds: ord = rank of the global id (ties are broken by global index) — or the id itself when a dense
+  // ord -> position table over the ids is affordable (1 GB = 268 M ids; 64 MB stay L2-resident, a larger table costs the
+  // work-list kernels a DRAM sector per neighbour of a deferred query, far less than ranking 10^7 ids per build: the tile
+  // kernels never read it): nothing to rank, nothing to sort
   ctx->gid_direct = false;
   ctx->inv_size = (size_t)n;
   if (ctx->d_gid && (hb[6] & 2u)) return pcp_fail(ctx, PCP_ERR_INVALID_ARG, "pcp_build_grid: negative global id");
-  if (ctx->d_gid && ctx->knobs.shard_full_sort == 0 && ((size_t)hb[7] + 1) * sizeof(uint32_t) <= ((size_t)64 << 20)) {
+  if (ctx->d_gid && ctx->knobs.shard_full_sort == 0 && ((size_t)hb[7] + 1) * sizeof(uint32_t) <= ((size_t)1 << 30)) {
     ctx->gid_direct = true;
     ctx->inv_size = (size_t)hb[7] + 1;
   } else if (ctx->d_gid) {
