@@ -408,6 +408,11 @@ PCP_API int pcp_odom_smoothness(pcp_ctx* ctx, const pcp_odom_params* prm, const 
  * first-seeded cluster that reaches it, and stays noise when its own index precedes that cluster's seed, as in
  * the reference's sequential walk.  *n_clusters = clusterID (HOST int32).  Synchronises. */
 PCP_API int pcp_dbscan(pcp_ctx* ctx, float radius, int min_pts, int32_t* labels, int32_t* n_clusters, int out_is_device);
+/* The same with the radius as the reference declares it: `double r` (include/dbscanCLuster.h:256; the call site passes
+ * the literal 0.2, src/dynaObjTest.cpp:133).  PCL compares squared distances with (float)(r * r) evaluated in double:
+ * for r = 0.2 that is 0x3d23d70a, one ulp below what the float 0.2f squares to — points whose squared distance is exactly
+ * that float are neighbours for pcp_dbscan(0.2f) and not for the reference.  pcp_dbscan(r) == pcp_dbscan_d((double)r). */
+PCP_API int pcp_dbscan_d(pcp_ctx* ctx, double radius, int min_pts, int32_t* labels, int32_t* n_clusters, int out_is_device);
 
 /* Per cluster 1..n_clusters of `labels` (host or device per labels_is_device), over the CURRENT cloud (set the
  * original 3-D cloud again after pcp_dbscan): centroid (pcl::compute3DCentroid), min and max corner

@@ -15,9 +15,15 @@ void orc_kdtree_radius_vec(const orc_kdtree* t, const float* q, float r2, std::v
 
 // state: 0 unvisited, -1 visited, -2 noise, > 0 cluster id (:262).  The caller passes the cloud the reference
 // searches in (cloud2d: z already zeroed, :264-267).  Returns clusterID.
+extern "C" int32_t orc_dbscan_d(const float* xyzi, int64_t n, double radius, int min_pts, int32_t* state);
 extern "C" int32_t orc_dbscan(const float* xyzi, int64_t n, float radius, int min_pts, int32_t* state) {
+  return orc_dbscan_d(xyzi, n, (double)radius, min_pts, state);
+}
+// the reference's own parameter type: double r (include/dbscanCLuster.h:256); pcl::KdTreeFLANN::radiusSearch(p, double
+// radius, ...) hands FLANN static_cast<float>(radius * radius)
+extern "C" int32_t orc_dbscan_d(const float* xyzi, int64_t n, double radius, int min_pts, int32_t* state) {
   orc_kdtree* tree = orc_kdtree_build(xyzi, n, 15);
-  const float r2 = orc_radius2(radius);
+  const float r2 = (float)(radius * radius);
   for (int64_t i = 0; i < n; ++i) state[i] = 0;
   int32_t cluster = 0;
   std::vector<int32_t> nb, tmp;

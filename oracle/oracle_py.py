@@ -62,6 +62,7 @@ def load() -> C.CDLL:
         "orc_odom_smoothness": (None, [vp, i32, i32, i32, i32, f32, i32, i32, i32, vp, vp]),
         "orc_atanf_mismatches": (i64, [C.c_uint32, C.c_uint32]),
         "orc_dbscan": (i32, [vp, i64, f32, i32, vp]),
+        "orc_dbscan_d": (i32, [vp, i64, C.c_double, i32, vp]),
         "orc_cluster_boxes": (None, [vp, i64, vp, i32, vp, vp, vp, vp]),
         "orc_mean_shift_step": (None, [vp, vp, i64, f32, i32, vp, vp, vp]),
         "orc_txt2pc": (i64, [C.c_char_p, i64, vp, i64]),
@@ -295,6 +296,14 @@ def dbscan(pts, radius: float, min_pts: int):
     pts = _f4(pts)
     state = np.zeros(pts.shape[0], np.int32)
     nc = load().orc_dbscan(pts.ctypes.data, pts.shape[0], radius, min_pts, state.ctypes.data)
+    return state, int(nc)
+
+
+def dbscan_d(pts, radius: float, min_pts: int):
+    """The same with the radius taken as the reference's `double r` (r2 = (float)(r * r) in double)."""
+    pts = _f4(pts)
+    state = np.zeros(pts.shape[0], np.int32)
+    nc = load().orc_dbscan_d(pts.ctypes.data, pts.shape[0], C.c_double(radius), min_pts, state.ctypes.data)
     return state, int(nc)
 
 

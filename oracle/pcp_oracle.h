@@ -124,6 +124,7 @@ int64_t orc_atanf_mismatches(uint32_t start, uint32_t stride);
 /* DynaTools::clusterDBSCAN (include/dbscanCLuster.h:256-300) on the cloud it searches in (z zeroed by the caller, as
  * :264-267): state[i] = cluster id 1.. or -2 (noise).  Returns the number of clusters. */
 int32_t orc_dbscan(const float* xyzi, int64_t n, float radius, int min_pts, int32_t* state);
+int32_t orc_dbscan_d(const float* xyzi, int64_t n, double radius, int min_pts, int32_t* state);  /* radius as the reference declares it */
 /* per cluster: compute3DCentroid, getMinMax3D (:312-325) and the member count */
 void orc_cluster_boxes(const float* xyzi, int64_t n, const int32_t* state, int32_t n_clusters, float* centroid3, float* min3,
                        float* max3, int32_t* counts);

@@ -44,7 +44,7 @@ EXPORTS = (
     "pcp_ring_calib_from_xml", "pcp_ring_project", "pcp_set_host_async", "pcp_alloc_pinned", "pcp_free_pinned", "pcp_halo_pack", "pcp_set_frames",
     "pcp_halo_push", "pcp_halo_wait", "pcp_peer_alloc", "pcp_peer_free", "pcp_peer_open", "pcp_peer_close",
     "pcp_ring_seg_params_default", "pcp_ring_segment", "pcp_decode_packets",
-    "pcp_dbscan", "pcp_cluster_boxes", "pcp_mean_shift", "pcp_set_cloud_txt",
+    "pcp_dbscan", "pcp_dbscan_d", "pcp_cluster_boxes", "pcp_mean_shift", "pcp_set_cloud_txt",
     "pcp_radius_count", "pcp_odom_params_default", "pcp_odom_range_image", "pcp_odom_smoothness",
     "pcp_bbox_pca", "pcp_carry_forward_static", "pcp_carry_forward_static_max", "pcp_set_cloud_xyz",
 )
@@ -174,6 +174,7 @@ def load() -> C.CDLL:
         "pcp_decode_packets": (i32, [vp, C.POINTER(RingCalib), vp, i64, i32, vp, i32, vp, i64, vp, vp]),
         "pcp_radius_count": (i32, [vp, f32, i32, vp, i32]),
         "pcp_dbscan": (i32, [vp, f32, i32, vp, vp, i32]),
+        "pcp_dbscan_d": (i32, [vp, C.c_double, i32, vp, vp, i32]),
         "pcp_set_cloud_txt": (i32, [vp, vp, i64, i32, vp, vp, i64, i32]),
         "pcp_set_cloud_xyz": (i32, [vp, vp, i64, i32, vp, vp, i64, i32]),
         "pcp_cluster_boxes": (i32, [vp, vp, i32, i32, vp, vp, vp, vp]),
@@ -537,6 +538,13 @@ class Pcp:
         labels = np.zeros(self.n, np.int32)
         nc = C.c_int32()
         self._ck(self.lib.pcp_dbscan(self.h, radius, min_pts, labels.ctypes.data, C.addressof(nc), 0))
+        return labels, int(nc.value)
+
+    def dbscan_d(self, radius: float, min_pts: int):
+        """The same with the radius as the reference's `double r` (pcp_dbscan_d)."""
+        labels = np.zeros(self.n, np.int32)
+        nc = C.c_int32()
+        self._ck(self.lib.pcp_dbscan_d(self.h, C.c_double(radius), min_pts, labels.ctypes.data, C.addressof(nc), 0))
         return labels, int(nc.value)
 
     def cluster_boxes(self, labels: np.ndarray, n_clusters: int):

@@ -563,11 +563,15 @@ PCP_API int pcp_odom_smoothness(pcp_ctx* ctx, const pcp_odom_params* prm, const 
 }
 
 PCP_API int pcp_dbscan(pcp_ctx* ctx, float radius, int min_pts, int32_t* labels, int32_t* n_clusters, int out_is_device) {
+  return pcp_dbscan_d(ctx, (double)radius, min_pts, labels, n_clusters, out_is_device);
+}
+
+PCP_API int pcp_dbscan_d(pcp_ctx* ctx, double radius, int min_pts, int32_t* labels, int32_t* n_clusters, int out_is_device) {
   int rc = require_grid(ctx, "pcp_dbscan");
   if (rc) return rc;
-  if (!(radius > 0.f) || min_pts < 1 || !labels || !n_clusters) return pcp_fail(ctx, PCP_ERR_INVALID_ARG, "pcp_dbscan: bad argument");
+  if (!(radius > 0.0) || min_pts < 1 || !labels || !n_clusters) return pcp_fail(ctx, PCP_ERR_INVALID_ARG, "pcp_dbscan: bad argument");
   if (ctx->d_gid) return pcp_fail(ctx, PCP_ERR_INVALID_ARG, "pcp_dbscan: not defined for shards of a cloud");
-  const float r2 = (float)((double)radius * (double)radius);
+  const float r2 = (float)(radius * radius);  // PCL: static_cast<float>(r * r) with the caller's double r
   int32_t* d_labels;
   if ((rc = pick_out(ctx, ctx->db_labels, labels, out_is_device, (size_t)ctx->n, &d_labels))) return rc;
   if ((rc = pcp_reserve(ctx, ctx->flags, sizeof(int)))) return rc;

@@ -109,10 +109,10 @@ int clusterDBSCAN(pcXYZIptr inCloud, double r, int minptNum, pcXYZIptr pcCluster
     flat[4 * i + 3] = inCloud->points[i].intensity;
   }
   int rc = pcp_set_cloud_host(ctx, flat.data(), (int64_t)n, 16);
-  if (!rc) rc = pcp_build_grid(ctx, (float)r, 0);
+  if (!rc) rc = pcp_build_grid(ctx, (float)(r * 1.0001), 0);  // a cell just above r: a 3 x 3 x 3 stencil covers the radius
   std::vector<int32_t> state(n);
   int32_t clusterID = 0;
-  if (!rc) rc = pcp_dbscan(ctx, (float)r, minptNum, state.data(), &clusterID, 0);
+  if (!rc) rc = pcp_dbscan_d(ctx, r, minptNum, state.data(), &clusterID, 0);  // r stays the double the reference declares
   if (rc) {
     fail(ctx, "clusterDBSCAN", rc);
     return 0;

@@ -40,6 +40,33 @@ def test_dbscan_labels_bit_exact(pcp, oracle, seed, n, r, min_pts):
     assert np.abs(cen - rcen).max() <= 1e-4 * 30.0
 
 
+def test_dbscan_double_radius_as_the_reference_passes_it(pcp, oracle):
+    """pcp_dbscan_d: the radius stays the `double r` of DynaTools::clusterDBSCAN (include/dbscanCLuster.h:256; call site 0.2,
+    src/dynaObjTest.cpp:133), so r2 = (float)(r * r) in double = 0x3d23d70a, one ulp below the square of 0.2f: a pair at
+    exactly that squared distance is no neighbour pair for the reference; a cloud at the call site's parameters gets the
+    labels of the literal walk with that r2."""
+    dx, dy = np.float32(0.19999999), np.float32(6.1e-5)
+    pair = np.array([[0, 0, 0, 0], [dx, dy, 0, 0]], np.float32)
+    pcp.set_cloud(pair)
+    pcp.build_grid(0.2 * 1.0001, 0)
+    assert pcp.dbscan_d(0.2, 2)[1] == 0 == oracle.dbscan_d(pair, 0.2, 2)[1]
+    assert pcp.dbscan(0.2, 2)[1] == 1 == oracle.dbscan(pair, 0.2, 2)[1]
+    pts = synth.urban(7, 40000, extent=25.0)
+    # coordinates on a 4 cm lattice: many pairs sit five steps apart, at squared distances one ulp around 0.04
+    flat = _flat(pts)
+    flat[:, :2] = (np.round(flat[:, :2] / 0.04) * np.float32(0.04)).astype(np.float32)
+    ref, ref_nc = oracle.dbscan_d(flat, 0.2, 8)
+    narrowed, _ = oracle.dbscan(flat, 0.2, 8)
+    assert (ref != narrowed).sum() > 1000  # the two radii label this cloud differently: the test can tell them apart
+    pcp.set_cloud(flat)
+    pcp.build_grid(0.2 * 1.0001, 0)
+    lab, nc = pcp.dbscan_d(0.2, 8)
+    assert nc == ref_nc and ref_nc > 0
+    np.testing.assert_array_equal(lab, ref)
+    lab_f, _ = pcp.dbscan(0.2, 8)
+    np.testing.assert_array_equal(lab_f, narrowed)
+
+
 def test_dbscan_3d_duplicates_and_degenerate(pcp, oracle):
     rs = np.random.default_rng(9)
     base = rs.uniform(0, 4, (3000, 4)).astype(np.float32)

@@ -298,3 +298,19 @@ def test_xyz2pc_known_answers(oracle):
     # ([istream.unformatted]: eof, delimiter, then n - 1 characters stored), so a 255-character line reads and 256 fail
     assert oracle.xyz2pc(b"5" * 255 + b"\n").shape == (2, 4) and oracle.xyz2pc(b"5" * 255).shape == (1, 4)
     assert oracle.xyz2pc(b"5" * 256 + b"\n") is None and oracle.xyz2pc(b"5" * 256) is None
+
+
+def test_dbscan_radius_is_the_references_double(oracle):
+    """clusterDBSCAN takes `double r` (include/dbscanCLuster.h:256; call site: 0.2, src/dynaObjTest.cpp:133) and PCL compares
+    squared distances with (float)(r * r) evaluated in double = 0x3d23d70a; the float 0.2f squares to 0x3d23d70b.  Two points
+    whose squared distance IS 0x3d23d70a are therefore no neighbours for the reference (strict <) — orc_dbscan_d — and
+    neighbours when the radius is narrowed to float first."""
+    dx, dy = np.float32(0.19999999), np.float32(6.1e-5)
+    d2 = np.float32(np.float32(dx * dx) + np.float32(dy * dy))
+    assert d2.view(np.uint32) == 0x3D23D70A == np.float32(0.2 * 0.2).view(np.uint32)
+    assert np.float32(np.float64(np.float32(0.2)) ** 2).view(np.uint32) == 0x3D23D70B
+    pts = np.array([[0, 0, 0, 0], [dx, dy, 0, 0]], np.float32)
+    assert oracle.dbscan_d(pts, 0.2, 2)[1] == 0       # the reference: each point alone, below minpts
+    assert oracle.dbscan(pts, 0.2, 2)[1] == 1         # radius narrowed to float: one cluster
+    st, nc = oracle.dbscan_d(pts, float(np.float32(0.2)), 2)  # the double that equals 0.2f behaves like the float path
+    assert nc == 1 and st.tolist() == [1, 1]
