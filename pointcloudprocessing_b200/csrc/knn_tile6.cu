@@ -1,7 +1,9 @@
-// knn_tile6.cu — k-NN + PCA fast path: one warp per tile of 32 consecutive cell-sorted queries, one lane per query.
+// knn_tile6.cu — k-NN / fixed-radius search + PCA fast path: one warp per tile of 32 consecutive cell-sorted queries, one
+// lane per query.
 //
-// Replaces, per point, nearestKSearch + computeCovarianceMatrixNormalized + SelfAdjointEigenSolver + the structure
-// features (src/smoothing.cpp:239-246, src/pcaAnalysis.cpp:44-87, :29-31).
+// Replaces, per point, nearestKSearch (src/smoothing.cpp:239-246) or radiusSearch (src/pcaAnalysis.cpp:25) +
+// computeCovarianceMatrixNormalized + SelfAdjointEigenSolver + the structure features (src/pcaAnalysis.cpp:44-87, :29-31).
+// The stages below describe the k-NN form; the radius form (T6_BIN_RADIUS) drops pass 1 and the scan, see the bin modes.
 //
 // The kernel is bound by latency and by what a warp keeps resident (shared memory, registers), not by arithmetic
 // (ncu, profiles/r02a_*: 9 % of a warp's cycles issue), so every stage is built to hold little and wait little:
@@ -86,15 +88,15 @@ constexpr int T6_REC_WORDS = 17;
 // Bin modes of the selection passes (template parameter BIN; chosen per k in the launcher, PCP_T6_BIN forces one):
 //   T6_BIN_SQRT   both passes evaluate round(NB sqrt~(Y)) (MUFU.SQRT): bins uniform in distance (the round-2 form, kept for A/B)
 //   T6_BIN_LOG    bins = top bits of the float Y itself (geometric): integer ops, no MUFU; pass 2 is the compare Y < edge
-// (measured and dropped: sqrt bins in pass 1 with the compare Y < y* in pass 2, y* found by bisection with the pass-1
-// instructions — needs a guard against a non-monotone MUFU and was the fastest form for no k)
 //   T6_BIN_RADIUS fixed-radius search (radiusSearch, src/pcaAnalysis.cpp:25): the threshold is known, so pass 1 and the scan
 //                 disappear; pass 2 collects the superset Y < 1 + eps (Y = d2 / r2 in the tile-local frame), the resolve step
 //                 keeps the members whose REFERENCE distance satisfies d2 < r2 (strict, FLANN's arithmetic) — exact by
 //                 construction, no proof needed; lanes with more hits than the column holds go to the work list
 constexpr int T6_BIN_SQRT = 0, T6_BIN_LOG = 1, T6_BIN_RADIUS = 2;
-// (measured and dropped: no shared reduction for candidates beyond the cover radius — `if (Y < 1) red...` — 1.16 -> 1.28 ms:
-// the reductions are cheap, the divergence around them is not)
+// Measured and dropped: sqrt bins in pass 1 with the compare Y < y* in pass 2, y* found by bisection with the pass-1
+// instructions (needs a guard against a non-monotone MUFU and was the fastest form for no k); no shared reduction for
+// candidates beyond the cover radius — `if (Y < 1) red...` — 1.16 -> 1.28 ms: the reductions are cheap, the divergence
+// around them is not.
 #ifndef T6_ORDER
 #define T6_ORDER 1    // warps of a CTA take tiles of similar candidate counts (tile_order_kernel): they reach the CTA barriers together
 #endif
