@@ -611,7 +611,7 @@ def main():
                 "mode": e2e_mode, "sequential_value": total_pts / e2e_seq_s, "host_binding_rank0": numa_note},
         "gpu_launches": int(launches),
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
-                     "kernel": "knn_tile_kernel + search_pca_worklist_kernel<0> (one stage: the tile kernel serves ~90 % of the queries, the work-list kernel the rest)",
+                     "kernel": "knn_tile6_kernel + search_pca_worklist_kernel<0> (one stage: the tile kernel serves ~90 % of the queries, the work-list kernel the rest)",
                      "bytes_per_point": ALGO_BYTES_PER_POINT, "peak_source": peak_src, "kernel_ms": kern_avg_s * 1e3,
                      "traffic_source": (f"profiles/r02_search_ncu_{source_id()}.txt (ncu --set full of this build)" if traffic else
                                         f"none: no capture of source id {source_id()} committed"),
